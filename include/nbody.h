@@ -1,0 +1,155 @@
+/*
+ * include/nbody.h -- C ABI of libnbody.so, the B200 (sm_100a) all-pairs
+ * gravity + kick/drift engine that stands behind the reference's step contract.
+ *
+ * The reference (/root/reference/index.html, "idx:NNN" below) has no FFI: its
+ * boundary is the in-file JS method PhysicsSystem.integrate(dt) (idx:247-262)
+ * which mutates physics.bodies[*].pos/vel/acc/temperature in place, reads G
+ * and softening from the global CONFIG at call time (idx:268-269) and is
+ * called subSteps times per frame by animate() (idx:877-879).  Each entry
+ * point below names the reference statement(s) it replaces.  The bindings a
+ * maintainer adds on the reference side (N-API addon + JS shim, or ctypes)
+ * are shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++ or torch types cross the ABI;
+ *   - every function returns NBODY_OK (0) or a negative nbody_status; no
+ *     exception crosses; nbody_last_error() gives the message;
+ *   - host arrays are caller-owned, borrowed for the duration of the call;
+ *     element type follows the context precision (float or double);
+ *       pos_mass[4n] = x,y,z,m      (Body.pos + Body.mass, idx:211,214)
+ *       vel[4n]      = vx,vy,vz,-   (Body.vel, idx:216)
+ *       acc[4n]      = ax,ay,az,-   (Body.acc, idx:217; state across steps)
+ *       temp[n]                     (Body.temperature, idx:223)
+ *   - a context is not thread-safe; different contexts are independent;
+ *   - step/kick/force calls are asynchronous on the context's stream;
+ *     download, energy and sync block until queued work is complete;
+ *   - there is no CPU fallback: without a CUDA device every call fails with
+ *     NBODY_ECUDA.
+ */
+#ifndef NBODY_H_
+#define NBODY_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define NBODY_API __attribute__((visibility("default")))
+#else
+#define NBODY_API
+#endif
+
+typedef struct nbody_ctx nbody_ctx; /* opaque: device buffers, streams, NCCL communicators */
+
+typedef enum { NBODY_F32 = 0, NBODY_F64 = 1 } nbody_prec;
+
+typedef enum {
+    NBODY_OK = 0,
+    NBODY_EINVAL = -1, /* bad argument or call order */
+    NBODY_ECUDA = -2,  /* CUDA runtime/driver error (includes "no device") */
+    NBODY_ENCCL = -3,  /* NCCL error or NCCL library not loadable */
+    NBODY_ENOMEM = -4  /* host or device allocation failed */
+} nbody_status;
+
+#define NBODY_NCCL_ID_BYTES 128
+
+/* ---- lifetime ---------------------------------------------------------- */
+
+/* One host process driving n_gpus devices (the N-API host is one process):
+ * i-bodies are sharded evenly by contiguous range, positions are exchanged
+ * every step.  device_ids may be NULL (devices 0..n_gpus-1).
+ * capacity = largest n that upload() will accept.  Replaces `new
+ * PhysicsSystem()` (idx:233-237, 734). */
+NBODY_API int nbody_create(nbody_ctx** out, nbody_prec prec, int n_gpus, const int* device_ids,
+                           size_t capacity);
+
+/* One process per GPU (torchrun-style launch): this process is `rank` of
+ * `world` and drives `device`.  nccl_id is the NBODY_NCCL_ID_BYTES blob made by
+ * nbody_nccl_unique_id() on rank 0 and broadcast by the caller (any transport);
+ * it may be NULL when world == 1. */
+NBODY_API int nbody_create_rank(nbody_ctx** out, nbody_prec prec, int rank, int world, int device,
+                                const void* nccl_id, size_t capacity);
+NBODY_API int nbody_nccl_unique_id(void* id_out /* NBODY_NCCL_ID_BYTES */);
+
+NBODY_API void nbody_destroy(nbody_ctx* ctx);
+
+/* ---- state ------------------------------------------------------------- */
+
+/* Replace the whole body list, as resetScenario / addBody do (idx:745,
+ * 239-245).  acc == NULL => acc = 0, like a new Body (idx:217).  temp == NULL
+ * => temperatures 0 and never updated.  In rank mode every rank passes the
+ * SAME full arrays and keeps the slice it owns. */
+NBODY_API int nbody_upload(nbody_ctx* ctx, size_t n, const void* pos_mass, const void* vel,
+                           const void* acc, const void* temp);
+
+/* Copy state back for the readers after the step (visuals.update, idx:881).
+ * Any pointer may be NULL.  In rank mode pos_mass is complete and vel/acc/temp
+ * are written only for the rank's own range [nbody_range()]. */
+NBODY_API int nbody_download(nbody_ctx* ctx, void* pos_mass, void* vel, void* acc, void* temp);
+
+/* ---- the hot path ------------------------------------------------------ */
+
+/* nsteps x PhysicsSystem.integrate(dt) with resolveCollisions removed
+ * (idx:247-262 minus idx:256), G and softening as read from CONFIG at
+ * idx:268-269.  nsteps = CONFIG.subSteps reproduces animate()'s inner loop
+ * (idx:877-879).  Temperatures decay by CONFIG.heatDecay = 0.998 per step when
+ * a temp array was uploaded (idx:227-230, 260); see nbody_set_heat_decay. */
+NBODY_API int nbody_step(nbody_ctx* ctx, double dt, double G, double softening, int nsteps);
+
+/* Split form, so a host can keep the reference's own collision stage between
+ * force evaluation and kick-2 (idx:255-259). */
+NBODY_API int nbody_kick1_drift(nbody_ctx* ctx, double dt);             /* idx:248-253 */
+NBODY_API int nbody_force(nbody_ctx* ctx, double G, double softening);  /* idx:264-291 */
+NBODY_API int nbody_kick2(nbody_ctx* ctx, double dt, double heat_decay /* <=0: no thermal */); /* idx:258-261 */
+
+NBODY_API int nbody_set_heat_decay(nbody_ctx* ctx, double heat_decay); /* CONFIG.heatDecay, idx:67 */
+
+/* ---- diagnostics (not in the reference) -------------------- */
+
+/* E_kin = sum 1/2 m v^2, E_pot = -G sum_{i<j} m_i m_j / sqrt(r^2 + eps^2),
+ * momentum = sum m v; evaluated in fp64 on the device whatever the state
+ * precision.  In rank mode each rank returns the same totals. */
+NBODY_API int nbody_energy(nbody_ctx* ctx, double G, double softening, double* kinetic,
+                           double* potential, double momentum[3]);
+
+NBODY_API int nbody_sync(nbody_ctx* ctx);
+NBODY_API const char* nbody_last_error(const nbody_ctx* ctx); /* valid until next call on ctx */
+NBODY_API const char* nbody_strerror(int status);
+NBODY_API const char* nbody_version(void);
+NBODY_API int nbody_device_count(void); /* >= 0, or negative nbody_status */
+
+/* ---- plumbing for hosts that own streams / want timings ------------------ */
+
+/* Run device 0's (or the rank's) work on a caller-owned CUDA stream
+ * (cudaStream_t / CUstream passed as void*, e.g. torch's current stream);
+ * NULL restores the context's own stream. */
+NBODY_API int nbody_set_stream(nbody_ctx* ctx, void* cuda_stream);
+
+/* Bracket every force-kernel launch with CUDA events on its own stream.
+ * nbody_read_timing synchronises, returns launches and summed milliseconds on
+ * device 0 (or the rank's device) since the last read, and resets both. */
+NBODY_API int nbody_enable_timing(nbody_ctx* ctx, int enable);
+NBODY_API int nbody_read_timing(nbody_ctx* ctx, long long* launches, double* force_ms);
+
+typedef struct {
+    size_t n;            /* bodies uploaded */
+    size_t n_padded;     /* rounded up to the i-tile; pads have mass 0 */
+    size_t i_begin;      /* first body this process/device 0 owns */
+    size_t i_end;        /* one past the last */
+    int n_gpus;          /* devices in this context (1 in rank mode) */
+    int world;           /* ranks (1 unless nbody_create_rank) */
+    int rank;
+    int sm_count;        /* of device 0 / the rank's device */
+    int j_chunks;        /* j-range split of the force kernel for this n */
+    int i_tile;          /* bodies per CTA */
+    long long kernel_launches; /* kernels launched by this context so far */
+} nbody_info;
+NBODY_API int nbody_get_info(nbody_ctx* ctx, nbody_info* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NBODY_H_ */

@@ -1,0 +1,106 @@
+"""ctypes binding of libnbody.so (include/nbody.h).
+
+There is no CPU fallback: if the shared library is missing, or a call fails,
+this module raises.  The library is built in-tree by `build()` (nvcc, sm_100a).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libnbody.so")
+CSRC = os.path.join(_HERE, "csrc")
+
+NBODY_F32, NBODY_F64 = 0, 1
+NBODY_OK, NBODY_EINVAL, NBODY_ECUDA, NBODY_ENCCL, NBODY_ENOMEM = 0, -1, -2, -3, -4
+NCCL_ID_BYTES = 128
+
+# every symbol include/nbody.h declares (tests check the library exports them all)
+SYMBOLS = (
+    "nbody_create", "nbody_create_rank", "nbody_nccl_unique_id", "nbody_destroy",
+    "nbody_upload", "nbody_download", "nbody_step", "nbody_kick1_drift", "nbody_force",
+    "nbody_kick2", "nbody_set_heat_decay", "nbody_energy", "nbody_sync", "nbody_last_error",
+    "nbody_strerror", "nbody_version", "nbody_device_count", "nbody_set_stream",
+    "nbody_enable_timing", "nbody_read_timing", "nbody_get_info",
+)
+
+
+class NBodyError(RuntimeError):
+    def __init__(self, status: int, message: str):
+        super().__init__(f"libnbody status {status}: {message}")
+        self.status = status
+
+
+class Info(ctypes.Structure):
+    _fields_ = [
+        ("n", ctypes.c_size_t), ("n_padded", ctypes.c_size_t), ("i_begin", ctypes.c_size_t),
+        ("i_end", ctypes.c_size_t), ("n_gpus", ctypes.c_int), ("world", ctypes.c_int),
+        ("rank", ctypes.c_int), ("sm_count", ctypes.c_int), ("j_chunks", ctypes.c_int),
+        ("i_tile", ctypes.c_int), ("kernel_launches", ctypes.c_longlong),
+    ]
+
+
+def build(force: bool = False) -> str:
+    """Compile libnbody.so (and the pipe microbenchmark) for sm_100a with nvcc."""
+    args = ["make", "-C", CSRC, "-s"]
+    if force:
+        args.append("-B")
+    subprocess.run(args, check=True)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib() -> ctypes.CDLL:
+    """Load libnbody.so.  Raises if it has not been built: no fallback exists."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: the CUDA engine has not been built "
+            "(run `python -c 'import __graft_entry__ as g; g.build()'`). There is no CPU fallback.")
+    L = ctypes.CDLL(LIB_PATH)
+    vp, sz, d, i = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_double, ctypes.c_int
+    pd = ctypes.POINTER(ctypes.c_double)
+    L.nbody_create.argtypes = [ctypes.POINTER(vp), i, i, ctypes.POINTER(i), sz]
+    L.nbody_create_rank.argtypes = [ctypes.POINTER(vp), i, i, i, i, vp, sz]
+    L.nbody_nccl_unique_id.argtypes = [vp]
+    L.nbody_destroy.argtypes = [vp]
+    L.nbody_destroy.restype = None
+    L.nbody_upload.argtypes = [vp, sz, vp, vp, vp, vp]
+    L.nbody_download.argtypes = [vp, vp, vp, vp, vp]
+    L.nbody_step.argtypes = [vp, d, d, d, i]
+    L.nbody_kick1_drift.argtypes = [vp, d]
+    L.nbody_force.argtypes = [vp, d, d]
+    L.nbody_kick2.argtypes = [vp, d, d]
+    L.nbody_set_heat_decay.argtypes = [vp, d]
+    L.nbody_energy.argtypes = [vp, d, d, pd, pd, pd]
+    L.nbody_sync.argtypes = [vp]
+    L.nbody_last_error.argtypes = [vp]
+    L.nbody_last_error.restype = ctypes.c_char_p
+    L.nbody_strerror.argtypes = [i]
+    L.nbody_strerror.restype = ctypes.c_char_p
+    L.nbody_version.restype = ctypes.c_char_p
+    L.nbody_device_count.restype = i
+    L.nbody_set_stream.argtypes = [vp, vp]
+    L.nbody_enable_timing.argtypes = [vp, i]
+    L.nbody_read_timing.argtypes = [vp, ctypes.POINTER(ctypes.c_longlong), pd]
+    L.nbody_get_info.argtypes = [vp, ctypes.POINTER(Info)]
+    _lib = L
+    return L
+
+
+def check(status: int, ctx=None) -> None:
+    if status == NBODY_OK:
+        return
+    L = lib()
+    msg = L.nbody_strerror(status).decode()
+    if ctx:
+        detail = L.nbody_last_error(ctx).decode()
+        if detail:
+            msg = f"{msg}: {detail}"
+    raise NBodyError(status, msg)

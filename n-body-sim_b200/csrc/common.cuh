@@ -1,0 +1,61 @@
+// Shared definitions of the device-side state layout and kernel parameters.
+//
+// HBM layout (DESIGN.md "Data layout"):
+//   fp32  pos_mass: PAIR-INTERLEAVED.  Bodies 2p and 2p+1 share 32 bytes:
+//           float4 A_p = (x0, x1, y0, y1), float4 B_p = (z0, z1, m0, m1)
+//         so that a j-tile lands in shared memory by one bulk copy and one
+//         LDS.128 yields two aligned 64-bit register pairs that feed the packed
+//         FADD2/FFMA2/FMUL2 pipe directly (two j-bodies per instruction).
+//   fp64  pos_mass: double4 (x, y, z, m) per body.
+//   vel, acc: Real4 per body (x, y, z, unused), indexed from the shard's i_begin.
+//   partial : Real4 [j_chunks][local bodies]; per-chunk acceleration sums.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+namespace nb {
+
+constexpr int kThreads = 256;       // compute threads per CTA (8 warps) + 1 producer warp
+constexpr int kStages = 4;          // j-tile ring depth
+constexpr int kTileBytes = 16384;   // bytes per j-tile stage (1024 fp32 bodies / 512 fp64 bodies)
+constexpr int kPadBodies = 2048;    // n is padded to this (256-body i-tiles x up to 8 shards)
+
+template <typename Real> struct Vec4;
+template <> struct Vec4<float> { using type = float4; };
+template <> struct Vec4<double> { using type = double4; };
+
+// Scalar element index of component c (0=x,1=y,2=z,3=m) of body i in pos_mass.
+template <typename Real> __host__ __device__ __forceinline__ size_t pm_index(size_t i, int c);
+template <> __host__ __device__ __forceinline__ size_t pm_index<float>(size_t i, int c)
+{
+    return 8 * (i >> 1) + 2 * c + (i & 1);
+}
+template <> __host__ __device__ __forceinline__ size_t pm_index<double>(size_t i, int c)
+{
+    return 4 * i + c;
+}
+
+enum EpilogueMode : int {
+    kForceOnly = 0,        // acc = G * sum                                   (idx:264-291)
+    kForceKick2 = 1,       // + vel += acc*h, thermal                         (idx:258-261)
+    kForceKick2Kick1 = 2   // + next step's vel += acc*h; pos += vel*dt       (idx:250-253)
+};
+
+template <typename Real> struct ForceParams {
+    const Real* pos_cur;    // full padded position array (all shards' bodies)
+    Real* pos_next;         // written in mode kForceKick2Kick1 (own range only)
+    Real* vel;              // local
+    Real* acc;              // local
+    Real* partial;          // [j_chunks][n_local] Real4
+    Real* temp;             // local, may be null
+    unsigned* tile_counter; // one per local i-tile; zero between launches
+    size_t n_pad;           // padded body count (j range)
+    size_t i_begin;         // first global body of this shard (multiple of i-tile)
+    size_t n_local;         // padded local body count (multiple of i-tile)
+    size_t chunk_len;       // bodies per j-chunk (multiple of 64)
+    int j_chunks;
+    int mode;
+    Real G, eps2, half_dt, dt, heat_decay;  // heat_decay <= 0: no thermal update
+};
+
+}  // namespace nb

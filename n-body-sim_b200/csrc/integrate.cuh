@@ -1,0 +1,139 @@
+// O(N) kernels: the stand-alone halves of PhysicsSystem.integrate
+// (/root/reference/index.html:250-253 and 258-261), layout conversion for
+// upload/download, and the fp64 energy/momentum diagnostic (not in the
+// reference).
+#pragma once
+#include "common.cuh"
+#include "epilogue.cuh"
+
+namespace nb {
+
+// vel += acc*halfDt ; pos += vel*dt  (idx:250-253), bodies [i_begin, i_begin+n_local)
+template <typename Real>
+__global__ void kick1_drift_kernel(Real* pos, Real* vel, const Real* acc, size_t i_begin,
+                                   size_t n_local, Real half_dt, Real dt)
+{
+    using V4 = typename Vec4<Real>::type;
+    const size_t il = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (il >= n_local) return;
+    V4 v = reinterpret_cast<V4*>(vel)[il];
+    const V4 a = reinterpret_cast<const V4*>(acc)[il];
+    v.x = add_rn(v.x, mul_rn(a.x, half_dt));
+    v.y = add_rn(v.y, mul_rn(a.y, half_dt));
+    v.z = add_rn(v.z, mul_rn(a.z, half_dt));
+    reinterpret_cast<V4*>(vel)[il] = v;
+    const size_t g = i_begin + il;
+    const size_t ix = pm_index<Real>(g, 0), iy = pm_index<Real>(g, 1), iz = pm_index<Real>(g, 2);
+    pos[ix] = add_rn(pos[ix], mul_rn(v.x, dt));
+    pos[iy] = add_rn(pos[iy], mul_rn(v.y, dt));
+    pos[iz] = add_rn(pos[iz], mul_rn(v.z, dt));
+}
+
+// vel += acc*halfDt ; updateThermal  (idx:258-261)
+template <typename Real>
+__global__ void kick2_kernel(Real* vel, const Real* acc, Real* temp, size_t n_local, Real half_dt,
+                             Real heat_decay)
+{
+    using V4 = typename Vec4<Real>::type;
+    const size_t il = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (il >= n_local) return;
+    V4 v = reinterpret_cast<V4*>(vel)[il];
+    const V4 a = reinterpret_cast<const V4*>(acc)[il];
+    v.x = add_rn(v.x, mul_rn(a.x, half_dt));
+    v.y = add_rn(v.y, mul_rn(a.y, half_dt));
+    v.z = add_rn(v.z, mul_rn(a.z, half_dt));
+    reinterpret_cast<V4*>(vel)[il] = v;
+    if (temp != nullptr && heat_decay > Real(0)) temp[il] = thermal(temp[il], heat_decay);
+}
+
+// Host AoS (x,y,z,m)[n] staged on the device -> device pos_mass layout, pads = 0.
+template <typename Real>
+__global__ void pack_pos_kernel(const Real* aos, Real* pos_a, Real* pos_b, size_t n, size_t n_pad)
+{
+    const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n_pad) return;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        const Real v = i < n ? aos[4 * i + c] : Real(0);
+        pos_a[pm_index<Real>(i, c)] = v;
+        pos_b[pm_index<Real>(i, c)] = v;  // mass is constant: both buffers carry it
+    }
+}
+
+template <typename Real>
+__global__ void unpack_pos_kernel(const Real* pos, Real* aos, size_t n)
+{
+    const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) aos[4 * i + c] = pos[pm_index<Real>(i, c)];
+}
+
+// ---- energy / momentum, fp64 accumulation whatever the state precision ------
+// out[block*5 + {0..4}] = {kinetic, potential(pair sum, unscaled by -G), px, py, pz}
+// for the i-bodies of this block against all n bodies; the host adds the block
+// rows in index order.
+constexpr int kEnergyThreads = 256;
+
+template <typename Real>
+__global__ void __launch_bounds__(kEnergyThreads)
+    energy_kernel(const Real* pos, const Real* vel, size_t n, size_t i_begin, size_t n_local_real,
+                  double eps2, double* out)
+{
+    using V4 = typename Vec4<Real>::type;
+    __shared__ double4 tile[kEnergyThreads];
+    __shared__ double red[5][kEnergyThreads / 32];
+    const int tid = threadIdx.x;
+    const size_t il = size_t(blockIdx.x) * kEnergyThreads + tid;
+    const bool live = il < n_local_real;
+    const size_t gi = i_begin + il;
+    double xi = 0, yi = 0, zi = 0, mi = 0;
+    double ke = 0, px = 0, py = 0, pz = 0, pot = 0;
+    if (live) {
+        xi = pos[pm_index<Real>(gi, 0)];
+        yi = pos[pm_index<Real>(gi, 1)];
+        zi = pos[pm_index<Real>(gi, 2)];
+        mi = pos[pm_index<Real>(gi, 3)];
+        const V4 v = reinterpret_cast<const V4*>(vel)[il];
+        const double vx = v.x, vy = v.y, vz = v.z;
+        ke = 0.5 * mi * (vx * vx + vy * vy + vz * vz);
+        px = mi * vx;
+        py = mi * vy;
+        pz = mi * vz;
+    }
+    for (size_t jb = 0; jb < n; jb += kEnergyThreads) {
+        const size_t j = jb + tid;
+        double4 b = make_double4(0, 0, 0, 0);
+        if (j < n)
+            b = make_double4(pos[pm_index<Real>(j, 0)], pos[pm_index<Real>(j, 1)],
+                             pos[pm_index<Real>(j, 2)], pos[pm_index<Real>(j, 3)]);
+        __syncthreads();
+        tile[tid] = b;
+        __syncthreads();
+        const int cnt = static_cast<int>(n - jb < kEnergyThreads ? n - jb : kEnergyThreads);
+#pragma unroll 4
+        for (int q = 0; q < cnt; ++q) {
+            const double4 o = tile[q];
+            const double dx = o.x - xi, dy = o.y - yi, dz = o.z - zi;
+            const double r2 = dx * dx + dy * dy + dz * dz + eps2;
+            const double term = o.w * rsqrt(r2);
+            pot += (jb + q == gi) ? 0.0 : term;
+        }
+    }
+    pot *= 0.5 * mi;  // each unordered pair is visited twice
+    double vals[5] = {ke, live ? pot : 0.0, px, py, pz};
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        double v = vals[k];
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((tid & 31) == 0) red[k][tid >> 5] = v;
+    }
+    __syncthreads();
+    if (tid < 5) {
+        double s = 0;
+        for (int w = 0; w < kEnergyThreads / 32; ++w) s += red[tid][w];
+        out[size_t(blockIdx.x) * 5 + tid] = s;
+    }
+}
+
+}  // namespace nb

@@ -1,0 +1,753 @@
+// libnbody.so -- implementation of include/nbody.h.
+// One nbody_ctx owns one Shard per device it drives.  In "rank mode"
+// (nbody_create_rank) the process holds a single Shard that is rank r of a
+// world of processes; otherwise it holds n_gpus Shards (ranks 0..n_gpus-1 of a
+// world inside this process).  Both run the same per-step schedule; only the
+// NCCL communicator construction differs.
+#include "../../include/nbody.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "force_f32.cuh"
+#include "force_f64.cuh"
+#include "integrate.cuh"
+#include "nccl_dyn.h"
+
+using namespace nb;
+
+namespace {
+
+struct Shard {
+    int device = 0;
+    int rank = 0;
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+    void* pos[2] = {nullptr, nullptr};  // full padded pos_mass, double-buffered
+    void* vel = nullptr;                // local range
+    void* acc = nullptr;
+    void* temp = nullptr;
+    void* partial = nullptr;
+    size_t partial_bytes = 0;
+    unsigned* counters = nullptr;
+    void* stage = nullptr;              // AoS staging for upload/download (4*cap_pad elements)
+    double* energy_out = nullptr;
+    size_t energy_rows = 0;
+    ncclComm_t comm = nullptr;
+    size_t i_begin = 0;                 // set by upload
+    size_t n_local = 0;                 // padded
+    size_t n_local_real = 0;            // bodies of [i_begin, i_begin+n_local) that are < n
+    // force-kernel timing (shard 0 only)
+    std::vector<cudaEvent_t> ev;
+    size_t ev_used = 0;
+};
+
+}  // namespace
+
+struct nbody_ctx {
+    nbody_prec prec = NBODY_F32;
+    size_t esz = 4;
+    size_t capacity = 0;
+    size_t cap_pad = 0;
+    size_t n = 0, n_pad = 0;
+    int cur = 0;
+    int world = 1;       // total ranks (devices across all processes)
+    bool rank_mode = false;
+    int my_rank = 0;     // rank of shards[0] in rank mode
+    std::vector<Shard> shards;
+    bool has_temp = false;
+    double heat_decay = 0.998;  // CONFIG.heatDecay, /root/reference/index.html:67
+    int R = 2;           // i-bodies per thread (fp32)
+    int i_tile = 512;
+    int j_chunks = 1;
+    size_t chunk_len = 0;
+    int sm_count = 0;
+    long long launches = 0;
+    bool timing = false;
+    long long t_launches = 0;
+    double t_ms = 0.0;
+    std::string err;
+};
+
+namespace {
+
+int fail(nbody_ctx* c, int code, const char* fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (c) c->err = buf;
+    return code;
+}
+
+#define CU(ctx, call)                                                                         \
+    do {                                                                                      \
+        cudaError_t e_ = (call);                                                              \
+        if (e_ != cudaSuccess)                                                                \
+            return fail(ctx, e_ == cudaErrorMemoryAllocation ? NBODY_ENOMEM : NBODY_ECUDA,    \
+                        "%s: %s", #call, cudaGetErrorString(e_));                             \
+    } while (0)
+
+#define NC(ctx, call)                                                                         \
+    do {                                                                                      \
+        ncclResult_t r_ = (call);                                                             \
+        if (r_ != 0)                                                                          \
+            return fail(ctx, NBODY_ENCCL, "%s: %s", #call,                                    \
+                        nccl().GetErrorString ? nccl().GetErrorString(r_) : "nccl error");    \
+    } while (0)
+
+size_t round_up(size_t a, size_t b) { return (a + b - 1) / b * b; }
+
+int env_int(const char* name, int dflt)
+{
+    const char* s = getenv(name);
+    return (s && *s) ? atoi(s) : dflt;
+}
+
+size_t pad_unit(const nbody_ctx* c) { return size_t(c->i_tile) * size_t(c->world); }
+
+// j-range decomposition: a pure function of n_pad and the i-tile, never of the
+// number of GPUs, so partial sums are added in the same order on 1/2/4/8 GPUs.
+void choose_chunks(nbody_ctx* c)
+{
+    const size_t tiles = c->n_pad / c->i_tile;
+    const size_t min_len = size_t(env_int("NBODY_MIN_CHUNK", 1024));
+    const size_t want_units = size_t(env_int("NBODY_WANT_UNITS", 148 * 64));
+    size_t len;
+    const int forced = env_int("NBODY_CHUNK_LEN", 0);
+    if (forced > 0) {
+        len = round_up(size_t(forced), 64);
+    } else {
+        size_t s = (want_units + tiles - 1) / tiles;
+        if (s < 1) s = 1;
+        len = round_up((c->n_pad + s - 1) / s, 64);
+        if (len < min_len) len = min_len;
+    }
+    if (len > c->n_pad) len = c->n_pad;
+    c->chunk_len = len;
+    c->j_chunks = int((c->n_pad + len - 1) / len);
+}
+
+int alloc_shard(nbody_ctx* c, Shard& s)
+{
+    CU(c, cudaSetDevice(s.device));
+    CU(c, cudaStreamCreateWithFlags(&s.own_stream, cudaStreamNonBlocking));
+    s.stream = s.own_stream;
+    const size_t local_cap = c->cap_pad / c->world;
+    const size_t v4 = 4 * c->esz;
+    CU(c, cudaMalloc(&s.pos[0], c->cap_pad * v4));
+    CU(c, cudaMalloc(&s.pos[1], c->cap_pad * v4));
+    CU(c, cudaMalloc(&s.stage, c->cap_pad * v4));
+    CU(c, cudaMalloc(&s.vel, local_cap * v4));
+    CU(c, cudaMalloc(&s.acc, local_cap * v4));
+    CU(c, cudaMalloc(&s.temp, local_cap * c->esz));
+    const size_t ntiles = local_cap / c->i_tile + 1;
+    CU(c, cudaMalloc(&s.counters, ntiles * sizeof(unsigned)));
+    CU(c, cudaMemset(s.counters, 0, ntiles * sizeof(unsigned)));
+    s.energy_rows = (local_cap + kEnergyThreads - 1) / kEnergyThreads + 1;
+    CU(c, cudaMalloc(&s.energy_out, s.energy_rows * 5 * sizeof(double)));
+    return NBODY_OK;
+}
+
+int set_kernel_attrs(nbody_ctx* c)
+{
+    const int sm32 = int(force_f32_smem_bytes());
+    const int sm64 = int(force_f64_smem_bytes());
+    CU(c, cudaFuncSetAttribute(force_f32_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
+    CU(c, cudaFuncSetAttribute(force_f32_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
+    CU(c, cudaFuncSetAttribute(force_f32_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
+    CU(c, cudaFuncSetAttribute(force_f32_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
+    CU(c, cudaFuncSetAttribute(force_f32_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
+    CU(c, cudaFuncSetAttribute(force_f32_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
+    CU(c, cudaFuncSetAttribute(force_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
+    return NBODY_OK;
+}
+
+int create_common(nbody_ctx** out, nbody_prec prec, int world, size_t capacity, nbody_ctx** made)
+{
+    if (!out) return NBODY_EINVAL;
+    *out = nullptr;
+    if ((prec != NBODY_F32 && prec != NBODY_F64) || world < 1 || capacity == 0) return NBODY_EINVAL;
+    nbody_ctx* c = new (std::nothrow) nbody_ctx();
+    if (!c) return NBODY_ENOMEM;
+    c->prec = prec;
+    c->esz = prec == NBODY_F32 ? 4 : 8;
+    c->world = world;
+    c->capacity = capacity;
+    if (prec == NBODY_F32) {
+        c->R = env_int("NBODY_R", 2);
+        if (c->R != 1 && c->R != 2 && c->R != 4) c->R = 2;
+    } else {
+        c->R = 1;
+    }
+    c->i_tile = kThreads * c->R;
+    c->cap_pad = round_up(capacity, pad_unit(c));
+    *made = c;
+    return NBODY_OK;
+}
+
+}  // namespace
+
+// ============================================================================
+// lifetime
+// ============================================================================
+
+extern "C" int nbody_device_count(void)
+{
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return NBODY_ECUDA;
+    }
+    return n;
+}
+
+extern "C" const char* nbody_version(void) { return "nbody-b200 0.1 (sm_100a)"; }
+
+extern "C" const char* nbody_strerror(int status)
+{
+    switch (status) {
+    case NBODY_OK: return "ok";
+    case NBODY_EINVAL: return "invalid argument";
+    case NBODY_ECUDA: return "CUDA error";
+    case NBODY_ENCCL: return "NCCL error";
+    case NBODY_ENOMEM: return "out of memory";
+    default: return "unknown status";
+    }
+}
+
+extern "C" const char* nbody_last_error(const nbody_ctx* ctx) { return ctx ? ctx->err.c_str() : ""; }
+
+extern "C" void nbody_destroy(nbody_ctx* c)
+{
+    if (!c) return;
+    for (Shard& s : c->shards) {
+        cudaSetDevice(s.device);
+        if (s.own_stream) cudaStreamSynchronize(s.own_stream);
+        if (s.comm && nccl().ok()) nccl().CommDestroy(s.comm);
+        for (cudaEvent_t e : s.ev) cudaEventDestroy(e);
+        cudaFree(s.pos[0]);
+        cudaFree(s.pos[1]);
+        cudaFree(s.stage);
+        cudaFree(s.vel);
+        cudaFree(s.acc);
+        cudaFree(s.temp);
+        cudaFree(s.partial);
+        cudaFree(s.counters);
+        cudaFree(s.energy_out);
+        if (s.own_stream) cudaStreamDestroy(s.own_stream);
+    }
+    delete c;
+}
+
+static int finish_create(nbody_ctx* c, nbody_ctx** out, int rc)
+{
+    if (rc != NBODY_OK) {
+        // keep the message reachable: callers get no ctx on failure, so print it
+        fprintf(stderr, "libnbody: create failed: %s\n", c->err.c_str());
+        nbody_destroy(c);
+        return rc;
+    }
+    *out = c;
+    return NBODY_OK;
+}
+
+static int create_body(nbody_ctx* c, const int* devs, int n_local_shards, const void* nccl_id)
+{
+    int ndev = 0;
+    CU(c, cudaGetDeviceCount(&ndev));
+    if (ndev < 1) return fail(c, NBODY_ECUDA, "no CUDA device");
+    c->shards.resize(n_local_shards);
+    for (int k = 0; k < n_local_shards; ++k) {
+        Shard& s = c->shards[k];
+        s.device = devs[k];
+        s.rank = c->rank_mode ? c->my_rank : k;
+        if (s.device < 0 || s.device >= ndev) return fail(c, NBODY_EINVAL, "device %d out of range (%d visible)", s.device, ndev);
+        cudaDeviceProp prop;
+        CU(c, cudaGetDeviceProperties(&prop, s.device));
+        if (prop.major < 10)
+            return fail(c, NBODY_ECUDA, "device %d is sm_%d%d; this library is built for sm_100a only", s.device, prop.major, prop.minor);
+        if (k == 0) c->sm_count = prop.multiProcessorCount;
+        int rc = alloc_shard(c, s);
+        if (rc != NBODY_OK) return rc;
+        rc = set_kernel_attrs(c);
+        if (rc != NBODY_OK) return rc;
+    }
+    if (c->world > 1) {
+        if (!nccl().ok()) return fail(c, NBODY_ENCCL, "%s", nccl().error.c_str());
+        if (c->rank_mode) {
+            if (!nccl_id) return fail(c, NBODY_EINVAL, "nccl_id is required when world > 1");
+            ncclUniqueId id;
+            memcpy(&id, nccl_id, sizeof id);
+            CU(c, cudaSetDevice(c->shards[0].device));
+            NC(c, nccl().CommInitRank(&c->shards[0].comm, c->world, id, c->my_rank));
+        } else {
+            std::vector<ncclComm_t> comms(n_local_shards);
+            NC(c, nccl().CommInitAll(comms.data(), n_local_shards, devs));
+            for (int k = 0; k < n_local_shards; ++k) c->shards[k].comm = comms[k];
+        }
+    }
+    return NBODY_OK;
+}
+
+extern "C" int nbody_create(nbody_ctx** out, nbody_prec prec, int n_gpus, const int* device_ids, size_t capacity)
+{
+    nbody_ctx* c = nullptr;
+    int rc = create_common(out, prec, n_gpus, capacity, &c);
+    if (rc != NBODY_OK) return rc;
+    std::vector<int> devs(n_gpus);
+    for (int k = 0; k < n_gpus; ++k) devs[k] = device_ids ? device_ids[k] : k;
+    return finish_create(c, out, create_body(c, devs.data(), n_gpus, nullptr));
+}
+
+extern "C" int nbody_create_rank(nbody_ctx** out, nbody_prec prec, int rank, int world, int device,
+                                 const void* nccl_id, size_t capacity)
+{
+    if (rank < 0 || rank >= world) return NBODY_EINVAL;
+    nbody_ctx* c = nullptr;
+    int rc = create_common(out, prec, world, capacity, &c);
+    if (rc != NBODY_OK) return rc;
+    c->rank_mode = true;
+    c->my_rank = rank;
+    return finish_create(c, out, create_body(c, &device, 1, nccl_id));
+}
+
+extern "C" int nbody_nccl_unique_id(void* id_out)
+{
+    if (!id_out) return NBODY_EINVAL;
+    if (!nccl().ok()) {
+        fprintf(stderr, "libnbody: %s\n", nccl().error.c_str());
+        return NBODY_ENCCL;
+    }
+    ncclUniqueId id;
+    if (nccl().GetUniqueId(&id) != 0) return NBODY_ENCCL;
+    memcpy(id_out, &id, sizeof id);
+    return NBODY_OK;
+}
+
+extern "C" int nbody_set_heat_decay(nbody_ctx* c, double heat_decay)
+{
+    if (!c) return NBODY_EINVAL;
+    c->heat_decay = heat_decay;
+    return NBODY_OK;
+}
+
+extern "C" int nbody_set_stream(nbody_ctx* c, void* cuda_stream)
+{
+    if (!c) return NBODY_EINVAL;
+    Shard& s = c->shards[0];
+    CU(c, cudaSetDevice(s.device));
+    CU(c, cudaStreamSynchronize(s.stream));
+    s.stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : s.own_stream;
+    return NBODY_OK;
+}
+
+extern "C" int nbody_sync(nbody_ctx* c)
+{
+    if (!c) return NBODY_EINVAL;
+    for (Shard& s : c->shards) {
+        CU(c, cudaSetDevice(s.device));
+        CU(c, cudaStreamSynchronize(s.stream));
+    }
+    return NBODY_OK;
+}
+
+extern "C" int nbody_get_info(nbody_ctx* c, nbody_info* o)
+{
+    if (!c || !o) return NBODY_EINVAL;
+    memset(o, 0, sizeof *o);
+    o->n = c->n;
+    o->n_padded = c->n_pad;
+    o->i_begin = std::min(c->shards[0].i_begin, c->n);
+    const Shard& last = c->shards.back();
+    o->i_end = std::min(last.i_begin + last.n_local, c->n);
+    o->n_gpus = int(c->shards.size());
+    o->world = c->world;
+    o->rank = c->rank_mode ? c->my_rank : 0;
+    o->sm_count = c->sm_count;
+    o->j_chunks = c->j_chunks;
+    o->i_tile = c->i_tile;
+    o->kernel_launches = c->launches;
+    return NBODY_OK;
+}
+
+// ============================================================================
+// state
+// ============================================================================
+
+namespace {
+
+template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, const Real* vel, const Real* acc, const Real* temp)
+{
+    const size_t v4 = 4 * sizeof(Real);
+    for (Shard& s : c->shards) {
+        CU(c, cudaSetDevice(s.device));
+        s.n_local = c->n_pad / c->world;
+        s.i_begin = size_t(s.rank) * s.n_local;
+        const size_t lo = std::min(s.i_begin, n), hi = std::min(s.i_begin + s.n_local, n);
+        s.n_local_real = hi - lo;
+        // positions + masses: host AoS -> staging -> device layout (both buffers)
+        CU(c, cudaMemcpyAsync(s.stage, pm, n * v4, cudaMemcpyHostToDevice, s.stream));
+        const unsigned blocks = unsigned((c->n_pad + 255) / 256);
+        pack_pos_kernel<Real><<<blocks, 256, 0, s.stream>>>(static_cast<const Real*>(s.stage), static_cast<Real*>(s.pos[0]),
+                                                           static_cast<Real*>(s.pos[1]), n, c->n_pad);
+        c->launches++;
+        CU(c, cudaGetLastError());
+        CU(c, cudaMemsetAsync(s.vel, 0, s.n_local * v4, s.stream));
+        CU(c, cudaMemsetAsync(s.acc, 0, s.n_local * v4, s.stream));
+        CU(c, cudaMemsetAsync(s.temp, 0, s.n_local * sizeof(Real), s.stream));
+        if (s.n_local_real) {
+            CU(c, cudaMemcpyAsync(s.vel, vel + 4 * lo, s.n_local_real * v4, cudaMemcpyHostToDevice, s.stream));
+            if (acc) CU(c, cudaMemcpyAsync(s.acc, acc + 4 * lo, s.n_local_real * v4, cudaMemcpyHostToDevice, s.stream));
+            if (temp) CU(c, cudaMemcpyAsync(s.temp, temp + lo, s.n_local_real * sizeof(Real), cudaMemcpyHostToDevice, s.stream));
+        }
+        // per-chunk partial sums
+        const size_t need = c->j_chunks > 1 ? size_t(c->j_chunks) * s.n_local * v4 : 0;
+        if (need > s.partial_bytes) {
+            CU(c, cudaStreamSynchronize(s.stream));
+            cudaFree(s.partial);
+            s.partial = nullptr;
+            s.partial_bytes = 0;
+            CU(c, cudaMalloc(&s.partial, need));
+            s.partial_bytes = need;
+        }
+    }
+    // host buffers are borrowed for the duration of the call only
+    for (Shard& s : c->shards) {
+        CU(c, cudaSetDevice(s.device));
+        CU(c, cudaStreamSynchronize(s.stream));
+    }
+    return NBODY_OK;
+}
+
+template <typename Real> int download_t(nbody_ctx* c, Real* pm, Real* vel, Real* acc, Real* temp)
+{
+    const size_t v4 = 4 * sizeof(Real);
+    if (pm && c->n) {
+        Shard& s = c->shards[0];  // every shard holds the complete position array
+        CU(c, cudaSetDevice(s.device));
+        const unsigned blocks = unsigned((c->n + 255) / 256);
+        unpack_pos_kernel<Real><<<blocks, 256, 0, s.stream>>>(static_cast<const Real*>(s.pos[c->cur]), static_cast<Real*>(s.stage), c->n);
+        c->launches++;
+        CU(c, cudaGetLastError());
+        CU(c, cudaMemcpyAsync(pm, s.stage, c->n * v4, cudaMemcpyDeviceToHost, s.stream));
+    }
+    for (Shard& s : c->shards) {
+        CU(c, cudaSetDevice(s.device));
+        const size_t lo = std::min(s.i_begin, c->n);
+        if (s.n_local_real) {
+            if (vel) CU(c, cudaMemcpyAsync(vel + 4 * lo, s.vel, s.n_local_real * v4, cudaMemcpyDeviceToHost, s.stream));
+            if (acc) CU(c, cudaMemcpyAsync(acc + 4 * lo, s.acc, s.n_local_real * v4, cudaMemcpyDeviceToHost, s.stream));
+            if (temp) CU(c, cudaMemcpyAsync(temp + lo, s.temp, s.n_local_real * sizeof(Real), cudaMemcpyDeviceToHost, s.stream));
+        }
+    }
+    for (Shard& s : c->shards) {
+        CU(c, cudaSetDevice(s.device));
+        CU(c, cudaStreamSynchronize(s.stream));
+    }
+    return NBODY_OK;
+}
+
+}  // namespace
+
+extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const void* vel, const void* acc, const void* temp)
+{
+    if (!c) return NBODY_EINVAL;
+    if (n == 0 || n > c->capacity) return fail(c, NBODY_EINVAL, "upload: n=%zu outside 1..capacity=%zu", n, c->capacity);
+    if (!pos_mass || !vel) return fail(c, NBODY_EINVAL, "upload: pos_mass and vel are required");
+    c->n = n;
+    c->n_pad = round_up(n, pad_unit(c));
+    c->cur = 0;
+    c->has_temp = temp != nullptr;
+    choose_chunks(c);
+    return c->prec == NBODY_F32
+               ? upload_t<float>(c, n, (const float*)pos_mass, (const float*)vel, (const float*)acc, (const float*)temp)
+               : upload_t<double>(c, n, (const double*)pos_mass, (const double*)vel, (const double*)acc, (const double*)temp);
+}
+
+extern "C" int nbody_download(nbody_ctx* c, void* pos_mass, void* vel, void* acc, void* temp)
+{
+    if (!c) return NBODY_EINVAL;
+    if (c->n == 0) return fail(c, NBODY_EINVAL, "download before upload");
+    return c->prec == NBODY_F32 ? download_t<float>(c, (float*)pos_mass, (float*)vel, (float*)acc, (float*)temp)
+                                : download_t<double>(c, (double*)pos_mass, (double*)vel, (double*)acc, (double*)temp);
+}
+
+// ============================================================================
+// the hot path
+// ============================================================================
+
+namespace {
+
+constexpr size_t kEventPool = 2048;  // pairs
+
+int fold_timing(nbody_ctx* c, Shard& s)
+{
+    if (s.ev_used == 0) return NBODY_OK;
+    CU(c, cudaSetDevice(s.device));
+    CU(c, cudaStreamSynchronize(s.stream));
+    for (size_t k = 0; k < s.ev_used; k += 2) {
+        float ms = 0.f;
+        CU(c, cudaEventElapsedTime(&ms, s.ev[k], s.ev[k + 1]));
+        c->t_ms += ms;
+        c->t_launches++;
+    }
+    s.ev_used = 0;
+    return NBODY_OK;
+}
+
+// All-gather the shards' freshly written slices of pos[which].
+int exchange_positions(nbody_ctx* c, int which)
+{
+    if (c->world == 1) return NBODY_OK;
+    const size_t v4 = 4 * c->esz;
+    if (!c->rank_mode) NC(c, nccl().GroupStart());
+    for (Shard& s : c->shards) {
+        if (!c->rank_mode) CU(c, cudaSetDevice(s.device));
+        char* base = static_cast<char*>(s.pos[which]);
+        const size_t bytes = s.n_local * v4;
+        NC(c, nccl().AllGather(base + size_t(s.rank) * bytes, base, bytes, ncclUint8_, s.comm, s.stream));
+    }
+    if (!c->rank_mode) NC(c, nccl().GroupEnd());
+    return NBODY_OK;
+}
+
+template <typename Real> ForceParams<Real> make_params(nbody_ctx* c, Shard& s, int mode, double dt, double G, double eps)
+{
+    ForceParams<Real> p;
+    p.pos_cur = static_cast<const Real*>(s.pos[c->cur]);
+    p.pos_next = static_cast<Real*>(s.pos[c->cur ^ 1]);
+    p.vel = static_cast<Real*>(s.vel);
+    p.acc = static_cast<Real*>(s.acc);
+    p.partial = static_cast<Real*>(s.partial);
+    p.temp = c->has_temp ? static_cast<Real*>(s.temp) : nullptr;
+    p.tile_counter = s.counters;
+    p.n_pad = c->n_pad;
+    p.i_begin = s.i_begin;
+    p.n_local = s.n_local;
+    p.chunk_len = c->chunk_len;
+    p.j_chunks = c->j_chunks;
+    p.mode = mode;
+    p.G = Real(G);
+    p.eps2 = Real(eps) * Real(eps);  // epsSq = softening*softening, idx:269
+    p.half_dt = Real(0.5) * Real(dt);  // halfDt = 0.5*dt, idx:248
+    p.dt = Real(dt);
+    p.heat_decay = Real(c->heat_decay);
+    return p;
+}
+
+int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
+{
+    for (Shard& s : c->shards) {
+        CU(c, cudaSetDevice(s.device));
+        const unsigned grid = unsigned(s.n_local / c->i_tile) * unsigned(c->j_chunks);
+        const bool time_it = c->timing && &s == &c->shards[0];
+        if (time_it) {
+            if (s.ev_used + 2 > s.ev.size()) {
+                if (s.ev.size() < 2 * kEventPool) {
+                    for (int k = 0; k < 2; ++k) {
+                        cudaEvent_t e;
+                        CU(c, cudaEventCreate(&e));
+                        s.ev.push_back(e);
+                    }
+                } else {
+                    int rc = fold_timing(c, s);
+                    if (rc != NBODY_OK) return rc;
+                }
+            }
+            CU(c, cudaEventRecord(s.ev[s.ev_used], s.stream));
+        }
+        if (c->prec == NBODY_F32) {
+            const ForceParams<float> p = make_params<float>(c, s, mode, dt, G, eps);
+            const size_t sm = force_f32_smem_bytes();
+            const bool z = (eps == 0.0);
+            const dim3 blk(kThreads + 32);
+            if (c->R == 1) {
+                if (z) force_f32_kernel<1, true><<<grid, blk, sm, s.stream>>>(p);
+                else force_f32_kernel<1, false><<<grid, blk, sm, s.stream>>>(p);
+            } else if (c->R == 2) {
+                if (z) force_f32_kernel<2, true><<<grid, blk, sm, s.stream>>>(p);
+                else force_f32_kernel<2, false><<<grid, blk, sm, s.stream>>>(p);
+            } else {
+                if (z) force_f32_kernel<4, true><<<grid, blk, sm, s.stream>>>(p);
+                else force_f32_kernel<4, false><<<grid, blk, sm, s.stream>>>(p);
+            }
+        } else {
+            const ForceParams<double> p = make_params<double>(c, s, mode, dt, G, eps);
+            force_f64_kernel<<<grid, kThreads + 32, force_f64_smem_bytes(), s.stream>>>(p);
+        }
+        c->launches++;
+        CU(c, cudaGetLastError());
+        if (time_it) {
+            CU(c, cudaEventRecord(s.ev[s.ev_used + 1], s.stream));
+            s.ev_used += 2;
+        }
+    }
+    return NBODY_OK;
+}
+
+int launch_kick1_drift(nbody_ctx* c, double dt)
+{
+    for (Shard& s : c->shards) {
+        CU(c, cudaSetDevice(s.device));
+        const unsigned blocks = unsigned((s.n_local + 255) / 256);
+        if (c->prec == NBODY_F32)
+            kick1_drift_kernel<float><<<blocks, 256, 0, s.stream>>>((float*)s.pos[c->cur], (float*)s.vel, (const float*)s.acc, s.i_begin,
+                                                                   s.n_local, 0.5f * float(dt), float(dt));
+        else
+            kick1_drift_kernel<double><<<blocks, 256, 0, s.stream>>>((double*)s.pos[c->cur], (double*)s.vel, (const double*)s.acc,
+                                                                    s.i_begin, s.n_local, 0.5 * dt, dt);
+        c->launches++;
+        CU(c, cudaGetLastError());
+    }
+    return exchange_positions(c, c->cur);
+}
+
+int check_ready(nbody_ctx* c, const char* what)
+{
+    if (!c) return NBODY_EINVAL;
+    if (c->n == 0) return fail(c, NBODY_EINVAL, "%s before upload", what);
+    return NBODY_OK;
+}
+
+}  // namespace
+
+extern "C" int nbody_step(nbody_ctx* c, double dt, double G, double softening, int nsteps)
+{
+    int rc = check_ready(c, "step");
+    if (rc != NBODY_OK) return rc;
+    if (nsteps < 0 || softening < 0.0) return fail(c, NBODY_EINVAL, "step: nsteps=%d softening=%g", nsteps, softening);
+    if (nsteps == 0) return NBODY_OK;
+    // First loop of integrate() for the first step (idx:250-253); later steps
+    // get theirs from the previous force kernel's epilogue, so positions cross
+    // HBM once per step.
+    rc = launch_kick1_drift(c, dt);
+    if (rc != NBODY_OK) return rc;
+    for (int s = 0; s < nsteps; ++s) {
+        const bool more = s + 1 < nsteps;
+        rc = launch_force(c, more ? kForceKick2Kick1 : kForceKick2, dt, G, softening);
+        if (rc != NBODY_OK) return rc;
+        if (more) {
+            rc = exchange_positions(c, c->cur ^ 1);
+            if (rc != NBODY_OK) return rc;
+            c->cur ^= 1;
+        }
+    }
+    return NBODY_OK;
+}
+
+extern "C" int nbody_kick1_drift(nbody_ctx* c, double dt)
+{
+    int rc = check_ready(c, "kick1_drift");
+    if (rc != NBODY_OK) return rc;
+    return launch_kick1_drift(c, dt);
+}
+
+extern "C" int nbody_force(nbody_ctx* c, double G, double softening)
+{
+    int rc = check_ready(c, "force");
+    if (rc != NBODY_OK) return rc;
+    if (softening < 0.0) return fail(c, NBODY_EINVAL, "force: softening=%g", softening);
+    return launch_force(c, kForceOnly, 0.0, G, softening);
+}
+
+extern "C" int nbody_kick2(nbody_ctx* c, double dt, double heat_decay)
+{
+    int rc = check_ready(c, "kick2");
+    if (rc != NBODY_OK) return rc;
+    for (Shard& s : c->shards) {
+        CU(c, cudaSetDevice(s.device));
+        const unsigned blocks = unsigned((s.n_local + 255) / 256);
+        if (c->prec == NBODY_F32)
+            kick2_kernel<float><<<blocks, 256, 0, s.stream>>>((float*)s.vel, (const float*)s.acc, c->has_temp ? (float*)s.temp : nullptr,
+                                                             s.n_local, 0.5f * float(dt), float(heat_decay));
+        else
+            kick2_kernel<double><<<blocks, 256, 0, s.stream>>>((double*)s.vel, (const double*)s.acc, c->has_temp ? (double*)s.temp : nullptr,
+                                                              s.n_local, 0.5 * dt, heat_decay);
+        c->launches++;
+        CU(c, cudaGetLastError());
+    }
+    return NBODY_OK;
+}
+
+extern "C" int nbody_enable_timing(nbody_ctx* c, int enable)
+{
+    if (!c) return NBODY_EINVAL;
+    int rc = fold_timing(c, c->shards[0]);
+    c->timing = enable != 0;
+    return rc;
+}
+
+extern "C" int nbody_read_timing(nbody_ctx* c, long long* launches, double* force_ms)
+{
+    if (!c) return NBODY_EINVAL;
+    int rc = fold_timing(c, c->shards[0]);
+    if (rc != NBODY_OK) return rc;
+    if (launches) *launches = c->t_launches;
+    if (force_ms) *force_ms = c->t_ms;
+    c->t_launches = 0;
+    c->t_ms = 0.0;
+    return NBODY_OK;
+}
+
+// ============================================================================
+// diagnostics
+// ============================================================================
+
+extern "C" int nbody_energy(nbody_ctx* c, double G, double softening, double* kinetic, double* potential, double momentum[3])
+{
+    int rc = check_ready(c, "energy");
+    if (rc != NBODY_OK) return rc;
+    double tot[5] = {0, 0, 0, 0, 0};
+    std::vector<std::vector<double>> rows(c->shards.size());
+    for (size_t k = 0; k < c->shards.size(); ++k) {
+        Shard& s = c->shards[k];
+        if (s.n_local_real == 0) continue;
+        CU(c, cudaSetDevice(s.device));
+        const unsigned blocks = unsigned((s.n_local_real + kEnergyThreads - 1) / kEnergyThreads);
+        if (c->prec == NBODY_F32)
+            energy_kernel<float><<<blocks, kEnergyThreads, 0, s.stream>>>((const float*)s.pos[c->cur], (const float*)s.vel, c->n, s.i_begin,
+                                                                         s.n_local_real, softening * softening, s.energy_out);
+        else
+            energy_kernel<double><<<blocks, kEnergyThreads, 0, s.stream>>>((const double*)s.pos[c->cur], (const double*)s.vel, c->n,
+                                                                          s.i_begin, s.n_local_real, softening * softening, s.energy_out);
+        c->launches++;
+        CU(c, cudaGetLastError());
+        rows[k].resize(size_t(blocks) * 5);
+        CU(c, cudaMemcpyAsync(rows[k].data(), s.energy_out, rows[k].size() * sizeof(double), cudaMemcpyDeviceToHost, s.stream));
+    }
+    for (size_t k = 0; k < c->shards.size(); ++k) {
+        Shard& s = c->shards[k];
+        CU(c, cudaSetDevice(s.device));
+        CU(c, cudaStreamSynchronize(s.stream));
+        for (size_t b = 0; b < rows[k].size() / 5; ++b)
+            for (int q = 0; q < 5; ++q) tot[q] += rows[k][5 * b + q];
+    }
+    if (c->rank_mode && c->world > 1) {  // add the other processes' shares
+        Shard& s = c->shards[0];
+        CU(c, cudaMemcpyAsync(s.energy_out, tot, sizeof tot, cudaMemcpyHostToDevice, s.stream));
+        NC(c, nccl().AllReduce(s.energy_out, s.energy_out, 5, ncclFloat64_, ncclSum_, s.comm, s.stream));
+        CU(c, cudaMemcpyAsync(tot, s.energy_out, sizeof tot, cudaMemcpyDeviceToHost, s.stream));
+        CU(c, cudaStreamSynchronize(s.stream));
+    }
+    if (kinetic) *kinetic = tot[0];
+    if (potential) *potential = -G * tot[1];
+    if (momentum) {
+        momentum[0] = tot[2];
+        momentum[1] = tot[3];
+        momentum[2] = tot[4];
+    }
+    return NBODY_OK;
+}

@@ -1,0 +1,45 @@
+"""One-process-per-GPU plumbing (torchrun launch): torch.distributed carries the
+128-byte NCCL id and the timing reductions, nothing else.  The position
+exchange itself runs inside libnbody.so on its own communicator.
+
+shard_range() restates the C side's partition (nbody_capi.cu: upload_t) so the
+host logic can be tested on CPU with the gloo backend.
+"""
+from __future__ import annotations
+
+import os
+from typing import Tuple
+
+I_TILE_F32 = 512   # kThreads * R (R = 2), csrc/common.cuh
+I_TILE_F64 = 256
+
+
+def padded_n(n: int, world: int, i_tile: int) -> int:
+    unit = i_tile * world
+    return (n + unit - 1) // unit * unit
+
+
+def shard_range(n: int, world: int, rank: int, i_tile: int) -> Tuple[int, int]:
+    """[begin, end) of the real bodies rank `rank` owns (contiguous
+    i-ranges of the padded array, pads at the tail)."""
+    n_local = padded_n(n, world, i_tile) // world
+    lo = min(rank * n_local, n)
+    hi = min((rank + 1) * n_local, n)
+    return lo, hi
+
+
+def create_rank_engine(capacity: int, precision: str = "f32"):
+    """Engine for this torchrun rank.  Requires torch.distributed to be initialised
+    (any backend) when WORLD_SIZE > 1."""
+    import torch.distributed as dist
+
+    from .engine import Engine, nccl_unique_id
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    device = int(os.environ.get("LOCAL_RANK", "0"))
+    if world == 1:
+        return Engine(capacity, precision=precision, rank=0, world=1, device=device)
+    box = [nccl_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    return Engine(capacity, precision=precision, rank=rank, world=world, device=device, nccl_id=box[0])

@@ -1,0 +1,166 @@
+"""Engine: thin, typed wrapper over the C ABI (include/nbody.h).
+
+Host arrays are numpy, float32 or float64 according to the engine precision,
+in the step-contract layout: pos_mass[n,4] = x,y,z,m; vel[n,4]; acc[n,4];
+temp[n].  All compute happens in libnbody.so on the GPU.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+from ._lib import NBODY_F32, NBODY_F64, NBodyError, check
+
+
+def _ptr(a: Optional[np.ndarray]):
+    return None if a is None else ctypes.c_void_p(a.ctypes.data)
+
+
+class Engine:
+    """One simulation context on one or more B200s.
+
+    precision: "f32" (production) or "f64" (reference-matching mode).
+    n_gpus / device_ids: single-process multi-GPU (the N-API host model).
+    rank/world/nccl_id: one-process-per-GPU model (see dist.create_rank_engine).
+    """
+
+    def __init__(self, capacity: int, precision: str = "f32", n_gpus: int = 1,
+                 device_ids: Optional[Sequence[int]] = None, *, rank: Optional[int] = None,
+                 world: Optional[int] = None, device: int = 0, nccl_id: Optional[bytes] = None):
+        if precision not in ("f32", "f64"):
+            raise ValueError("precision must be 'f32' or 'f64'")
+        self.precision = precision
+        self.dtype = np.float32 if precision == "f32" else np.float64
+        self._L = _lib.lib()
+        self._ctx = ctypes.c_void_p()
+        prec = NBODY_F32 if precision == "f32" else NBODY_F64
+        if rank is None:
+            ids = None
+            if device_ids is not None:
+                ids = (ctypes.c_int * n_gpus)(*device_ids)
+            st = self._L.nbody_create(ctypes.byref(self._ctx), prec, n_gpus, ids, capacity)
+        else:
+            buf = None
+            if nccl_id is not None:
+                if len(nccl_id) != _lib.NCCL_ID_BYTES:
+                    raise ValueError("nccl_id must be 128 bytes")
+                buf = ctypes.create_string_buffer(bytes(nccl_id), _lib.NCCL_ID_BYTES)
+            st = self._L.nbody_create_rank(ctypes.byref(self._ctx), prec, rank, world, device,
+                                           ctypes.cast(buf, ctypes.c_void_p) if buf else None, capacity)
+        if st != _lib.NBODY_OK:
+            self._ctx = ctypes.c_void_p()
+            check(st)
+        self.n = 0
+
+    # -- lifetime ----------------------------------------------------------------
+    def close(self) -> None:
+        if getattr(self, "_ctx", None) and self._ctx.value:
+            self._L.nbody_destroy(self._ctx)
+            self._ctx = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # -- state ---------------------------------------------------------------------
+    def _arr(self, a, shape, name):
+        if a is None:
+            return None
+        a = np.ascontiguousarray(a, dtype=self.dtype)
+        if a.shape != shape:
+            raise ValueError(f"{name} must have shape {shape}, got {a.shape}")
+        return a
+
+    def upload(self, pos_mass, vel, acc=None, temp=None) -> None:
+        pm = np.ascontiguousarray(pos_mass, dtype=self.dtype)
+        if pm.ndim != 2 or pm.shape[1] != 4:
+            raise ValueError("pos_mass must be [n,4]")
+        n = pm.shape[0]
+        v = self._arr(vel, (n, 4), "vel")
+        a = self._arr(acc, (n, 4), "acc")
+        t = self._arr(temp, (n,), "temp")
+        check(self._L.nbody_upload(self._ctx, n, _ptr(pm), _ptr(v), _ptr(a), _ptr(t)), self._ctx)
+        self.n = n
+
+    def download(self, pos_mass=True, vel=True, acc=True, temp=False, out=None):
+        """Returns dict of arrays.  `out` may hold preallocated arrays to fill."""
+        n = self.n
+        out = dict(out or {})
+        want = {"pos_mass": pos_mass, "vel": vel, "acc": acc, "temp": temp}
+        for k, w in want.items():
+            if w and k not in out:
+                out[k] = np.zeros((n,) if k == "temp" else (n, 4), dtype=self.dtype)
+        for k, a in out.items():
+            if a.dtype != self.dtype or not a.flags.c_contiguous:
+                raise ValueError(f"out[{k}] must be contiguous {self.dtype}")
+        check(self._L.nbody_download(self._ctx, _ptr(out.get("pos_mass")), _ptr(out.get("vel")),
+                                     _ptr(out.get("acc")), _ptr(out.get("temp"))), self._ctx)
+        return out
+
+    # -- hot path ------------------------------------------------------------------
+    def step(self, dt: float, G: float, softening: float, nsteps: int = 1) -> None:
+        check(self._L.nbody_step(self._ctx, dt, G, softening, nsteps), self._ctx)
+
+    def kick1_drift(self, dt: float) -> None:
+        check(self._L.nbody_kick1_drift(self._ctx, dt), self._ctx)
+
+    def force(self, G: float, softening: float) -> None:
+        check(self._L.nbody_force(self._ctx, G, softening), self._ctx)
+
+    def kick2(self, dt: float, heat_decay: float = 0.998) -> None:
+        check(self._L.nbody_kick2(self._ctx, dt, heat_decay), self._ctx)
+
+    def set_heat_decay(self, heat_decay: float) -> None:
+        check(self._L.nbody_set_heat_decay(self._ctx, heat_decay), self._ctx)
+
+    # -- diagnostics / plumbing ------------------------------------------------------
+    def energy(self, G: float, softening: float):
+        ke, pe = ctypes.c_double(), ctypes.c_double()
+        mom = (ctypes.c_double * 3)()
+        check(self._L.nbody_energy(self._ctx, G, softening, ctypes.byref(ke), ctypes.byref(pe), mom),
+              self._ctx)
+        return ke.value, pe.value, np.array(list(mom))
+
+    def sync(self) -> None:
+        check(self._L.nbody_sync(self._ctx), self._ctx)
+
+    def set_stream(self, cuda_stream: int) -> None:
+        check(self._L.nbody_set_stream(self._ctx, ctypes.c_void_p(cuda_stream or None)), self._ctx)
+
+    def enable_timing(self, on: bool = True) -> None:
+        check(self._L.nbody_enable_timing(self._ctx, int(on)), self._ctx)
+
+    def read_timing(self):
+        """(force-kernel launches, summed device ms) since the last read."""
+        n, ms = ctypes.c_longlong(), ctypes.c_double()
+        check(self._L.nbody_read_timing(self._ctx, ctypes.byref(n), ctypes.byref(ms)), self._ctx)
+        return n.value, ms.value
+
+    def info(self) -> dict:
+        inf = _lib.Info()
+        check(self._L.nbody_get_info(self._ctx, ctypes.byref(inf)), self._ctx)
+        return {k: getattr(inf, k) for k, _ in _lib.Info._fields_}
+
+
+def device_count() -> int:
+    n = _lib.lib().nbody_device_count()
+    if n < 0:
+        raise NBodyError(n, "cannot query CUDA devices")
+    return n
+
+
+def nccl_unique_id() -> bytes:
+    buf = ctypes.create_string_buffer(_lib.NCCL_ID_BYTES)
+    check(_lib.lib().nbody_nccl_unique_id(ctypes.cast(buf, ctypes.c_void_p)))
+    return buf.raw

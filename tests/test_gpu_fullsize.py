@@ -1,0 +1,94 @@
+"""Full-size and multi-GPU checks through size-independent properties: sampled
+bodies against the oracle in O(k*N), Newton's third law (sum m*a = 0), energy /
+momentum conservation over many steps, invariance to the j-chunk decomposition
+and to the number of GPUs."""
+import os
+
+import numpy as np
+import pytest
+
+from .conftest import norm_rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def test_f32_1m_uniform_cube_sampled_vs_oracle(nb, oracle):
+    """Config 4 at full size: N=1,048,576, G=1, eps=1."""
+    s = nb.scenes.uniform_cube(1048576)
+    pm32 = s.pos_mass.astype(np.float32)
+    with nb.Engine(s.n, precision="f32") as e:
+        e.upload(pm32, np.zeros((s.n, 4), np.float32))
+        e.force(s.G, s.softening)
+        acc = e.download()["acc"].astype(np.float64)
+        info = e.info()
+    idx = np.unique(np.concatenate([[0, 1, 511, 512, s.n - 1], np.random.default_rng(4).integers(0, s.n, 43)]))
+    ref = oracle.acc_subset(pm32.astype(np.float64), idx, s.G, s.softening)
+    err = norm_rel_err(acc[idx], ref)
+    per_body = np.linalg.norm(acc[idx, :3] - ref[:, :3], axis=1) / np.linalg.norm(ref[:, :3], axis=1)
+    print(f"1M cube f32: sampled norm-rel err {err:.3e}, worst per-body {per_body.max():.3e}, j_chunks={info['j_chunks']}")
+    assert err < 2e-5 and per_body.max() < 1e-3     # a uniform cube nearly cancels: per-body is the loose one
+    net = (pm32[:, 3:4].astype(np.float64) * acc[:, :3]).sum(axis=0)
+    scale = np.abs(pm32[:, 3:4] * acc[:, :3]).sum()
+    assert np.abs(net).max() < 1e-5 * scale          # sum m_i a_i = 0 (idx:282-288)
+
+
+def test_f32_two_galaxies_131072_conservation(nb):
+    """Config 3 at full size, shortened to 200 steps here (bench/energy script runs 10k):
+    momentum stays put and energy drift stays small."""
+    s = nb.scenes.two_galaxies(131072)
+    pm, vel, _ = s.astype(np.float32)
+    with nb.Engine(s.n, precision="f32") as e:
+        e.upload(pm, vel)
+        ke0, pe0, m0 = e.energy(s.G, s.softening)
+        e.step(s.dt, s.G, s.softening, 200)
+        ke1, pe1, m1 = e.energy(s.G, s.softening)
+    drift = abs((ke1 + pe1) - (ke0 + pe0)) / abs(ke0 + pe0)
+    print(f"two_galaxies 131072 f32: E0={ke0 + pe0:.6e} drift after 200 steps {drift:.3e}; dP={np.abs(m1 - m0).max():.3e}")
+    assert drift < 1e-4
+    assert np.abs(m1 - m0).max() < 1e-3 * 1100.0 * 1.0   # total mass 1100, bulk speed 1
+
+
+def test_chunking_invariance(nb):
+    """The j-range split only changes fp32 summation order."""
+    s = nb.scenes.plummer(65536)
+    pm, vel, _ = s.astype(np.float32)
+    res = []
+    for chunk in ("0", "65536", "4096", "1024"):
+        os.environ["NBODY_CHUNK_LEN"] = chunk
+        try:
+            with nb.Engine(s.n, precision="f32") as e:
+                e.upload(pm, vel)
+                e.force(s.G, s.softening)
+                res.append((e.info()["j_chunks"], e.download()["acc"]))
+        finally:
+            os.environ.pop("NBODY_CHUNK_LEN", None)
+    assert res[1][0] == 1 and res[3][0] == 64
+    for jc, acc in res[1:]:
+        assert norm_rel_err(acc, res[0][1]) < 5e-6, jc
+
+
+def _multi_gpu(nb):
+    n = nb.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    return n
+
+
+@pytest.mark.parametrize("precision", ["f32", "f64"])
+def test_multi_gpu_bit_identical(nb, precision):
+    """i-range sharding + NCCL all-gather of positions: same bits on 1 and P GPUs
+    (SURVEY.md 8e 'Determinism')."""
+    ng = _multi_gpu(nb)
+    s = nb.scenes.two_galaxies(32768)
+    dt = np.float32 if precision == "f32" else np.float64
+    pm, vel, t = s.astype(dt)
+    outs = []
+    for g in sorted({1, 2, min(ng, 4), min(ng, 8)}):
+        with nb.Engine(s.n, precision=precision, n_gpus=g) as e:
+            e.upload(pm, vel, None, t)
+            e.step(s.dt, s.G, s.softening, 5)
+            outs.append((g, e.download(temp=True), e.energy(s.G, s.softening)))
+    for g, o, en in outs[1:]:
+        for k in ("pos_mass", "vel", "acc", "temp"):
+            assert np.array_equal(o[k], outs[0][1][k]), (g, k)
+        assert abs(en[0] - outs[0][2][0]) < 1e-12 * abs(en[0])

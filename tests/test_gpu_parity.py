@@ -1,0 +1,265 @@
+"""GPU parity tests: the CUDA path (through the C ABI, via nbody_b200.Engine)
+against the CPU oracle on the same seeded inputs.
+
+Parity metric, per array: max_i |x_i^test - x_i^ref|_2 / max_i |x_i^ref|_2.
+Gates: fp64 <= 1e-12 per step (north_star); the integrator part of fp64 is
+bit-exact given equal acc.  fp32 tolerances are stated beside each test.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from .conftest import norm_rel_err
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+F64_GATE = 1e-12
+
+
+def run_engine(nb, scene, precision, nsteps, acc0=None, temp=True, per_call=None):
+    dt = np.float32 if precision == "f32" else np.float64
+    pm, vel, t = scene.astype(dt)
+    with nb.Engine(scene.n, precision=precision) as e:
+        e.upload(pm, vel, None if acc0 is None else acc0.astype(dt), t if temp else None)
+        if per_call is None:
+            e.step(scene.dt, scene.G, scene.softening, nsteps)
+        else:
+            for _ in range(nsteps // per_call):
+                e.step(scene.dt, scene.G, scene.softening, per_call)
+        return e.download(temp=temp)
+
+
+# ---------------------------------------------------------------- fp64 -----------
+def test_f64_default_scene_1000_steps(nb, oracle):
+    """Config 1: N=151, G=0.5, eps=0.5, dt=0.008, 1000 x integrate (gravity-only)."""
+    s = nb.scenes.galaxy_default()
+    out = run_engine(nb, s, "f64", 1000, per_call=2)   # animate(): subSteps=2 per frame, idx:877-879
+    p, v, a, t = oracle.integrate(s.pos_mass, s.vel, np.zeros_like(s.vel), s.temp, s.dt, s.G, s.softening, nsteps=1000)
+    # 1000 chaotic steps amplify 1e-16 force differences; the per-step gate is below
+    assert norm_rel_err(out["pos_mass"], p) < 1e-9
+    assert norm_rel_err(out["vel"], v) < 1e-9
+    assert np.array_equal(out["pos_mass"][:, 3], s.pos_mass[:, 3])
+    np.testing.assert_array_equal(out["temp"], t)      # thermal decay is bit-exact
+
+
+def test_f64_per_step_gate_default_scene(nb, oracle):
+    """Every step restarted from the oracle's state: <= 1e-12 (north_star gate)."""
+    s = nb.scenes.galaxy_default()
+    p, v, a = s.pos_mass.copy(), s.vel.copy(), np.zeros_like(s.vel)
+    with nb.Engine(s.n, precision="f64") as e:
+        for step in range(20):
+            e.upload(p, v, a, s.temp)
+            e.step(s.dt, s.G, s.softening, 1)
+            out = e.download()
+            p, v, a, _ = oracle.integrate(p, v, a, None, s.dt, s.G, s.softening, nsteps=1)
+            assert np.array_equal(out["pos_mass"], p), step   # drift from identical state: bit-exact
+            assert norm_rel_err(out["acc"], a) < F64_GATE
+            assert norm_rel_err(out["vel"], v) < F64_GATE
+
+
+def test_f64_plummer_16384_per_step_gate(nb, oracle):
+    """Config 2: N=16,384 Plummer fp64, per-step gate (oracle: OpenMP variant,
+    bit-identical to the serial one -- tests/test_oracle.py)."""
+    s = nb.scenes.plummer(16384)
+    p, v, a = s.pos_mass.copy(), s.vel.copy(), np.zeros_like(s.vel)
+    worst = 0.0
+    with nb.Engine(s.n, precision="f64") as e:
+        for step in range(3):
+            e.upload(p, v, a)
+            e.step(s.dt, s.G, s.softening, 1)
+            out = e.download()
+            p, v = oracle.kick1_drift(p, v, a, s.dt)
+            a = oracle.compute_gravity(p, s.G, s.softening, mt=True)
+            v, _ = oracle.kick2(v, a, None, s.dt)
+            assert np.array_equal(out["pos_mass"], p)
+            ea, ev = norm_rel_err(out["acc"], a), norm_rel_err(out["vel"], v)
+            worst = max(worst, ea, ev)
+            assert ea < F64_GATE and ev < F64_GATE
+    print(f"plummer16384 f64 worst per-step norm-rel err {worst:.3e}")
+
+
+def test_f64_plummer_2048_100_steps(nb, oracle):
+    s = nb.scenes.plummer(2048)
+    out = run_engine(nb, s, "f64", 100)
+    p, v, a, _ = oracle.integrate(s.pos_mass, s.vel, np.zeros_like(s.vel), None, s.dt, s.G, s.softening, nsteps=100)
+    assert norm_rel_err(out["pos_mass"], p) < 1e-11
+    assert norm_rel_err(out["vel"], v) < 1e-10
+
+
+@pytest.mark.parametrize("name", ["galaxy151_f64", "plummer512_f64"])
+def test_f64_golden_fixtures(nb, name):
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    with nb.Engine(g["pos_mass0"].shape[0], precision="f64") as e:
+        e.upload(g["pos_mass0"], g["vel0"], None, g["temp0"])
+        e.step(float(g["dt"]), float(g["G"]), float(g["softening"]), int(g["nsteps"]))
+        out = e.download(temp=True)
+    assert norm_rel_err(out["pos_mass"], g["pos_mass"]) < 1e-11
+    assert norm_rel_err(out["vel"], g["vel"]) < 1e-11
+    assert norm_rel_err(out["acc"], g["acc"]) < 1e-11
+    np.testing.assert_array_equal(out["temp"], g["temp"])
+
+
+# ---------------------------------------------------------------- fp32 -----------
+# fp32 per-step tolerances (norm-relative): the rsqrt approximation (2 ulp) and fp32
+# accumulation give acc ~1e-6; pos/vel after ONE step from identical state are far tighter.
+F32_ACC_TOL = 2e-5
+F32_VEL_TOL = 1e-6
+F32_POS_TOL = 1e-6
+
+
+@pytest.mark.parametrize("scene,n", [("galaxy_default", 151), ("plummer", 1000), ("two_galaxies", 4096),
+                                     ("uniform_cube", 8192), ("cold_collapse", 5000)])
+def test_f32_force_vs_oracle(nb, oracle, scene, n):
+    s = nb.scenes.SCENES[scene]() if scene == "galaxy_default" else nb.scenes.SCENES[scene](n)
+    pm32 = s.pos_mass.astype(np.float32)
+    ref = oracle.compute_gravity(pm32.astype(np.float64), s.G, s.softening, mt=True)
+    with nb.Engine(s.n, precision="f32") as e:
+        e.upload(pm32, s.vel.astype(np.float32))
+        e.force(s.G, s.softening)
+        acc = e.download()["acc"]
+    err = norm_rel_err(acc, ref)
+    print(f"{scene} n={s.n} f32 acc norm-rel err {err:.3e}")
+    assert err < F32_ACC_TOL
+
+
+def test_f32_step_vs_oracle(nb, oracle):
+    s = nb.scenes.two_galaxies(4096)
+    pm, vel, t = s.astype(np.float32)
+    out = run_engine(nb, s, "f32", 1)
+    p, v, a, _ = oracle.integrate(pm.astype(np.float64), vel.astype(np.float64), np.zeros((s.n, 4)), None, s.dt, s.G,
+                                  s.softening, nsteps=1)
+    assert norm_rel_err(out["pos_mass"], p) < F32_POS_TOL
+    assert norm_rel_err(out["vel"], v) < F32_VEL_TOL
+    assert norm_rel_err(out["acc"], a) < F32_ACC_TOL
+
+
+@pytest.mark.parametrize("precision", ["f32", "f64"])
+def test_fused_steps_equal_single_steps(nb, precision):
+    """step(nsteps=k) (kick-1/drift folded into the previous force epilogue) must be
+    BIT-identical to k calls of step(1) and to the split entry points."""
+    s = nb.scenes.plummer(3000)
+    s.softening = 0.05
+    a = run_engine(nb, s, precision, 6)
+    b = run_engine(nb, s, precision, 6, per_call=1)
+    for k in ("pos_mass", "vel", "acc"):
+        assert np.array_equal(a[k], b[k]), k
+    dt = np.float32 if precision == "f32" else np.float64
+    pm, vel, _ = s.astype(dt)
+    with nb.Engine(s.n, precision=precision) as e:
+        e.upload(pm, vel)
+        for _ in range(6):
+            e.kick1_drift(s.dt)
+            e.force(s.G, s.softening)
+            e.kick2(s.dt, 0.998)
+        c = e.download()
+    for k in ("pos_mass", "vel", "acc"):
+        assert np.array_equal(a[k], c[k]), k
+
+
+@pytest.mark.parametrize("precision", ["f32", "f64"])
+@pytest.mark.parametrize("n", [1, 2, 3, 255, 256, 257, 511, 513, 1025])
+def test_ragged_sizes(nb, oracle, precision, n):
+    s = nb.scenes.uniform_cube(n)
+    s.softening = 0.5
+    dt = np.float32 if precision == "f32" else np.float64
+    pm = s.pos_mass.astype(dt)
+    pm[:, 3] = 1.0
+    ref = oracle.compute_gravity(pm.astype(np.float64), 1.0, s.softening)
+    with nb.Engine(max(n, 4), precision=precision) as e:
+        e.upload(pm, np.zeros((n, 4), dt))
+        e.force(1.0, s.softening)
+        acc = e.download()["acc"]
+    if n == 1:
+        assert not acc.any()
+    else:
+        assert norm_rel_err(acc, ref) < (F32_ACC_TOL if precision == "f32" else F64_GATE)
+
+
+@pytest.mark.parametrize("precision", ["f32", "f64"])
+def test_zero_softening(nb, oracle, precision):
+    """softening = 0: the reference never evaluates the self pair (idx:273); the
+    all-pairs sweep must not turn it into NaN."""
+    s = nb.scenes.uniform_cube(700)
+    dt = np.float32 if precision == "f32" else np.float64
+    pm = s.pos_mass.astype(dt)
+    ref = oracle.compute_gravity(pm.astype(np.float64), 1.0, 0.0)
+    with nb.Engine(s.n, precision=precision) as e:
+        e.upload(pm, np.zeros((s.n, 4), dt))
+        e.force(1.0, 0.0)
+        acc = e.download()["acc"]
+    assert np.isfinite(acc).all()
+    assert norm_rel_err(acc, ref) < (5e-5 if precision == "f32" else F64_GATE)
+
+
+def test_thermal_and_acc_state(nb, oracle):
+    """temperature rides along (idx:260); uploaded acc is state for kick-1 (idx:251)."""
+    s = nb.scenes.galaxy_default()
+    acc0 = oracle.compute_gravity(s.pos_mass, s.G, s.softening)
+    out = run_engine(nb, s, "f64", 5, acc0=acc0)
+    p, v, a, t = oracle.integrate(s.pos_mass, s.vel, acc0, s.temp, s.dt, s.G, s.softening, nsteps=5)
+    assert norm_rel_err(out["pos_mass"], p) < F64_GATE and norm_rel_err(out["vel"], v) < F64_GATE
+    np.testing.assert_array_equal(out["temp"], t)
+    assert out["temp"][0] == 1000 * 0.998 ** 5 or abs(out["temp"][0] - 1000 * 0.998 ** 5) < 1e-9
+
+
+def test_energy_matches_oracle(nb, oracle):
+    s = nb.scenes.plummer(2000)
+    for precision in ("f32", "f64"):
+        dt = np.float32 if precision == "f32" else np.float64
+        pm, vel, _ = s.astype(dt)
+        with nb.Engine(s.n, precision=precision) as e:
+            e.upload(pm, vel)
+            ke, pe, mom = e.energy(s.G, s.softening)
+        ke0, pe0, mom0 = oracle.energy(pm.astype(np.float64), vel.astype(np.float64), s.G, s.softening)
+        assert abs(ke - ke0) < 1e-12 * abs(ke0) and abs(pe - pe0) < 1e-12 * abs(pe0)
+        assert np.abs(mom - mom0).max() < 1e-15
+
+
+def test_error_paths(nb):
+    with nb.Engine(100, precision="f32") as e:
+        with pytest.raises(nb.NBodyError) as ei:
+            e.step(0.01, 1.0, 0.1, 1)            # step before upload
+        assert ei.value.status == -1
+        with pytest.raises(nb.NBodyError):
+            e.upload(np.zeros((200, 4), np.float32), np.zeros((200, 4), np.float32))  # over capacity
+        e.upload(np.ones((10, 4), np.float32), np.zeros((10, 4), np.float32))
+        with pytest.raises(nb.NBodyError):
+            e.step(0.01, 1.0, -1.0, 1)           # negative softening
+        e.step(0.01, 1.0, 0.1, 0)                # zero steps: no-op
+        info = e.info()
+        assert info["n"] == 10 and info["n_padded"] % info["i_tile"] == 0 and info["sm_count"] > 0
+
+
+def test_physics_system_mirror(nb, oracle):
+    """The reference-shaped host API: Body / PhysicsSystem.addBody / integrate (idx:208-262)."""
+    import random
+    ps = nb.PhysicsSystem(precision="f64")
+    nb.resetScenario(ps, "galaxy", rng=random.Random(7))
+    assert len(ps.bodies) == 151
+    pm = np.array([[b.pos.x, b.pos.y, b.pos.z, b.mass] for b in ps.bodies])
+    vel = np.array([[b.vel.x, b.vel.y, b.vel.z, 0] for b in ps.bodies])
+    temp = np.array([b.temperature for b in ps.bodies])
+    for _ in range(nb.CONFIG.subSteps):                      # animate(), idx:877-879
+        ps.integrate(nb.CONFIG.dt / nb.CONFIG.subSteps)
+    p, v, a, t = oracle.integrate(pm, vel, np.zeros_like(vel), temp, 0.008, 0.5, 0.5, nsteps=2)
+    got_p = np.array([[b.pos.x, b.pos.y, b.pos.z, b.mass] for b in ps.bodies])
+    got_v = np.array([[b.vel.x, b.vel.y, b.vel.z, 0] for b in ps.bodies])
+    got_a = np.array([[b.acc.x, b.acc.y, b.acc.z, 0] for b in ps.bodies])
+    assert norm_rel_err(got_p, p) < F64_GATE and norm_rel_err(got_v, v) < F64_GATE and norm_rel_err(got_a, a) < F64_GATE
+    assert ps.bodies[0].temperature == t[0]
+    # split form with a host collision stage that does nothing == plain integrate
+    ps2 = nb.PhysicsSystem(precision="f64")
+    nb.resetScenario(ps2, "galaxy", rng=random.Random(7))
+    calls = []
+    for _ in range(2):
+        ps2.integrate(0.008, collide=lambda sysm, dt: calls.append(dt))
+    assert calls == [0.008, 0.008]
+    got_p2 = np.array([[b.pos.x, b.pos.y, b.pos.z, b.mass] for b in ps2.bodies])
+    assert np.array_equal(got_p2, got_p)
+    # maxBodies cap drops the oldest body (idx:240-242)
+    ps3 = nb.PhysicsSystem(precision="f64")
+    for k in range(nb.CONFIG.maxBodies + 5):
+        ps3.addBody(nb.Body(1.0, nb.V3(k, 0, 0), nb.V3(0, 0, 0)))
+    assert len(ps3.bodies) == nb.CONFIG.maxBodies and ps3.bodies[0].pos.x == 5
