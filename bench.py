@@ -161,7 +161,10 @@ def main():
     scene = nb.scenes.uniform_cube(args.n)
     pm, vel, _ = scene.astype(np.float32)
     eng = nb.create_rank_engine(args.n, "f32")
-    stream = torch.cuda.current_stream()
+    # a real (non-default) stream: the engine, the L2 flush and the timing events all run on it
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
     eng.set_stream(stream.cuda_stream)
     eng.upload(pm, vel)
     info = eng.info()
