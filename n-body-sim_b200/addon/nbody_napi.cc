@@ -1,0 +1,342 @@
+// nbody_napi.cc -- Node-API addon: a thin shim from JS typed arrays to the C ABI
+// of libnbody.so (include/nbody.h).  This is the "N-API addon ... that the
+// unchanged JS host calls with typed arrays" of BASELINE.json:north_star; the JS
+// side is physics_shim.js, which replaces the body of PhysicsSystem.integrate
+// (/root/reference/index.html:247-262).
+//
+// JS surface (all functions throw a JS Error carrying nbody_last_error on a
+// non-zero status, because the reference's integrate() has no error channel):
+//   create(precision: 'f32'|'f64', nGpus: int, capacity: int) -> ctx (external)
+//   destroy(ctx)
+//   upload(ctx, posMass, vel, acc|null, temp|null)        Float32Array/Float64Array
+//   download(ctx, posMass|null, vel|null, acc|null, temp|null)
+//   step(ctx, dt, G, softening, nsteps)                   nsteps x integrate(dt)
+//   kick1Drift(ctx, dt) / force(ctx, G, softening) / kick2(ctx, dt, heatDecay)
+//   energy(ctx, G, softening) -> {kinetic, potential, momentum: [px,py,pz]}
+//   sync(ctx); info(ctx) -> {n, nPadded, nGpus, jChunks, iTile, kernelLaunches}
+//   version() -> string; deviceCount() -> int
+#include "napi_min.h"
+
+#include <cstdio>
+#include <cstring>
+
+#include "../../include/nbody.h"
+
+namespace {
+
+struct Handle {
+    nbody_ctx* ctx;
+    nbody_prec prec;
+};
+
+napi_value undefined(napi_env env)
+{
+    napi_value u = nullptr;
+    napi_get_undefined(env, &u);
+    return u;
+}
+
+napi_value fail(napi_env env, const char* what, int status, const nbody_ctx* ctx)
+{
+    char msg[640];
+    const char* detail = ctx ? nbody_last_error(ctx) : "";
+    snprintf(msg, sizeof msg, "nbody.%s: %s%s%s", what, nbody_strerror(status), detail[0] ? ": " : "", detail);
+    napi_throw_error(env, "NBODY", msg);
+    return undefined(env);
+}
+
+struct Args {
+    size_t argc = 8;
+    napi_value v[8] = {};
+};
+
+bool get_args(napi_env env, napi_callback_info info, Args& a, size_t need, const char* what)
+{
+    if (napi_get_cb_info(env, info, &a.argc, a.v, nullptr, nullptr) != napi_ok || a.argc < need) {
+        char msg[96];
+        snprintf(msg, sizeof msg, "nbody.%s: expected %zu arguments", what, need);
+        napi_throw_error(env, "NBODY", msg);
+        return false;
+    }
+    return true;
+}
+
+Handle* get_handle(napi_env env, napi_value v, const char* what)
+{
+    void* p = nullptr;
+    if (napi_get_value_external(env, v, &p) != napi_ok || !p || !static_cast<Handle*>(p)->ctx) {
+        char msg[96];
+        snprintf(msg, sizeof msg, "nbody.%s: first argument is not a live context", what);
+        napi_throw_error(env, "NBODY", msg);
+        return nullptr;
+    }
+    return static_cast<Handle*>(p);
+}
+
+bool get_double(napi_env env, napi_value v, double* out) { return napi_get_value_double(env, v, out) == napi_ok; }
+
+// null/undefined -> (nullptr, 0).  Otherwise the array must match the context precision.
+bool get_array(napi_env env, napi_value v, nbody_prec prec, void** data, size_t* len, const char* what)
+{
+    *data = nullptr;
+    *len = 0;
+    napi_valuetype t = napi_undefined;
+    napi_typeof(env, v, &t);
+    if (t == napi_undefined || t == napi_null) return true;
+    bool is_ta = false;
+    napi_typedarray_type ty = napi_int8_array;
+    if (napi_is_typedarray(env, v, &is_ta) != napi_ok || !is_ta ||
+        napi_get_typedarray_info(env, v, &ty, len, data, nullptr, nullptr) != napi_ok ||
+        ty != (prec == NBODY_F32 ? napi_float32_array : napi_float64_array)) {
+        char msg[160];
+        snprintf(msg, sizeof msg, "nbody.%s: arrays must be %s (the context precision)", what,
+                 prec == NBODY_F32 ? "Float32Array" : "Float64Array");
+        napi_throw_error(env, "NBODY", msg);
+        return false;
+    }
+    return true;
+}
+
+void finalize_handle(napi_env, void* data, void*)
+{
+    Handle* h = static_cast<Handle*>(data);
+    if (h->ctx) nbody_destroy(h->ctx);
+    delete h;
+}
+
+// ---- lifetime ---------------------------------------------------------------
+
+napi_value Create(napi_env env, napi_callback_info info)
+{
+    Args a;
+    if (!get_args(env, info, a, 3, "create")) return undefined(env);
+    char prec_s[8] = {};
+    size_t n = 0;
+    napi_get_value_string_utf8(env, a.v[0], prec_s, sizeof prec_s, &n);
+    double n_gpus = 1, capacity = 0;
+    if (!get_double(env, a.v[1], &n_gpus) || !get_double(env, a.v[2], &capacity) ||
+        (strcmp(prec_s, "f32") != 0 && strcmp(prec_s, "f64") != 0) || capacity < 1) {
+        napi_throw_error(env, "NBODY", "nbody.create(precision 'f32'|'f64', nGpus, capacity)");
+        return undefined(env);
+    }
+    Handle* h = new Handle{nullptr, strcmp(prec_s, "f64") == 0 ? NBODY_F64 : NBODY_F32};
+    const int rc = nbody_create(&h->ctx, h->prec, int(n_gpus), nullptr, size_t(capacity));
+    if (rc != NBODY_OK) {
+        delete h;
+        return fail(env, "create", rc, nullptr);
+    }
+    napi_value ext = nullptr;
+    napi_create_external(env, h, finalize_handle, nullptr, &ext);
+    return ext;
+}
+
+napi_value Destroy(napi_env env, napi_callback_info info)
+{
+    Args a;
+    if (!get_args(env, info, a, 1, "destroy")) return undefined(env);
+    void* p = nullptr;
+    if (napi_get_value_external(env, a.v[0], &p) == napi_ok && p) {
+        Handle* h = static_cast<Handle*>(p);
+        if (h->ctx) nbody_destroy(h->ctx);
+        h->ctx = nullptr;  // the finalizer frees the Handle itself
+    }
+    return undefined(env);
+}
+
+// ---- state --------------------------------------------------------------------
+
+napi_value Upload(napi_env env, napi_callback_info info)
+{
+    Args a;
+    if (!get_args(env, info, a, 3, "upload")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "upload");
+    if (!h) return undefined(env);
+    void* p[4] = {};
+    size_t len[4] = {};
+    for (int k = 0; k < 4; ++k)
+        if (size_t(k + 1) < a.argc && !get_array(env, a.v[k + 1], h->prec, &p[k], &len[k], "upload")) return undefined(env);
+    const size_t n = len[0] / 4;
+    if (!p[0] || !p[1] || len[0] % 4 || len[1] != len[0] || (p[2] && len[2] != len[0]) || (p[3] && len[3] != n)) {
+        napi_throw_error(env, "NBODY", "nbody.upload: posMass[4n], vel[4n], acc[4n]|null, temp[n]|null");
+        return undefined(env);
+    }
+    const int rc = nbody_upload(h->ctx, n, p[0], p[1], p[2], p[3]);
+    return rc == NBODY_OK ? undefined(env) : fail(env, "upload", rc, h->ctx);
+}
+
+napi_value Download(napi_env env, napi_callback_info info)
+{
+    Args a;
+    if (!get_args(env, info, a, 2, "download")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "download");
+    if (!h) return undefined(env);
+    nbody_info inf;
+    nbody_get_info(h->ctx, &inf);
+    void* p[4] = {};
+    size_t len[4] = {};
+    for (int k = 0; k < 4; ++k) {
+        if (size_t(k + 1) >= a.argc) break;
+        if (!get_array(env, a.v[k + 1], h->prec, &p[k], &len[k], "download")) return undefined(env);
+        if (p[k] && len[k] < (k == 3 ? inf.n : 4 * inf.n)) {
+            napi_throw_error(env, "NBODY", "nbody.download: array shorter than the uploaded body count");
+            return undefined(env);
+        }
+    }
+    const int rc = nbody_download(h->ctx, p[0], p[1], p[2], p[3]);
+    return rc == NBODY_OK ? undefined(env) : fail(env, "download", rc, h->ctx);
+}
+
+// ---- the hot path ---------------------------------------------------------------
+
+// step(ctx, dt, G, softening, nsteps): nsteps x PhysicsSystem.integrate(dt), idx:247-262
+napi_value Step(napi_env env, napi_callback_info info)
+{
+    Args a;
+    if (!get_args(env, info, a, 5, "step")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "step");
+    if (!h) return undefined(env);
+    double dt, G, eps;
+    int32_t nsteps = 1;
+    if (!get_double(env, a.v[1], &dt) || !get_double(env, a.v[2], &G) || !get_double(env, a.v[3], &eps) ||
+        napi_get_value_int32(env, a.v[4], &nsteps) != napi_ok) {
+        napi_throw_error(env, "NBODY", "nbody.step(ctx, dt, G, softening, nsteps): numbers expected");
+        return undefined(env);
+    }
+    const int rc = nbody_step(h->ctx, dt, G, eps, nsteps);
+    return rc == NBODY_OK ? undefined(env) : fail(env, "step", rc, h->ctx);
+}
+
+napi_value Kick1Drift(napi_env env, napi_callback_info info)  // idx:248-253
+{
+    Args a;
+    if (!get_args(env, info, a, 2, "kick1Drift")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "kick1Drift");
+    double dt;
+    if (!h || !get_double(env, a.v[1], &dt)) return undefined(env);
+    const int rc = nbody_kick1_drift(h->ctx, dt);
+    return rc == NBODY_OK ? undefined(env) : fail(env, "kick1Drift", rc, h->ctx);
+}
+
+napi_value Force(napi_env env, napi_callback_info info)  // computeGravity, idx:264-291
+{
+    Args a;
+    if (!get_args(env, info, a, 3, "force")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "force");
+    double G, eps;
+    if (!h || !get_double(env, a.v[1], &G) || !get_double(env, a.v[2], &eps)) return undefined(env);
+    const int rc = nbody_force(h->ctx, G, eps);
+    return rc == NBODY_OK ? undefined(env) : fail(env, "force", rc, h->ctx);
+}
+
+napi_value Kick2(napi_env env, napi_callback_info info)  // idx:258-261
+{
+    Args a;
+    if (!get_args(env, info, a, 3, "kick2")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "kick2");
+    double dt, decay;
+    if (!h || !get_double(env, a.v[1], &dt) || !get_double(env, a.v[2], &decay)) return undefined(env);
+    const int rc = nbody_kick2(h->ctx, dt, decay);
+    return rc == NBODY_OK ? undefined(env) : fail(env, "kick2", rc, h->ctx);
+}
+
+napi_value SetHeatDecay(napi_env env, napi_callback_info info)  // CONFIG.heatDecay, idx:67
+{
+    Args a;
+    if (!get_args(env, info, a, 2, "setHeatDecay")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "setHeatDecay");
+    double decay;
+    if (!h || !get_double(env, a.v[1], &decay)) return undefined(env);
+    nbody_set_heat_decay(h->ctx, decay);
+    return undefined(env);
+}
+
+// ---- diagnostics ------------------------------------------------------------------
+
+napi_value Energy(napi_env env, napi_callback_info info)
+{
+    Args a;
+    if (!get_args(env, info, a, 3, "energy")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "energy");
+    double G, eps;
+    if (!h || !get_double(env, a.v[1], &G) || !get_double(env, a.v[2], &eps)) return undefined(env);
+    double ke = 0, pe = 0, mom[3] = {0, 0, 0};
+    const int rc = nbody_energy(h->ctx, G, eps, &ke, &pe, mom);
+    if (rc != NBODY_OK) return fail(env, "energy", rc, h->ctx);
+    napi_value obj, v, arr;
+    napi_create_object(env, &obj);
+    napi_create_double(env, ke, &v);
+    napi_set_named_property(env, obj, "kinetic", v);
+    napi_create_double(env, pe, &v);
+    napi_set_named_property(env, obj, "potential", v);
+    napi_create_array_with_length(env, 3, &arr);
+    for (uint32_t k = 0; k < 3; ++k) {
+        napi_create_double(env, mom[k], &v);
+        napi_set_element(env, arr, k, v);
+    }
+    napi_set_named_property(env, obj, "momentum", arr);
+    return obj;
+}
+
+napi_value Sync(napi_env env, napi_callback_info info)
+{
+    Args a;
+    if (!get_args(env, info, a, 1, "sync")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "sync");
+    if (!h) return undefined(env);
+    const int rc = nbody_sync(h->ctx);
+    return rc == NBODY_OK ? undefined(env) : fail(env, "sync", rc, h->ctx);
+}
+
+napi_value Info(napi_env env, napi_callback_info info)
+{
+    Args a;
+    if (!get_args(env, info, a, 1, "info")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "info");
+    if (!h) return undefined(env);
+    nbody_info inf;
+    const int rc = nbody_get_info(h->ctx, &inf);
+    if (rc != NBODY_OK) return fail(env, "info", rc, h->ctx);
+    napi_value obj, v;
+    napi_create_object(env, &obj);
+    const struct { const char* k; double x; } rows[] = {
+        {"n", double(inf.n)}, {"nPadded", double(inf.n_padded)}, {"nGpus", double(inf.n_gpus)},
+        {"jChunks", double(inf.j_chunks)}, {"iTile", double(inf.i_tile)}, {"smCount", double(inf.sm_count)},
+        {"kernelLaunches", double(inf.kernel_launches)}};
+    for (const auto& r : rows) {
+        napi_create_double(env, r.x, &v);
+        napi_set_named_property(env, obj, r.k, v);
+    }
+    return obj;
+}
+
+napi_value Version(napi_env env, napi_callback_info)
+{
+    napi_value s = nullptr;
+    napi_create_string_utf8(env, nbody_version(), NAPI_AUTO_LENGTH, &s);
+    return s;
+}
+
+napi_value DeviceCount(napi_env env, napi_callback_info)
+{
+    napi_value v = nullptr;
+    napi_create_int32(env, nbody_device_count(), &v);
+    return v;
+}
+
+}  // namespace
+
+// Node loads the addon through this well-known symbol (what NAPI_MODULE_INIT expands to).
+extern "C" __attribute__((visibility("default"))) napi_value napi_register_module_v1(napi_env env, napi_value exports)
+{
+    const struct { const char* name; napi_callback cb; } fns[] = {
+        {"create", Create}, {"destroy", Destroy}, {"upload", Upload}, {"download", Download},
+        {"step", Step}, {"kick1Drift", Kick1Drift}, {"force", Force}, {"kick2", Kick2},
+        {"setHeatDecay", SetHeatDecay}, {"energy", Energy}, {"sync", Sync}, {"info", Info},
+        {"version", Version}, {"deviceCount", DeviceCount}};
+    for (const auto& f : fns) {
+        napi_value fn = nullptr;
+        if (napi_create_function(env, f.name, NAPI_AUTO_LENGTH, f.cb, nullptr, &fn) != napi_ok) return exports;
+        napi_set_named_property(env, exports, f.name, fn);
+    }
+    return exports;
+}
