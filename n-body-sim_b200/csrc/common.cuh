@@ -15,10 +15,18 @@
 
 namespace nb {
 
-constexpr int kThreads = 256;       // compute threads per CTA (8 warps) + 1 producer warp
+// fp64 kernel: 8 compute warps + 1 producer warp, one i-body per thread
+constexpr int kThreads = 256;       // compute threads per CTA
 constexpr int kStages = 4;          // j-tile ring depth
-constexpr int kTileBytes = 16384;   // bytes per j-tile stage (1024 fp32 bodies / 512 fp64 bodies)
-constexpr int kPadBodies = 2048;    // n is padded to this (256-body i-tiles x up to 8 shards)
+constexpr int kTileBytes = 16384;   // bytes per j-tile stage (512 fp64 bodies)
+// fp32 kernel (shape chosen by the force_lab sweeps, profiles/r1_force_lab_sweep*.txt):
+// 4 compute warps + 1 producer warp, R i-bodies per thread, 3 CTAs per SM at 128 registers
+constexpr int kF32Threads = 128;    // compute threads per CTA
+constexpr int kF32TilePairs = 256;  // j-PAIRS per ring stage (8 KiB, 512 bodies)
+constexpr int kF32Stages = 4;
+// The j extent and every j-chunk are multiples of this many bodies (one ring stage of
+// either kernel), so tiles are always full.
+constexpr int kJUnit = 512;
 
 template <typename Real> struct Vec4;
 template <> struct Vec4<float> { using type = float4; };
@@ -49,10 +57,10 @@ template <typename Real> struct ForceParams {
     Real* partial;          // [j_chunks][n_local] Real4
     Real* temp;             // local, may be null
     unsigned* tile_counter; // one per local i-tile; zero between launches
-    size_t n_pad;           // padded body count (j range)
+    size_t n_j;             // j extent: n rounded up to kJUnit (independent of the GPU count)
     size_t i_begin;         // first global body of this shard (multiple of i-tile)
     size_t n_local;         // padded local body count (multiple of i-tile)
-    size_t chunk_len;       // bodies per j-chunk (multiple of 64)
+    size_t chunk_len;       // bodies per j-chunk (multiple of kJUnit)
     int j_chunks;
     int mode;
     Real G, eps2, half_dt, dt, heat_decay;  // heat_decay <= 0: no thermal update

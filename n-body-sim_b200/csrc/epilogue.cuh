@@ -61,16 +61,16 @@ __device__ __forceinline__ void finish_body(const ForceParams<Real>& p, size_t i
 // per-chunk partial sums; the CTA that arrives last adds them in ascending
 // chunk order (a fixed order: results do not depend on CTA scheduling or on
 // how many GPUs share the work) and runs the integrator.  Returns true in the
-// last CTA only.  Called by the kThreads compute threads (named barrier 1).
-__device__ __forceinline__ bool tile_arrive_last(unsigned* counter, int j_chunks, int* s_flag)
+// last CTA only.  Called by the CTA's `nthreads` compute threads (named barrier 1).
+__device__ __forceinline__ bool tile_arrive_last(unsigned* counter, int j_chunks, int* s_flag, int nthreads)
 {
     __threadfence();
-    asm volatile("bar.sync 1, %0;" ::"r"(kThreads) : "memory");
+    asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
     if (threadIdx.x == 0) {
         const unsigned prev = atomicAdd(counter, 1u);
         *s_flag = (prev == static_cast<unsigned>(j_chunks - 1));
     }
-    asm volatile("bar.sync 1, %0;" ::"r"(kThreads) : "memory");
+    asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
     const bool last = (*s_flag != 0);
     if (last) __threadfence();
     return last;

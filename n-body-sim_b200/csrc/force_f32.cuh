@@ -2,17 +2,23 @@
 // Replaces PhysicsSystem.computeGravity (/root/reference/index.html:264-291) and
 // the two O(N) loops of integrate (idx:250-253, 258-261).
 //
-// Work unit = one CTA = (i-tile of kThreads*R bodies) x (j-chunk).  i-bodies live
-// in registers; the j-chunk streams through a kStages-deep shared-memory ring
-// filled by 1-D bulk copies (TMA, UBLKCP) issued by a dedicated producer warp and
-// tracked with full/empty mbarriers.  Because pos_mass is pair-interleaved in
-// HBM, one broadcast LDS.128 pair delivers two j-bodies as aligned 64-bit
-// register pairs, and each interaction PAIR costs
+// Work unit = one CTA = (i-tile of kF32Threads*R bodies) x (j-chunk).  i-bodies live
+// in registers; the j-chunk streams through a kF32Stages-deep shared-memory ring of
+// FULL 8 KiB tiles (256 j-pairs) filled by 1-D bulk copies (TMA, UBLKCP) issued by a
+// dedicated producer warp and tracked with full/empty mbarriers.  Because pos_mass is
+// pair-interleaved in HBM, one broadcast LDS.128 pair delivers two j-bodies as aligned
+// 64-bit register pairs, and each interaction PAIR costs
 //     3 FADD2 + 3 FFMA2 + 2 MUFU.RSQ + 3 FMUL2 + 3 FFMA2
-// = 12 packed FP32 instructions + 2 MUFU for two interactions: the 12
-// FP32-lane-ops per interaction of the roofline in 7 issue slots
-// instead of 13, which leaves issue slots for LDS/loop overhead and makes the
-// FP32 pipe, not instruction issue, the bound.  G is applied once per body.
+// = 12 packed FP32 instructions + 2 MUFU for two interactions: the 12 FP32-lane-ops
+// per interaction of the roofline in 7 issue slots instead of 13.
+// G is applied once per body.
+//
+// Shape (4 compute warps, R = 4, unroll 4, 128 registers, 3 CTAs/SM) is the best of
+// the force_lab sweeps (profiles/r1_force_lab_sweep*.txt): 9.2 interactions/clk/SM.
+// The plateau is insensitive to ring depth, unroll and occupancy, and an 11-op
+// formulation (mass-scaled coordinates) does not move it: the packed FP32
+// instructions sustain ~112 lanes/clk/SM (pipe_bench), i.e. 12 x 2.29 = 27.5 cycles
+// per interaction pair per SM sub-partition, and the kernel runs at 27.8.
 #pragma once
 #include "common.cuh"
 #include "epilogue.cuh"
@@ -57,20 +63,25 @@ __device__ __forceinline__ float rsqrt_approx(float x)
     return r;
 }
 
-constexpr size_t force_f32_smem_bytes() { return size_t(kStages) * kTileBytes + 2 * kStages * 8; }
+#ifndef NB_F32_UNROLL
+#define NB_F32_UNROLL 16
+#endif
+constexpr int kF32Unroll = NB_F32_UNROLL;  // j-pairs per inner-loop iteration
+constexpr int kF32TileBytes = kF32TilePairs * 32;
+constexpr size_t force_f32_smem_bytes() { return size_t(kF32Stages) * kF32TileBytes + 2 * kF32Stages * 8; }
 
 // ZERO_SOFT: softening == 0.  The reference never evaluates the self pair
 // (idx:273, j starts at i+1); an all-pairs sweep does, and with eps = 0 it
 // would be 0 * inf.  Clamping r^2 (FMNMX, ALU pipe, not the FMA pipe) makes the
 // self term an exact 0 again.  Distinct coincident bodies then also give 0
 // where the reference gives NaN.
-template <int R, bool ZERO_SOFT>
-__global__ void __launch_bounds__(kThreads + 32) force_f32_kernel(const ForceParams<float> p)
+template <int R, bool ZERO_SOFT, int U = kF32Unroll>
+__global__ void __launch_bounds__(kF32Threads + 32) force_f32_kernel(const ForceParams<float> p)
 {
+    constexpr int kWarps = kF32Threads / 32;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    float4* tiles = reinterpret_cast<float4*>(smem_raw);
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + size_t(kStages) * kTileBytes);
-    uint64_t* empty = full + kStages;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + size_t(kF32Stages) * kF32TileBytes);
+    uint64_t* empty = full + kF32Stages;
     __shared__ int s_last;
 
     const int tid = threadIdx.x;
@@ -79,43 +90,40 @@ __global__ void __launch_bounds__(kThreads + 32) force_f32_kernel(const ForcePar
     const int chunk = blockIdx.x % p.j_chunks;
     const size_t tile_i = blockIdx.x / p.j_chunks;
 
+    // chunk_len and n_j are multiples of kJUnit = one tile: every tile is full
     const size_t j0 = size_t(chunk) * p.chunk_len;
-    const size_t j1 = (j0 + p.chunk_len < p.n_pad) ? j0 + p.chunk_len : p.n_pad;
-    const size_t chunk_bytes = (j1 - j0) * 16;
-    const int ntiles = static_cast<int>((chunk_bytes + kTileBytes - 1) / kTileBytes);
+    const size_t j1 = (j0 + p.chunk_len < p.n_j) ? j0 + p.chunk_len : p.n_j;
+    const int ntiles = static_cast<int>((j1 - j0) / (2 * kF32TilePairs));
     const unsigned char* src = reinterpret_cast<const unsigned char*>(p.pos_cur) + j0 * 16;
 
     if (tid == 0) {
-        for (int s = 0; s < kStages; ++s) {
+        for (int s = 0; s < kF32Stages; ++s) {
             mbar_init(&full[s], 1);
-            mbar_init(&empty[s], kThreads / 32);
+            mbar_init(&empty[s], kWarps);
         }
         fence_mbar_init();
     }
     __syncthreads();
 
-    if (warp == kThreads / 32) {  // ---- producer warp: one lane drives the TMA ring ----
+    if (warp == kWarps) {  // ---- producer warp: one lane drives the TMA ring ----
         if (lane == 0) {
             for (int t = 0; t < ntiles; ++t) {
-                const int slot = t % kStages;
-                const int k = t / kStages;
+                const int slot = t % kF32Stages;
+                const int k = t / kF32Stages;
                 if (k > 0) mbar_wait(&empty[slot], (k - 1) & 1);
-                const size_t off = size_t(t) * kTileBytes;
-                const uint32_t bytes =
-                    static_cast<uint32_t>(chunk_bytes - off < kTileBytes ? chunk_bytes - off : kTileBytes);
-                mbar_expect_tx(&full[slot], bytes);
-                bulk_g2s(smem_raw + size_t(slot) * kTileBytes, src + off, bytes, &full[slot]);
+                mbar_expect_tx(&full[slot], kF32TileBytes);
+                bulk_g2s(smem_raw + size_t(slot) * kF32TileBytes, src + size_t(t) * kF32TileBytes, kF32TileBytes, &full[slot]);
             }
         }
         return;
     }
 
     // ---- compute warps ----
-    const size_t il0 = tile_i * size_t(kThreads * R) + tid;  // local index of this thread's body r=0
+    const size_t il0 = tile_i * size_t(kF32Threads * R) + tid;  // local index of this thread's body r=0
     f32x2 nx[R], ny[R], nz[R], ax[R], ay[R], az[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-        const size_t g = p.i_begin + il0 + size_t(r) * kThreads;
+        const size_t g = p.i_begin + il0 + size_t(r) * kF32Threads;
         const float x = p.pos_cur[pm_index<float>(g, 0)];
         const float y = p.pos_cur[pm_index<float>(g, 1)];
         const float z = p.pos_cur[pm_index<float>(g, 2)];
@@ -127,20 +135,19 @@ __global__ void __launch_bounds__(kThreads + 32) force_f32_kernel(const ForcePar
     const f32x2 eps2 = pack2(p.eps2, p.eps2);
 
     for (int t = 0; t < ntiles; ++t) {
-        const int slot = t % kStages;
-        mbar_wait(&full[slot], (t / kStages) & 1);
-        const float4* tp = tiles + size_t(slot) * (kTileBytes / 16);
-        const size_t off = size_t(t) * kTileBytes;
-        const int npairs =
-            static_cast<int>((chunk_bytes - off < kTileBytes ? chunk_bytes - off : kTileBytes) / 32);
-#pragma unroll 4
-        for (int q = 0; q < npairs; ++q) {
-            const float4 A = tp[2 * q];      // x0 x1 y0 y1
-            const float4 B = tp[2 * q + 1];  // z0 z1 m0 m1
-            const f32x2 jx = pack2(A.x, A.y), jy = pack2(A.z, A.w);
-            const f32x2 jz = pack2(B.x, B.y), jm = pack2(B.z, B.w);
+        const int slot = t % kF32Stages;
+        mbar_wait(&full[slot], (t / kF32Stages) & 1);
+        const float4* tp = reinterpret_cast<const float4*>(smem_raw + size_t(slot) * kF32TileBytes);
+#pragma unroll U
+        for (int q = 0; q < kF32TilePairs; ++q) {
 #pragma unroll
             for (int r = 0; r < R; ++r) {
+                // (the loads are re-stated per i-body and merged by the compiler: this form
+                // schedules best, see force_lab)
+                const float4 A = tp[2 * q];      // x0 x1 y0 y1
+                const float4 B = tp[2 * q + 1];  // z0 z1 m0 m1
+                const f32x2 jx = pack2(A.x, A.y), jy = pack2(A.z, A.w);
+                const f32x2 jz = pack2(B.x, B.y), jm = pack2(B.z, B.w);
                 const f32x2 dx = add2(jx, nx[r]);
                 const f32x2 dy = add2(jy, ny[r]);
                 const f32x2 dz = add2(jz, nz[r]);
@@ -180,19 +187,19 @@ __global__ void __launch_bounds__(kThreads + 32) force_f32_kernel(const ForcePar
 
     if (p.j_chunks == 1) {
 #pragma unroll
-        for (int r = 0; r < R; ++r) finish_body<float>(p, il0 + size_t(r) * kThreads, sx[r], sy[r], sz[r], p.G);
+        for (int r = 0; r < R; ++r) finish_body<float>(p, il0 + size_t(r) * kF32Threads, sx[r], sy[r], sz[r], p.G);
         return;
     }
 
     float4* part = reinterpret_cast<float4*>(p.partial);
 #pragma unroll
     for (int r = 0; r < R; ++r)
-        part[size_t(chunk) * p.n_local + il0 + size_t(r) * kThreads] = make_float4(sx[r], sy[r], sz[r], 0.f);
+        part[size_t(chunk) * p.n_local + il0 + size_t(r) * kF32Threads] = make_float4(sx[r], sy[r], sz[r], 0.f);
 
-    if (!tile_arrive_last(&p.tile_counter[tile_i], p.j_chunks, &s_last)) return;
+    if (!tile_arrive_last(&p.tile_counter[tile_i], p.j_chunks, &s_last, kF32Threads)) return;
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-        const size_t il = il0 + size_t(r) * kThreads;
+        const size_t il = il0 + size_t(r) * kF32Threads;
         float tx = 0.f, ty = 0.f, tz = 0.f;
         for (int c = 0; c < p.j_chunks; ++c) {
             const float4 v = __ldcg(&part[size_t(c) * p.n_local + il]);

@@ -34,7 +34,7 @@ __global__ void __launch_bounds__(kThreads + 32) force_f64_kernel(const ForcePar
     const size_t tile_i = blockIdx.x / p.j_chunks;
 
     const size_t j0 = size_t(chunk) * p.chunk_len;
-    const size_t j1 = (j0 + p.chunk_len < p.n_pad) ? j0 + p.chunk_len : p.n_pad;
+    const size_t j1 = (j0 + p.chunk_len < p.n_j) ? j0 + p.chunk_len : p.n_j;
     const size_t chunk_bytes = (j1 - j0) * 32;
     const int ntiles = static_cast<int>((chunk_bytes + kTileBytes - 1) / kTileBytes);
     const unsigned char* src = reinterpret_cast<const unsigned char*>(p.pos_cur) + j0 * 32;
@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(kThreads + 32) force_f64_kernel(const ForcePar
     }
     double4* part = reinterpret_cast<double4*>(p.partial);
     part[size_t(chunk) * p.n_local + il] = make_double4(ax, ay, az, 0.0);
-    if (!tile_arrive_last(&p.tile_counter[tile_i], p.j_chunks, &s_last)) return;
+    if (!tile_arrive_last(&p.tile_counter[tile_i], p.j_chunks, &s_last, kThreads)) return;
     double tx = 0.0, ty = 0.0, tz = 0.0;
     for (int c = 0; c < p.j_chunks; ++c) {
         const double2* q = reinterpret_cast<const double2*>(&part[size_t(c) * p.n_local + il]);

@@ -58,7 +58,8 @@ struct nbody_ctx {
     size_t esz = 4;
     size_t capacity = 0;
     size_t cap_pad = 0;
-    size_t n = 0, n_pad = 0;
+    size_t n = 0, n_pad = 0;   // bodies uploaded; padded for even i-sharding (pads have mass 0)
+    size_t n_j = 0;            // j extent = n rounded up to kJUnit: independent of the GPU count
     int cur = 0;
     int world = 1;       // total ranks (devices across all processes)
     bool rank_mode = false;
@@ -66,7 +67,7 @@ struct nbody_ctx {
     std::vector<Shard> shards;
     bool has_temp = false;
     double heat_decay = 0.998;  // CONFIG.heatDecay, /root/reference/index.html:67
-    int R = 2;           // i-bodies per thread (fp32)
+    int R = 4;           // i-bodies per thread (fp32)
     int i_tile = 512;
     int j_chunks = 1;
     size_t chunk_len = 0;
@@ -115,28 +116,37 @@ int env_int(const char* name, int dflt)
     return (s && *s) ? atoi(s) : dflt;
 }
 
-size_t pad_unit(const nbody_ctx* c) { return size_t(c->i_tile) * size_t(c->world); }
+size_t gcd_sz(size_t a, size_t b) { return b ? gcd_sz(b, a % b) : a; }
 
-// j-range decomposition: a pure function of n_pad and the i-tile, never of the
-// number of GPUs, so partial sums are added in the same order on 1/2/4/8 GPUs.
+// n is padded to whole i-tiles per shard AND to whole j-tiles: lcm(i_tile * world, kJUnit)
+size_t pad_unit(const nbody_ctx* c)
+{
+    const size_t a = size_t(c->i_tile) * size_t(c->world);
+    return a / gcd_sz(a, size_t(kJUnit)) * size_t(kJUnit);
+}
+
+// j-range decomposition: a pure function of n (through n_j) and the i-tile, never of
+// the number of GPUs, so partial sums are added in the same order on 1/2/4/8 GPUs.
+// Enough (i-tile, j-chunk) units that the tail of the last wave is ~1% of the launch:
+// 148 SMs x 3 resident CTAs x 48.
 void choose_chunks(nbody_ctx* c)
 {
-    const size_t tiles = c->n_pad / c->i_tile;
-    const size_t min_len = size_t(env_int("NBODY_MIN_CHUNK", 1024));
-    const size_t want_units = size_t(env_int("NBODY_WANT_UNITS", 148 * 64));
+    const size_t tiles = (c->n_j + c->i_tile - 1) / c->i_tile;
+    const size_t want_units = size_t(env_int("NBODY_WANT_UNITS", 148 * 3 * 48));
+    const size_t max_chunks = c->n_j / kJUnit;
     size_t len;
     const int forced = env_int("NBODY_CHUNK_LEN", 0);
     if (forced > 0) {
-        len = round_up(size_t(forced), 64);
+        len = round_up(size_t(forced), kJUnit);
     } else {
         size_t s = (want_units + tiles - 1) / tiles;
         if (s < 1) s = 1;
-        len = round_up((c->n_pad + s - 1) / s, 64);
-        if (len < min_len) len = min_len;
+        if (s > max_chunks) s = max_chunks;
+        len = round_up((c->n_j + s - 1) / s, kJUnit);
     }
-    if (len > c->n_pad) len = c->n_pad;
+    if (len > c->n_j) len = c->n_j;
     c->chunk_len = len;
-    c->j_chunks = int((c->n_pad + len - 1) / len);
+    c->j_chunks = int((c->n_j + len - 1) / len);
 }
 
 int alloc_shard(nbody_ctx* c, Shard& s)
@@ -164,8 +174,6 @@ int set_kernel_attrs(nbody_ctx* c)
 {
     const int sm32 = int(force_f32_smem_bytes());
     const int sm64 = int(force_f64_smem_bytes());
-    CU(c, cudaFuncSetAttribute(force_f32_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
-    CU(c, cudaFuncSetAttribute(force_f32_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f32_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f32_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f32_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
@@ -186,12 +194,13 @@ int create_common(nbody_ctx** out, nbody_prec prec, int world, size_t capacity, 
     c->world = world;
     c->capacity = capacity;
     if (prec == NBODY_F32) {
-        c->R = env_int("NBODY_R", 2);
-        if (c->R != 1 && c->R != 2 && c->R != 4) c->R = 2;
+        c->R = env_int("NBODY_R", 4);
+        if (c->R != 2 && c->R != 4) c->R = 4;
+        c->i_tile = kF32Threads * c->R;
     } else {
         c->R = 1;
+        c->i_tile = kThreads;
     }
-    c->i_tile = kThreads * c->R;
     c->cap_pad = round_up(capacity, pad_unit(c));
     *made = c;
     return NBODY_OK;
@@ -469,6 +478,7 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     if (!pos_mass || !vel) return fail(c, NBODY_EINVAL, "upload: pos_mass and vel are required");
     c->n = n;
     c->n_pad = round_up(n, pad_unit(c));
+    c->n_j = round_up(n, size_t(kJUnit));
     c->cur = 0;
     c->has_temp = temp != nullptr;
     choose_chunks(c);
@@ -534,7 +544,7 @@ template <typename Real> ForceParams<Real> make_params(nbody_ctx* c, Shard& s, i
     p.partial = static_cast<Real*>(s.partial);
     p.temp = c->has_temp ? static_cast<Real*>(s.temp) : nullptr;
     p.tile_counter = s.counters;
-    p.n_pad = c->n_pad;
+    p.n_j = c->n_j;
     p.i_begin = s.i_begin;
     p.n_local = s.n_local;
     p.chunk_len = c->chunk_len;
@@ -573,11 +583,8 @@ int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
             const ForceParams<float> p = make_params<float>(c, s, mode, dt, G, eps);
             const size_t sm = force_f32_smem_bytes();
             const bool z = (eps == 0.0);
-            const dim3 blk(kThreads + 32);
-            if (c->R == 1) {
-                if (z) force_f32_kernel<1, true><<<grid, blk, sm, s.stream>>>(p);
-                else force_f32_kernel<1, false><<<grid, blk, sm, s.stream>>>(p);
-            } else if (c->R == 2) {
+            const dim3 blk(kF32Threads + 32);
+            if (c->R == 2) {
                 if (z) force_f32_kernel<2, true><<<grid, blk, sm, s.stream>>>(p);
                 else force_f32_kernel<2, false><<<grid, blk, sm, s.stream>>>(p);
             } else {

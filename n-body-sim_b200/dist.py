@@ -10,12 +10,16 @@ from __future__ import annotations
 import os
 from typing import Tuple
 
-I_TILE_F32 = 512   # kThreads * R (R = 2), csrc/common.cuh
-I_TILE_F64 = 256
+import math
+
+I_TILE_F32 = 512   # kF32Threads * R (128 x 4), csrc/common.cuh
+I_TILE_F64 = 256   # kThreads
+J_UNIT = 512       # kJUnit: one j-tile of either kernel
 
 
 def padded_n(n: int, world: int, i_tile: int) -> int:
-    unit = i_tile * world
+    """nbody_capi.cu pad_unit(): whole i-tiles per shard and whole j-tiles."""
+    unit = math.lcm(i_tile * world, J_UNIT)
     return (n + unit - 1) // unit * unit
 
 
