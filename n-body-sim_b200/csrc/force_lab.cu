@@ -413,5 +413,7 @@ int main(int argc, char** argv)
     run<4, 4, 4, 2, 256, 1, 12>(L, "<- lab best");
     run<4, 4, 4, 4, 256, 1, 12>(L);
     run<4, 4, 4, 4, 256, 3, 12>(L);
+    run<4, 2, 4, 2, 256, 1, 11>(L);
+    run<4, 4, 4, 2, 256, 1, 11>(L);
     return 0;
 }
