@@ -273,7 +273,8 @@ def main():
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": f"uniform cube N={args.n} fp32, G=1 eps=1 dt=0.01 (BASELINE configs[3]); "
                                        "one step = integrate(dt) = N^2 interactions",
-                           "n": args.n, "parallelism": f"i-range shards x{world}, NCCL all-gather of positions",
+                           "n": args.n, "parallelism": f"i-range shards x{world}, positions exchanged by " + {0: "nothing (1 GPU)", 1: "ncclAllGather",
+                                       2: "fused peer stores over NVLink + epoch barrier"}[info["exchange"]],
                            "l2": "flushed between steps (256 MiB write)", "j_chunks": info["j_chunks"], "i_tile": info["i_tile"],
                            "flop_convention": "20 flop/interaction", "tflops_20": value * 20e-3},
                 "roofline": roof, "gpu_launches": int(launches_all), "clocks": clocks}

@@ -60,7 +60,10 @@ typedef enum {
 
 /* One host process driving n_gpus devices (the N-API host is one process):
  * i-bodies are sharded evenly by contiguous range, positions are exchanged
- * every step.  device_ids may be NULL (devices 0..n_gpus-1).
+ * every step: by default the kernels that move bodies store each
+ * new position straight into every peer's buffer over NVLink (peer access / CUDA
+ * IPC) and a one-warp epoch barrier follows; NBODY_EXCHANGE=nccl in the
+ * environment, or a peer that cannot be mapped, selects ncclAllGather instead.  device_ids may be NULL (devices 0..n_gpus-1).
  * capacity = largest n that upload() will accept.  Replaces `new
  * PhysicsSystem()` (idx:233-237, 734). */
 NBODY_API int nbody_create(nbody_ctx** out, nbody_prec prec, int n_gpus, const int* device_ids,
@@ -146,6 +149,7 @@ typedef struct {
     int j_chunks;        /* j-range split of the force kernel for this n */
     int i_tile;          /* bodies per CTA */
     long long kernel_launches; /* kernels launched by this context so far */
+    int exchange;        /* position exchange: 0 none (1 GPU), 1 ncclAllGather, 2 fused peer stores over NVLink */
 } nbody_info;
 NBODY_API int nbody_get_info(nbody_ctx* ctx, nbody_info* out);
 

@@ -27,6 +27,16 @@ constexpr int kF32Stages = 4;
 // The j extent and every j-chunk are multiples of this many bodies (one ring stage of
 // either kernel), so tiles are always full.
 constexpr int kJUnit = 512;
+// Peer-store exchange (exchange.cuh): a position update is stored straight into every
+// rank's copy of the next position buffer over NVLink; at most this many ranks.
+constexpr int kMaxPeers = 8;
+
+// Destinations of one position update: the `other` position buffer of this rank and,
+// in peer-store mode, of every peer (peer-mapped or IPC-opened device pointers).
+template <typename Real> struct PosOut {
+    Real* dst[kMaxPeers];
+    int n;
+};
 
 template <typename Real> struct Vec4;
 template <> struct Vec4<float> { using type = float4; };
@@ -51,7 +61,7 @@ enum EpilogueMode : int {
 
 template <typename Real> struct ForceParams {
     const Real* pos_cur;    // full padded position array (all shards' bodies)
-    Real* pos_next;         // written in mode kForceKick2Kick1 (own range only)
+    PosOut<Real> out;       // written in mode kForceKick2Kick1 (own range, on every rank in peer-store mode)
     Real* vel;              // local
     Real* acc;              // local
     Real* partial;          // [j_chunks][n_local] Real4

@@ -22,8 +22,8 @@ template <typename Real> __device__ __forceinline__ Real thermal(Real t, Real he
 
 // Finish body `il` (local index) whose summed acceleration is (sx,sy,sz)*scale.
 // mode: see EpilogueMode.  Writes acc, vel, temp and -- in mode 2 -- the next
-// step's drifted position into pos_next (the OTHER position buffer: other CTAs
-// are still reading pos_cur).
+// step's drifted position into p.out (the OTHER position buffer of every rank:
+// other CTAs, here and on the peers, are still reading pos_cur).
 template <typename Real>
 __device__ __forceinline__ void finish_body(const ForceParams<Real>& p, size_t il, Real sx, Real sy,
                                             Real sz, Real scale)
@@ -50,9 +50,16 @@ __device__ __forceinline__ void finish_body(const ForceParams<Real>& p, size_t i
         v.z = add_rn(v.z, mul_rn(a.z, p.half_dt));
         const size_t g = p.i_begin + il;
         const size_t ix = pm_index<Real>(g, 0), iy = pm_index<Real>(g, 1), iz = pm_index<Real>(g, 2);
-        p.pos_next[ix] = add_rn(p.pos_cur[ix], mul_rn(v.x, p.dt));
-        p.pos_next[iy] = add_rn(p.pos_cur[iy], mul_rn(v.y, p.dt));
-        p.pos_next[iz] = add_rn(p.pos_cur[iz], mul_rn(v.z, p.dt));
+        const Real nx = add_rn(p.pos_cur[ix], mul_rn(v.x, p.dt));
+        const Real ny = add_rn(p.pos_cur[iy], mul_rn(v.y, p.dt));
+        const Real nz = add_rn(p.pos_cur[iz], mul_rn(v.z, p.dt));
+        // the position exchange, fused: one store per rank (own buffer first, then NVLink peers)
+        for (int k = 0; k < p.out.n; ++k) {
+            Real* o = p.out.dst[k];
+            o[ix] = nx;
+            o[iy] = ny;
+            o[iz] = nz;
+        }
     }
     reinterpret_cast<V4*>(p.vel)[il] = v;
 }

@@ -306,7 +306,7 @@ template <int R, int U> void run_product(Lab& L, int want_per_slot)
     CHECK(cudaMemset(counters, 0, sizeof(unsigned) * tiles_i));
     CHECK(cudaMalloc(&vel, size_t(L.n) * 16));
     ForceParams<float> p{};
-    p.pos_cur = L.d_j12; p.pos_next = nullptr; p.vel = vel; p.acc = reinterpret_cast<float*>(L.d_acc); p.partial = partial; p.temp = nullptr;
+    p.pos_cur = L.d_j12; p.out.n = 0; p.vel = vel; p.acc = reinterpret_cast<float*>(L.d_acc); p.partial = partial; p.temp = nullptr;
     p.tile_counter = counters; p.n_j = L.n; p.i_begin = 0; p.n_local = L.n; p.chunk_len = len; p.j_chunks = chunks; p.mode = kForceOnly;
     p.G = 1.f; p.eps2 = L.eps2; p.half_dt = 0.f; p.dt = 0.f; p.heat_decay = 0.f;
     const int grid = tiles_i * chunks;

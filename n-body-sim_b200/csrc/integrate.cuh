@@ -8,9 +8,11 @@
 
 namespace nb {
 
-// vel += acc*halfDt ; pos += vel*dt  (idx:250-253), bodies [i_begin, i_begin+n_local)
+// vel += acc*halfDt ; pos += vel*dt  (idx:250-253), bodies [i_begin, i_begin+n_local).
+// Out of place: reads pos_in, writes the updated positions to every destination in `out`
+// (this rank's other buffer and, in peer-store mode, every peer's).
 template <typename Real>
-__global__ void kick1_drift_kernel(Real* pos, Real* vel, const Real* acc, size_t i_begin,
+__global__ void kick1_drift_kernel(const Real* pos_in, PosOut<Real> out, Real* vel, const Real* acc, size_t i_begin,
                                    size_t n_local, Real half_dt, Real dt)
 {
     using V4 = typename Vec4<Real>::type;
@@ -24,9 +26,15 @@ __global__ void kick1_drift_kernel(Real* pos, Real* vel, const Real* acc, size_t
     reinterpret_cast<V4*>(vel)[il] = v;
     const size_t g = i_begin + il;
     const size_t ix = pm_index<Real>(g, 0), iy = pm_index<Real>(g, 1), iz = pm_index<Real>(g, 2);
-    pos[ix] = add_rn(pos[ix], mul_rn(v.x, dt));
-    pos[iy] = add_rn(pos[iy], mul_rn(v.y, dt));
-    pos[iz] = add_rn(pos[iz], mul_rn(v.z, dt));
+    const Real nx = add_rn(pos_in[ix], mul_rn(v.x, dt));
+    const Real ny = add_rn(pos_in[iy], mul_rn(v.y, dt));
+    const Real nz = add_rn(pos_in[iz], mul_rn(v.z, dt));
+    for (int k = 0; k < out.n; ++k) {
+        Real* o = out.dst[k];
+        o[ix] = nx;
+        o[iy] = ny;
+        o[iz] = nz;
+    }
 }
 
 // vel += acc*halfDt ; updateThermal  (idx:258-261)

@@ -18,6 +18,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "exchange.cuh"
 #include "force_f32.cuh"
 #include "force_f64.cuh"
 #include "integrate.cuh"
@@ -43,6 +44,12 @@ struct Shard {
     double* energy_out = nullptr;
     size_t energy_rows = 0;
     ncclComm_t comm = nullptr;
+    // peer-store exchange (exchange.cuh): every rank's two position buffers and flag array as mapped on this device
+    void* peer_pos[kMaxPeers][2] = {};
+    PeerFlags peer_flags = {};
+    unsigned long long* flags = nullptr; // this rank's flag array (kMaxPeers entries)
+    unsigned* xerr = nullptr;            // exchange timeout flag
+    std::vector<void*> ipc_opened;       // IPC mappings to close (rank mode)
     size_t i_begin = 0;                 // set by upload
     size_t n_local = 0;                 // padded
     size_t n_local_real = 0;            // bodies of [i_begin, i_begin+n_local) that are < n
@@ -66,6 +73,8 @@ struct nbody_ctx {
     int my_rank = 0;     // rank of shards[0] in rank mode
     std::vector<Shard> shards;
     bool has_temp = false;
+    bool p2p = false;               // peer-store exchange instead of ncclAllGather
+    unsigned long long epoch = 0;   // exchange barrier epoch (same sequence on every rank)
     double heat_decay = 0.998;  // CONFIG.heatDecay, /root/reference/index.html:67
     int R = 4;           // i-bodies per thread (fp32)
     int i_tile = 512;
@@ -80,6 +89,8 @@ struct nbody_ctx {
 };
 
 namespace {
+
+int check_exchange(nbody_ctx* c);  // defined with the exchange code below
 
 int fail(nbody_ctx* c, int code, const char* fmt, ...)
 {
@@ -165,6 +176,10 @@ int alloc_shard(nbody_ctx* c, Shard& s)
     const size_t ntiles = local_cap / c->i_tile + 1;
     CU(c, cudaMalloc(&s.counters, ntiles * sizeof(unsigned)));
     CU(c, cudaMemset(s.counters, 0, ntiles * sizeof(unsigned)));
+    CU(c, cudaMalloc(&s.flags, kMaxPeers * sizeof(unsigned long long)));
+    CU(c, cudaMemset(s.flags, 0, kMaxPeers * sizeof(unsigned long long)));
+    CU(c, cudaMalloc(&s.xerr, sizeof(unsigned)));
+    CU(c, cudaMemset(s.xerr, 0, sizeof(unsigned)));
     s.energy_rows = (local_cap + kEnergyThreads - 1) / kEnergyThreads + 1;
     CU(c, cudaMalloc(&s.energy_out, s.energy_rows * 5 * sizeof(double)));
     return NBODY_OK;
@@ -247,6 +262,9 @@ extern "C" void nbody_destroy(nbody_ctx* c)
         if (s.own_stream) cudaStreamSynchronize(s.own_stream);
         if (s.comm && nccl().ok()) nccl().CommDestroy(s.comm);
         for (cudaEvent_t e : s.ev) cudaEventDestroy(e);
+        for (void* m : s.ipc_opened) cudaIpcCloseMemHandle(m);
+        cudaFree(s.flags);
+        cudaFree(s.xerr);
         cudaFree(s.pos[0]);
         cudaFree(s.pos[1]);
         cudaFree(s.stage);
@@ -270,6 +288,95 @@ static int finish_create(nbody_ctx* c, nbody_ctx** out, int rc)
         return rc;
     }
     *out = c;
+    return NBODY_OK;
+}
+
+// Map every rank's position buffers and flag array on every device (exchange.cuh).
+// Single process: peer access between the context's devices.  Rank mode: CUDA IPC
+// handles, gathered once over the NCCL communicator that already exists.  If any rank
+// cannot map a peer, ALL ranks fall back to ncclAllGather (c->p2p stays false).
+static int setup_peer_exchange(nbody_ctx* c)
+{
+    const char* mode = getenv("NBODY_EXCHANGE");
+    if ((mode && strcmp(mode, "nccl") == 0) || c->world > kMaxPeers) return NBODY_OK;
+    if (!c->rank_mode) {
+        for (Shard& a : c->shards)
+            for (Shard& b : c->shards) {
+                if (a.device == b.device) continue;
+                int can = 0;
+                CU(c, cudaDeviceCanAccessPeer(&can, a.device, b.device));
+                if (!can) return NBODY_OK;
+            }
+        for (Shard& a : c->shards) {
+            CU(c, cudaSetDevice(a.device));
+            for (Shard& b : c->shards) {
+                if (a.device != b.device) {
+                    cudaError_t e = cudaDeviceEnablePeerAccess(b.device, 0);
+                    if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+                    else if (e != cudaSuccess) return fail(c, NBODY_ECUDA, "cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+                }
+                a.peer_pos[b.rank][0] = b.pos[0];
+                a.peer_pos[b.rank][1] = b.pos[1];
+                a.peer_flags.flags[b.rank] = b.flags;
+            }
+        }
+        c->p2p = true;
+        return NBODY_OK;
+    }
+    struct Blob {
+        cudaIpcMemHandle_t pos0, pos1, flags;
+        int ok;
+    };
+    Shard& s = c->shards[0];
+    CU(c, cudaSetDevice(s.device));
+    std::vector<Blob> all(c->world);
+    Blob mine;
+    memset(&mine, 0, sizeof mine);
+    mine.ok = cudaIpcGetMemHandle(&mine.pos0, s.pos[0]) == cudaSuccess && cudaIpcGetMemHandle(&mine.pos1, s.pos[1]) == cudaSuccess &&
+              cudaIpcGetMemHandle(&mine.flags, s.flags) == cudaSuccess;
+    cudaGetLastError();
+    Blob* dev = nullptr;
+    CU(c, cudaMalloc(&dev, sizeof(Blob) * c->world));
+    auto gather = [&](const Blob& b) -> int {
+        CU(c, cudaMemcpyAsync(dev + c->my_rank, &b, sizeof(Blob), cudaMemcpyHostToDevice, s.stream));
+        NC(c, nccl().AllGather(dev + c->my_rank, dev, sizeof(Blob), ncclUint8_, s.comm, s.stream));
+        CU(c, cudaMemcpyAsync(all.data(), dev, sizeof(Blob) * c->world, cudaMemcpyDeviceToHost, s.stream));
+        CU(c, cudaStreamSynchronize(s.stream));
+        return NBODY_OK;
+    };
+    int rc = gather(mine);
+    if (rc != NBODY_OK) return rc;
+    bool ok = true;
+    for (int r = 0; r < c->world; ++r) ok = ok && all[r].ok;
+    if (ok) {
+        for (int r = 0; r < c->world && ok; ++r) {
+            if (r == c->my_rank) {
+                s.peer_pos[r][0] = s.pos[0];
+                s.peer_pos[r][1] = s.pos[1];
+                s.peer_flags.flags[r] = s.flags;
+                continue;
+            }
+            void* ptr[3] = {nullptr, nullptr, nullptr};
+            const cudaIpcMemHandle_t* h[3] = {&all[r].pos0, &all[r].pos1, &all[r].flags};
+            for (int k = 0; k < 3 && ok; ++k) {
+                if (cudaIpcOpenMemHandle(&ptr[k], *h[k], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                    cudaGetLastError();
+                    ok = false;
+                } else {
+                    s.ipc_opened.push_back(ptr[k]);
+                }
+            }
+            s.peer_pos[r][0] = ptr[0];
+            s.peer_pos[r][1] = ptr[1];
+            s.peer_flags.flags[r] = static_cast<unsigned long long*>(ptr[2]);
+        }
+    }
+    mine.ok = ok;  // second round: did EVERY rank map every peer?
+    rc = gather(mine);
+    cudaFree(dev);
+    if (rc != NBODY_OK) return rc;
+    for (int r = 0; r < c->world; ++r) ok = ok && all[r].ok;
+    c->p2p = ok;
     return NBODY_OK;
 }
 
@@ -307,6 +414,7 @@ static int create_body(nbody_ctx* c, const int* devs, int n_local_shards, const 
             NC(c, nccl().CommInitAll(comms.data(), n_local_shards, devs));
             for (int k = 0; k < n_local_shards; ++k) c->shards[k].comm = comms[k];
         }
+        return setup_peer_exchange(c);
     }
     return NBODY_OK;
 }
@@ -370,7 +478,7 @@ extern "C" int nbody_sync(nbody_ctx* c)
         CU(c, cudaSetDevice(s.device));
         CU(c, cudaStreamSynchronize(s.stream));
     }
-    return NBODY_OK;
+    return check_exchange(c);
 }
 
 extern "C" int nbody_get_info(nbody_ctx* c, nbody_info* o)
@@ -389,6 +497,7 @@ extern "C" int nbody_get_info(nbody_ctx* c, nbody_info* o)
     o->j_chunks = c->j_chunks;
     o->i_tile = c->i_tile;
     o->kernel_launches = c->launches;
+    o->exchange = c->world == 1 ? 0 : (c->p2p ? 2 : 1);
     return NBODY_OK;
 }
 
@@ -466,7 +575,7 @@ template <typename Real> int download_t(nbody_ctx* c, Real* pm, Real* vel, Real*
         CU(c, cudaSetDevice(s.device));
         CU(c, cudaStreamSynchronize(s.stream));
     }
-    return NBODY_OK;
+    return check_exchange(c);
 }
 
 }  // namespace
@@ -518,10 +627,23 @@ int fold_timing(nbody_ctx* c, Shard& s)
     return NBODY_OK;
 }
 
-// All-gather the shards' freshly written slices of pos[which].
+// Complete the exchange of the slices just written to pos[which].
+// Peer-store mode: the update kernel already stored every slice on every rank; queue
+// the epoch barrier.  Otherwise: ncclAllGather of the own slices, in place.
 int exchange_positions(nbody_ctx* c, int which)
 {
     if (c->world == 1) return NBODY_OK;
+    if (c->p2p) {
+        c->epoch++;
+        const unsigned long long timeout_ns = (unsigned long long)env_int("NBODY_EXCHANGE_TIMEOUT_S", 60) * 1000000000ull;
+        for (Shard& s : c->shards) {
+            CU(c, cudaSetDevice(s.device));
+            exchange_barrier_kernel<<<1, 32, 0, s.stream>>>(s.peer_flags, s.rank, c->world, c->epoch, timeout_ns, s.xerr);
+            c->launches++;
+            CU(c, cudaGetLastError());
+        }
+        return NBODY_OK;
+    }
     const size_t v4 = 4 * c->esz;
     if (!c->rank_mode) NC(c, nccl().GroupStart());
     for (Shard& s : c->shards) {
@@ -534,11 +656,36 @@ int exchange_positions(nbody_ctx* c, int which)
     return NBODY_OK;
 }
 
+// Where a position update of shard s goes: its own `which` buffer, plus every peer's in peer-store mode.
+template <typename Real> PosOut<Real> make_out(nbody_ctx* c, Shard& s, int which)
+{
+    PosOut<Real> o;
+    o.n = 0;
+    o.dst[o.n++] = static_cast<Real*>(s.pos[which]);
+    if (c->p2p)
+        for (int r = 0; r < c->world; ++r)
+            if (r != s.rank) o.dst[o.n++] = static_cast<Real*>(s.peer_pos[r][which]);
+    return o;
+}
+
+// After a synchronisation: did an exchange barrier time out on a lost peer?
+int check_exchange(nbody_ctx* c)
+{
+    if (!c->p2p) return NBODY_OK;
+    for (Shard& s : c->shards) {
+        unsigned e = 0;
+        CU(c, cudaSetDevice(s.device));
+        CU(c, cudaMemcpy(&e, s.xerr, sizeof e, cudaMemcpyDeviceToHost));
+        if (e) return fail(c, NBODY_ECUDA, "position exchange timed out waiting for rank %u", e - 1);
+    }
+    return NBODY_OK;
+}
+
 template <typename Real> ForceParams<Real> make_params(nbody_ctx* c, Shard& s, int mode, double dt, double G, double eps)
 {
     ForceParams<Real> p;
     p.pos_cur = static_cast<const Real*>(s.pos[c->cur]);
-    p.pos_next = static_cast<Real*>(s.pos[c->cur ^ 1]);
+    p.out = make_out<Real>(c, s, c->cur ^ 1);
     p.vel = static_cast<Real*>(s.vel);
     p.acc = static_cast<Real*>(s.acc);
     p.partial = static_cast<Real*>(s.partial);
@@ -605,21 +752,26 @@ int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
     return NBODY_OK;
 }
 
+// idx:248-253 for every shard's own range, written to the OTHER buffer of every rank,
+// then the exchange, then the buffers swap (same flow as a fused force step).
 int launch_kick1_drift(nbody_ctx* c, double dt)
 {
+    const int nxt = c->cur ^ 1;
     for (Shard& s : c->shards) {
         CU(c, cudaSetDevice(s.device));
         const unsigned blocks = unsigned((s.n_local + 255) / 256);
         if (c->prec == NBODY_F32)
-            kick1_drift_kernel<float><<<blocks, 256, 0, s.stream>>>((float*)s.pos[c->cur], (float*)s.vel, (const float*)s.acc, s.i_begin,
-                                                                   s.n_local, 0.5f * float(dt), float(dt));
+            kick1_drift_kernel<float><<<blocks, 256, 0, s.stream>>>((const float*)s.pos[c->cur], make_out<float>(c, s, nxt), (float*)s.vel,
+                                                                   (const float*)s.acc, s.i_begin, s.n_local, 0.5f * float(dt), float(dt));
         else
-            kick1_drift_kernel<double><<<blocks, 256, 0, s.stream>>>((double*)s.pos[c->cur], (double*)s.vel, (const double*)s.acc,
-                                                                    s.i_begin, s.n_local, 0.5 * dt, dt);
+            kick1_drift_kernel<double><<<blocks, 256, 0, s.stream>>>((const double*)s.pos[c->cur], make_out<double>(c, s, nxt), (double*)s.vel,
+                                                                    (const double*)s.acc, s.i_begin, s.n_local, 0.5 * dt, dt);
         c->launches++;
         CU(c, cudaGetLastError());
     }
-    return exchange_positions(c, c->cur);
+    const int rc = exchange_positions(c, nxt);
+    if (rc == NBODY_OK) c->cur = nxt;
+    return rc;
 }
 
 int check_ready(nbody_ctx* c, const char* what)

@@ -74,21 +74,43 @@ def _multi_gpu(nb):
     return n
 
 
+@pytest.mark.parametrize("exchange", ["peer", "nccl"])
 @pytest.mark.parametrize("precision", ["f32", "f64"])
-def test_multi_gpu_bit_identical(nb, precision):
-    """i-range sharding + NCCL all-gather of positions: same bits on 1 and P GPUs
-    (SURVEY.md 8e 'Determinism')."""
+def test_multi_gpu_bit_identical(nb, precision, exchange):
+    """i-range sharding + position exchange (fused peer stores over NVLink, or
+    ncclAllGather): same bits on 1 and P GPUs (SURVEY.md 8e 'Determinism')."""
     ng = _multi_gpu(nb)
     s = nb.scenes.two_galaxies(32768)
     dt = np.float32 if precision == "f32" else np.float64
     pm, vel, t = s.astype(dt)
     outs = []
-    for g in sorted({1, 2, min(ng, 4), min(ng, 8)}):
-        with nb.Engine(s.n, precision=precision, n_gpus=g) as e:
-            e.upload(pm, vel, None, t)
-            e.step(s.dt, s.G, s.softening, 5)
-            outs.append((g, e.download(temp=True), e.energy(s.G, s.softening)))
+    os.environ["NBODY_EXCHANGE"] = exchange
+    try:
+        for g in sorted({1, 2, min(ng, 4), min(ng, 8)}):
+            with nb.Engine(s.n, precision=precision, n_gpus=g) as e:
+                e.upload(pm, vel, None, t)
+                e.step(s.dt, s.G, s.softening, 5)
+                e.step(s.dt, s.G, s.softening, 1)       # a second call: kick1_drift stores to the peers again
+                assert e.info()["exchange"] == (0 if g == 1 else (2 if exchange == "peer" else 1))
+                outs.append((g, e.download(temp=True), e.energy(s.G, s.softening)))
+    finally:
+        os.environ.pop("NBODY_EXCHANGE", None)
     for g, o, en in outs[1:]:
         for k in ("pos_mass", "vel", "acc", "temp"):
             assert np.array_equal(o[k], outs[0][1][k]), (g, k)
         assert abs(en[0] - outs[0][2][0]) < 1e-12 * abs(en[0])
+
+
+def test_multi_gpu_ragged_and_split_api(nb, oracle):
+    """Ragged N on 2 GPUs through the split entry points (kick1_drift / force / kick2)."""
+    _multi_gpu(nb)
+    s = nb.scenes.plummer(3001)
+    p, v, a, _ = oracle.integrate(s.pos_mass, s.vel, np.zeros_like(s.vel), None, s.dt, s.G, s.softening, nsteps=2)
+    with nb.Engine(s.n, precision="f64", n_gpus=2) as e:
+        e.upload(s.pos_mass, s.vel)
+        for _ in range(2):
+            e.kick1_drift(s.dt)
+            e.force(s.G, s.softening)
+            e.kick2(s.dt, 0.0)
+        o = e.download()
+    assert norm_rel_err(o["pos_mass"], p) < 1e-12 and norm_rel_err(o["vel"], v) < 1e-12 and norm_rel_err(o["acc"], a) < 1e-12
