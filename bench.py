@@ -131,7 +131,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--n", type=int, default=1048576)
+    ap.add_argument("--n", "--bodies", dest="n", type=int, default=1048576)   # --bodies: torchrun's argparse trips over --n
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--ref-sample", type=int, default=16384)
     ap.add_argument("--cpu-sample", type=int, default=16384)

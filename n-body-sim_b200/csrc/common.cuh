@@ -24,9 +24,11 @@ constexpr int kTileBytes = 16384;   // bytes per j-tile stage (512 fp64 bodies)
 constexpr int kF32Threads = 128;    // compute threads per CTA
 constexpr int kF32TilePairs = 256;  // j-PAIRS per ring stage (8 KiB, 512 bodies)
 constexpr int kF32Stages = 4;
-// The j extent and every j-chunk are multiples of this many bodies (one ring stage of
-// either kernel), so tiles are always full.
+// The j extent and every j-chunk are multiples of the kernel's j unit.  fp32: one ring
+// stage (tiles are always full).  fp64: 64 bodies -- its ring takes partial tiles, and the
+// reference's own N=151 scene then splits into several CTAs instead of one.
 constexpr int kJUnit = 512;
+constexpr int kJUnitF64 = 64;
 // Peer-store exchange (exchange.cuh): a position update is stored straight into every
 // rank's copy of the next position buffer over NVLink; at most this many ranks.
 constexpr int kMaxPeers = 8;

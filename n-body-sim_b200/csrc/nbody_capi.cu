@@ -78,6 +78,7 @@ struct nbody_ctx {
     double heat_decay = 0.998;  // CONFIG.heatDecay, /root/reference/index.html:67
     int R = 4;           // i-bodies per thread (fp32)
     int i_tile = 512;
+    int j_unit = kJUnit;  // bodies; granularity of the j extent and of the j-chunks
     int j_chunks = 1;
     size_t chunk_len = 0;
     int sm_count = 0;
@@ -129,31 +130,32 @@ int env_int(const char* name, int dflt)
 
 size_t gcd_sz(size_t a, size_t b) { return b ? gcd_sz(b, a % b) : a; }
 
-// n is padded to whole i-tiles per shard AND to whole j-tiles: lcm(i_tile * world, kJUnit)
+// n is padded to whole i-tiles per shard AND to whole j units: lcm(i_tile * world, j_unit)
 size_t pad_unit(const nbody_ctx* c)
 {
     const size_t a = size_t(c->i_tile) * size_t(c->world);
-    return a / gcd_sz(a, size_t(kJUnit)) * size_t(kJUnit);
+    return a / gcd_sz(a, size_t(c->j_unit)) * size_t(c->j_unit);
 }
 
 // j-range decomposition: a pure function of n (through n_j) and the i-tile, never of
 // the number of GPUs, so partial sums are added in the same order on 1/2/4/8 GPUs.
-// Enough (i-tile, j-chunk) units that the tail of the last wave is ~1% of the launch:
-// 148 SMs x 3 resident CTAs x 48.
+// Enough (i-tile, j-chunk) units that the tail of the last wave stays ~1-3% of the launch
+// even when 8 GPUs share the i-tiles: 148 SMs x 3 resident CTAs x 256 (measured: with x48
+// the N=1M kernel lost 4% at 8 GPUs to a 6.3-wave grid).
 void choose_chunks(nbody_ctx* c)
 {
     const size_t tiles = (c->n_j + c->i_tile - 1) / c->i_tile;
-    const size_t want_units = size_t(env_int("NBODY_WANT_UNITS", 148 * 3 * 48));
-    const size_t max_chunks = c->n_j / kJUnit;
+    const size_t want_units = size_t(env_int("NBODY_WANT_UNITS", 148 * 3 * 256));
+    const size_t max_chunks = c->n_j / c->j_unit;
     size_t len;
     const int forced = env_int("NBODY_CHUNK_LEN", 0);
     if (forced > 0) {
-        len = round_up(size_t(forced), kJUnit);
+        len = round_up(size_t(forced), size_t(c->j_unit));
     } else {
         size_t s = (want_units + tiles - 1) / tiles;
         if (s < 1) s = 1;
         if (s > max_chunks) s = max_chunks;
-        len = round_up((c->n_j + s - 1) / s, kJUnit);
+        len = round_up((c->n_j + s - 1) / s, size_t(c->j_unit));
     }
     if (len > c->n_j) len = c->n_j;
     c->chunk_len = len;
@@ -215,6 +217,7 @@ int create_common(nbody_ctx** out, nbody_prec prec, int world, size_t capacity, 
     } else {
         c->R = 1;
         c->i_tile = kThreads;
+        c->j_unit = kJUnitF64;
     }
     c->cap_pad = round_up(capacity, pad_unit(c));
     *made = c;
@@ -587,7 +590,7 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     if (!pos_mass || !vel) return fail(c, NBODY_EINVAL, "upload: pos_mass and vel are required");
     c->n = n;
     c->n_pad = round_up(n, pad_unit(c));
-    c->n_j = round_up(n, size_t(kJUnit));
+    c->n_j = round_up(n, size_t(c->j_unit));
     c->cur = 0;
     c->has_temp = temp != nullptr;
     choose_chunks(c);

@@ -14,19 +14,20 @@ import math
 
 I_TILE_F32 = 512   # kF32Threads * R (128 x 4), csrc/common.cuh
 I_TILE_F64 = 256   # kThreads
-J_UNIT = 512       # kJUnit: one j-tile of either kernel
+J_UNIT_F32 = 512   # kJUnit: one ring stage of the fp32 kernel
+J_UNIT_F64 = 64    # kJUnitF64
 
 
-def padded_n(n: int, world: int, i_tile: int) -> int:
-    """nbody_capi.cu pad_unit(): whole i-tiles per shard and whole j-tiles."""
-    unit = math.lcm(i_tile * world, J_UNIT)
+def padded_n(n: int, world: int, i_tile: int, j_unit: int = J_UNIT_F32) -> int:
+    """nbody_capi.cu pad_unit(): whole i-tiles per shard and whole j units."""
+    unit = math.lcm(i_tile * world, j_unit)
     return (n + unit - 1) // unit * unit
 
 
-def shard_range(n: int, world: int, rank: int, i_tile: int) -> Tuple[int, int]:
+def shard_range(n: int, world: int, rank: int, i_tile: int, j_unit: int = J_UNIT_F32) -> Tuple[int, int]:
     """[begin, end) of the real bodies rank `rank` owns (contiguous
     i-ranges of the padded array, pads at the tail)."""
-    n_local = padded_n(n, world, i_tile) // world
+    n_local = padded_n(n, world, i_tile, j_unit) // world
     lo = min(rank * n_local, n)
     hi = min((rank + 1) * n_local, n)
     return lo, hi
