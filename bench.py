@@ -268,7 +268,7 @@ def main():
         if clocks and clocks.get("sm_mhz"):
             pc = sms * FP32_LANES_PER_SM * clocks["sm_mhz"] * 1e6 / ISSUE_SLOTS * 1e-9
             roof["frac_at_sampled_clock"] = achieved / pc
-        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        line = {"metric": METRIC if args.n == 1048576 else METRIC.replace("N=1M", f"N={args.n}"), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": f"uniform cube N={args.n} fp32, G=1 eps=1 dt=0.01 (BASELINE configs[3]); "

@@ -3,7 +3,7 @@
 N=${1:-2}
 mkdir -p gpurun_out
 nvidia-smi -L > gpurun_out/multi_probe.log
-timeout 1500 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu_multi.log 2>&1; echo "pytest rc=$?" >> gpurun_out/multi_probe.log
+timeout 900 python -m pytest tests -m gpu -q -x ${PYTEST_K:+-k "$PYTEST_K"} > gpurun_out/pytest_gpu_multi.log 2>&1; echo "pytest rc=$?" >> gpurun_out/multi_probe.log
 for g in 1 2 4 8; do
   [ $g -le $N ] || continue
   if [ $g -eq 1 ]; then timeout 600 python bench.py --gpus 1 --steps 5 --warmup 3 > gpurun_out/scale_$g.log 2> gpurun_out/scale_$g.err
