@@ -110,6 +110,35 @@ NBODY_API int nbody_kick2(nbody_ctx* ctx, double dt, double heat_decay /* <=0: n
 
 NBODY_API int nbody_set_heat_decay(nbody_ctx* ctx, double heat_decay); /* CONFIG.heatDecay, idx:67 */
 
+/* ---- collision broad phase ------------------------------ */
+
+/* Body.radius (idx:221) of the n uploaded bodies, element type per the context
+ * precision; enables the contact stage.  Every upload() drops the radii (a new
+ * body list has new radii).  While radii are set, fp32 force sweeps also track
+ * each body's nearest neighbour (one ALU-pipe FMNMX per j-pair), so that
+ * nbody_contacts called right after nbody_force / the last step of nbody_step
+ * only scans bodies that can be touching something.  NULL switches it off.
+ * In rank mode every rank passes the same full array. */
+NBODY_API int nbody_set_radius(nbody_ctx* ctx, const void* radius);
+
+/* The O(N^2) overlap search of resolveCollisions (idx:301-313), on the device:
+ * every pair i<j with |pos_j - pos_i|^2 < (r_i + r_j + margin)^2, the deciding
+ * comparison evaluated in fp64 in the reference's association on the state as
+ * stored, written as (i,j) uint32 pairs in the order the reference visits them
+ * (ascending i, then ascending j).  margin = 0 is the reference's test; a
+ * positive margin lets a host run the order-dependent response (idx:314-389,
+ * which moves bodies, idx:351-352) on a superset.  *count = pairs found; if it
+ * exceeds cap nothing is written and NBODY_ENOMEM is returned (call again with
+ * room for *count).  Synchronous.  In rank mode each rank gets the pairs whose
+ * i lies in its own range. */
+NBODY_API int nbody_contacts(nbody_ctx* ctx, double margin, unsigned* pairs /* 2*cap */, size_t cap,
+                             size_t* count);
+
+/* What the last nbody_contacts did: out = {bodies flagged by the force sweep's
+ * nearest-neighbour tracking, bodies scanned by the pair kernel, pairs found,
+ * 1 if the flags were used (0: every body was scanned)}. */
+NBODY_API int nbody_contact_stats(nbody_ctx* ctx, long long out[4]);
+
 /* ---- diagnostics (not in the reference) -------------------- */
 
 /* E_kin = sum 1/2 m v^2, E_pot = -G sum_{i<j} m_i m_j / sqrt(r^2 + eps^2),

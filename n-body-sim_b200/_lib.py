@@ -24,6 +24,7 @@ SYMBOLS = (
     "nbody_kick2", "nbody_set_heat_decay", "nbody_energy", "nbody_sync", "nbody_last_error",
     "nbody_strerror", "nbody_version", "nbody_device_count", "nbody_set_stream",
     "nbody_enable_timing", "nbody_read_timing", "nbody_get_info",
+    "nbody_set_radius", "nbody_contacts", "nbody_contact_stats",
 )
 
 
@@ -90,6 +91,9 @@ def lib() -> ctypes.CDLL:
     L.nbody_enable_timing.argtypes = [vp, i]
     L.nbody_read_timing.argtypes = [vp, ctypes.POINTER(ctypes.c_longlong), pd]
     L.nbody_get_info.argtypes = [vp, ctypes.POINTER(Info)]
+    L.nbody_set_radius.argtypes = [vp, vp]
+    L.nbody_contacts.argtypes = [vp, d, vp, sz, ctypes.POINTER(sz)]
+    L.nbody_contact_stats.argtypes = [vp, ctypes.POINTER(ctypes.c_longlong)]
     _lib = L
     return L
 

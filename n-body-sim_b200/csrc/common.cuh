@@ -68,6 +68,7 @@ template <typename Real> struct ForceParams {
     Real* acc;              // local
     Real* partial;          // [j_chunks][n_local] Real4
     Real* temp;             // local, may be null
+    Real* near;             // local; NEAR kernels only: max_j!=i rsqrt(d^2+eps2) (contacts.cuh)
     unsigned* tile_counter; // one per local i-tile; zero between launches
     size_t n_j;             // j extent: n rounded up to kJUnit (independent of the GPU count)
     size_t i_begin;         // first global body of this shard (multiple of i-tile)

@@ -1,0 +1,109 @@
+// Broad phase of PhysicsSystem.resolveCollisions (/root/reference/index.html:301-313):
+// find every pair i<j whose spheres overlap, distSq < (r_i + r_j)^2, on the device.
+// SURVEY.md 8(f) row 1.  The order-dependent response (idx:314-389) stays on the host.
+//
+// Two stages, so that the O(N^2) overlap search costs (almost) nothing on top of the
+// force sweep that already visits every pair:
+//   1. force_f32_kernel<.., NEAR=true> keeps, per i-body, the largest 1/sqrt(d^2+eps^2)
+//      over all j != i (one FMNMX on the ALU pipe per j-pair, off the FMA pipe that
+//      bounds the kernel).  flag_near_kernel turns it into a candidate list: body i is
+//      a candidate iff its nearest neighbour could touch it even if that neighbour had
+//      the largest radius in the scene (conservative; slack covers fp32 and MUFU error).
+//   2. contact_pairs_kernel tests the candidates (or, without stage 1, every body)
+//      against all j > i.  The test that decides is evaluated in fp64 in the reference's
+//      association -- (vx*vx + vy*vy) + vz*vz < minDist*minDist -- on the state as stored,
+//      so the pair SET is exactly the reference's for those positions; in fp32 contexts
+//      an fp32 pre-test with slack keeps the fp64 work to near-contacts only.
+// Pairs are appended with an atomic counter; the host sorts them into the reference's
+// visiting order (ascending i, then ascending j).
+#pragma once
+#include "common.cuh"
+
+namespace nb {
+
+constexpr int kContactThreads = 128;
+
+// near[il]   : max over j != i of rsqrt(d^2 + eps2) from the force kernel (local index)
+// radius[g]  : Body.radius (idx:221), global index, replicated on every device
+// cand[]     : out, global indices of candidate bodies (unordered)
+__global__ void flag_near_kernel(const float* near, const float* radius, size_t i_begin, size_t n_local_real,
+                                 float reach /* r_max + margin */, float eps2, unsigned* cand, unsigned* n_cand)
+{
+    const size_t il = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (il >= n_local_real) return;
+    const float nr = near[il];
+    const float D = radius[i_begin + il] + reach;
+    // touching possible  <=>  d^2 < D^2  <=>  near^2 * (D^2 + eps2) > 1   (1e-5 slack >> fp32 + MUFU error)
+    if (nr * nr * (D * D + eps2) * 1.00001f >= 1.0f) {
+        const unsigned k = atomicAdd(n_cand, 1u);
+        cand[k] = static_cast<unsigned>(i_begin + il);
+    }
+}
+
+__device__ __forceinline__ bool overlap_exact(double xi, double yi, double zi, double ri, double xj, double yj,
+                                              double zj, double rj, double margin)
+{
+    // vec.subVectors(B.pos, A.pos); distSq = vec.lengthSq(); minDist = A.radius + B.radius   (idx:309-311)
+    const double vx = __dsub_rn(xj, xi), vy = __dsub_rn(yj, yi), vz = __dsub_rn(zj, zi);
+    const double distSq = __dadd_rn(__dadd_rn(__dmul_rn(vx, vx), __dmul_rn(vy, vy)), __dmul_rn(vz, vz));
+    const double minDist = __dadd_rn(__dadd_rn(ri, rj), margin);
+    return distSq < __dmul_rn(minDist, minDist);  // idx:313
+}
+
+// grid = (candidate blocks, j-chunks).  cand == nullptr: candidates are i_begin .. i_begin+n_cand-1.
+template <typename Real>
+__global__ void __launch_bounds__(kContactThreads)
+    contact_pairs_kernel(const Real* pos, const Real* radius, const unsigned* cand, unsigned n_cand, size_t i_begin,
+                         size_t n, size_t chunk_len, double margin, uint2* pairs, unsigned long long cap,
+                         unsigned long long* count)
+{
+    __shared__ Real sx[kContactThreads], sy[kContactThreads], sz[kContactThreads], sr[kContactThreads];
+    const int tid = threadIdx.x;
+    const unsigned k = blockIdx.x * kContactThreads + tid;
+    const bool live = k < n_cand;
+    size_t i = 0;
+    Real xi = 0, yi = 0, zi = 0, ri = 0;
+    if (live) {
+        i = cand ? size_t(cand[k]) : i_begin + k;
+        xi = pos[pm_index<Real>(i, 0)];
+        yi = pos[pm_index<Real>(i, 1)];
+        zi = pos[pm_index<Real>(i, 2)];
+        ri = radius[i];
+    }
+    const size_t j0 = size_t(blockIdx.y) * chunk_len;
+    const size_t j1 = (j0 + chunk_len < n) ? j0 + chunk_len : n;
+    const Real fmargin = Real(margin);
+    for (size_t jb = j0; jb < j1; jb += kContactThreads) {
+        const size_t j = jb + tid;
+        __syncthreads();
+        if (j < j1) {
+            sx[tid] = pos[pm_index<Real>(j, 0)];
+            sy[tid] = pos[pm_index<Real>(j, 1)];
+            sz[tid] = pos[pm_index<Real>(j, 2)];
+            sr[tid] = radius[j];
+        }
+        __syncthreads();
+        if (!live || jb + kContactThreads <= i + 1) continue;  // the tile holds no j > i
+        const int cnt = static_cast<int>(j1 - jb < size_t(kContactThreads) ? j1 - jb : size_t(kContactThreads));
+#pragma unroll 4
+        for (int q = 0; q < cnt; ++q) {
+            bool hit;
+            if (sizeof(Real) == 4) {
+                const float dx = float(sx[q]) - float(xi), dy = float(sy[q]) - float(yi), dz = float(sz[q]) - float(zi);
+                const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                const float md = float(ri) + float(sr[q]) + float(fmargin);
+                hit = d2 <= md * md * 1.00001f;
+            } else {
+                hit = true;
+            }
+            if (hit && jb + q > i &&
+                overlap_exact(double(xi), double(yi), double(zi), double(ri), double(sx[q]), double(sy[q]),
+                              double(sz[q]), double(sr[q]), margin)) {
+                const unsigned long long at = atomicAdd(count, 1ull);
+                if (at < cap) pairs[at] = make_uint2(static_cast<unsigned>(i), static_cast<unsigned>(jb + q));
+            }
+        }
+    }
+}
+
+}  // namespace nb

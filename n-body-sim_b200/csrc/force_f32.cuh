@@ -75,8 +75,62 @@ constexpr size_t force_f32_smem_bytes() { return size_t(kF32Stages) * kF32TileBy
 // would be 0 * inf.  Clamping r^2 (FMNMX, ALU pipe, not the FMA pipe) makes the
 // self term an exact 0 again.  Distinct coincident bodies then also give 0
 // where the reference gives NaN.
-template <int R, bool ZERO_SOFT, int U = kF32Unroll>
-__global__ void __launch_bounds__(kF32Threads + 32) force_f32_kernel(const ForceParams<float> p)
+//
+// NEAR: also keep, per i-body, max over j != i of 1/sqrt(d^2+eps^2) -- the nearest
+// neighbour -- for the collision broad phase (contacts.cuh; resolveCollisions'
+// overlap search, idx:301-313, rides on the sweep that already visits every pair).
+// One FMNMX per j-pair on the ALU pipe.  DIAG marks the one j-tile that contains
+// the CTA's own i-bodies, where the self pair has to be masked out of the maximum.
+template <int R, bool ZERO_SOFT, int U, bool NEAR, bool DIAG>
+__device__ __forceinline__ void consume_tile(const float4* __restrict__ tp, const f32x2 (&nx)[R], const f32x2 (&ny)[R],
+                                             const f32x2 (&nz)[R], f32x2 (&ax)[R], f32x2 (&ay)[R], f32x2 (&az)[R],
+                                             float (&nr)[R], const f32x2 eps2, const int self0)
+{
+#pragma unroll U
+    for (int q = 0; q < kF32TilePairs; ++q) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            // (the loads are re-stated per i-body and merged by the compiler: this form
+            // schedules best, see force_lab)
+            const float4 A = tp[2 * q];      // x0 x1 y0 y1
+            const float4 B = tp[2 * q + 1];  // z0 z1 m0 m1
+            const f32x2 jx = pack2(A.x, A.y), jy = pack2(A.z, A.w);
+            const f32x2 jz = pack2(B.x, B.y), jm = pack2(B.z, B.w);
+            const f32x2 dx = add2(jx, nx[r]);
+            const f32x2 dy = add2(jy, ny[r]);
+            const f32x2 dz = add2(jz, nz[r]);
+            f32x2 r2 = fma2(dx, dx, eps2);
+            r2 = fma2(dy, dy, r2);
+            r2 = fma2(dz, dz, r2);
+            float r2a, r2b;
+            unpack2(r2, r2a, r2b);
+            if (ZERO_SOFT) {
+                r2a = fmaxf(r2a, 1e-20f);
+                r2b = fmaxf(r2b, 1e-20f);
+            }
+            const float ia = rsqrt_approx(r2a), ib = rsqrt_approx(r2b);
+            if (NEAR) {
+                float ma = ia, mb = ib;
+                if (DIAG) {
+                    const int s = self0 + r * kF32Threads;  // this body's index inside the tile
+                    ma = (2 * q == s) ? 0.f : ia;
+                    mb = (2 * q + 1 == s) ? 0.f : ib;
+                }
+                nr[r] = fmaxf(nr[r], fmaxf(ma, mb));
+            }
+            const f32x2 inv = pack2(ia, ib);
+            const f32x2 inv2 = mul2(inv, inv);
+            const f32x2 mi = mul2(jm, inv);
+            const f32x2 s = mul2(mi, inv2);  // m_j / (r^2+eps^2)^1.5
+            ax[r] = fma2(s, dx, ax[r]);
+            ay[r] = fma2(s, dy, ay[r]);
+            az[r] = fma2(s, dz, az[r]);
+        }
+    }
+}
+
+template <int R, bool ZERO_SOFT, int U, bool NEAR>
+__device__ __forceinline__ void force_f32_body(const ForceParams<float>& p)
 {
     constexpr int kWarps = kF32Threads / 32;
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -134,41 +188,23 @@ __global__ void __launch_bounds__(kF32Threads + 32) force_f32_kernel(const Force
     }
     const f32x2 eps2 = pack2(p.eps2, p.eps2);
 
+    float nr[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) nr[r] = 0.f;
+    // NEAR: the j-tile (512 bodies, 512-aligned) that contains this CTA's i-bodies
+    const size_t i0 = p.i_begin + tile_i * size_t(kF32Threads * R);
+    const size_t diag_start = i0 / size_t(2 * kF32TilePairs) * size_t(2 * kF32TilePairs);
+    const int diag_t = (NEAR && diag_start >= j0 && diag_start < j1) ? int((diag_start - j0) / (2 * kF32TilePairs)) : -1;
+    const int self0 = int(i0 - diag_start) + tid;
+
     for (int t = 0; t < ntiles; ++t) {
         const int slot = t % kF32Stages;
         mbar_wait(&full[slot], (t / kF32Stages) & 1);
         const float4* tp = reinterpret_cast<const float4*>(smem_raw + size_t(slot) * kF32TileBytes);
-#pragma unroll U
-        for (int q = 0; q < kF32TilePairs; ++q) {
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                // (the loads are re-stated per i-body and merged by the compiler: this form
-                // schedules best, see force_lab)
-                const float4 A = tp[2 * q];      // x0 x1 y0 y1
-                const float4 B = tp[2 * q + 1];  // z0 z1 m0 m1
-                const f32x2 jx = pack2(A.x, A.y), jy = pack2(A.z, A.w);
-                const f32x2 jz = pack2(B.x, B.y), jm = pack2(B.z, B.w);
-                const f32x2 dx = add2(jx, nx[r]);
-                const f32x2 dy = add2(jy, ny[r]);
-                const f32x2 dz = add2(jz, nz[r]);
-                f32x2 r2 = fma2(dx, dx, eps2);
-                r2 = fma2(dy, dy, r2);
-                r2 = fma2(dz, dz, r2);
-                float r2a, r2b;
-                unpack2(r2, r2a, r2b);
-                if (ZERO_SOFT) {
-                    r2a = fmaxf(r2a, 1e-20f);
-                    r2b = fmaxf(r2b, 1e-20f);
-                }
-                const f32x2 inv = pack2(rsqrt_approx(r2a), rsqrt_approx(r2b));
-                const f32x2 inv2 = mul2(inv, inv);
-                const f32x2 mi = mul2(jm, inv);
-                const f32x2 s = mul2(mi, inv2);  // m_j / (r^2+eps^2)^1.5
-                ax[r] = fma2(s, dx, ax[r]);
-                ay[r] = fma2(s, dy, ay[r]);
-                az[r] = fma2(s, dz, az[r]);
-            }
-        }
+        if (NEAR && t == diag_t)
+            consume_tile<R, ZERO_SOFT, U, NEAR, true>(tp, nx, ny, nz, ax, ay, az, nr, eps2, self0);
+        else
+            consume_tile<R, ZERO_SOFT, U, NEAR, false>(tp, nx, ny, nz, ax, ay, az, nr, eps2, self0);
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[slot]);
     }
@@ -187,29 +223,55 @@ __global__ void __launch_bounds__(kF32Threads + 32) force_f32_kernel(const Force
 
     if (p.j_chunks == 1) {
 #pragma unroll
-        for (int r = 0; r < R; ++r) finish_body<float>(p, il0 + size_t(r) * kF32Threads, sx[r], sy[r], sz[r], p.G);
+        for (int r = 0; r < R; ++r) {
+            finish_body<float>(p, il0 + size_t(r) * kF32Threads, sx[r], sy[r], sz[r], p.G);
+            if (NEAR) p.near[il0 + size_t(r) * kF32Threads] = nr[r];
+        }
         return;
     }
 
     float4* part = reinterpret_cast<float4*>(p.partial);
 #pragma unroll
     for (int r = 0; r < R; ++r)
-        part[size_t(chunk) * p.n_local + il0 + size_t(r) * kF32Threads] = make_float4(sx[r], sy[r], sz[r], 0.f);
+        part[size_t(chunk) * p.n_local + il0 + size_t(r) * kF32Threads] = make_float4(sx[r], sy[r], sz[r], NEAR ? nr[r] : 0.f);
 
     if (!tile_arrive_last(&p.tile_counter[tile_i], p.j_chunks, &s_last, kF32Threads)) return;
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         const size_t il = il0 + size_t(r) * kF32Threads;
-        float tx = 0.f, ty = 0.f, tz = 0.f;
+        float tx = 0.f, ty = 0.f, tz = 0.f, tn = 0.f;
         for (int c = 0; c < p.j_chunks; ++c) {
             const float4 v = __ldcg(&part[size_t(c) * p.n_local + il]);
             tx += v.x;
             ty += v.y;
             tz += v.z;
+            if (NEAR) tn = fmaxf(tn, v.w);
         }
         finish_body<float>(p, il, tx, ty, tz, p.G);
+        if (NEAR) p.near[il] = tn;
     }
     if (tid == 0) p.tile_counter[tile_i] = 0;  // ready for the next launch
+}
+
+template <int R, bool ZERO_SOFT, int U = kF32Unroll>
+__global__ void __launch_bounds__(kF32Threads + 32) force_f32_kernel(const ForceParams<float> p)
+{
+    force_f32_body<R, ZERO_SOFT, U, false>(p);
+}
+
+// The NEAR variant keeps 4 more live values per thread and a second (masked) copy of the
+// inner loop; it is built for 2 CTAs per SM (the force_lab sweeps found the plateau flat
+// from 9 to 40 warps per SM).
+#ifndef NB_NEAR_MIN_CTAS
+#define NB_NEAR_MIN_CTAS 2
+#endif
+#ifndef NB_NEAR_UNROLL
+#define NB_NEAR_UNROLL 8  // 164 registers, no spills (unroll 16 spills at 168)
+#endif
+template <int R, bool ZERO_SOFT, int U = NB_NEAR_UNROLL>
+__global__ void __launch_bounds__(kF32Threads + 32, NB_NEAR_MIN_CTAS) force_f32_near_kernel(const ForceParams<float> p)
+{
+    force_f32_body<R, ZERO_SOFT, U, true>(p);
 }
 
 }  // namespace nb

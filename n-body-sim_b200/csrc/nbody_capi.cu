@@ -18,6 +18,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "contacts.cuh"
 #include "exchange.cuh"
 #include "force_f32.cuh"
 #include "force_f64.cuh"
@@ -43,6 +44,14 @@ struct Shard {
     void* stage = nullptr;              // AoS staging for upload/download (4*cap_pad elements)
     double* energy_out = nullptr;
     size_t energy_rows = 0;
+    // collision broad phase (contacts.cuh)
+    void* radius = nullptr;             // full padded array, Real, replicated like the masses
+    float* near = nullptr;              // local: nearest-neighbour rsqrt from the NEAR force kernel
+    unsigned* cand = nullptr;           // local: candidate body indices
+    unsigned* cand_count = nullptr;
+    uint2* pairs = nullptr;
+    size_t pair_cap = 0;
+    unsigned long long* pair_count = nullptr;
     ncclComm_t comm = nullptr;
     // peer-store exchange (exchange.cuh): every rank's two position buffers and flag array as mapped on this device
     void* peer_pos[kMaxPeers][2] = {};
@@ -73,6 +82,11 @@ struct nbody_ctx {
     int my_rank = 0;     // rank of shards[0] in rank mode
     std::vector<Shard> shards;
     bool has_temp = false;
+    bool has_radius = false;        // nbody_set_radius was called for the current body list
+    bool near_valid = false;        // Shard::near describes the CURRENT positions (last launch was a NEAR force pass)
+    double near_eps2 = 0.0;         // softening^2 of that pass
+    double r_max = 0.0;             // largest radius
+    long long cstat[4] = {0, 0, 0, 0};  // last nbody_contacts: flagged, scanned, pairs, used_flags
     bool p2p = false;               // peer-store exchange instead of ncclAllGather
     unsigned long long epoch = 0;   // exchange barrier epoch (same sequence on every rank)
     double heat_decay = 0.998;  // CONFIG.heatDecay, /root/reference/index.html:67
@@ -184,6 +198,11 @@ int alloc_shard(nbody_ctx* c, Shard& s)
     CU(c, cudaMemset(s.xerr, 0, sizeof(unsigned)));
     s.energy_rows = (local_cap + kEnergyThreads - 1) / kEnergyThreads + 1;
     CU(c, cudaMalloc(&s.energy_out, s.energy_rows * 5 * sizeof(double)));
+    CU(c, cudaMalloc(&s.radius, c->cap_pad * c->esz));
+    CU(c, cudaMalloc(&s.near, local_cap * sizeof(float)));
+    CU(c, cudaMalloc(&s.cand, local_cap * sizeof(unsigned)));
+    CU(c, cudaMalloc(&s.cand_count, sizeof(unsigned)));
+    CU(c, cudaMalloc(&s.pair_count, sizeof(unsigned long long)));
     return NBODY_OK;
 }
 
@@ -195,6 +214,8 @@ int set_kernel_attrs(nbody_ctx* c)
     CU(c, cudaFuncSetAttribute(force_f32_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f32_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f32_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
+    CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
+    CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
     return NBODY_OK;
 }
@@ -277,6 +298,12 @@ extern "C" void nbody_destroy(nbody_ctx* c)
         cudaFree(s.partial);
         cudaFree(s.counters);
         cudaFree(s.energy_out);
+        cudaFree(s.radius);
+        cudaFree(s.near);
+        cudaFree(s.cand);
+        cudaFree(s.cand_count);
+        cudaFree(s.pairs);
+        cudaFree(s.pair_count);
         if (s.own_stream) cudaStreamDestroy(s.own_stream);
     }
     delete c;
@@ -593,6 +620,8 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     c->n_j = round_up(n, size_t(c->j_unit));
     c->cur = 0;
     c->has_temp = temp != nullptr;
+    c->has_radius = false;  // a new body list: radii must be set again (Body.radius follows mass, idx:221)
+    c->near_valid = false;
     choose_chunks(c);
     return c->prec == NBODY_F32
                ? upload_t<float>(c, n, (const float*)pos_mass, (const float*)vel, (const float*)acc, (const float*)temp)
@@ -693,6 +722,7 @@ template <typename Real> ForceParams<Real> make_params(nbody_ctx* c, Shard& s, i
     p.acc = static_cast<Real*>(s.acc);
     p.partial = static_cast<Real*>(s.partial);
     p.temp = c->has_temp ? static_cast<Real*>(s.temp) : nullptr;
+    p.near = reinterpret_cast<Real*>(s.near);  // written by the fp32 NEAR kernels only
     p.tile_counter = s.counters;
     p.n_j = c->n_j;
     p.i_begin = s.i_begin;
@@ -710,6 +740,12 @@ template <typename Real> ForceParams<Real> make_params(nbody_ctx* c, Shard& s, i
 
 int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
 {
+    // With radii set, the fp32 sweep also tracks each body's nearest neighbour for the
+    // collision broad phase (contacts.cuh).  The result describes the positions the
+    // sweep READ, so it stays valid only when the epilogue does not drift them.
+    const bool track_near = c->has_radius && c->prec == NBODY_F32 && c->R == 4 && env_int("NBODY_NEAR", 1) != 0;
+    c->near_valid = track_near && mode != kForceKick2Kick1;
+    c->near_eps2 = double(float(eps) * float(eps));
     for (Shard& s : c->shards) {
         CU(c, cudaSetDevice(s.device));
         const unsigned grid = unsigned(s.n_local / c->i_tile) * unsigned(c->j_chunks);
@@ -734,7 +770,10 @@ int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
             const size_t sm = force_f32_smem_bytes();
             const bool z = (eps == 0.0);
             const dim3 blk(kF32Threads + 32);
-            if (c->R == 2) {
+            if (track_near) {
+                if (z) force_f32_near_kernel<4, true><<<grid, blk, sm, s.stream>>>(p);
+                else force_f32_near_kernel<4, false><<<grid, blk, sm, s.stream>>>(p);
+            } else if (c->R == 2) {
                 if (z) force_f32_kernel<2, true><<<grid, blk, sm, s.stream>>>(p);
                 else force_f32_kernel<2, false><<<grid, blk, sm, s.stream>>>(p);
             } else {
@@ -772,6 +811,7 @@ int launch_kick1_drift(nbody_ctx* c, double dt)
         c->launches++;
         CU(c, cudaGetLastError());
     }
+    c->near_valid = false;
     const int rc = exchange_positions(c, nxt);
     if (rc == NBODY_OK) c->cur = nxt;
     return rc;
@@ -911,5 +951,145 @@ extern "C" int nbody_energy(nbody_ctx* c, double G, double softening, double* ki
         momentum[1] = tot[3];
         momentum[2] = tot[4];
     }
+    return NBODY_OK;
+}
+
+// ============================================================================
+// collision broad phase (contacts.cuh)
+// ============================================================================
+
+extern "C" int nbody_set_radius(nbody_ctx* c, const void* radius)
+{
+    int rc = check_ready(c, "set_radius");
+    if (rc != NBODY_OK) return rc;
+    if (!radius) {
+        c->has_radius = false;
+        c->near_valid = false;
+        return NBODY_OK;
+    }
+    double rmax = 0.0;
+    for (size_t i = 0; i < c->n; ++i) {
+        const double r = c->prec == NBODY_F32 ? double(static_cast<const float*>(radius)[i]) : static_cast<const double*>(radius)[i];
+        if (!(r >= 0.0)) return fail(c, NBODY_EINVAL, "set_radius: radius[%zu] = %g", i, r);
+        rmax = std::max(rmax, r);
+    }
+    for (Shard& s : c->shards) {
+        CU(c, cudaSetDevice(s.device));
+        CU(c, cudaMemsetAsync(s.radius, 0, c->n_pad * c->esz, s.stream));
+        CU(c, cudaMemcpyAsync(s.radius, radius, c->n * c->esz, cudaMemcpyHostToDevice, s.stream));
+    }
+    for (Shard& s : c->shards) {
+        CU(c, cudaSetDevice(s.device));
+        CU(c, cudaStreamSynchronize(s.stream));
+    }
+    c->r_max = rmax;
+    c->has_radius = true;
+    c->near_valid = false;
+    return NBODY_OK;
+}
+
+namespace {
+
+// One shard's pairs (i in the shard's own range) appended to `keys` as (i << 32 | j).
+int shard_contacts(nbody_ctx* c, Shard& s, double margin, bool use_flags, std::vector<unsigned long long>& keys)
+{
+    CU(c, cudaSetDevice(s.device));
+    if (s.n_local_real == 0) return NBODY_OK;
+    unsigned n_cand = unsigned(s.n_local_real);
+    if (use_flags) {
+        CU(c, cudaMemsetAsync(s.cand_count, 0, sizeof(unsigned), s.stream));
+        const unsigned blocks = unsigned((s.n_local_real + 255) / 256);
+        flag_near_kernel<<<blocks, 256, 0, s.stream>>>(s.near, static_cast<const float*>(s.radius), s.i_begin, s.n_local_real,
+                                                       float(c->r_max + margin) * 1.000001f, float(c->near_eps2), s.cand, s.cand_count);
+        c->launches++;
+        CU(c, cudaGetLastError());
+        CU(c, cudaMemcpyAsync(&n_cand, s.cand_count, sizeof n_cand, cudaMemcpyDeviceToHost, s.stream));
+        CU(c, cudaStreamSynchronize(s.stream));
+        c->cstat[0] += n_cand;
+    }
+    c->cstat[1] += n_cand;
+    if (n_cand == 0) return NBODY_OK;
+    if (s.pair_cap == 0) {
+        s.pair_cap = 1 << 16;
+        CU(c, cudaMalloc(&s.pairs, s.pair_cap * sizeof(uint2)));
+    }
+    for (;;) {
+        const unsigned gx = (n_cand + kContactThreads - 1) / kContactThreads;
+        // enough CTAs to fill the chip: split the j range when there are few candidate blocks
+        size_t jch = (size_t(c->sm_count) * 8 + gx - 1) / gx;
+        const size_t max_jch = (c->n + kContactThreads - 1) / kContactThreads;
+        jch = std::max<size_t>(1, std::min(jch, std::min<size_t>(max_jch, 65535)));
+        const size_t chunk_len = round_up((c->n + jch - 1) / jch, size_t(kContactThreads));
+        jch = (c->n + chunk_len - 1) / chunk_len;
+        CU(c, cudaMemsetAsync(s.pair_count, 0, sizeof(unsigned long long), s.stream));
+        const dim3 grid(gx, unsigned(jch));
+        const unsigned* cand = use_flags ? s.cand : nullptr;
+        if (c->prec == NBODY_F32)
+            contact_pairs_kernel<float><<<grid, kContactThreads, 0, s.stream>>>((const float*)s.pos[c->cur], (const float*)s.radius, cand, n_cand,
+                                                                                 s.i_begin, c->n, chunk_len, margin, s.pairs, s.pair_cap, s.pair_count);
+        else
+            contact_pairs_kernel<double><<<grid, kContactThreads, 0, s.stream>>>((const double*)s.pos[c->cur], (const double*)s.radius, cand, n_cand,
+                                                                                  s.i_begin, c->n, chunk_len, margin, s.pairs, s.pair_cap, s.pair_count);
+        c->launches++;
+        CU(c, cudaGetLastError());
+        unsigned long long found = 0;
+        CU(c, cudaMemcpyAsync(&found, s.pair_count, sizeof found, cudaMemcpyDeviceToHost, s.stream));
+        CU(c, cudaStreamSynchronize(s.stream));
+        if (found > s.pair_cap) {  // grow and search again
+            cudaFree(s.pairs);
+            s.pairs = nullptr;
+            s.pair_cap = size_t(found + found / 4 + 1024);
+            CU(c, cudaMalloc(&s.pairs, s.pair_cap * sizeof(uint2)));
+            continue;
+        }
+        if (found) {
+            std::vector<uint2> host(found);
+            CU(c, cudaMemcpyAsync(host.data(), s.pairs, found * sizeof(uint2), cudaMemcpyDeviceToHost, s.stream));
+            CU(c, cudaStreamSynchronize(s.stream));
+            for (const uint2& q : host) keys.push_back((unsigned long long)q.x << 32 | q.y);
+        }
+        return NBODY_OK;
+    }
+}
+
+}  // namespace
+
+extern "C" int nbody_contacts(nbody_ctx* c, double margin, unsigned* pairs, size_t cap, size_t* count)
+{
+    int rc = check_ready(c, "contacts");
+    if (rc != NBODY_OK) return rc;
+    if (!count) return fail(c, NBODY_EINVAL, "contacts: count is required");
+    *count = 0;
+    if (!c->has_radius) return fail(c, NBODY_EINVAL, "contacts before set_radius");
+    if (!(margin >= 0.0)) return fail(c, NBODY_EINVAL, "contacts: margin=%g", margin);
+    if (c->n > 0xffffffffull) return fail(c, NBODY_EINVAL, "contacts: n exceeds 32-bit pair indices");
+    const bool use_flags = c->near_valid;
+    c->cstat[0] = c->cstat[1] = c->cstat[2] = 0;
+    c->cstat[3] = use_flags;
+    std::vector<unsigned long long> keys;
+    try {
+        for (Shard& s : c->shards) {
+            rc = shard_contacts(c, s, margin, use_flags, keys);
+            if (rc != NBODY_OK) return rc;
+        }
+        std::sort(keys.begin(), keys.end());  // the reference's visiting order: ascending i, then j (idx:301-305)
+    } catch (const std::bad_alloc&) {
+        return fail(c, NBODY_ENOMEM, "contacts: host allocation failed");
+    }
+    c->cstat[2] = (long long)keys.size();
+    *count = keys.size();
+    if (keys.size() > cap) return fail(c, NBODY_ENOMEM, "contacts: %zu pairs found, room for %zu", keys.size(), cap);
+    if (!pairs && !keys.empty()) return fail(c, NBODY_EINVAL, "contacts: pairs is NULL");
+    for (size_t k = 0; k < keys.size(); ++k) {
+        pairs[2 * k] = unsigned(keys[k] >> 32);
+        pairs[2 * k + 1] = unsigned(keys[k] & 0xffffffffull);
+    }
+    return NBODY_OK;
+}
+
+extern "C" int nbody_contact_stats(nbody_ctx* c, long long out[4])
+{
+    if (!c || !out) return NBODY_EINVAL;
+    for (int k = 0; k < 4; ++k) out[k] = c->cstat[k];
     return NBODY_OK;
 }

@@ -124,6 +124,34 @@ class Engine:
     def set_heat_decay(self, heat_decay: float) -> None:
         check(self._L.nbody_set_heat_decay(self._ctx, heat_decay), self._ctx)
 
+    # -- collision broad phase ------------------------------------
+    def set_radius(self, radius) -> None:
+        """Body.radius (idx:221) of the uploaded bodies; enables the contact stage."""
+        r = self._arr(radius, (self.n,), "radius")
+        check(self._L.nbody_set_radius(self._ctx, _ptr(r)), self._ctx)
+
+    def contacts(self, margin: float = 0.0) -> np.ndarray:
+        """Pairs (i, j), i < j, with |pos_j - pos_i|^2 < (r_i + r_j + margin)^2, in the
+        order resolveCollisions visits them (idx:301-313).  uint32 [k, 2]."""
+        cap = max(1024, getattr(self, "_pair_cap", 0))
+        while True:
+            out = np.empty((cap, 2), dtype=np.uint32)
+            cnt = ctypes.c_size_t()
+            st = self._L.nbody_contacts(self._ctx, float(margin), ctypes.c_void_p(out.ctypes.data), cap, ctypes.byref(cnt))
+            if st == _lib.NBODY_ENOMEM and cnt.value > cap:
+                cap = int(cnt.value * 1.25) + 16
+                continue
+            check(st, self._ctx)
+            self._pair_cap = cap
+            return out[:cnt.value].copy()
+
+    def contact_stats(self) -> dict:
+        """What the last contacts() call did: bodies flagged by the force kernel's
+        nearest-neighbour tracking, bodies scanned by the pair kernel, pairs found."""
+        st = (ctypes.c_longlong * 4)()
+        check(self._L.nbody_contact_stats(self._ctx, st), self._ctx)
+        return {"flagged": st[0], "scanned": st[1], "pairs": st[2], "used_flags": bool(st[3])}
+
     # -- diagnostics / plumbing ------------------------------------------------------
     def energy(self, G: float, softening: float):
         ke, pe = ctypes.c_double(), ctypes.c_double()

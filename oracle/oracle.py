@@ -25,8 +25,8 @@ _ip = ctypes.POINTER(ctypes.c_int64)
 
 def build(force: bool = False) -> str:
     """Compile liboracle.so with the committed Makefile (gcc only, seconds)."""
-    src = os.path.join(_HERE, "nbody_oracle.c")
-    stale = (not os.path.exists(_LIB_PATH)) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(src)
+    srcs = [os.path.join(_HERE, f) for f in os.listdir(_HERE) if f.endswith(".c") or f == "Makefile"]
+    stale = (not os.path.exists(_LIB_PATH)) or os.path.getmtime(_LIB_PATH) < max(os.path.getmtime(f) for f in srcs)
     if force or stale:
         subprocess.run(["make", "-C", _HERE, "-s"], check=True)
     return _LIB_PATH
@@ -52,6 +52,36 @@ def lib() -> ctypes.CDLL:
         for f in ("oracle_compute_gravity", "oracle_compute_gravity_mt", "oracle_kick1_drift",
                   "oracle_kick2", "oracle_integrate", "oracle_acc_subset", "oracle_energy"):
             getattr(L, f).restype = None
+        # collision stage (collide_oracle.c)
+        wp, u64 = ctypes.c_void_p, ctypes.c_uint64
+        _i32p, _u32p = ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_uint32)
+        L.oracle_world_create.argtypes = [u64, sz]
+        L.oracle_world_create.restype = wp
+        L.oracle_world_destroy.argtypes = [wp]
+        L.oracle_world_destroy.restype = None
+        L.oracle_world_seed.argtypes = [wp, u64]
+        L.oracle_world_seed.restype = None
+        L.oracle_world_config.argtypes = [wp, d, d, d, d]
+        L.oracle_world_config.restype = None
+        L.oracle_world_add.argtypes = [wp, d, _dp, _dp, i, d]
+        L.oracle_world_add.restype = None
+        L.oracle_world_clear.argtypes = [wp]
+        L.oracle_world_clear.restype = None
+        L.oracle_world_size.argtypes = [wp]
+        L.oracle_world_size.restype = sz
+        L.oracle_world_contacts.argtypes = [wp]
+        L.oracle_world_contacts.restype = sz
+        L.oracle_world_counters.argtypes = [wp, ctypes.POINTER(ctypes.c_long)]
+        L.oracle_world_counters.restype = None
+        L.oracle_world_get.argtypes = [wp, _dp, _dp, _dp, _dp, _dp, _i32p, _dp]
+        L.oracle_world_get.restype = None
+        L.oracle_world_resolve_collisions.argtypes = [wp, d]
+        L.oracle_world_resolve_collisions.restype = None
+        L.oracle_world_integrate.argtypes = [wp, d, d, d, i, i]
+        L.oracle_world_integrate.restype = None
+        for f in ("oracle_overlap_pairs", "oracle_overlap_pairs_mt"):
+            getattr(L, f).argtypes = [sz, _dp, _dp, d, _u32p, sz]
+            getattr(L, f).restype = sz
         _lib = L
     return _lib
 
@@ -122,3 +152,78 @@ def energy(pos_mass, vel, G, softening):
 
 def max_threads() -> int:
     return int(lib().oracle_max_threads())
+
+
+# ---- collision stage (collide_oracle.c) ---------------------------
+
+TYPES = ("rock", "metal", "ice")   # CONFIG.materials, idx:70-74
+
+
+def overlap_pairs(pos_mass, radius, margin=0.0, mt=True):
+    """(i,j) pairs, i<j, in the reference's visiting order, whose spheres overlap by the
+    test of idx:309-313 widened by `margin`.  uint32 [k,2]."""
+    pm, r = _f64(pos_mass), _f64(radius)
+    n = pm.shape[0]
+    fn = lib().oracle_overlap_pairs_mt if mt else lib().oracle_overlap_pairs
+    cap = 1 << 16
+    while True:
+        out = np.zeros((cap, 2), dtype=np.uint32)
+        k = fn(n, _p(pm), _p(r), float(margin), out.ctypes.data_as(ctypes.POINTER(ctypes.c_uint32)), cap)
+        if k <= cap:
+            return out[:k].copy()
+        cap = int(k)
+
+
+class World:
+    """The reference's PhysicsSystem with its COMPLETE integrate(dt) (idx:233-443):
+    gravity, collisions, merge, fracture.  Math.random is a splitmix64 stream seeded here."""
+
+    def __init__(self, seed=0x5EED0001, max_bodies=300):
+        self._L = lib()
+        self._w = ctypes.c_void_p(self._L.oracle_world_create(int(seed), int(max_bodies)))
+
+    def __del__(self):
+        if getattr(self, "_w", None):
+            self._L.oracle_world_destroy(self._w)
+            self._w = None
+
+    def seed(self, seed):
+        """Re-seed the Math.random stand-in (sequential splitmix64)."""
+        self._L.oracle_world_seed(self._w, int(seed))
+
+    def config(self, fractureThreshold=25.0, minFragmentMass=0.2, mergeTime=0.5, heatDecay=0.998):
+        self._L.oracle_world_config(self._w, fractureThreshold, minFragmentMass, mergeTime, heatDecay)
+
+    def add(self, mass, pos, vel, type="rock", temp=0.0):
+        p, v = _f64(pos, (3,)), _f64(vel, (3,))
+        self._L.oracle_world_add(self._w, float(mass), _p(p), _p(v), TYPES.index(type), float(temp))
+
+    def clear(self):
+        self._L.oracle_world_clear(self._w)
+
+    def __len__(self):
+        return int(self._L.oracle_world_size(self._w))
+
+    @property
+    def n_contacts(self):
+        return int(self._L.oracle_world_contacts(self._w))
+
+    def counters(self):
+        c = (ctypes.c_long * 5)()
+        self._L.oracle_world_counters(self._w, c)
+        return dict(zip(("merge", "fracture", "overlap", "flash", "explosion"), list(c)))
+
+    def state(self):
+        n = len(self)
+        pm, v, a = np.zeros((n, 4)), np.zeros((n, 4)), np.zeros((n, 4))
+        t, r, ident = np.zeros(n), np.zeros(n), np.zeros(n)
+        ty = np.zeros(n, dtype=np.int32)
+        self._L.oracle_world_get(self._w, _p(pm), _p(v), _p(a), _p(t), _p(r),
+                                 ty.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), _p(ident))
+        return {"pos_mass": pm, "vel": v, "acc": a, "temp": t, "radius": r, "type": ty, "id": ident}
+
+    def resolve_collisions(self, dt):
+        self._L.oracle_world_resolve_collisions(self._w, float(dt))
+
+    def integrate(self, dt, G, softening, collisions=True, nsteps=1):
+        self._L.oracle_world_integrate(self._w, float(dt), float(G), float(softening), int(bool(collisions)), int(nsteps))

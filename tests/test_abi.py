@@ -58,8 +58,12 @@ def test_no_cpu_fallback_without_gpu(nb):
     with pytest.raises(nb.NBodyError) as e:
         nb.Engine(64)
     assert e.value.status == -2  # NBODY_ECUDA
+    ps = nb.PhysicsSystem()          # the device context is created on first use ...
+    ps.addBody(nb.physics.Body(1.0, nb.physics.V3(0, 0, 0), nb.physics.V3(0, 0, 0)))
     with pytest.raises(nb.NBodyError):
-        nb.PhysicsSystem()
+        ps.integrate(0.008)          # ... and every step needs it: no host path computes gravity
+    with pytest.raises(nb.NBodyError):
+        nb.PhysicsSystem(collisions=True).engine
 
 
 def test_product_never_imports_oracle():
