@@ -129,8 +129,9 @@ NBODY_API int nbody_set_radius(nbody_ctx* ctx, const void* radius);
  * positive margin lets a host run the order-dependent response (idx:314-389,
  * which moves bodies, idx:351-352) on a superset.  *count = pairs found; if it
  * exceeds cap nothing is written and NBODY_ENOMEM is returned (call again with
- * room for *count).  Synchronous.  In rank mode each rank gets the pairs whose
- * i lies in its own range. */
+ * room for *count).  Synchronous.  In rank mode each rank gets the pairs its own
+ * bodies' scans found; the union over ranks is the complete set (a pair with a
+ * dominant body can appear on two ranks: sort and de-duplicate after merging). */
 NBODY_API int nbody_contacts(nbody_ctx* ctx, double margin, unsigned* pairs /* 2*cap */, size_t cap,
                              size_t* count);
 

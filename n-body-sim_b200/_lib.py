@@ -10,7 +10,8 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libnbody.so")
+# NBODY_LIB: load another build of the same library (kernel-variant experiments, scripts/)
+LIB_PATH = os.environ.get("NBODY_LIB") or os.path.join(_HERE, "libnbody.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 NBODY_F32, NBODY_F64 = 0, 1

@@ -26,13 +26,19 @@ constexpr int kContactThreads = 128;
 // near[il]   : max over j != i of rsqrt(d^2 + eps2) from the force kernel (local index)
 // radius[g]  : Body.radius (idx:221), global index, replicated on every device
 // cand[]     : out, global indices of candidate bodies (unordered)
+// Bodies with radius > r_split ("big": a few dominant bodies, e.g. a galaxy's central mass)
+// are left out here and out of `reach`; the host scans them against everybody instead, so
+// one huge radius does not make every body a candidate.
 __global__ void flag_near_kernel(const float* near, const float* radius, size_t i_begin, size_t n_local_real,
-                                 float reach /* r_max + margin */, float eps2, unsigned* cand, unsigned* n_cand)
+                                 float reach /* largest non-big radius + margin */, float r_split, float eps2,
+                                 unsigned* cand, unsigned* n_cand)
 {
     const size_t il = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (il >= n_local_real) return;
     const float nr = near[il];
-    const float D = radius[i_begin + il] + reach;
+    const float ri = radius[i_begin + il];
+    if (ri > r_split) return;
+    const float D = ri + reach;
     // touching possible  <=>  d^2 < D^2  <=>  near^2 * (D^2 + eps2) > 1   (1e-5 slack >> fp32 + MUFU error)
     if (nr * nr * (D * D + eps2) * 1.00001f >= 1.0f) {
         const unsigned k = atomicAdd(n_cand, 1u);
@@ -51,7 +57,9 @@ __device__ __forceinline__ bool overlap_exact(double xi, double yi, double zi, d
 }
 
 // grid = (candidate blocks, j-chunks).  cand == nullptr: candidates are i_begin .. i_begin+n_cand-1.
-template <typename Real>
+// BOTH: test every j != i and emit (min, max) -- used for the big bodies, whose partners
+// with a smaller index need not be candidates themselves (the host removes duplicates).
+template <typename Real, bool BOTH>
 __global__ void __launch_bounds__(kContactThreads)
     contact_pairs_kernel(const Real* pos, const Real* radius, const unsigned* cand, unsigned n_cand, size_t i_begin,
                          size_t n, size_t chunk_len, double margin, uint2* pairs, unsigned long long cap,
@@ -83,7 +91,7 @@ __global__ void __launch_bounds__(kContactThreads)
             sr[tid] = radius[j];
         }
         __syncthreads();
-        if (!live || jb + kContactThreads <= i + 1) continue;  // the tile holds no j > i
+        if (!live || (!BOTH && jb + kContactThreads <= i + 1)) continue;  // the tile holds no j > i
         const int cnt = static_cast<int>(j1 - jb < size_t(kContactThreads) ? j1 - jb : size_t(kContactThreads));
 #pragma unroll 4
         for (int q = 0; q < cnt; ++q) {
@@ -96,11 +104,19 @@ __global__ void __launch_bounds__(kContactThreads)
             } else {
                 hit = true;
             }
-            if (hit && jb + q > i &&
-                overlap_exact(double(xi), double(yi), double(zi), double(ri), double(sx[q]), double(sy[q]),
-                              double(sz[q]), double(sr[q]), margin)) {
+            const size_t j = jb + q;
+            if (!hit || (BOTH ? j == i : j <= i)) continue;
+            // A = the lower index, B = the higher, as the reference's i<j loop has them (idx:306-309)
+            const bool swap = BOTH && j < i;
+            const double ax = swap ? double(sx[q]) : double(xi), ay = swap ? double(sy[q]) : double(yi);
+            const double az = swap ? double(sz[q]) : double(zi), ar = swap ? double(sr[q]) : double(ri);
+            const double bx = swap ? double(xi) : double(sx[q]), by = swap ? double(yi) : double(sy[q]);
+            const double bz = swap ? double(zi) : double(sz[q]), br = swap ? double(ri) : double(sr[q]);
+            if (overlap_exact(ax, ay, az, ar, bx, by, bz, br, margin)) {
                 const unsigned long long at = atomicAdd(count, 1ull);
-                if (at < cap) pairs[at] = make_uint2(static_cast<unsigned>(i), static_cast<unsigned>(jb + q));
+                if (at < cap)
+                    pairs[at] = swap ? make_uint2(static_cast<unsigned>(j), static_cast<unsigned>(i))
+                                     : make_uint2(static_cast<unsigned>(i), static_cast<unsigned>(j));
             }
         }
     }

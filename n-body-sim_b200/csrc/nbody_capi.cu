@@ -49,6 +49,8 @@ struct Shard {
     float* near = nullptr;              // local: nearest-neighbour rsqrt from the NEAR force kernel
     unsigned* cand = nullptr;           // local: candidate body indices
     unsigned* cand_count = nullptr;
+    unsigned* big = nullptr;            // the big bodies of this shard's own range (global indices)
+    unsigned n_big = 0;
     uint2* pairs = nullptr;
     size_t pair_cap = 0;
     unsigned long long* pair_count = nullptr;
@@ -86,6 +88,8 @@ struct nbody_ctx {
     bool near_valid = false;        // Shard::near describes the CURRENT positions (last launch was a NEAR force pass)
     double near_eps2 = 0.0;         // softening^2 of that pass
     double r_max = 0.0;             // largest radius
+    double r_split = 0.0;           // bodies with a larger radius are "big": scanned against everybody (contacts.cuh)
+    double r_small_max = 0.0;       // largest radius that is not big
     long long cstat[4] = {0, 0, 0, 0};  // last nbody_contacts: flagged, scanned, pairs, used_flags
     bool p2p = false;               // peer-store exchange instead of ncclAllGather
     unsigned long long epoch = 0;   // exchange barrier epoch (same sequence on every rank)
@@ -302,6 +306,7 @@ extern "C" void nbody_destroy(nbody_ctx* c)
         cudaFree(s.near);
         cudaFree(s.cand);
         cudaFree(s.cand_count);
+        cudaFree(s.big);
         cudaFree(s.pairs);
         cudaFree(s.pair_count);
         if (s.own_stream) cudaStreamDestroy(s.own_stream);
@@ -967,16 +972,42 @@ extern "C" int nbody_set_radius(nbody_ctx* c, const void* radius)
         c->near_valid = false;
         return NBODY_OK;
     }
+    std::vector<double> r(c->n);
     double rmax = 0.0;
     for (size_t i = 0; i < c->n; ++i) {
-        const double r = c->prec == NBODY_F32 ? double(static_cast<const float*>(radius)[i]) : static_cast<const double*>(radius)[i];
-        if (!(r >= 0.0)) return fail(c, NBODY_EINVAL, "set_radius: radius[%zu] = %g", i, r);
-        rmax = std::max(rmax, r);
+        r[i] = c->prec == NBODY_F32 ? double(static_cast<const float*>(radius)[i]) : static_cast<const double*>(radius)[i];
+        if (!(r[i] >= 0.0)) return fail(c, NBODY_EINVAL, "set_radius: radius[%zu] = %g", i, r[i]);
+        rmax = std::max(rmax, r[i]);
     }
+    // A few dominant bodies (a galaxy's central mass, idx:750) would make every body a
+    // candidate of the nearest-neighbour test; split them off when they are few.
+    std::vector<double> sorted(r);
+    std::nth_element(sorted.begin(), sorted.begin() + sorted.size() / 2, sorted.end());
+    const double split = 4.0 * sorted[sorted.size() / 2];
+    size_t n_big = 0;
+    double small_max = 0.0;
+    for (double v : r) {
+        if (v > split) n_big++;
+        else small_max = std::max(small_max, v);
+    }
+    const bool use_split = n_big > 0 && n_big <= std::max<size_t>(64, c->n / 256);
+    c->r_split = use_split ? split : rmax;
+    c->r_small_max = use_split ? small_max : rmax;
     for (Shard& s : c->shards) {
         CU(c, cudaSetDevice(s.device));
         CU(c, cudaMemsetAsync(s.radius, 0, c->n_pad * c->esz, s.stream));
         CU(c, cudaMemcpyAsync(s.radius, radius, c->n * c->esz, cudaMemcpyHostToDevice, s.stream));
+        std::vector<unsigned> big;
+        if (use_split)
+            for (size_t i = s.i_begin; i < std::min(s.i_begin + s.n_local, c->n); ++i)
+                if (r[i] > split) big.push_back(unsigned(i));
+        cudaFree(s.big);
+        s.big = nullptr;
+        s.n_big = unsigned(big.size());
+        if (s.n_big) {
+            CU(c, cudaMalloc(&s.big, big.size() * sizeof(unsigned)));
+            CU(c, cudaMemcpy(s.big, big.data(), big.size() * sizeof(unsigned), cudaMemcpyHostToDevice));
+        }
     }
     for (Shard& s : c->shards) {
         CU(c, cudaSetDevice(s.device));
@@ -990,7 +1021,28 @@ extern "C" int nbody_set_radius(nbody_ctx* c, const void* radius)
 
 namespace {
 
-// One shard's pairs (i in the shard's own range) appended to `keys` as (i << 32 | j).
+template <typename Real, bool BOTH>
+int launch_pairs(nbody_ctx* c, Shard& s, const unsigned* cand, unsigned n_cand, double margin)
+{
+    if (n_cand == 0) return NBODY_OK;
+    const unsigned gx = (n_cand + kContactThreads - 1) / kContactThreads;
+    // enough CTAs to fill the chip: split the j range when there are few candidate blocks
+    size_t jch = (size_t(c->sm_count) * 8 + gx - 1) / gx;
+    const size_t max_jch = (c->n + kContactThreads - 1) / kContactThreads;
+    jch = std::max<size_t>(1, std::min(jch, std::min<size_t>(max_jch, 65535)));
+    const size_t chunk_len = round_up((c->n + jch - 1) / jch, size_t(kContactThreads));
+    jch = (c->n + chunk_len - 1) / chunk_len;
+    const dim3 grid(gx, unsigned(jch));
+    contact_pairs_kernel<Real, BOTH><<<grid, kContactThreads, 0, s.stream>>>(static_cast<const Real*>(s.pos[c->cur]), static_cast<const Real*>(s.radius),
+                                                                             cand, n_cand, s.i_begin, c->n, chunk_len, margin, s.pairs, s.pair_cap,
+                                                                             s.pair_count);
+    c->launches++;
+    CU(c, cudaGetLastError());
+    return NBODY_OK;
+}
+
+// One shard's pairs appended to `keys` as (i << 32 | j): the pairs whose lower index lies in
+// the shard's own range, plus the lower-index partners of its big bodies.
 int shard_contacts(nbody_ctx* c, Shard& s, double margin, bool use_flags, std::vector<unsigned long long>& keys)
 {
     CU(c, cudaSetDevice(s.device));
@@ -1000,38 +1052,33 @@ int shard_contacts(nbody_ctx* c, Shard& s, double margin, bool use_flags, std::v
         CU(c, cudaMemsetAsync(s.cand_count, 0, sizeof(unsigned), s.stream));
         const unsigned blocks = unsigned((s.n_local_real + 255) / 256);
         flag_near_kernel<<<blocks, 256, 0, s.stream>>>(s.near, static_cast<const float*>(s.radius), s.i_begin, s.n_local_real,
-                                                       float(c->r_max + margin) * 1.000001f, float(c->near_eps2), s.cand, s.cand_count);
+                                                       float(c->r_small_max + margin) * 1.000001f, float(c->r_split), float(c->near_eps2),
+                                                       s.cand, s.cand_count);
         c->launches++;
         CU(c, cudaGetLastError());
         CU(c, cudaMemcpyAsync(&n_cand, s.cand_count, sizeof n_cand, cudaMemcpyDeviceToHost, s.stream));
         CU(c, cudaStreamSynchronize(s.stream));
-        c->cstat[0] += n_cand;
+        c->cstat[0] += n_cand + s.n_big;
     }
-    c->cstat[1] += n_cand;
-    if (n_cand == 0) return NBODY_OK;
+    const unsigned n_big = use_flags ? s.n_big : 0;
+    c->cstat[1] += n_cand + n_big;
+    if (n_cand + n_big == 0) return NBODY_OK;
     if (s.pair_cap == 0) {
         s.pair_cap = 1 << 16;
         CU(c, cudaMalloc(&s.pairs, s.pair_cap * sizeof(uint2)));
     }
     for (;;) {
-        const unsigned gx = (n_cand + kContactThreads - 1) / kContactThreads;
-        // enough CTAs to fill the chip: split the j range when there are few candidate blocks
-        size_t jch = (size_t(c->sm_count) * 8 + gx - 1) / gx;
-        const size_t max_jch = (c->n + kContactThreads - 1) / kContactThreads;
-        jch = std::max<size_t>(1, std::min(jch, std::min<size_t>(max_jch, 65535)));
-        const size_t chunk_len = round_up((c->n + jch - 1) / jch, size_t(kContactThreads));
-        jch = (c->n + chunk_len - 1) / chunk_len;
         CU(c, cudaMemsetAsync(s.pair_count, 0, sizeof(unsigned long long), s.stream));
-        const dim3 grid(gx, unsigned(jch));
         const unsigned* cand = use_flags ? s.cand : nullptr;
-        if (c->prec == NBODY_F32)
-            contact_pairs_kernel<float><<<grid, kContactThreads, 0, s.stream>>>((const float*)s.pos[c->cur], (const float*)s.radius, cand, n_cand,
-                                                                                 s.i_begin, c->n, chunk_len, margin, s.pairs, s.pair_cap, s.pair_count);
-        else
-            contact_pairs_kernel<double><<<grid, kContactThreads, 0, s.stream>>>((const double*)s.pos[c->cur], (const double*)s.radius, cand, n_cand,
-                                                                                  s.i_begin, c->n, chunk_len, margin, s.pairs, s.pair_cap, s.pair_count);
-        c->launches++;
-        CU(c, cudaGetLastError());
+        int rc;
+        if (c->prec == NBODY_F32) {
+            rc = launch_pairs<float, false>(c, s, cand, n_cand, margin);
+            if (rc == NBODY_OK) rc = launch_pairs<float, true>(c, s, s.big, n_big, margin);
+        } else {
+            rc = launch_pairs<double, false>(c, s, cand, n_cand, margin);
+            if (rc == NBODY_OK) rc = launch_pairs<double, true>(c, s, s.big, n_big, margin);
+        }
+        if (rc != NBODY_OK) return rc;
         unsigned long long found = 0;
         CU(c, cudaMemcpyAsync(&found, s.pair_count, sizeof found, cudaMemcpyDeviceToHost, s.stream));
         CU(c, cudaStreamSynchronize(s.stream));
@@ -1073,6 +1120,7 @@ extern "C" int nbody_contacts(nbody_ctx* c, double margin, unsigned* pairs, size
             if (rc != NBODY_OK) return rc;
         }
         std::sort(keys.begin(), keys.end());  // the reference's visiting order: ascending i, then j (idx:301-305)
+        keys.erase(std::unique(keys.begin(), keys.end()), keys.end());  // a big body's scan repeats pairs its partner also found
     } catch (const std::bad_alloc&) {
         return fail(c, NBODY_ENOMEM, "contacts: host allocation failed");
     }
