@@ -51,7 +51,8 @@ typedef enum {
     NBODY_EINVAL = -1, /* bad argument or call order */
     NBODY_ECUDA = -2,  /* CUDA runtime/driver error (includes "no device") */
     NBODY_ENCCL = -3,  /* NCCL error or NCCL library not loadable */
-    NBODY_ENOMEM = -4  /* host or device allocation failed */
+    NBODY_ENOMEM = -4, /* host or device allocation failed (or an output buffer too small) */
+    NBODY_EIO = -5     /* snapshot file could not be read/written or is malformed */
 } nbody_status;
 
 #define NBODY_NCCL_ID_BYTES 128
@@ -139,6 +140,50 @@ NBODY_API int nbody_contacts(nbody_ctx* ctx, double margin, unsigned* pairs /* 2
  * nearest-neighbour tracking, bodies scanned by the pair kernel, pairs found,
  * 1 if the flags were used (0: every body was scanned)}. */
 NBODY_API int nbody_contact_stats(nbody_ctx* ctx, long long out[4]);
+
+/* ---- renderer feed: position history and ribbon trails ---- */
+
+/* Keep Body.history on the device: the last `depth` positions of every body,
+ * newest first (CONFIG.trailLength = 80, idx:58, 540, 564-565).  depth = 0 frees
+ * the ring; 2 <= depth <= 256 otherwise.  The ring is (re)filled with `depth`
+ * copies of the current position at the first push after it was enabled or after
+ * an upload that changed n, as a Body seen for the first time is (idx:540); an
+ * upload with the same n keeps it.  Kept on device 0 (every device holds all
+ * positions). */
+NBODY_API int nbody_history_enable(nbody_ctx* ctx, int depth);
+
+/* One visuals.update() worth of history: unshift the current position, drop the
+ * oldest (idx:564-565).  Asynchronous on the context's stream. */
+NBODY_API int nbody_history_push(nbody_ctx* ctx);
+
+/* out[n][depth][3] (context precision) = Body.history of every body, newest first. */
+NBODY_API int nbody_history_download(nbody_ctx* ctx, void* out);
+
+/* The ribbon loop of VisualSystem.update (idx:567-592) for every body: out is
+ * float[n][depth][6], the `positions` Float32Array of each trail mesh (idx:524,
+ * 582-588): vertex pair i = history[i] +/- perp, perp = normalize(cross(camera -
+ * history[i], dir_i)) * radius * 0.8 * max(0, 1 - i/(depth-1)).  Needs
+ * nbody_set_radius.  fp64 contexts reproduce the JS arithmetic and its float
+ * rounding exactly. */
+NBODY_API int nbody_trail_ribbons(nbody_ctx* ctx, const double camera[3], float* out);
+
+/* ---- snapshots (the reference saves nothing) ---- */
+
+/* Raw little-endian dump of the state.  64-byte header:
+ *   0  char     magic[8] = "NBODYSN1"
+ *   8  uint64   n
+ *   16 uint64   step            (caller's step counter)
+ *   24 float64  dt, 32 float64 G, 40 float64 softening
+ *   48 uint32   precision       (0 = float32, 1 = float64: element type of the arrays)
+ *   52 uint32   flags           (bit 0: temp present, bit 1: radius present)
+ *   56 uint64   reserved (0)
+ * then pos_mass[4n], vel[4n], acc[4n], [temp[n]], [radius[n]] in the host layout
+ * above.  save synchronises and downloads; load uploads (n <= capacity, same
+ * precision) and returns the header fields through the non-NULL pointers. */
+NBODY_API int nbody_snapshot_save(nbody_ctx* ctx, const char* path, unsigned long long step, double dt,
+                                  double G, double softening);
+NBODY_API int nbody_snapshot_load(nbody_ctx* ctx, const char* path, unsigned long long* step, double* dt,
+                                  double* G, double* softening);
 
 /* ---- diagnostics (not in the reference) -------------------- */
 

@@ -4,7 +4,7 @@ Arecibo130117/N-body-sim (PhysicsSystem.integrate, /root/reference/index.html:24
 The directory name carries a hyphen; import it as `nbody_b200` (the shim at the
 repo root registers this package under that name).
 """
-from . import physics, scenes  # noqa: F401
+from . import physics, scenes, snapshot  # noqa: F401
 from ._lib import NBodyError, build  # noqa: F401
 from .dist import create_rank_engine, padded_n, shard_range  # noqa: F401
 from .engine import Engine, device_count, nccl_unique_id  # noqa: F401

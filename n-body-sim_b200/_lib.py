@@ -15,7 +15,7 @@ LIB_PATH = os.environ.get("NBODY_LIB") or os.path.join(_HERE, "libnbody.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 NBODY_F32, NBODY_F64 = 0, 1
-NBODY_OK, NBODY_EINVAL, NBODY_ECUDA, NBODY_ENCCL, NBODY_ENOMEM = 0, -1, -2, -3, -4
+NBODY_OK, NBODY_EINVAL, NBODY_ECUDA, NBODY_ENCCL, NBODY_ENOMEM, NBODY_EIO = 0, -1, -2, -3, -4, -5
 NCCL_ID_BYTES = 128
 
 # every symbol include/nbody.h declares (tests check the library exports them all)
@@ -26,6 +26,8 @@ SYMBOLS = (
     "nbody_strerror", "nbody_version", "nbody_device_count", "nbody_set_stream",
     "nbody_enable_timing", "nbody_read_timing", "nbody_get_info",
     "nbody_set_radius", "nbody_contacts", "nbody_contact_stats",
+    "nbody_history_enable", "nbody_history_push", "nbody_history_download", "nbody_trail_ribbons",
+    "nbody_snapshot_save", "nbody_snapshot_load",
 )
 
 
@@ -95,6 +97,13 @@ def lib() -> ctypes.CDLL:
     L.nbody_set_radius.argtypes = [vp, vp]
     L.nbody_contacts.argtypes = [vp, d, vp, sz, ctypes.POINTER(sz)]
     L.nbody_contact_stats.argtypes = [vp, ctypes.POINTER(ctypes.c_longlong)]
+    L.nbody_history_enable.argtypes = [vp, i]
+    L.nbody_history_push.argtypes = [vp]
+    L.nbody_history_download.argtypes = [vp, vp]
+    L.nbody_trail_ribbons.argtypes = [vp, pd, vp]
+    ull = ctypes.c_ulonglong
+    L.nbody_snapshot_save.argtypes = [vp, ctypes.c_char_p, ull, d, d, d]
+    L.nbody_snapshot_load.argtypes = [vp, ctypes.c_char_p, ctypes.POINTER(ull), pd, pd, pd]
     _lib = L
     return L
 

@@ -24,6 +24,7 @@
 #include "force_f64.cuh"
 #include "integrate.cuh"
 #include "nccl_dyn.h"
+#include "trails.cuh"
 
 using namespace nb;
 
@@ -54,6 +55,10 @@ struct Shard {
     uint2* pairs = nullptr;
     size_t pair_cap = 0;
     unsigned long long* pair_count = nullptr;
+    // position history ring (trails.cuh), first shard only: every shard holds all positions
+    void* hist = nullptr;               // Real4 [depth][hist_stride]
+    float* ribbons = nullptr;           // float [n][depth][6] staging for nbody_trail_ribbons
+    size_t ribbons_bytes = 0;
     ncclComm_t comm = nullptr;
     // peer-store exchange (exchange.cuh): every rank's two position buffers and flag array as mapped on this device
     void* peer_pos[kMaxPeers][2] = {};
@@ -91,6 +96,10 @@ struct nbody_ctx {
     double r_split = 0.0;           // bodies with a larger radius are "big": scanned against everybody (contacts.cuh)
     double r_small_max = 0.0;       // largest radius that is not big
     long long cstat[4] = {0, 0, 0, 0};  // last nbody_contacts: flagged, scanned, pairs, used_flags
+    int hist_depth = 0;             // 0: no ring
+    size_t hist_stride = 0;         // bodies per slot (= cap_pad)
+    size_t hist_n = 0;              // body count the ring was filled for (0: refill on the next push)
+    int hist_head = 0;              // slot of the newest sample
     bool p2p = false;               // peer-store exchange instead of ncclAllGather
     unsigned long long epoch = 0;   // exchange barrier epoch (same sequence on every rank)
     double heat_decay = 0.998;  // CONFIG.heatDecay, /root/reference/index.html:67
@@ -276,6 +285,7 @@ extern "C" const char* nbody_strerror(int status)
     case NBODY_ECUDA: return "CUDA error";
     case NBODY_ENCCL: return "NCCL error";
     case NBODY_ENOMEM: return "out of memory";
+    case NBODY_EIO: return "file I/O error";
     default: return "unknown status";
     }
 }
@@ -309,6 +319,8 @@ extern "C" void nbody_destroy(nbody_ctx* c)
         cudaFree(s.big);
         cudaFree(s.pairs);
         cudaFree(s.pair_count);
+        cudaFree(s.hist);
+        cudaFree(s.ribbons);
         if (s.own_stream) cudaStreamDestroy(s.own_stream);
     }
     delete c;
@@ -626,6 +638,7 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     c->cur = 0;
     c->has_temp = temp != nullptr;
     c->has_radius = false;  // a new body list: radii must be set again (Body.radius follows mass, idx:221)
+    if (c->hist_n != n) c->hist_n = 0;  // history ring: refilled at the next push (trails.cuh)
     c->near_valid = false;
     choose_chunks(c);
     return c->prec == NBODY_F32
@@ -1139,5 +1152,247 @@ extern "C" int nbody_contact_stats(nbody_ctx* c, long long out[4])
 {
     if (!c || !out) return NBODY_EINVAL;
     for (int k = 0; k < 4; ++k) out[k] = c->cstat[k];
+    return NBODY_OK;
+}
+
+// ============================================================================
+// renderer feed: position history ring + ribbon trails (trails.cuh)
+// ============================================================================
+
+extern "C" int nbody_history_enable(nbody_ctx* c, int depth)
+{
+    if (!c) return NBODY_EINVAL;
+    if (depth != 0 && (depth < 2 || depth > 256)) return fail(c, NBODY_EINVAL, "history_enable: depth=%d outside 2..256", depth);
+    Shard& s = c->shards[0];
+    CU(c, cudaSetDevice(s.device));
+    CU(c, cudaStreamSynchronize(s.stream));
+    cudaFree(s.hist);
+    s.hist = nullptr;
+    c->hist_depth = 0;
+    c->hist_n = 0;
+    c->hist_head = 0;
+    if (depth == 0) return NBODY_OK;
+    c->hist_stride = c->cap_pad;
+    CU(c, cudaMalloc(&s.hist, size_t(depth) * c->hist_stride * 4 * c->esz));
+    c->hist_depth = depth;
+    const int smem = depth * kTrailBodies * int(4 * c->esz);
+    if (c->prec == NBODY_F32) CU(c, cudaFuncSetAttribute(trail_ribbons_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    else CU(c, cudaFuncSetAttribute(trail_ribbons_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    return NBODY_OK;
+}
+
+extern "C" int nbody_history_push(nbody_ctx* c)
+{
+    int rc = check_ready(c, "history_push");
+    if (rc != NBODY_OK) return rc;
+    if (c->hist_depth == 0) return fail(c, NBODY_EINVAL, "history_push before history_enable");
+    Shard& s = c->shards[0];
+    CU(c, cudaSetDevice(s.device));
+    const int fill = c->hist_n != c->n;
+    if (fill) c->hist_head = 0;
+    else c->hist_head = (c->hist_head + c->hist_depth - 1) % c->hist_depth;  // unshift: the newest sample moves one slot back
+    const unsigned blocks = unsigned((c->n + 255) / 256);
+    if (c->prec == NBODY_F32)
+        history_push_kernel<float><<<blocks, 256, 0, s.stream>>>((const float*)s.pos[c->cur], (float4*)s.hist, c->n, c->hist_stride, c->hist_head,
+                                                                 c->hist_depth, fill);
+    else
+        history_push_kernel<double><<<blocks, 256, 0, s.stream>>>((const double*)s.pos[c->cur], (double4*)s.hist, c->n, c->hist_stride, c->hist_head,
+                                                                  c->hist_depth, fill);
+    c->launches++;
+    CU(c, cudaGetLastError());
+    c->hist_n = c->n;
+    return NBODY_OK;
+}
+
+namespace {
+int history_ready(nbody_ctx* c, const char* what)
+{
+    int rc = check_ready(c, what);
+    if (rc != NBODY_OK) return rc;
+    if (c->hist_depth == 0 || c->hist_n != c->n) return fail(c, NBODY_EINVAL, "%s: no history for the current body list (enable, then push)", what);
+    return NBODY_OK;
+}
+}  // namespace
+
+extern "C" int nbody_history_download(nbody_ctx* c, void* out)
+{
+    int rc = history_ready(c, "history_download");
+    if (rc != NBODY_OK) return rc;
+    if (!out) return fail(c, NBODY_EINVAL, "history_download: out is NULL");
+    Shard& s = c->shards[0];
+    CU(c, cudaSetDevice(s.device));
+    const size_t elems = c->n * size_t(c->hist_depth) * 3;
+    const size_t bytes = elems * c->esz;
+    if (bytes > s.ribbons_bytes) {
+        CU(c, cudaStreamSynchronize(s.stream));
+        cudaFree(s.ribbons);
+        s.ribbons = nullptr;
+        s.ribbons_bytes = 0;
+        CU(c, cudaMalloc(&s.ribbons, bytes));
+        s.ribbons_bytes = bytes;
+    }
+    const unsigned blocks = unsigned((c->n * size_t(c->hist_depth) + 255) / 256);
+    if (c->prec == NBODY_F32)
+        history_gather_kernel<float><<<blocks, 256, 0, s.stream>>>((const float4*)s.hist, (float*)s.ribbons, c->n, c->hist_stride, c->hist_head, c->hist_depth);
+    else
+        history_gather_kernel<double><<<blocks, 256, 0, s.stream>>>((const double4*)s.hist, (double*)s.ribbons, c->n, c->hist_stride, c->hist_head, c->hist_depth);
+    c->launches++;
+    CU(c, cudaGetLastError());
+    CU(c, cudaMemcpyAsync(out, s.ribbons, bytes, cudaMemcpyDeviceToHost, s.stream));
+    CU(c, cudaStreamSynchronize(s.stream));
+    return NBODY_OK;
+}
+
+namespace {
+// Builds the ribbons into Shard::ribbons (device); shared by the download call and the timing hook.
+int build_ribbons(nbody_ctx* c, const double camera[3])
+{
+    Shard& s = c->shards[0];
+    CU(c, cudaSetDevice(s.device));
+    const size_t bytes = c->n * size_t(c->hist_depth) * 6 * sizeof(float);
+    if (bytes > s.ribbons_bytes) {
+        CU(c, cudaStreamSynchronize(s.stream));
+        cudaFree(s.ribbons);
+        s.ribbons = nullptr;
+        s.ribbons_bytes = 0;
+        CU(c, cudaMalloc(&s.ribbons, bytes));
+        s.ribbons_bytes = bytes;
+    }
+    const unsigned blocks = unsigned((c->n + kTrailBodies - 1) / kTrailBodies);
+    const size_t smem = size_t(c->hist_depth) * kTrailBodies * 4 * c->esz;
+    if (c->prec == NBODY_F32)
+        trail_ribbons_kernel<float><<<blocks, kTrailThreads, smem, s.stream>>>((const float4*)s.hist, (const float*)s.radius, s.ribbons, c->n, c->hist_stride,
+                                                                               c->hist_head, c->hist_depth, c->hist_depth, float(camera[0]),
+                                                                               float(camera[1]), float(camera[2]));
+    else
+        trail_ribbons_kernel<double><<<blocks, kTrailThreads, smem, s.stream>>>((const double4*)s.hist, (const double*)s.radius, s.ribbons, c->n,
+                                                                                c->hist_stride, c->hist_head, c->hist_depth, c->hist_depth, camera[0],
+                                                                                camera[1], camera[2]);
+    c->launches++;
+    CU(c, cudaGetLastError());
+    return NBODY_OK;
+}
+}  // namespace
+
+extern "C" int nbody_trail_ribbons(nbody_ctx* c, const double camera[3], float* out)
+{
+    int rc = history_ready(c, "trail_ribbons");
+    if (rc != NBODY_OK) return rc;
+    if (!camera) return fail(c, NBODY_EINVAL, "trail_ribbons: camera is NULL");
+    if (!c->has_radius) return fail(c, NBODY_EINVAL, "trail_ribbons before set_radius");
+    rc = build_ribbons(c, camera);
+    if (rc != NBODY_OK) return rc;
+    Shard& s = c->shards[0];
+    if (out) {  // out == NULL: build on the device only (timing)
+        CU(c, cudaMemcpyAsync(out, s.ribbons, c->n * size_t(c->hist_depth) * 6 * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
+        CU(c, cudaStreamSynchronize(s.stream));
+    }
+    return NBODY_OK;
+}
+
+// ============================================================================
+// snapshots
+// ============================================================================
+
+namespace {
+struct SnapHeader {
+    char magic[8];
+    unsigned long long n, step;
+    double dt, G, softening;
+    unsigned prec, flags;
+    unsigned long long reserved;
+};
+static_assert(sizeof(SnapHeader) == 64, "snapshot header is 64 bytes");
+const char kSnapMagic[8] = {'N', 'B', 'O', 'D', 'Y', 'S', 'N', '1'};
+}  // namespace
+
+extern "C" int nbody_snapshot_save(nbody_ctx* c, const char* path, unsigned long long step, double dt, double G, double softening)
+{
+    int rc = check_ready(c, "snapshot_save");
+    if (rc != NBODY_OK) return rc;
+    if (!path) return fail(c, NBODY_EINVAL, "snapshot_save: path is NULL");
+    if (c->rank_mode && c->world > 1) return fail(c, NBODY_EINVAL, "snapshot_save: a rank holds only its own vel/acc; gather on the host instead");
+    const size_t n = c->n, esz = c->esz;
+    std::vector<char> pm, vel, acc, temp, rad;
+    try {
+        pm.resize(4 * n * esz);
+        vel.resize(4 * n * esz);
+        acc.resize(4 * n * esz);
+        if (c->has_temp) temp.resize(n * esz);
+        if (c->has_radius) rad.resize(n * esz);
+    } catch (const std::bad_alloc&) {
+        return fail(c, NBODY_ENOMEM, "snapshot_save: host allocation failed");
+    }
+    rc = nbody_download(c, pm.data(), vel.data(), acc.data(), c->has_temp ? temp.data() : nullptr);
+    if (rc != NBODY_OK) return rc;
+    if (c->has_radius) {
+        Shard& s = c->shards[0];
+        CU(c, cudaSetDevice(s.device));
+        CU(c, cudaMemcpy(rad.data(), s.radius, n * esz, cudaMemcpyDeviceToHost));
+    }
+    SnapHeader h;
+    memset(&h, 0, sizeof h);
+    memcpy(h.magic, kSnapMagic, 8);
+    h.n = n;
+    h.step = step;
+    h.dt = dt;
+    h.G = G;
+    h.softening = softening;
+    h.prec = unsigned(c->prec);
+    h.flags = (c->has_temp ? 1u : 0u) | (c->has_radius ? 2u : 0u);
+    FILE* f = fopen(path, "wb");
+    if (!f) return fail(c, NBODY_EIO, "snapshot_save: cannot open %s", path);
+    bool ok = fwrite(&h, sizeof h, 1, f) == 1;
+    for (const std::vector<char>* a : {&pm, &vel, &acc, &temp, &rad})
+        if (ok && !a->empty()) ok = fwrite(a->data(), 1, a->size(), f) == a->size();
+    ok = (fclose(f) == 0) && ok;
+    return ok ? NBODY_OK : fail(c, NBODY_EIO, "snapshot_save: short write to %s", path);
+}
+
+extern "C" int nbody_snapshot_load(nbody_ctx* c, const char* path, unsigned long long* step, double* dt, double* G, double* softening)
+{
+    if (!c) return NBODY_EINVAL;
+    if (!path) return fail(c, NBODY_EINVAL, "snapshot_load: path is NULL");
+    FILE* f = fopen(path, "rb");
+    if (!f) return fail(c, NBODY_EIO, "snapshot_load: cannot open %s", path);
+    SnapHeader h;
+    if (fread(&h, sizeof h, 1, f) != 1 || memcmp(h.magic, kSnapMagic, 8) != 0) {
+        fclose(f);
+        return fail(c, NBODY_EIO, "snapshot_load: %s is not an NBODYSN1 snapshot", path);
+    }
+    if (h.prec != unsigned(c->prec) || h.n == 0 || h.n > c->capacity || (h.flags & ~3u)) {
+        fclose(f);
+        return fail(c, NBODY_EINVAL, "snapshot_load: n=%llu precision=%u flags=%u do not fit this context (capacity %zu, precision %d)", h.n, h.prec,
+                    h.flags, c->capacity, int(c->prec));
+    }
+    const size_t n = size_t(h.n), esz = c->esz;
+    std::vector<char> pm, vel, acc, temp, rad;
+    try {
+        pm.resize(4 * n * esz);
+        vel.resize(4 * n * esz);
+        acc.resize(4 * n * esz);
+        if (h.flags & 1u) temp.resize(n * esz);
+        if (h.flags & 2u) rad.resize(n * esz);
+    } catch (const std::bad_alloc&) {
+        fclose(f);
+        return fail(c, NBODY_ENOMEM, "snapshot_load: host allocation failed");
+    }
+    bool ok = true;
+    for (std::vector<char>* a : {&pm, &vel, &acc, &temp, &rad})
+        if (ok && !a->empty()) ok = fread(a->data(), 1, a->size(), f) == a->size();
+    char extra;
+    ok = ok && fread(&extra, 1, 1, f) == 0;  // nothing may follow
+    fclose(f);
+    if (!ok) return fail(c, NBODY_EIO, "snapshot_load: %s is truncated or has trailing bytes", path);
+    int rc = nbody_upload(c, n, pm.data(), vel.data(), acc.data(), (h.flags & 1u) ? temp.data() : nullptr);
+    if (rc != NBODY_OK) return rc;
+    if (h.flags & 2u) {
+        rc = nbody_set_radius(c, rad.data());
+        if (rc != NBODY_OK) return rc;
+    }
+    if (step) *step = h.step;
+    if (dt) *dt = h.dt;
+    if (G) *G = h.G;
+    if (softening) *softening = h.softening;
     return NBODY_OK;
 }

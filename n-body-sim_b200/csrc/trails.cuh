@@ -1,0 +1,128 @@
+// Device-side position history ring and ribbon-trail vertex builder: the renderer feed
+// of SURVEY.md 8(f) row 3.  In the reference every Body carries `history`, the last
+// CONFIG.trailLength = 80 positions, newest first (/root/reference/index.html:58, 540,
+// 564-565), and VisualSystem.update turns it into a camera-facing ribbon of
+// trailLength x 2 vertices per body every frame (idx:567-592).  Keeping the ring on the
+// device lets a host renderer pull trails (or finished ribbon vertices) with one copy
+// instead of re-uploading 80 positions per body per frame.
+//
+// Ring layout: hist[slot][body] as Real4 (x, y, z, unused), body-fastest, so a push is one
+// coalesced n x 16 B (fp32) store.  `head` is the slot of the newest sample; sample i
+// (0 = newest) lives in slot (head + i) % depth.  Both kernels are HBM-bound:
+//   push    : 16 B read + 16 B written per body (fp32; 32 + 32 fp64)
+//   ribbons : depth x 16 B read + depth x 24 B written per body (fp32 state; output is
+//             always float, like the reference's Float32Array, idx:524)
+#pragma once
+#include "common.cuh"
+#include "epilogue.cuh"
+
+namespace nb {
+
+// body.history.unshift(body.pos.clone()) for every body (idx:564); fill_all: a body seen
+// for the first time gets trailLength copies of its position (idx:540).
+template <typename Real>
+__global__ void history_push_kernel(const Real* pos, typename Vec4<Real>::type* hist, size_t n, size_t stride,
+                                    int slot, int depth, int fill_all)
+{
+    using V4 = typename Vec4<Real>::type;
+    const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    V4 v;
+    v.x = pos[pm_index<Real>(i, 0)];
+    v.y = pos[pm_index<Real>(i, 1)];
+    v.z = pos[pm_index<Real>(i, 2)];
+    v.w = Real(0);
+    if (fill_all) {
+        for (int s = 0; s < depth; ++s) hist[size_t(s) * stride + i] = v;
+    } else {
+        hist[size_t(slot) * stride + i] = v;
+    }
+}
+
+// out[body][i][0..2] = history[i], newest first (what Body.history holds).
+template <typename Real>
+__global__ void history_gather_kernel(const typename Vec4<Real>::type* hist, Real* out, size_t n, size_t stride,
+                                      int head, int depth)
+{
+    const size_t t = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (t >= n * size_t(depth)) return;
+    const size_t b = t / depth;
+    const int i = int(t % depth);
+    const auto v = hist[size_t((head + i) % depth) * stride + b];
+    out[3 * t + 0] = v.x;
+    out[3 * t + 1] = v.y;
+    out[3 * t + 2] = v.z;
+}
+
+__device__ __forceinline__ float sub_rn(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ double sub_rn(double a, double b) { return __dsub_rn(a, b); }
+__device__ __forceinline__ float sqrt_rn(float a) { return __fsqrt_rn(a); }
+__device__ __forceinline__ double sqrt_rn(double a) { return __dsqrt_rn(a); }
+__device__ __forceinline__ float div_rn(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ double div_rn(double a, double b) { return __ddiv_rn(a, b); }
+__device__ __forceinline__ float to_f32(float a) { return a; }
+__device__ __forceinline__ float to_f32(double a) { return __double2float_rn(a); }
+
+// The ribbon loop of VisualSystem.update (idx:567-592) for kTrailBodies bodies per CTA.
+// The CTA stages its bodies' rings in shared memory with coalesced body-fastest reads,
+// then every thread builds vertex pairs with point-fastest coalesced stores.  Arithmetic
+// is rounded operation by operation in the reference's association (no FMA), so the
+// fp64 context reproduces the JS doubles and their Float32Array rounding exactly.
+constexpr int kTrailBodies = 16;
+constexpr int kTrailThreads = 256;
+
+template <typename Real>
+__global__ void __launch_bounds__(kTrailThreads)
+    trail_ribbons_kernel(const typename Vec4<Real>::type* hist, const Real* radius, float* out, size_t n,
+                         size_t stride, int head, int depth, int trail_len, Real cx, Real cy, Real cz)
+{
+    using V4 = typename Vec4<Real>::type;
+    extern __shared__ __align__(16) unsigned char trail_smem[];
+    V4* sh = reinterpret_cast<V4*>(trail_smem);  // [depth][kTrailBodies], sample-major
+    const size_t b0 = size_t(blockIdx.x) * kTrailBodies;
+    const int nb_here = int(n - b0 < size_t(kTrailBodies) ? n - b0 : size_t(kTrailBodies));
+    for (int t = threadIdx.x; t < depth * kTrailBodies; t += kTrailThreads) {
+        const int i = t / kTrailBodies, lb = t % kTrailBodies;
+        if (lb < nb_here) sh[t] = hist[size_t((head + i) % depth) * stride + b0 + lb];
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < nb_here * depth; t += kTrailThreads) {
+        const int lb = t / depth, i = t % depth;
+        const V4 p = sh[i * kTrailBodies + lb];
+        // widthRatio = 1 - i/(trailLength-1); currentWidth = radius*0.8*max(0, widthRatio)   (idx:569-570)
+        const Real ratio = sub_rn(Real(1), div_rn(Real(i), Real(trail_len - 1)));
+        const Real width = mul_rn(mul_rn(radius[b0 + lb], Real(0.8)), ratio > Real(0) ? ratio : Real(0));
+        const Real tx = sub_rn(cx, p.x), ty = sub_rn(cy, p.y), tz = sub_rn(cz, p.z);  // vecToCam, idx:572
+        V4 a, b;                                                                      // vecDir, idx:574-578
+        if (i < depth - 1) {
+            a = p;
+            b = sh[(i + 1) * kTrailBodies + lb];
+        } else if (i > 0) {
+            a = sh[(i - 1) * kTrailBodies + lb];
+            b = p;
+        } else {
+            a = p;
+            b = p;
+        }
+        const Real dx = sub_rn(a.x, b.x), dy = sub_rn(a.y, b.y), dz = sub_rn(a.z, b.z);
+        // crossVectors(vecToCam, vecDir).normalize().multiplyScalar(currentWidth), idx:580
+        Real px = sub_rn(mul_rn(ty, dz), mul_rn(tz, dy));
+        Real py = sub_rn(mul_rn(tz, dx), mul_rn(tx, dz));
+        Real pz = sub_rn(mul_rn(tx, dy), mul_rn(ty, dx));
+        Real len = sqrt_rn(add_rn(add_rn(mul_rn(px, px), mul_rn(py, py)), mul_rn(pz, pz)));
+        if (len == Real(0)) len = Real(1);  // length() || 1
+        const Real s = div_rn(Real(1), len);
+        px = mul_rn(mul_rn(px, s), width);
+        py = mul_rn(mul_rn(py, s), width);
+        pz = mul_rn(mul_rn(pz, s), width);
+        float* o = out + (b0 * size_t(depth) + size_t(t)) * 6;  // posArr[i*6 + 0..5], idx:582-588
+        o[0] = to_f32(add_rn(p.x, px));
+        o[1] = to_f32(add_rn(p.y, py));
+        o[2] = to_f32(add_rn(p.z, pz));
+        o[3] = to_f32(sub_rn(p.x, px));
+        o[4] = to_f32(sub_rn(p.y, py));
+        o[5] = to_f32(sub_rn(p.z, pz));
+    }
+}
+
+}  // namespace nb

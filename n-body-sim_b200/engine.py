@@ -7,6 +7,7 @@ temp[n].  All compute happens in libnbody.so on the GPU.
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Optional, Sequence
 
 import numpy as np
@@ -151,6 +152,41 @@ class Engine:
         st = (ctypes.c_longlong * 4)()
         check(self._L.nbody_contact_stats(self._ctx, st), self._ctx)
         return {"flagged": st[0], "scanned": st[1], "pairs": st[2], "used_flags": bool(st[3])}
+
+    # -- renderer feed: Body.history and ribbon trails -----------------
+    def history_enable(self, depth: int = 80) -> None:
+        """Keep the last `depth` positions of every body on the device (CONFIG.trailLength, idx:58)."""
+        check(self._L.nbody_history_enable(self._ctx, int(depth)), self._ctx)
+        self._hist_depth = int(depth)
+
+    def history_push(self) -> None:
+        """body.history.unshift(pos.clone()); pop the oldest (idx:564-565), for every body."""
+        check(self._L.nbody_history_push(self._ctx), self._ctx)
+
+    def history(self) -> np.ndarray:
+        """Body.history of every body: [n, depth, 3], newest first."""
+        out = np.empty((self.n, self._hist_depth, 3), dtype=self.dtype)
+        check(self._L.nbody_history_download(self._ctx, _ptr(out)), self._ctx)
+        return out
+
+    def trail_ribbons(self, camera, download: bool = True) -> Optional[np.ndarray]:
+        """The ribbon vertex arrays VisualSystem.update builds (idx:567-592): float32
+        [n, depth, 6].  download=False builds them on the device only."""
+        cam = (ctypes.c_double * 3)(*[float(x) for x in camera])
+        out = np.empty((self.n, self._hist_depth, 6), dtype=np.float32) if download else None
+        check(self._L.nbody_trail_ribbons(self._ctx, cam, _ptr(out)), self._ctx)
+        return out
+
+    # -- snapshots ------------------------------------------------------------------------
+    def save_snapshot(self, path: str, step: int = 0, dt: float = 0.0, G: float = 0.0, softening: float = 0.0) -> None:
+        check(self._L.nbody_snapshot_save(self._ctx, os.fsencode(path), int(step), dt, G, softening), self._ctx)
+
+    def load_snapshot(self, path: str) -> dict:
+        step, dt, G, eps = ctypes.c_ulonglong(), ctypes.c_double(), ctypes.c_double(), ctypes.c_double()
+        check(self._L.nbody_snapshot_load(self._ctx, os.fsencode(path), ctypes.byref(step), ctypes.byref(dt),
+                                          ctypes.byref(G), ctypes.byref(eps)), self._ctx)
+        self.n = self.info()["n"]
+        return {"step": step.value, "dt": dt.value, "G": G.value, "softening": eps.value}
 
     # -- diagnostics / plumbing ------------------------------------------------------
     def energy(self, G: float, softening: float):

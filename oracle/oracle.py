@@ -79,6 +79,8 @@ def lib() -> ctypes.CDLL:
         L.oracle_world_resolve_collisions.restype = None
         L.oracle_world_integrate.argtypes = [wp, d, d, d, i, i]
         L.oracle_world_integrate.restype = None
+        L.oracle_trail_ribbons.argtypes = [sz, i, i, _dp, _dp, _dp, ctypes.POINTER(ctypes.c_float)]
+        L.oracle_trail_ribbons.restype = None
         for f in ("oracle_overlap_pairs", "oracle_overlap_pairs_mt"):
             getattr(L, f).argtypes = [sz, _dp, _dp, d, _u32p, sz]
             getattr(L, f).restype = sz
@@ -227,3 +229,31 @@ class World:
 
     def integrate(self, dt, G, softening, collisions=True, nsteps=1):
         self._L.oracle_world_integrate(self._w, float(dt), float(G), float(softening), int(bool(collisions)), int(nsteps))
+
+
+# ---- renderer feed (visual_oracle.c) --------------------------------
+
+def history_push(hist, pos):
+    """body.history.unshift(pos.clone()); pop (idx:564-565).  hist [n,depth,3] newest first, or
+    None for bodies seen for the first time: depth copies of pos, then the unshift (idx:540, 564)."""
+    pos = _f64(pos)[:, :3]
+    out = np.empty_like(hist)
+    out[:, 1:] = hist[:, :-1]
+    out[:, 0] = pos
+    return out
+
+
+def history_init(pos, depth=80):
+    """A body seen for the first time: trailLength copies of its position (idx:540)."""
+    return np.repeat(_f64(pos)[:, None, :3], depth, axis=1).copy()
+
+
+def trail_ribbons(hist, radius, camera, trail_length=None):
+    """float32 [n, depth, 6]: the ribbon vertex arrays of idx:567-592."""
+    h = _f64(hist)
+    n, depth, _ = h.shape
+    r, cam = _f64(radius, (n,)), _f64(camera, (3,))
+    out = np.zeros((n, depth, 6), dtype=np.float32)
+    lib().oracle_trail_ribbons(n, depth, int(trail_length or depth), _p(h), _p(r), _p(cam),
+                               out.ctypes.data_as(ctypes.POINTER(ctypes.c_float)))
+    return out

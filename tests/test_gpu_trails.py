@@ -1,0 +1,131 @@
+"""GPU tests of the renderer feed and snapshots through the C ABI:
+device-side Body.history ring, ribbon-trail vertex builder (idx:563-592) against the
+oracle, NBODYSN1 snapshot save/load against the host module."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+CAMERA = (0.0, 80.0, 150.0)   # camera.position.set(0, 80, 150), idx:705
+
+
+def _radius(s):
+    return (3 * s.pos_mass[:, 3] / (4 * np.pi)) ** (1 / 3)
+
+
+def test_history_ring_and_ribbons_f64_bit_exact(nb, oracle):
+    """Default scene, 200 frames of 2 sub-steps (animate(), idx:877-881): the device ring
+    equals history.unshift/pop on the downloaded positions, wrap-around included, and the
+    ribbon vertices equal the oracle's bit for bit (fp64 JS arithmetic, Float32Array store)."""
+    s = nb.scenes.galaxy_default()
+    rad = _radius(s)
+    with nb.Engine(s.n, precision="f64") as e:
+        e.upload(s.pos_mass, s.vel)
+        e.set_radius(rad)
+        with pytest.raises(nb.NBodyError):
+            e.history_push()                                  # not enabled yet
+        e.history_enable(80)
+        with pytest.raises(nb.NBodyError):
+            e.history()                                       # nothing pushed yet
+        hist = None
+        for frame in range(200):
+            e.step(s.dt, s.G, s.softening, 2)
+            e.history_push()
+            pos = e.download(vel=False, acc=False)["pos_mass"]
+            hist = oracle.history_push(oracle.history_init(pos, 80), pos) if hist is None else oracle.history_push(hist, pos)
+            if frame in (0, 1, 79, 80, 81, 199):
+                assert np.array_equal(e.history(), hist), frame
+                assert np.array_equal(e.trail_ribbons(CAMERA), oracle.trail_ribbons(hist, rad, CAMERA)), frame
+        # an upload with the same n keeps the ring; a different n refills it (idx:540)
+        out = e.download()
+        e.upload(out["pos_mass"], out["vel"], out["acc"])
+        e.set_radius(rad)
+        assert np.array_equal(e.history(), hist)
+        e.upload(out["pos_mass"][:100], out["vel"][:100])
+        with pytest.raises(nb.NBodyError):
+            e.history()
+        e.history_push()
+        assert np.array_equal(e.history(), oracle.history_init(out["pos_mass"][:100], 80))
+
+
+def test_ribbons_f32_close(nb, oracle):
+    s = nb.scenes.two_galaxies(4096)
+    pm, vel, _ = s.astype(np.float32)
+    rad = _radius(s).astype(np.float32) + 0.3
+    with nb.Engine(s.n, precision="f32") as e:
+        e.upload(pm, vel)
+        e.set_radius(rad)
+        e.history_enable(16)
+        for _ in range(20):
+            e.step(s.dt, s.G, s.softening, 1)
+            e.history_push()
+        hist = e.history()
+        rib = e.trail_ribbons(CAMERA)
+        assert e.trail_ribbons(CAMERA, download=False) is None
+    ref = oracle.trail_ribbons(hist.astype(np.float64), rad.astype(np.float64), CAMERA)
+    # fp32 cross products of ~200-unit vectors with ~1e-2 steps: absolute error far below a ribbon width
+    assert np.abs(rib - ref).max() < 2e-3 * float(rad.max())
+    mid = 0.5 * (rib[:, :, :3] + rib[:, :, 3:])
+    np.testing.assert_allclose(mid, hist, rtol=0, atol=1e-4)
+
+
+@pytest.mark.parametrize("precision", ["f64", "f32"])
+def test_snapshot_save_load(nb, oracle, tmp_path, precision):
+    s = nb.scenes.galaxy_default()
+    dt = np.float32 if precision == "f32" else np.float64
+    pm, vel, temp = s.astype(dt)
+    rad = _radius(s).astype(dt)
+    p1, p2 = str(tmp_path / "a.nbs"), str(tmp_path / "b.nbs")
+    with nb.Engine(s.n, precision=precision) as e:
+        e.upload(pm, vel, None, temp)
+        e.set_radius(rad)
+        e.step(s.dt, s.G, s.softening, 3)
+        want = e.download(temp=True)
+        e.save_snapshot(p1, step=3, dt=s.dt, G=s.G, softening=s.softening)
+    d = nb.snapshot.read(p1)
+    assert (d["n"], d["step"], d["dt"], d["G"], d["softening"], d["dtype"]) == (s.n, 3, s.dt, s.G, s.softening, np.dtype(dt))
+    for k in ("pos_mass", "vel", "acc", "temp"):
+        assert np.array_equal(d[k], want[k]), k
+    assert np.array_equal(d["radius"], rad)
+    # a file written by the host module loads into a fresh context and continues identically
+    nb.snapshot.write(p2, d["pos_mass"], d["vel"], d["acc"], d["temp"], d["radius"], step=3, dt=s.dt, G=s.G, softening=s.softening)
+    assert open(p1, "rb").read() == open(p2, "rb").read()
+    with nb.Engine(s.n + 9, precision=precision) as e:
+        meta = e.load_snapshot(p2)
+        assert meta == {"step": 3, "dt": s.dt, "G": s.G, "softening": s.softening} and e.n == s.n
+        e.step(meta["dt"], meta["G"], meta["softening"], 2)
+        got = e.download(temp=True)
+        e.contacts(0.0)                                       # the radii came with the file
+    with nb.Engine(s.n, precision=precision) as e:
+        e.upload(pm, vel, None, temp)
+        e.step(s.dt, s.G, s.softening, 3)
+        e.sync()
+        e.step(s.dt, s.G, s.softening, 2)
+        straight = e.download(temp=True)
+    for k in ("pos_mass", "vel", "acc", "temp"):
+        assert np.array_equal(got[k], straight[k]), k        # checkpoint/resume is exact
+
+
+def test_snapshot_errors(nb, tmp_path):
+    from nbody_b200 import _lib
+    s = nb.scenes.galaxy_default()
+    p = str(tmp_path / "a.nbs")
+    nb.snapshot.write(p, s.pos_mass, s.vel)
+    with nb.Engine(s.n, precision="f32") as e:
+        with pytest.raises(nb.NBodyError) as ei:
+            e.load_snapshot(p)                                # float64 file, float32 context
+        assert ei.value.status == _lib.NBODY_EINVAL
+    with nb.Engine(s.n - 1, precision="f64") as e:
+        with pytest.raises(nb.NBodyError):
+            e.load_snapshot(p)                                # n > capacity
+    with nb.Engine(s.n, precision="f64") as e:
+        with pytest.raises(nb.NBodyError) as ei:
+            e.load_snapshot(str(tmp_path / "missing.nbs"))
+        assert ei.value.status == _lib.NBODY_EIO
+        raw = open(p, "rb").read()
+        open(p, "wb").write(raw[:-16])
+        with pytest.raises(nb.NBodyError) as ei:
+            e.load_snapshot(p)
+        assert ei.value.status == _lib.NBODY_EIO
+        with pytest.raises(nb.NBodyError):
+            e.save_snapshot(p)                                # nothing uploaded
