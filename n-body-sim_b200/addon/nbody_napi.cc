@@ -15,6 +15,12 @@
 //   energy(ctx, G, softening) -> {kinetic, potential, momentum: [px,py,pz]}
 //   sync(ctx); info(ctx) -> {n, nPadded, nGpus, jChunks, iTile, kernelLaunches}
 //   version() -> string; deviceCount() -> int
+//   setRadius(ctx, radius|null)                            Body.radius, idx:221; enables contacts
+//   contacts(ctx, margin, pairs: Uint32Array) -> count     overlap search of resolveCollisions, idx:301-313;
+//                                                          count > pairs.length/2: nothing written, call again
+//   historyEnable(ctx, depth) / historyPush(ctx) / historyDownload(ctx, out)      Body.history, idx:540, 564-565
+//   trailRibbons(ctx, camX, camY, camZ, out: Float32Array)  ribbon vertices, idx:567-592
+//   snapshotSave(ctx, path, step, dt, G, softening) / snapshotLoad(ctx, path) -> {step, dt, G, softening}
 #include "napi_min.h"
 
 #include <cstdio>
@@ -323,6 +329,148 @@ napi_value DeviceCount(napi_env env, napi_callback_info)
     return v;
 }
 
+// ---- collision broad phase, renderer feed, snapshots --------
+
+bool get_typed(napi_env env, napi_value v, napi_typedarray_type want, void** data, size_t* len)
+{
+    bool is_ta = false;
+    napi_typedarray_type ty = napi_int8_array;
+    return napi_is_typedarray(env, v, &is_ta) == napi_ok && is_ta &&
+           napi_get_typedarray_info(env, v, &ty, len, data, nullptr, nullptr) == napi_ok && ty == want;
+}
+
+napi_value number(napi_env env, double x)
+{
+    napi_value v = nullptr;
+    napi_create_double(env, x, &v);
+    return v;
+}
+
+napi_value SetRadius(napi_env env, napi_callback_info info)  // Body.radius, idx:221
+{
+    Args a;
+    if (!get_args(env, info, a, 2, "setRadius")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "setRadius");
+    if (!h) return undefined(env);
+    void* p = nullptr;
+    size_t len = 0;
+    if (!get_array(env, a.v[1], h->prec, &p, &len, "setRadius")) return undefined(env);
+    nbody_info inf;
+    nbody_get_info(h->ctx, &inf);
+    if (p && len < inf.n) {
+        napi_throw_error(env, "NBODY", "nbody.setRadius: array shorter than the uploaded body count");
+        return undefined(env);
+    }
+    const int rc = nbody_set_radius(h->ctx, p);
+    return rc == NBODY_OK ? undefined(env) : fail(env, "setRadius", rc, h->ctx);
+}
+
+napi_value Contacts(napi_env env, napi_callback_info info)  // the pair search of idx:301-313
+{
+    Args a;
+    if (!get_args(env, info, a, 3, "contacts")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "contacts");
+    double margin;
+    void* p = nullptr;
+    size_t len = 0;
+    if (!h || !get_double(env, a.v[1], &margin)) return undefined(env);
+    if (!get_typed(env, a.v[2], napi_uint32_array, &p, &len)) {
+        napi_throw_error(env, "NBODY", "nbody.contacts(ctx, margin, pairs: Uint32Array)");
+        return undefined(env);
+    }
+    size_t count = 0;
+    const int rc = nbody_contacts(h->ctx, margin, static_cast<unsigned*>(p), len / 2, &count);
+    if (rc != NBODY_OK && !(rc == NBODY_ENOMEM && count > len / 2)) return fail(env, "contacts", rc, h->ctx);
+    return number(env, double(count));
+}
+
+napi_value HistoryEnable(napi_env env, napi_callback_info info)
+{
+    Args a;
+    if (!get_args(env, info, a, 2, "historyEnable")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "historyEnable");
+    int32_t depth = 0;
+    if (!h || napi_get_value_int32(env, a.v[1], &depth) != napi_ok) return undefined(env);
+    const int rc = nbody_history_enable(h->ctx, depth);
+    return rc == NBODY_OK ? undefined(env) : fail(env, "historyEnable", rc, h->ctx);
+}
+
+napi_value HistoryPush(napi_env env, napi_callback_info info)  // history.unshift / pop, idx:564-565
+{
+    Args a;
+    if (!get_args(env, info, a, 1, "historyPush")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "historyPush");
+    if (!h) return undefined(env);
+    const int rc = nbody_history_push(h->ctx);
+    return rc == NBODY_OK ? undefined(env) : fail(env, "historyPush", rc, h->ctx);
+}
+
+napi_value HistoryDownload(napi_env env, napi_callback_info info)
+{
+    Args a;
+    if (!get_args(env, info, a, 2, "historyDownload")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "historyDownload");
+    if (!h) return undefined(env);
+    void* p = nullptr;
+    size_t len = 0;
+    if (!get_array(env, a.v[1], h->prec, &p, &len, "historyDownload") || !p) return undefined(env);
+    const int rc = nbody_history_download(h->ctx, p);  // the shim sizes `out` as n*depth*3
+    return rc == NBODY_OK ? undefined(env) : fail(env, "historyDownload", rc, h->ctx);
+}
+
+napi_value TrailRibbons(napi_env env, napi_callback_info info)  // idx:567-592
+{
+    Args a;
+    if (!get_args(env, info, a, 5, "trailRibbons")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "trailRibbons");
+    double cam[3];
+    void* p = nullptr;
+    size_t len = 0;
+    if (!h || !get_double(env, a.v[1], &cam[0]) || !get_double(env, a.v[2], &cam[1]) || !get_double(env, a.v[3], &cam[2])) return undefined(env);
+    if (!get_typed(env, a.v[4], napi_float32_array, &p, &len)) {
+        napi_throw_error(env, "NBODY", "nbody.trailRibbons(ctx, camX, camY, camZ, out: Float32Array)");
+        return undefined(env);
+    }
+    const int rc = nbody_trail_ribbons(h->ctx, cam, static_cast<float*>(p));
+    return rc == NBODY_OK ? undefined(env) : fail(env, "trailRibbons", rc, h->ctx);
+}
+
+napi_value SnapshotSave(napi_env env, napi_callback_info info)
+{
+    Args a;
+    if (!get_args(env, info, a, 6, "snapshotSave")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "snapshotSave");
+    char path[1024] = {};
+    size_t n = 0;
+    double step, dt, G, eps;
+    if (!h || napi_get_value_string_utf8(env, a.v[1], path, sizeof path, &n) != napi_ok || !get_double(env, a.v[2], &step) ||
+        !get_double(env, a.v[3], &dt) || !get_double(env, a.v[4], &G) || !get_double(env, a.v[5], &eps))
+        return undefined(env);
+    const int rc = nbody_snapshot_save(h->ctx, path, (unsigned long long)step, dt, G, eps);
+    return rc == NBODY_OK ? undefined(env) : fail(env, "snapshotSave", rc, h->ctx);
+}
+
+napi_value SnapshotLoad(napi_env env, napi_callback_info info)
+{
+    Args a;
+    if (!get_args(env, info, a, 2, "snapshotLoad")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "snapshotLoad");
+    char path[1024] = {};
+    size_t n = 0;
+    if (!h || napi_get_value_string_utf8(env, a.v[1], path, sizeof path, &n) != napi_ok) return undefined(env);
+    unsigned long long step = 0;
+    double dt = 0, G = 0, eps = 0;
+    const int rc = nbody_snapshot_load(h->ctx, path, &step, &dt, &G, &eps);
+    if (rc != NBODY_OK) return fail(env, "snapshotLoad", rc, h->ctx);
+    napi_value obj;
+    napi_create_object(env, &obj);
+    napi_set_named_property(env, obj, "step", number(env, double(step)));
+    napi_set_named_property(env, obj, "dt", number(env, dt));
+    napi_set_named_property(env, obj, "G", number(env, G));
+    napi_set_named_property(env, obj, "softening", number(env, eps));
+    return obj;
+}
+
 }  // namespace
 
 // Node loads the addon through this well-known symbol (what NAPI_MODULE_INIT expands to).
@@ -332,7 +480,10 @@ extern "C" __attribute__((visibility("default"))) napi_value napi_register_modul
         {"create", Create}, {"destroy", Destroy}, {"upload", Upload}, {"download", Download},
         {"step", Step}, {"kick1Drift", Kick1Drift}, {"force", Force}, {"kick2", Kick2},
         {"setHeatDecay", SetHeatDecay}, {"energy", Energy}, {"sync", Sync}, {"info", Info},
-        {"version", Version}, {"deviceCount", DeviceCount}};
+        {"version", Version}, {"deviceCount", DeviceCount},
+        {"setRadius", SetRadius}, {"contacts", Contacts}, {"historyEnable", HistoryEnable}, {"historyPush", HistoryPush},
+        {"historyDownload", HistoryDownload}, {"trailRibbons", TrailRibbons}, {"snapshotSave", SnapshotSave},
+        {"snapshotLoad", SnapshotLoad}};
     for (const auto& f : fns) {
         napi_value fn = nullptr;
         if (napi_create_function(env, f.name, NAPI_AUTO_LENGTH, f.cb, nullptr, &fn) != napi_ok) return exports;

@@ -10,6 +10,14 @@
 //   default mode: kick1Drift + force on the GPU, the page's OWN
 //     resolveCollisions(dt) (idx:256) on the host, kick2 on the GPU -- the
 //     order of idx:250-261.
+//   opts.collisions === 'gpu-broad-phase': the O(N^2) overlap search of
+//     resolveCollisions (idx:301-313) also runs on the GPU (addon.contacts).
+//     When no pair of spheres overlaps the host stage is skipped altogether
+//     (the reference loop would only empty contactPairs, idx:376-380) and the
+//     bodies never leave the device between force and kick-2; when some do, the
+//     page's own resolveCollisions(dt) runs unchanged.  A host that wants the
+//     response restricted to the candidate pairs can follow the Python mirror
+//     (n-body-sim_b200/physics.py, PhysicsSystem.resolveCollisions).
 //
 // Body objects are marshalled to typed arrays per call (~12 KB at the page's
 // N <= 300, idx:57); hosts that own typed arrays already should call the addon
@@ -22,6 +30,9 @@ function installGpuIntegrate(physics, CONFIG, addon, opts = {}) {
   let capacity = opts.capacity || Math.max(CONFIG.maxBodies, 1024);
   let ctx = addon.create(precision, opts.nGpus || 1, capacity);
   let pm = new Arr(4 * capacity), vel = new Arr(4 * capacity), acc = new Arr(4 * capacity), temp = new Arr(capacity);
+
+  let radius = new Arr(capacity);
+  const pairScratch = new Uint32Array(2);                // only the count is needed here
 
   function ensure(n) {
     if (n <= capacity) return;
@@ -70,7 +81,21 @@ function installGpuIntegrate(physics, CONFIG, addon, opts = {}) {
       return;
     }
     addon.kick1Drift(ctx, dt);                           // idx:250-253
-    addon.force(ctx, CONFIG.G, CONFIG.softening);        // idx:255
+    if (opts.collisions === 'gpu-broad-phase') {
+      const n = bodies.length;
+      if (radius.length < n) radius = new Arr(capacity);
+      for (let i = 0; i < n; i++) radius[i] = bodies[i].radius;      // idx:221
+      addon.setRadius(ctx, radius.subarray(0, n));
+      addon.force(ctx, CONFIG.G, CONFIG.softening);      // idx:255, also tracks every body's nearest neighbour
+      if (addon.contacts(ctx, 0, pairScratch) === 0) {   // idx:301-313: nothing overlaps
+        this.contactPairs.clear();                       // idx:376-380
+        addon.kick2(ctx, dt, CONFIG.heatDecay);          // idx:258-261
+        unpack(bodies, ALL);
+        return;
+      }
+    } else {
+      addon.force(ctx, CONFIG.G, CONFIG.softening);      // idx:255
+    }
     unpack(bodies, ALL);
     this.resolveCollisions(dt);                          // idx:256: the page's own code, unchanged
     pack(this.bodies);                                   // collisions may edit pos/vel and the body list

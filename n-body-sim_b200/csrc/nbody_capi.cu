@@ -1175,7 +1175,7 @@ extern "C" int nbody_history_enable(nbody_ctx* c, int depth)
     c->hist_stride = c->cap_pad;
     CU(c, cudaMalloc(&s.hist, size_t(depth) * c->hist_stride * 4 * c->esz));
     c->hist_depth = depth;
-    const int smem = depth * kTrailBodies * int(4 * c->esz);
+    const int smem = depth * 512;  // trail_bodies() x sizeof(Real4) = 512 B per ring row in either precision
     if (c->prec == NBODY_F32) CU(c, cudaFuncSetAttribute(trail_ribbons_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     else CU(c, cudaFuncSetAttribute(trail_ribbons_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     return NBODY_OK;
@@ -1258,8 +1258,9 @@ int build_ribbons(nbody_ctx* c, const double camera[3])
         CU(c, cudaMalloc(&s.ribbons, bytes));
         s.ribbons_bytes = bytes;
     }
-    const unsigned blocks = unsigned((c->n + kTrailBodies - 1) / kTrailBodies);
-    const size_t smem = size_t(c->hist_depth) * kTrailBodies * 4 * c->esz;
+    const size_t bpb = c->prec == NBODY_F32 ? trail_bodies<float>() : trail_bodies<double>();
+    const unsigned blocks = unsigned((c->n + bpb - 1) / bpb);
+    const size_t smem = size_t(c->hist_depth) * 512;
     if (c->prec == NBODY_F32)
         trail_ribbons_kernel<float><<<blocks, kTrailThreads, smem, s.stream>>>((const float4*)s.hist, (const float*)s.radius, s.ribbons, c->n, c->hist_stride,
                                                                                c->hist_head, c->hist_depth, c->hist_depth, float(camera[0]),

@@ -68,8 +68,9 @@ __device__ __forceinline__ float to_f32(double a) { return __double2float_rn(a);
 // then every thread builds vertex pairs with point-fastest coalesced stores.  Arithmetic
 // is rounded operation by operation in the reference's association (no FMA), so the
 // fp64 context reproduces the JS doubles and their Float32Array rounding exactly.
-constexpr int kTrailBodies = 16;
 constexpr int kTrailThreads = 256;
+// bodies per CTA: one ring row of the CTA is 512 contiguous bytes in either precision
+template <typename Real> __host__ __device__ constexpr int trail_bodies() { return sizeof(Real) == 4 ? 32 : 16; }
 
 template <typename Real>
 __global__ void __launch_bounds__(kTrailThreads)
@@ -77,6 +78,7 @@ __global__ void __launch_bounds__(kTrailThreads)
                          size_t stride, int head, int depth, int trail_len, Real cx, Real cy, Real cz)
 {
     using V4 = typename Vec4<Real>::type;
+    constexpr int kTrailBodies = trail_bodies<Real>();
     extern __shared__ __align__(16) unsigned char trail_smem[];
     V4* sh = reinterpret_cast<V4*>(trail_smem);  // [depth][kTrailBodies], sample-major
     const size_t b0 = size_t(blockIdx.x) * kTrailBodies;
@@ -115,13 +117,11 @@ __global__ void __launch_bounds__(kTrailThreads)
         px = mul_rn(mul_rn(px, s), width);
         py = mul_rn(mul_rn(py, s), width);
         pz = mul_rn(mul_rn(pz, s), width);
-        float* o = out + (b0 * size_t(depth) + size_t(t)) * 6;  // posArr[i*6 + 0..5], idx:582-588
-        o[0] = to_f32(add_rn(p.x, px));
-        o[1] = to_f32(add_rn(p.y, py));
-        o[2] = to_f32(add_rn(p.z, pz));
-        o[3] = to_f32(sub_rn(p.x, px));
-        o[4] = to_f32(sub_rn(p.y, py));
-        o[5] = to_f32(sub_rn(p.z, pz));
+        // posArr[i*6 + 0..5], idx:582-588; 24 B per thread, 8-byte aligned: three 64-bit stores
+        float2* o = reinterpret_cast<float2*>(out + (b0 * size_t(depth) + size_t(t)) * 6);
+        o[0] = make_float2(to_f32(add_rn(p.x, px)), to_f32(add_rn(p.y, py)));
+        o[1] = make_float2(to_f32(add_rn(p.z, pz)), to_f32(sub_rn(p.x, px)));
+        o[2] = make_float2(to_f32(sub_rn(p.y, py)), to_f32(sub_rn(p.z, pz)));
     }
 }
 

@@ -12,6 +12,7 @@
 // Build: g++ -std=c++17 -rdynamic napi_mock_host.cc -ldl   (-rdynamic exports napi_*).
 #include <dlfcn.h>
 
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -193,6 +194,13 @@ static napi_value typed(bool f64, void* data, size_t len)
     return v;
 }
 
+static napi_value typed_as(napi_typedarray_type ty, void* data, size_t len)
+{
+    napi_value v = typed(true, data, len);
+    v->ta_type = ty;
+    return v;
+}
+
 // call exports[name](args...); a thrown "JS Error" ends the program unless expect_throw
 static napi_value call(const char* name, std::vector<napi_value> args, bool expect_throw = false)
 {
@@ -210,6 +218,9 @@ static napi_value call(const char* name, std::vector<napi_value> args, bool expe
     }
     return r;
 }
+
+static std::string g_out_path;  // collide mode writes <out>.pairs, <out>.ribbons and <out>.nbs next to the state
+static bool g_collide = false;
 
 template <typename T> static void run(bool f64, const char* prec, const std::vector<double>& in, size_t n, double dt, double G,
                                       double eps, int nsteps, bool split, std::vector<double>& out)
@@ -233,7 +244,48 @@ template <typename T> static void run(bool f64, const char* prec, const std::vec
     call("setHeatDecay", {ctx, num(0.998)});
     call("upload", {ctx, typed(f64, pm.data(), 4 * n), typed(f64, vel.data(), 4 * n), typed(f64, acc.data(), 4 * n),
                     typed(f64, temp.data(), n)});
-    if (!split) {
+    if (g_collide) {
+        // physics_shim.js `collisions: 'gpu-broad-phase'`: the overlap search of resolveCollisions (idx:301-313) on the
+        // device between force and kick-2, Body.history kept on the device, ribbons and a snapshot at the end
+        const int depth = 8;
+        std::vector<T> radius(n);
+        for (size_t k = 0; k < n; ++k) radius[k] = T(1.5 * std::cbrt(3.0 * double(pm[4 * k + 3]) / (4.0 * 3.14159265358979323846)));
+        std::vector<unsigned> pairs(2 * 4096);
+        call("contacts", {ctx, num(0), typed_as(napi_uint32_array, pairs.data(), pairs.size())}, true);  // no radii yet: throws
+        call("setRadius", {ctx, typed(f64, radius.data(), n)});
+        call("historyEnable", {ctx, num(depth)});
+        double count = 0;
+        for (int s = 0; s < nsteps; ++s) {
+            call("kick1Drift", {ctx, num(dt)});
+            call("force", {ctx, num(G), num(eps)});
+            std::vector<unsigned> tiny(2);
+            count = call("contacts", {ctx, num(0), typed_as(napi_uint32_array, tiny.data(), tiny.size())})->num;  // too small: count only
+            if (count > 1 && (tiny[0] || tiny[1])) exit(5);
+            count = call("contacts", {ctx, num(0), typed_as(napi_uint32_array, pairs.data(), pairs.size())})->num;
+            call("kick2", {ctx, num(dt), num(0.998)});
+            call("historyPush", {ctx});
+        }
+        std::vector<float> ribbons(n * depth * 6);
+        std::vector<T> hist(n * depth * 3);
+        call("trailRibbons", {ctx, num(0), num(80), num(150), typed_as(napi_float32_array, ribbons.data(), ribbons.size())});
+        call("historyDownload", {ctx, typed(f64, hist.data(), hist.size())});
+        call("snapshotSave", {ctx, str((g_out_path + ".nbs").c_str()), num(nsteps), num(dt), num(G), num(eps)});
+        napi_value meta = call("snapshotLoad", {ctx, str((g_out_path + ".nbs").c_str())});
+        if (meta->props["step"]->num != nsteps || meta->props["dt"]->num != dt) exit(6);
+        call("setRadius", {ctx, typed(f64, radius.data(), n)});
+        FILE* fp = fopen((g_out_path + ".pairs").c_str(), "wb");
+        fwrite(pairs.data(), sizeof(unsigned), size_t(2 * count), fp);
+        fclose(fp);
+        fp = fopen((g_out_path + ".ribbons").c_str(), "wb");
+        fwrite(ribbons.data(), sizeof(float), ribbons.size(), fp);
+        fclose(fp);
+        fp = fopen((g_out_path + ".history").c_str(), "wb");
+        for (T v : hist) {
+            const double d = double(v);
+            fwrite(&d, 8, 1, fp);
+        }
+        fclose(fp);
+    } else if (!split) {
         call("step", {ctx, num(dt), num(G), num(eps), num(nsteps)});
     } else {
         for (int s = 0; s < nsteps; ++s) {  // physics_shim.js default mode with a no-op collision stage
@@ -296,6 +348,8 @@ int main(int argc, char** argv)
     const double dt = in[1], G = in[2], eps = in[3];
     const int nsteps = atoi(argv[4]);
     const bool split = strcmp(argv[5], "split") == 0;
+    g_collide = strcmp(argv[5], "collide") == 0;
+    g_out_path = argv[3];
     const bool f64 = strcmp(argv[6], "f64") == 0;
     std::vector<double> out;
     if (f64)

@@ -57,3 +57,34 @@ def test_addon_matches_oracle(nb, oracle, tmp_path, mode, prec, tol):
         assert np.array_equal(temp, t)
         ke, pe, _ = oracle.energy(p, v, s.G, s.softening)
         assert abs(meta["kinetic"] - ke) < 1e-10 * abs(ke) and abs(meta["potential"] - pe) < 1e-10 * abs(pe)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("prec", ["f64", "f32"])
+def test_addon_collision_and_renderer_feed(nb, oracle, tmp_path, prec):
+    """setRadius / contacts / history / trailRibbons / snapshot through the addon glue."""
+    s = nb.scenes.galaxy_default()
+    acc0 = np.zeros_like(s.vel)
+    fin, fout = tmp_path / "in.bin", tmp_path / "out.bin"
+    _fixture_bytes(s, acc0, s.temp).tofile(fin)
+    nsteps, depth = 12, 8
+    r = subprocess.run([HOST, ADDON, str(fin), str(fout), str(nsteps), "collide", prec], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    dt = np.float32 if prec == "f32" else np.float64
+    pm, vel, acc, temp = _split(np.fromfile(fout, dtype=np.float64), s.n)
+    radius = (1.5 * np.cbrt(3.0 * s.pos_mass[:, 3].astype(dt).astype(np.float64) / (4.0 * np.pi))).astype(dt)
+    pairs = np.fromfile(str(fout) + ".pairs", dtype=np.uint32).reshape(-1, 2)
+    ref = oracle.overlap_pairs(pm, radius.astype(np.float64), 0.0, mt=False)   # kick-2 does not move bodies
+    assert len(ref) > 0 and np.array_equal(pairs, ref)
+    snap = nb.snapshot.read(str(fout) + ".nbs")
+    assert snap["step"] == nsteps and snap["dtype"] == np.dtype(dt)
+    assert np.array_equal(snap["pos_mass"].astype(np.float64), pm) and np.array_equal(snap["vel"].astype(np.float64), vel)
+    assert np.array_equal(snap["radius"], radius)
+    hist = np.fromfile(str(fout) + ".history", dtype=np.float64).reshape(s.n, depth, 3)
+    assert np.array_equal(hist[:, 0], pm[:, :3])                               # newest sample = current position
+    rib = np.fromfile(str(fout) + ".ribbons", dtype=np.float32).reshape(s.n, depth, 6)
+    want = oracle.trail_ribbons(hist, radius.astype(np.float64), (0, 80, 150))
+    if prec == "f64":
+        assert np.array_equal(rib, want)
+    else:
+        assert np.abs(rib - want).max() < 2e-3 * float(radius.max())
