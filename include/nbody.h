@@ -167,6 +167,29 @@ NBODY_API int nbody_history_download(nbody_ctx* ctx, void* out);
  * rounding exactly. */
 NBODY_API int nbody_trail_ribbons(nbody_ctx* ctx, const double camera[3], float* out);
 
+/* ---- headless body renderer ------------------------------- */
+
+/* Per-body material inputs of the planet shader: Body.type (0 rock, 1 metal, 2 ice:
+ * CONFIG.materials colours, idx:70-74) and the `seed` uniform each mesh material draws
+ * at creation (Math.random()*100, idx:492).  Either may be NULL (rock / 0).  Dropped by
+ * every upload(), like the radii. */
+NBODY_API int nbody_set_materials(nbody_ctx* ctx, const int* type, const float* seed);
+
+/* Render every body as the page's planet shaders would shade it (planetVertexShader +
+ * planetFragmentShader, idx:83-202), with no graphics API: each sphere (centre pos,
+ * radius from nbody_set_radius, idx:545-546) is ray-cast from a perspective camera
+ * (THREE.PerspectiveCamera(fov_deg, width/height, 0.1, 3000) at cam_position looking at
+ * cam_target, +y up; the page uses fov 45, position (0,80,150), target 0, idx:704-705),
+ * the nearest body per pixel wins (lower index on a tie), and the fragment shader runs
+ * on the hit point with the body's temperature (the uploaded temp array), type and seed.
+ * rgba: float[height][width][4] = gl_FragColor BEFORE three.js's tone mapping and bloom
+ * (library passes, not restated); background 0,0,0,0; row 0 is the top of the image.
+ * ids: int[height][width] = body index or -1; may be NULL.  rgba may be NULL too: the
+ * frame is then rendered and left on the device.  All arithmetic is fp32, one rounded
+ * operation per GLSL operation (no FMA contraction), in every context precision. */
+NBODY_API int nbody_render(nbody_ctx* ctx, int width, int height, const double cam_position[3],
+                           const double cam_target[3], double fov_deg, float* rgba, int* ids);
+
 /* ---- snapshots (the reference saves nothing) ---- */
 
 /* Raw little-endian dump of the state.  64-byte header:

@@ -27,7 +27,7 @@ SYMBOLS = (
     "nbody_enable_timing", "nbody_read_timing", "nbody_get_info",
     "nbody_set_radius", "nbody_contacts", "nbody_contact_stats",
     "nbody_history_enable", "nbody_history_push", "nbody_history_download", "nbody_trail_ribbons",
-    "nbody_snapshot_save", "nbody_snapshot_load",
+    "nbody_snapshot_save", "nbody_snapshot_load", "nbody_set_materials", "nbody_render",
 )
 
 
@@ -101,6 +101,8 @@ def lib() -> ctypes.CDLL:
     L.nbody_history_push.argtypes = [vp]
     L.nbody_history_download.argtypes = [vp, vp]
     L.nbody_trail_ribbons.argtypes = [vp, pd, vp]
+    L.nbody_set_materials.argtypes = [vp, vp, vp]
+    L.nbody_render.argtypes = [vp, i, i, pd, pd, d, vp, vp]
     ull = ctypes.c_ulonglong
     L.nbody_snapshot_save.argtypes = [vp, ctypes.c_char_p, ull, d, d, d]
     L.nbody_snapshot_load.argtypes = [vp, ctypes.c_char_p, ctypes.POINTER(ull), pd, pd, pd]

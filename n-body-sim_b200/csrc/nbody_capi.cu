@@ -24,6 +24,7 @@
 #include "force_f64.cuh"
 #include "integrate.cuh"
 #include "nccl_dyn.h"
+#include "render.cuh"
 #include "trails.cuh"
 
 using namespace nb;
@@ -59,6 +60,14 @@ struct Shard {
     void* hist = nullptr;               // Real4 [depth][hist_stride]
     float* ribbons = nullptr;           // float [n][depth][6] staging for nbody_trail_ribbons
     size_t ribbons_bytes = 0;
+    // headless renderer (render.cu), first shard only
+    int* mat_type = nullptr;            // Body.type per body (0 rock, 1 metal, 2 ice)
+    float* mat_seed = nullptr;          // the `seed` uniform of each body's material (idx:492)
+    void* temp_full = nullptr;          // all temperatures gathered on this device (multi-GPU contexts)
+    unsigned long long* zbuf = nullptr;
+    float4* image = nullptr;
+    int* image_ids = nullptr;
+    size_t image_pixels = 0;
     ncclComm_t comm = nullptr;
     // peer-store exchange (exchange.cuh): every rank's two position buffers and flag array as mapped on this device
     void* peer_pos[kMaxPeers][2] = {};
@@ -100,6 +109,7 @@ struct nbody_ctx {
     size_t hist_stride = 0;         // bodies per slot (= cap_pad)
     size_t hist_n = 0;              // body count the ring was filled for (0: refill on the next push)
     int hist_head = 0;              // slot of the newest sample
+    bool has_materials = false;     // nbody_set_materials was called for the current body list
     bool p2p = false;               // peer-store exchange instead of ncclAllGather
     unsigned long long epoch = 0;   // exchange barrier epoch (same sequence on every rank)
     double heat_decay = 0.998;  // CONFIG.heatDecay, /root/reference/index.html:67
@@ -321,6 +331,12 @@ extern "C" void nbody_destroy(nbody_ctx* c)
         cudaFree(s.pair_count);
         cudaFree(s.hist);
         cudaFree(s.ribbons);
+        cudaFree(s.mat_type);
+        cudaFree(s.mat_seed);
+        cudaFree(s.temp_full);
+        cudaFree(s.zbuf);
+        cudaFree(s.image);
+        cudaFree(s.image_ids);
         if (s.own_stream) cudaStreamDestroy(s.own_stream);
     }
     delete c;
@@ -639,6 +655,7 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     c->has_temp = temp != nullptr;
     c->has_radius = false;  // a new body list: radii must be set again (Body.radius follows mass, idx:221)
     if (c->hist_n != n) c->hist_n = 0;  // history ring: refilled at the next push (trails.cuh)
+    c->has_materials = false;
     c->near_valid = false;
     choose_chunks(c);
     return c->prec == NBODY_F32
@@ -1395,5 +1412,110 @@ extern "C" int nbody_snapshot_load(nbody_ctx* c, const char* path, unsigned long
     if (dt) *dt = h.dt;
     if (G) *G = h.G;
     if (softening) *softening = h.softening;
+    return NBODY_OK;
+}
+
+// ============================================================================
+// headless body renderer (render.cu)
+// ============================================================================
+
+extern "C" int nbody_set_materials(nbody_ctx* c, const int* type, const float* seed)
+{
+    int rc = check_ready(c, "set_materials");
+    if (rc != NBODY_OK) return rc;
+    Shard& s = c->shards[0];
+    CU(c, cudaSetDevice(s.device));
+    if (type)
+        for (size_t i = 0; i < c->n; ++i)
+            if (type[i] < 0 || type[i] > 2) return fail(c, NBODY_EINVAL, "set_materials: type[%zu] = %d (0 rock, 1 metal, 2 ice)", i, type[i]);
+    if (!s.mat_type) {
+        CU(c, cudaMalloc(&s.mat_type, c->cap_pad * sizeof(int)));
+        CU(c, cudaMalloc(&s.mat_seed, c->cap_pad * sizeof(float)));
+    }
+    CU(c, cudaMemsetAsync(s.mat_type, 0, c->n * sizeof(int), s.stream));
+    CU(c, cudaMemsetAsync(s.mat_seed, 0, c->n * sizeof(float), s.stream));
+    if (type) CU(c, cudaMemcpyAsync(s.mat_type, type, c->n * sizeof(int), cudaMemcpyHostToDevice, s.stream));
+    if (seed) CU(c, cudaMemcpyAsync(s.mat_seed, seed, c->n * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+    CU(c, cudaStreamSynchronize(s.stream));
+    c->has_materials = true;
+    return NBODY_OK;
+}
+
+extern "C" int nbody_render(nbody_ctx* c, int width, int height, const double cam_position[3], const double cam_target[3],
+                            double fov_deg, float* rgba, int* ids)
+{
+    int rc = check_ready(c, "render");
+    if (rc != NBODY_OK) return rc;
+    if (width < 1 || height < 1 || size_t(width) * size_t(height) > (size_t(1) << 28))
+        return fail(c, NBODY_EINVAL, "render: %d x %d", width, height);
+    if (!cam_position || !cam_target || !(fov_deg > 0.0 && fov_deg < 180.0)) return fail(c, NBODY_EINVAL, "render: camera");
+    if (!c->has_radius) return fail(c, NBODY_EINVAL, "render before set_radius");
+    if (c->rank_mode && c->world > 1) return fail(c, NBODY_EINVAL, "render: a rank holds only its own temperatures; render from a single-process context");
+    if (c->n > 0xffffffffull) return fail(c, NBODY_EINVAL, "render: n exceeds the 32-bit body id of the depth buffer");
+    // Matrix4.lookAt(position, target, up = +y) in double, stored as float (render.cuh)
+    RenderCamera cam;
+    double z[3] = {cam_position[0] - cam_target[0], cam_position[1] - cam_target[1], cam_position[2] - cam_target[2]};
+    double l = sqrt(z[0] * z[0] + z[1] * z[1] + z[2] * z[2]);
+    if (!(l > 0.0)) return fail(c, NBODY_EINVAL, "render: camera position equals its target");
+    for (double& v : z) v /= l;
+    double x[3] = {1.0 * z[2] - 0.0 * z[1], 0.0 * z[0] - 0.0 * z[2], 0.0 * z[1] - 1.0 * z[0]};
+    l = sqrt(x[0] * x[0] + x[1] * x[1] + x[2] * x[2]);
+    if (!(l > 0.0)) return fail(c, NBODY_EINVAL, "render: the camera looks along its up axis");
+    for (double& v : x) v /= l;
+    const double y[3] = {z[1] * x[2] - z[2] * x[1], z[2] * x[0] - z[0] * x[2], z[0] * x[1] - z[1] * x[0]};
+    for (int k = 0; k < 3; ++k) {
+        cam.pos[k] = float(cam_position[k]);
+        cam.xa[k] = float(x[k]);
+        cam.ya[k] = float(y[k]);
+        cam.za[k] = float(z[k]);
+    }
+    cam.tan_half = float(tan(fov_deg * 3.14159265358979323846 / 360.0));
+    cam.aspect = float(width) / float(height);
+    cam.near = 0.1f;  // PerspectiveCamera(45, aspect, 0.1, 3000), idx:704
+
+    Shard& s = c->shards[0];
+    CU(c, cudaSetDevice(s.device));
+    const size_t pixels = size_t(width) * size_t(height);
+    if (pixels > s.image_pixels) {
+        CU(c, cudaStreamSynchronize(s.stream));
+        cudaFree(s.zbuf);
+        cudaFree(s.image);
+        cudaFree(s.image_ids);
+        s.zbuf = nullptr;
+        s.image = nullptr;
+        s.image_ids = nullptr;
+        s.image_pixels = 0;
+        CU(c, cudaMalloc(&s.zbuf, pixels * sizeof(unsigned long long)));
+        CU(c, cudaMalloc(&s.image, pixels * sizeof(float4)));
+        CU(c, cudaMalloc(&s.image_ids, pixels * sizeof(int)));
+        s.image_pixels = pixels;
+    }
+    // temperatures: the renderer's `temperature` uniform (idx:553); sharded state is gathered on this device
+    const void* temp = c->has_temp ? s.temp : nullptr;
+    if (c->has_temp && c->shards.size() > 1) {
+        if (!s.temp_full) CU(c, cudaMalloc(&s.temp_full, c->cap_pad * c->esz));
+        for (Shard& o : c->shards) {
+            if (o.n_local_real == 0) continue;
+            CU(c, cudaSetDevice(o.device));
+            CU(c, cudaStreamSynchronize(o.stream));
+            CU(c, cudaMemcpy(static_cast<char*>(s.temp_full) + std::min(o.i_begin, c->n) * c->esz, o.temp, o.n_local_real * c->esz, cudaMemcpyDefault));
+        }
+        CU(c, cudaSetDevice(s.device));
+        temp = s.temp_full;
+    }
+    const int* type = c->has_materials ? s.mat_type : nullptr;
+    const float* seed = c->has_materials ? s.mat_seed : nullptr;
+    cudaError_t e;
+    if (c->prec == NBODY_F32)
+        e = render_launch<float>((const float*)s.pos[c->cur], (const float*)s.radius, (const float*)temp, type, seed, c->n, cam, width, height, s.zbuf,
+                                 s.image, ids ? s.image_ids : nullptr, s.stream);
+    else
+        e = render_launch<double>((const double*)s.pos[c->cur], (const double*)s.radius, (const double*)temp, type, seed, c->n, cam, width, height,
+                                  s.zbuf, s.image, ids ? s.image_ids : nullptr, s.stream);
+    c->launches += 2;
+    if (e != cudaSuccess) return fail(c, NBODY_ECUDA, "render: %s", cudaGetErrorString(e));
+    if (rgba) CU(c, cudaMemcpyAsync(rgba, s.image, pixels * sizeof(float4), cudaMemcpyDeviceToHost, s.stream));
+    if (ids) CU(c, cudaMemcpyAsync(ids, s.image_ids, pixels * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+    if (rgba || ids) CU(c, cudaStreamSynchronize(s.stream));  // rgba == NULL: the frame stays on the device (timing)
     return NBODY_OK;
 }

@@ -177,6 +177,32 @@ class Engine:
         check(self._L.nbody_trail_ribbons(self._ctx, cam, _ptr(out)), self._ctx)
         return out
 
+    # -- headless body renderer ------------------------------------------
+    def set_materials(self, type=None, seed=None) -> None:
+        """Body.type per body (0 rock, 1 metal, 2 ice or the names) and each material's `seed` uniform (idx:492)."""
+        t = s = None
+        if type is not None:
+            names = {"rock": 0, "metal": 1, "ice": 2}
+            t = np.ascontiguousarray([names.get(x, x) for x in type], dtype=np.int32)
+            if t.shape != (self.n,):
+                raise ValueError("type must have one entry per body")
+        if seed is not None:
+            s = np.ascontiguousarray(seed, dtype=np.float32)
+            if s.shape != (self.n,):
+                raise ValueError("seed must have one entry per body")
+        check(self._L.nbody_set_materials(self._ctx, _ptr(t), _ptr(s)), self._ctx)
+
+    def render(self, width: int, height: int, camera=(0.0, 80.0, 150.0), target=(0.0, 0.0, 0.0), fov_deg: float = 45.0,
+               ids: bool = False, download: bool = True):
+        """The planet shaders (idx:83-202) on ray-cast spheres: float32 [height, width, 4]
+        (gl_FragColor before tone mapping); with ids=True also int32 [height, width]."""
+        cam = (ctypes.c_double * 3)(*[float(x) for x in camera])
+        tgt = (ctypes.c_double * 3)(*[float(x) for x in target])
+        img = np.empty((height, width, 4), dtype=np.float32) if download else None
+        idb = np.empty((height, width), dtype=np.int32) if (ids and download) else None
+        check(self._L.nbody_render(self._ctx, int(width), int(height), cam, tgt, float(fov_deg), _ptr(img), _ptr(idb)), self._ctx)
+        return (img, idb) if ids else img
+
     # -- snapshots ------------------------------------------------------------------------
     def save_snapshot(self, path: str, step: int = 0, dt: float = 0.0, G: float = 0.0, softening: float = 0.0) -> None:
         check(self._L.nbody_snapshot_save(self._ctx, os.fsencode(path), int(step), dt, G, softening), self._ctx)

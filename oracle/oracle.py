@@ -81,6 +81,10 @@ def lib() -> ctypes.CDLL:
         L.oracle_world_integrate.restype = None
         L.oracle_trail_ribbons.argtypes = [sz, i, i, _dp, _dp, _dp, ctypes.POINTER(ctypes.c_float)]
         L.oracle_trail_ribbons.restype = None
+        _fp = ctypes.POINTER(ctypes.c_float)
+        L.oracle_render.argtypes = [sz, _fp, _fp, _fp, ctypes.POINTER(ctypes.c_int), _fp, i, i, _dp, _dp, d, _fp,
+                                    ctypes.POINTER(ctypes.c_int32)]
+        L.oracle_render.restype = None
         for f in ("oracle_overlap_pairs", "oracle_overlap_pairs_mt"):
             getattr(L, f).argtypes = [sz, _dp, _dp, d, _u32p, sz]
             getattr(L, f).restype = sz
@@ -257,3 +261,21 @@ def trail_ribbons(hist, radius, camera, trail_length=None):
     lib().oracle_trail_ribbons(n, depth, int(trail_length or depth), _p(h), _p(r), _p(cam),
                                out.ctypes.data_as(ctypes.POINTER(ctypes.c_float)))
     return out
+
+
+def render(pos_mass, radius, temp, type, seed, width, height, camera=(0.0, 80.0, 150.0), target=(0.0, 0.0, 0.0), fov_deg=45.0):
+    """The planet shaders (idx:83-202) on ray-cast spheres, fp32 like GLSL.  Inputs are rounded to
+    float32 first (WebGL uniforms).  Returns (rgba float32 [h,w,4], ids int32 [h,w])."""
+    f32 = lambda a: np.ascontiguousarray(a, dtype=np.float32)
+    pm, r, t, sd = f32(pos_mass), f32(radius), f32(temp), f32(seed)
+    n = pm.shape[0]
+    ty = np.ascontiguousarray(type, dtype=np.int32)
+    assert pm.shape == (n, 4) and r.shape == (n,) and t.shape == (n,) and sd.shape == (n,) and ty.shape == (n,)
+    cam, tgt = _f64(camera, (3,)), _f64(target, (3,))
+    rgba = np.zeros((height, width, 4), dtype=np.float32)
+    ids = np.zeros((height, width), dtype=np.int32)
+    fp = ctypes.POINTER(ctypes.c_float)
+    lib().oracle_render(n, pm.ctypes.data_as(fp), r.ctypes.data_as(fp), t.ctypes.data_as(fp),
+                        ty.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), sd.ctypes.data_as(fp), int(width), int(height),
+                        _p(cam), _p(tgt), float(fov_deg), rgba.ctypes.data_as(fp), ids.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)))
+    return rgba, ids
