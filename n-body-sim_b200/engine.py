@@ -198,8 +198,9 @@ class Engine:
         (gl_FragColor before tone mapping); with ids=True also int32 [height, width]."""
         cam = (ctypes.c_double * 3)(*[float(x) for x in camera])
         tgt = (ctypes.c_double * 3)(*[float(x) for x in target])
-        img = np.empty((height, width, 4), dtype=np.float32) if download else None
-        idb = np.empty((height, width), dtype=np.int32) if (ids and download) else None
+        ok = width > 0 and height > 0                      # bad sizes: let the library report them
+        img = np.empty((height, width, 4), dtype=np.float32) if (download and ok) else None
+        idb = np.empty((height, width), dtype=np.int32) if (ids and download and ok) else None
         check(self._L.nbody_render(self._ctx, int(width), int(height), cam, tgt, float(fov_deg), _ptr(img), _ptr(idb)), self._ctx)
         return (img, idb) if ids else img
 
