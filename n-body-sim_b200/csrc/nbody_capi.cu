@@ -64,7 +64,7 @@ struct Shard {
     int* mat_type = nullptr;            // Body.type per body (0 rock, 1 metal, 2 ice)
     float* mat_seed = nullptr;          // the `seed` uniform of each body's material (idx:492)
     void* temp_full = nullptr;          // all temperatures gathered on this device (multi-GPU contexts)
-    unsigned long long* zbuf = nullptr;
+    RenderScratch render_scratch;
     float4* image = nullptr;
     int* image_ids = nullptr;
     size_t image_pixels = 0;
@@ -334,7 +334,7 @@ extern "C" void nbody_destroy(nbody_ctx* c)
         cudaFree(s.mat_type);
         cudaFree(s.mat_seed);
         cudaFree(s.temp_full);
-        cudaFree(s.zbuf);
+        render_scratch_free(s.render_scratch);
         cudaFree(s.image);
         cudaFree(s.image_ids);
         if (s.own_stream) cudaStreamDestroy(s.own_stream);
@@ -1478,14 +1478,12 @@ extern "C" int nbody_render(nbody_ctx* c, int width, int height, const double ca
     const size_t pixels = size_t(width) * size_t(height);
     if (pixels > s.image_pixels) {
         CU(c, cudaStreamSynchronize(s.stream));
-        cudaFree(s.zbuf);
+        render_scratch_free(s.render_scratch);
         cudaFree(s.image);
         cudaFree(s.image_ids);
-        s.zbuf = nullptr;
         s.image = nullptr;
         s.image_ids = nullptr;
         s.image_pixels = 0;
-        CU(c, cudaMalloc(&s.zbuf, pixels * sizeof(unsigned long long)));
         CU(c, cudaMalloc(&s.image, pixels * sizeof(float4)));
         CU(c, cudaMalloc(&s.image_ids, pixels * sizeof(int)));
         s.image_pixels = pixels;
@@ -1507,12 +1505,12 @@ extern "C" int nbody_render(nbody_ctx* c, int width, int height, const double ca
     const float* seed = c->has_materials ? s.mat_seed : nullptr;
     cudaError_t e;
     if (c->prec == NBODY_F32)
-        e = render_launch<float>((const float*)s.pos[c->cur], (const float*)s.radius, (const float*)temp, type, seed, c->n, cam, width, height, s.zbuf,
+        e = render_launch<float>((const float*)s.pos[c->cur], (const float*)s.radius, (const float*)temp, type, seed, c->n, cam, width, height, s.render_scratch,
                                  s.image, ids ? s.image_ids : nullptr, s.stream);
     else
         e = render_launch<double>((const double*)s.pos[c->cur], (const double*)s.radius, (const double*)temp, type, seed, c->n, cam, width, height,
-                                  s.zbuf, s.image, ids ? s.image_ids : nullptr, s.stream);
-    c->launches += 2;
+                                  s.render_scratch, s.image, ids ? s.image_ids : nullptr, s.stream);
+    c->launches += 4;  // bin count, scan, bin fill, tile render
     if (e != cudaSuccess) return fail(c, NBODY_ECUDA, "render: %s", cudaGetErrorString(e));
     if (rgba) CU(c, cudaMemcpyAsync(rgba, s.image, pixels * sizeof(float4), cudaMemcpyDeviceToHost, s.stream));
     if (ids) CU(c, cudaMemcpyAsync(ids, s.image_ids, pixels * sizeof(int), cudaMemcpyDeviceToHost, s.stream));

@@ -16,11 +16,21 @@ struct RenderCamera {
     float near;      // 0.1 in the page
 };
 
-// zbuf: width*height 64-bit (depth bits << 32 | body) scratch; rgba: width*height float4
-// (gl_FragColor before tone mapping; background 0,0,0,0); ids: width*height or nullptr.
+// Per-context scratch of the tile binning (render.cu): bodies per tile, list offsets, the lists.
+struct RenderScratch {
+    unsigned* counts = nullptr;
+    unsigned* offsets = nullptr;
+    unsigned* list = nullptr;
+    size_t ntiles_cap = 0, list_cap = 0;
+    size_t last_list_entries = 0;
+};
+void render_scratch_free(RenderScratch& s);
+
+// rgba: width*height float4 (gl_FragColor before tone mapping; background 0,0,0,0); ids: width*height or nullptr.
+// Synchronises the stream once per frame (the tile-list length is read back to size the lists).
 template <typename Real>
 cudaError_t render_launch(const Real* pos, const Real* radius, const Real* temp, const int* type, const float* seed, size_t n,
-                          const RenderCamera& cam, int w, int h, unsigned long long* zbuf, float4* rgba, int* ids,
+                          const RenderCamera& cam, int w, int h, RenderScratch& scratch, float4* rgba, int* ids,
                           cudaStream_t stream);
 
 }  // namespace nb
