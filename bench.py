@@ -270,6 +270,10 @@ def main():
                 "kernel": "force_f32_kernel", "kernel_ms": k_ms_max, "kernel_launches": k_launches,
                 "peak_def": f"{sms} SMs x 128 FP32 lanes x {pk['sm_max_mhz']:.0f} MHz ({pk['src']} sm_max_mhz) / 13 issue slots per interaction",
                 "frac_fp32_pipe_only": achieved / (peak_max * 13 / 12),
+                "kernel_variant": ("equal-mass: 11 FP32 lane-ops + 1 MUFU per interaction (the per-pair mass multiply drops out; "
+                                   "configs[3] has equal masses 1/N)" if info.get("uniform_mass") else
+                                   "general: 12 FP32 lane-ops + 1 MUFU per interaction"),
+                "frac_vs_own_op_count": achieved / (peak_max * 13 / (12 if info.get("uniform_mass") else 13)),
                 "hbm": {"algorithmic_bytes_per_launch": 64.0 * args.n / world + 16.0 * args.n,
                         "achieved_gbs": (64.0 * args.n / world + 16.0 * args.n) / (k_ms_max * 1e-3) * 1e-9,
                         "peak_gbs": pk["hbm_gbs"], "note": "HBM is negligible for this path (SURVEY.md 8d)"}}
@@ -284,7 +288,8 @@ def main():
                            "n": args.n, "parallelism": f"i-range shards x{world}, positions exchanged by " + {0: "nothing (1 GPU)", 1: "ncclAllGather",
                                        2: "fused peer stores over NVLink + epoch barrier"}[info["exchange"]],
                            "l2": "flushed between steps (256 MiB write)", "j_chunks": info["j_chunks"], "i_tile": info["i_tile"],
-                           "flop_convention": "20 flop/interaction", "tflops_20": value * 20e-3},
+                           "flop_convention": "20 flop/interaction", "tflops_20": value * 20e-3,
+                           "equal_mass_kernel": bool(info.get("uniform_mass"))},
                 "roofline": roof, "gpu_launches": int(launches_all), "clocks": clocks}
         if not args.no_e2e:
             line["e2e"] = {"value": inter_step / e2e_s * 1e-9, "unit": UNIT, "h2d_bytes_per_step": int(h2d),

@@ -54,15 +54,16 @@ __global__ void kick2_kernel(Real* vel, const Real* acc, Real* temp, size_t n_lo
     if (temp != nullptr && heat_decay > Real(0)) temp[il] = thermal(temp[il], heat_decay);
 }
 
-// Host AoS (x,y,z,m)[n] staged on the device -> device pos_mass layout, pads = 0.
+// Host AoS (x,y,z,m)[n] staged on the device -> device pos_mass layout.  Pads are massless
+// bodies at the origin, or (pad_x != 0: the equal-mass force kernel ignores masses) bodies far away.
 template <typename Real>
-__global__ void pack_pos_kernel(const Real* aos, Real* pos_a, Real* pos_b, size_t n, size_t n_pad)
+__global__ void pack_pos_kernel(const Real* aos, Real* pos_a, Real* pos_b, size_t n, size_t n_pad, Real pad_x)
 {
     const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= n_pad) return;
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
-        const Real v = i < n ? aos[4 * i + c] : Real(0);
+        const Real v = i < n ? aos[4 * i + c] : (c == 0 ? pad_x : Real(0));
         pos_a[pm_index<Real>(i, c)] = v;
         pos_b[pm_index<Real>(i, c)] = v;  // mass is constant: both buffers carry it
     }

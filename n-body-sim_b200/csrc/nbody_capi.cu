@@ -29,6 +29,11 @@
 
 using namespace nb;
 
+#ifndef NB_UNIFORM_UNROLL
+#define NB_UNIFORM_UNROLL 16
+#endif
+constexpr int kUniUnroll = NB_UNIFORM_UNROLL;  // inner-loop unroll of the equal-mass force kernel
+
 namespace {
 
 struct Shard {
@@ -98,6 +103,8 @@ struct nbody_ctx {
     int my_rank = 0;     // rank of shards[0] in rank mode
     std::vector<Shard> shards;
     bool has_temp = false;
+    bool uniform = false;           // fp32: every uploaded mass is the same value -> the 11-op force kernel
+    double uniform_mass = 0.0;
     bool has_radius = false;        // nbody_set_radius was called for the current body list
     bool near_valid = false;        // Shard::near describes the CURRENT positions (last launch was a NEAR force pass)
     double near_eps2 = 0.0;         // softening^2 of that pass
@@ -237,6 +244,8 @@ int set_kernel_attrs(nbody_ctx* c)
     CU(c, cudaFuncSetAttribute(force_f32_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f32_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f32_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
+    CU(c, cudaFuncSetAttribute(force_f32_kernel<4, false, kUniUnroll, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
+    CU(c, cudaFuncSetAttribute(force_f32_kernel<4, true, kUniUnroll, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
@@ -561,6 +570,7 @@ extern "C" int nbody_get_info(nbody_ctx* c, nbody_info* o)
     o->i_tile = c->i_tile;
     o->kernel_launches = c->launches;
     o->exchange = c->world == 1 ? 0 : (c->p2p ? 2 : 1);
+    o->uniform_mass = c->uniform ? 1 : 0;
     return NBODY_OK;
 }
 
@@ -583,7 +593,7 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
         CU(c, cudaMemcpyAsync(s.stage, pm, n * v4, cudaMemcpyHostToDevice, s.stream));
         const unsigned blocks = unsigned((c->n_pad + 255) / 256);
         pack_pos_kernel<Real><<<blocks, 256, 0, s.stream>>>(static_cast<const Real*>(s.stage), static_cast<Real*>(s.pos[0]),
-                                                           static_cast<Real*>(s.pos[1]), n, c->n_pad);
+                                                           static_cast<Real*>(s.pos[1]), n, c->n_pad, c->uniform ? Real(1e18) : Real(0));
         c->launches++;
         CU(c, cudaGetLastError());
         CU(c, cudaMemsetAsync(s.vel, 0, s.n_local * v4, s.stream));
@@ -653,6 +663,15 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     c->n_j = round_up(n, size_t(c->j_unit));
     c->cur = 0;
     c->has_temp = temp != nullptr;
+    c->uniform = false;
+    if (c->prec == NBODY_F32 && c->R == 4 && env_int("NBODY_UNIFORM", 1) != 0) {
+        const float* pm = static_cast<const float*>(pos_mass);
+        const float m0 = pm[3];
+        bool same = m0 > 0.0f;
+        for (size_t i = 1; same && i < n; ++i) same = pm[4 * i + 3] == m0;
+        c->uniform = same;
+        c->uniform_mass = m0;
+    }
     c->has_radius = false;  // a new body list: radii must be set again (Body.radius follows mass, idx:221)
     if (c->hist_n != n) c->hist_n = 0;  // history ring: refilled at the next push (trails.cuh)
     c->has_materials = false;
@@ -801,13 +820,18 @@ int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
             CU(c, cudaEventRecord(s.ev[s.ev_used], s.stream));
         }
         if (c->prec == NBODY_F32) {
-            const ForceParams<float> p = make_params<float>(c, s, mode, dt, G, eps);
+            ForceParams<float> p = make_params<float>(c, s, mode, dt, G, eps);
+            const bool uniform = c->uniform && !track_near;
+            if (uniform) p.G = float(G) * float(c->uniform_mass);  // equal masses: the common m joins G (force_f32.cuh, UNIFORM)
             const size_t sm = force_f32_smem_bytes();
             const bool z = (eps == 0.0);
             const dim3 blk(kF32Threads + 32);
             if (track_near) {
                 if (z) force_f32_near_kernel<4, true><<<grid, blk, sm, s.stream>>>(p);
                 else force_f32_near_kernel<4, false><<<grid, blk, sm, s.stream>>>(p);
+            } else if (uniform) {
+                if (z) force_f32_kernel<4, true, kUniUnroll, true><<<grid, blk, sm, s.stream>>>(p);
+                else force_f32_kernel<4, false, kUniUnroll, true><<<grid, blk, sm, s.stream>>>(p);
             } else if (c->R == 2) {
                 if (z) force_f32_kernel<2, true><<<grid, blk, sm, s.stream>>>(p);
                 else force_f32_kernel<2, false><<<grid, blk, sm, s.stream>>>(p);

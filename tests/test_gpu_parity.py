@@ -263,3 +263,44 @@ def test_physics_system_mirror(nb, oracle):
     for k in range(nb.CONFIG.maxBodies + 5):
         ps3.addBody(nb.Body(1.0, nb.V3(k, 0, 0), nb.V3(0, 0, 0)))
     assert len(ps3.bodies) == nb.CONFIG.maxBodies and ps3.bodies[0].pos.x == 5
+
+
+# ---------------------------------------------------------------- equal-mass fast path -----------
+@pytest.mark.parametrize("n,eps", [(4096, 0.3), (5000, 0.05), (3000, 0.0)])
+def test_f32_uniform_mass_kernel(nb, oracle, n, eps):
+    """Equal masses (BASELINE configs 4, 5): the fp32 kernel drops the per-pair mass multiply and
+    parks the pad bodies at 1e18.  Same tolerance as the general kernel; NBODY_UNIFORM=0 and a
+    scene with one different mass take the general kernel and agree with it to rounding."""
+    rng = np.random.default_rng(n)
+    pm = np.concatenate([rng.uniform(-10, 10, (n, 3)), np.full((n, 1), 1.0 / n)], axis=1).astype(np.float32)
+    vel = np.zeros((n, 4), np.float32)
+    ref = oracle.compute_gravity(pm.astype(np.float64), 1.0, eps, mt=True)
+    with nb.Engine(n, precision="f32") as e:
+        e.upload(pm, vel)
+        assert e.info()["uniform_mass"] == 1
+        e.force(1.0, eps)
+        acc_u = e.download()["acc"]
+        e.step(0.01, 1.0, eps, 3)                               # pads stay harmless over fused steps
+        out_u = e.download()
+        ke_u = e.energy(1.0, eps)
+        pm2 = pm.copy()
+        pm2[n // 2, 3] *= 1.5
+        e.upload(pm2, vel)
+        assert e.info()["uniform_mass"] == 0
+    assert norm_rel_err(acc_u, ref) < 2e-5
+    os.environ["NBODY_UNIFORM"] = "0"
+    try:
+        with nb.Engine(n, precision="f32") as e:
+            e.upload(pm, vel)
+            assert e.info()["uniform_mass"] == 0
+            e.force(1.0, eps)
+            acc_g = e.download()["acc"]
+            e.step(0.01, 1.0, eps, 3)
+            out_g = e.download()
+            ke_g = e.energy(1.0, eps)
+    finally:
+        del os.environ["NBODY_UNIFORM"]
+    assert norm_rel_err(acc_u, acc_g) < 2e-6
+    assert norm_rel_err(out_u["pos_mass"], out_g["pos_mass"]) < 1e-6
+    assert np.isfinite(out_u["vel"]).all()
+    assert abs(ke_u[0] - ke_g[0]) <= 1e-4 * abs(ke_g[0]) + 1e-12 and abs(ke_u[1] - ke_g[1]) <= 1e-5 * abs(ke_g[1])
