@@ -275,10 +275,10 @@ __global__ void __launch_bounds__(kF32Threads + 32) force_f32_kernel(const Force
 #ifndef NB_NEAR_UNROLL
 #define NB_NEAR_UNROLL 4  // measured (profiles/r1c_near_variants.jsonl): U=4 @2 CTAs/SM +6.0 % over the plain sweep; U=8 +15 %, U=4 @3 CTAs +11 %
 #endif
-template <int R, bool ZERO_SOFT, int U = NB_NEAR_UNROLL>
+template <int R, bool ZERO_SOFT, bool UNIFORM = false, int U = NB_NEAR_UNROLL>
 __global__ void __launch_bounds__(kF32Threads + 32, NB_NEAR_MIN_CTAS) force_f32_near_kernel(const ForceParams<float> p)
 {
-    force_f32_body<R, ZERO_SOFT, U, true>(p);
+    force_f32_body<R, ZERO_SOFT, U, true, UNIFORM>(p);
 }
 
 }  // namespace nb

@@ -246,6 +246,8 @@ int set_kernel_attrs(nbody_ctx* c)
     CU(c, cudaFuncSetAttribute(force_f32_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f32_kernel<4, false, kUniUnroll, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f32_kernel<4, true, kUniUnroll, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
+    CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
+    CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
@@ -821,12 +823,15 @@ int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
         }
         if (c->prec == NBODY_F32) {
             ForceParams<float> p = make_params<float>(c, s, mode, dt, G, eps);
-            const bool uniform = c->uniform && !track_near;
+            const bool uniform = c->uniform;
             if (uniform) p.G = float(G) * float(c->uniform_mass);  // equal masses: the common m joins G (force_f32.cuh, UNIFORM)
             const size_t sm = force_f32_smem_bytes();
             const bool z = (eps == 0.0);
             const dim3 blk(kF32Threads + 32);
-            if (track_near) {
+            if (track_near && uniform) {
+                if (z) force_f32_near_kernel<4, true, true><<<grid, blk, sm, s.stream>>>(p);
+                else force_f32_near_kernel<4, false, true><<<grid, blk, sm, s.stream>>>(p);
+            } else if (track_near) {
                 if (z) force_f32_near_kernel<4, true><<<grid, blk, sm, s.stream>>>(p);
                 else force_f32_near_kernel<4, false><<<grid, blk, sm, s.stream>>>(p);
             } else if (uniform) {
@@ -1216,7 +1221,7 @@ extern "C" int nbody_history_enable(nbody_ctx* c, int depth)
     c->hist_stride = c->cap_pad;
     CU(c, cudaMalloc(&s.hist, size_t(depth) * c->hist_stride * 4 * c->esz));
     c->hist_depth = depth;
-    const int smem = depth * 512;  // trail_bodies() x sizeof(Real4) = 512 B per ring row in either precision
+    const int smem = (depth + 1) * 512;  // trail_bodies() x sizeof(Real4) = 512 B per sample in either precision, one padding element per body
     if (c->prec == NBODY_F32) CU(c, cudaFuncSetAttribute(trail_ribbons_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     else CU(c, cudaFuncSetAttribute(trail_ribbons_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     return NBODY_OK;
@@ -1301,7 +1306,7 @@ int build_ribbons(nbody_ctx* c, const double camera[3])
     }
     const size_t bpb = c->prec == NBODY_F32 ? trail_bodies<float>() : trail_bodies<double>();
     const unsigned blocks = unsigned((c->n + bpb - 1) / bpb);
-    const size_t smem = size_t(c->hist_depth) * 512;
+    const size_t smem = size_t(c->hist_depth + 1) * 512;
     if (c->prec == NBODY_F32)
         trail_ribbons_kernel<float><<<blocks, kTrailThreads, smem, s.stream>>>((const float4*)s.hist, (const float*)s.radius, s.ribbons, c->n, c->hist_stride,
                                                                                c->hist_head, c->hist_depth, c->hist_depth, float(camera[0]),

@@ -80,27 +80,35 @@ __global__ void __launch_bounds__(kTrailThreads)
     using V4 = typename Vec4<Real>::type;
     constexpr int kTrailBodies = trail_bodies<Real>();
     extern __shared__ __align__(16) unsigned char trail_smem[];
-    V4* sh = reinterpret_cast<V4*>(trail_smem);  // [depth][kTrailBodies], sample-major
+    V4* sh = reinterpret_cast<V4*>(trail_smem);  // [kTrailBodies][depth + 1]: body-major, one element of padding per row
+    const int row = depth + 1;                   // (sample-major rows made every read of the vertex loop a 32-way bank conflict)
     const size_t b0 = size_t(blockIdx.x) * kTrailBodies;
     const int nb_here = int(n - b0 < size_t(kTrailBodies) ? n - b0 : size_t(kTrailBodies));
+    // slot of sample i is (head + i) mod depth; both loops advance their indices incrementally
+    // (an integer division per element costs as much as the vertex arithmetic)
     for (int t = threadIdx.x; t < depth * kTrailBodies; t += kTrailThreads) {
-        const int i = t / kTrailBodies, lb = t % kTrailBodies;
-        if (lb < nb_here) sh[t] = hist[size_t((head + i) % depth) * stride + b0 + lb];
+        const int i = t / kTrailBodies, lb = t % kTrailBodies;  // kTrailBodies is a power of two
+        int slot = head + i;
+        if (slot >= depth) slot -= depth;
+        if (lb < nb_here) sh[lb * row + i] = hist[size_t(slot) * stride + b0 + lb];
     }
     __syncthreads();
+    const int step_lb = kTrailThreads / depth, step_i = kTrailThreads % depth;
+    int lb = threadIdx.x / depth, i = threadIdx.x % depth;
+    const Real inv_span = div_rn(Real(1), Real(trail_len - 1));
     for (int t = threadIdx.x; t < nb_here * depth; t += kTrailThreads) {
-        const int lb = t / depth, i = t % depth;
-        const V4 p = sh[i * kTrailBodies + lb];
+        const V4 p = sh[lb * row + i];
         // widthRatio = 1 - i/(trailLength-1); currentWidth = radius*0.8*max(0, widthRatio)   (idx:569-570)
-        const Real ratio = sub_rn(Real(1), div_rn(Real(i), Real(trail_len - 1)));
+        // fp64 divides like the reference; fp32 (tolerance parity only) multiplies by the reciprocal
+        const Real ratio = sizeof(Real) == 8 ? sub_rn(Real(1), div_rn(Real(i), Real(trail_len - 1))) : Real(1) - Real(i) * inv_span;
         const Real width = mul_rn(mul_rn(radius[b0 + lb], Real(0.8)), ratio > Real(0) ? ratio : Real(0));
         const Real tx = sub_rn(cx, p.x), ty = sub_rn(cy, p.y), tz = sub_rn(cz, p.z);  // vecToCam, idx:572
         V4 a, b;                                                                      // vecDir, idx:574-578
         if (i < depth - 1) {
             a = p;
-            b = sh[(i + 1) * kTrailBodies + lb];
+            b = sh[lb * row + i + 1];
         } else if (i > 0) {
-            a = sh[(i - 1) * kTrailBodies + lb];
+            a = sh[lb * row + i - 1];
             b = p;
         } else {
             a = p;
@@ -111,9 +119,15 @@ __global__ void __launch_bounds__(kTrailThreads)
         Real px = sub_rn(mul_rn(ty, dz), mul_rn(tz, dy));
         Real py = sub_rn(mul_rn(tz, dx), mul_rn(tx, dz));
         Real pz = sub_rn(mul_rn(tx, dy), mul_rn(ty, dx));
-        Real len = sqrt_rn(add_rn(add_rn(mul_rn(px, px), mul_rn(py, py)), mul_rn(pz, pz)));
-        if (len == Real(0)) len = Real(1);  // length() || 1
-        const Real s = div_rn(Real(1), len);
+        const Real len2 = add_rn(add_rn(mul_rn(px, px), mul_rn(py, py)), mul_rn(pz, pz));
+        Real s;
+        if (sizeof(Real) == 8) {
+            Real len = sqrt_rn(len2);
+            if (len == Real(0)) len = Real(1);  // length() || 1
+            s = div_rn(Real(1), len);
+        } else {
+            s = len2 > Real(0) ? Real(rsqrtf(float(len2))) : Real(0);  // one MUFU; a zero vector stays zero
+        }
         px = mul_rn(mul_rn(px, s), width);
         py = mul_rn(mul_rn(py, s), width);
         pz = mul_rn(mul_rn(pz, s), width);
@@ -122,6 +136,12 @@ __global__ void __launch_bounds__(kTrailThreads)
         o[0] = make_float2(to_f32(add_rn(p.x, px)), to_f32(add_rn(p.y, py)));
         o[1] = make_float2(to_f32(add_rn(p.z, pz)), to_f32(sub_rn(p.x, px)));
         o[2] = make_float2(to_f32(sub_rn(p.y, py)), to_f32(sub_rn(p.z, pz)));
+        lb += step_lb;
+        i += step_i;
+        if (i >= depth) {
+            i -= depth;
+            ++lb;
+        }
     }
 }
 

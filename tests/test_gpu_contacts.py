@@ -44,12 +44,13 @@ def test_f64_default_scene_pairs_exact(nb, oracle):
         assert not e.contact_stats()["used_flags"]           # fp64: every body is scanned
 
 
-@pytest.mark.parametrize("n,box,eps", [(4096, 12.0, 0.5), (5000, 9.0, 0.05), (20000, 25.0, 0.0)])
-def test_f32_pairs_exact_with_and_without_flags(nb, oracle, n, box, eps):
+@pytest.mark.parametrize("n,box,eps,mass", [(4096, 12.0, 0.5, (0.05, 0.4)), (5000, 9.0, 0.05, (0.05, 0.4)),
+                                            (20000, 25.0, 0.0, (0.05, 0.4)), (5000, 10.0, 0.2, (0.2, 0.2))])
+def test_f32_pairs_exact_with_and_without_flags(nb, oracle, n, box, eps, mass):
     """fp32 context: the fp32 pre-test only prefilters; the deciding comparison is fp64 on
     the stored fp32 state, so the set equals the oracle's on the same rounded inputs.  The
     list must be the same whether or not the force sweep's nearest-neighbour flags are used."""
-    pm, vel, rad = crowd(n, 7 + n, box)
+    pm, vel, rad = crowd(n, 7 + n, box, mass)            # equal masses: the equal-mass variants of both sweeps
     pm32, vel32, rad32 = pm.astype(np.float32), vel.astype(np.float32), rad.astype(np.float32)
     ref_in = (pm32.astype(np.float64), rad32.astype(np.float64))
     with nb.Engine(n, precision="f32") as e:
