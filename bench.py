@@ -122,7 +122,7 @@ def run_reference(args, rank):
     all_cores = {"value": float(sample_n) * (sample_n - 1) / t_mt * 1e-9, "unit": UNIT, "cores": oracle.max_threads(),
                  "note": "courtesy: OpenMP over i on all host cores, force evaluation only; not the reference's (single-threaded) path"}
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"uniform cube N={args.n} (configs[3]); each step = one integrate(dt) on the first "
                                    f"{sample_n} bodies (bounded sample)", "n": args.n, "sample_n": sample_n},
