@@ -1,0 +1,117 @@
+"""Edge cases of the rows next to the hot path through the C ABI: smallest
+and ragged body counts, extreme ring depths, degenerate geometry, multi-GPU gathers."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _rad(m):
+    return (3 * np.asarray(m, np.float64) / (4 * np.pi)) ** (1 / 3)
+
+
+@pytest.mark.parametrize("precision", ["f32", "f64"])
+@pytest.mark.parametrize("n", [1, 2, 33, 513])
+def test_tiny_and_ragged_counts(nb, oracle, precision, n):
+    """n = 1 (no pair exists), n = 2, and counts that fill neither a CTA nor a tile."""
+    dt = np.float32 if precision == "f32" else np.float64
+    rng = np.random.default_rng(n)
+    pm = np.concatenate([rng.uniform(-3, 3, (n, 3)), rng.uniform(0.5, 2.0, (n, 1))], axis=1).astype(dt)
+    vel = np.zeros((n, 4), dt)
+    rad = _rad(pm[:, 3]).astype(dt)
+    with nb.Engine(n, precision=precision) as e:
+        e.upload(pm, vel, None, np.full(n, 60.0, dt))
+        e.set_radius(rad)
+        e.force(0.5, 0.5)
+        got = e.contacts(0.1)
+        ref = oracle.overlap_pairs(pm.astype(np.float64), rad.astype(np.float64), 0.1, mt=False)
+        assert np.array_equal(got, ref)
+        if n == 1:
+            assert len(got) == 0
+        e.history_enable(2)                                   # the smallest ring
+        e.history_push()
+        e.kick1_drift(0.01)
+        e.history_push()
+        out = e.download(temp=True)
+        h = e.history()
+        assert h.shape == (n, 2, 3) and np.array_equal(h[:, 0], out["pos_mass"][:, :3]) and np.array_equal(h[:, 1], pm[:, :3])
+        rib = e.trail_ribbons((0, 80, 150))
+        want = oracle.trail_ribbons(h.astype(np.float64), rad.astype(np.float64), (0, 80, 150))
+        if precision == "f64":
+            assert np.array_equal(rib, want)
+        else:
+            assert np.abs(rib - want).max() < 2e-3 * float(rad.max())
+        img, ids = e.render(80, 45, ids=True)
+    ref_img, ref_ids = oracle.render(out["pos_mass"], rad, out["temp"], np.zeros(n, np.int32), np.zeros(n), 80, 45)
+    assert np.array_equal(ids, ref_ids) and np.array_equal(img, ref_img)
+
+
+def test_deep_ring_and_wraparound(nb, oracle):
+    """depth 256 (the maximum) in fp64: 128 KB of shared memory per CTA, three wrap-arounds."""
+    s = nb.scenes.galaxy_default()
+    rad = _rad(s.pos_mass[:, 3])
+    with nb.Engine(s.n, precision="f64") as e:
+        for bad in (1, 257, -3):
+            with pytest.raises(nb.NBodyError):
+                e.history_enable(bad)
+        e.upload(s.pos_mass, s.vel)
+        e.set_radius(rad)
+        e.history_enable(256)
+        for k in range(600):
+            e.kick1_drift(0.004)
+            e.history_push()
+        h = e.history()
+        # acc = 0 throughout (no force pass): every push is the previous position plus vel*dt, rounded step by step
+        p = s.pos_mass[:, :3].copy()
+        track = []
+        for k in range(600):
+            p = p + s.vel[:, :3] * 0.004
+            track.append(p.copy())
+        want = np.stack(track[::-1][:256], axis=1)
+        assert np.array_equal(h, want)
+        assert np.array_equal(e.trail_ribbons((5, 6, 7)), oracle.trail_ribbons(want, rad, (5, 6, 7)))
+        e.history_enable(0)                                   # frees the ring
+        with pytest.raises(nb.NBodyError):
+            e.history_push()
+
+
+def test_coincident_and_zero_radius_bodies(nb, oracle):
+    """Coincident centres (distSq = 0), a zero radius, touching exactly: the strict < of idx:313 decides."""
+    pm = np.array([[0, 0, 0, 1.0], [0, 0, 0, 1.0], [3, 0, 0, 1.0], [5, 0, 0, 1.0], [9, 0, 0, 1.0]])
+    rad = np.array([1.0, 0.0, 1.0, 1.0, 0.0])              # bodies 2 and 3 touch exactly: 2 == 1 + 1 -> no contact
+    with nb.Engine(5, precision="f64") as e:
+        e.upload(pm, np.zeros((5, 4)))
+        e.set_radius(rad)
+        got = e.contacts(0.0)
+        assert np.array_equal(got, oracle.overlap_pairs(pm, rad, 0.0, mt=False))
+        assert got.tolist() == [[0, 1]]
+        assert e.contacts(1e-9).tolist() == [[0, 1], [2, 3]]
+        with pytest.raises(nb.NBodyError):
+            e.set_radius(np.array([1.0, -1.0, 1.0, 1.0, 1.0]))
+        img, ids = e.render(64, 36, ids=True)                 # zero-radius bodies are never drawn
+        assert not np.isin(ids, [1, 4]).any() and np.isfinite(img).all()
+
+
+def test_multi_gpu_render_and_trails(nb, oracle):
+    """Two devices: temperatures are sharded and gathered for the frame; positions are everywhere."""
+    if nb.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    s = nb.scenes.galaxy_default()
+    pm, vel, _ = s.astype(np.float32)
+    rad = (_rad(pm[:, 3]) * 3).astype(np.float32)
+    temp = np.linspace(0, 300, s.n).astype(np.float32)
+    out = {}
+    for g in (1, 2):
+        with nb.Engine(s.n, precision="f32", n_gpus=g) as e:
+            e.upload(pm, vel, None, temp)
+            e.set_radius(rad)
+            e.history_enable(8)
+            for _ in range(3):
+                e.step(s.dt, s.G, s.softening, 2)
+                e.history_push()
+            out[g] = (e.render(160, 90), e.history(), e.trail_ribbons((0, 80, 150)), e.download(temp=True))
+    for a, b in zip(out[1][:3], out[2][:3]):
+        assert np.array_equal(a, b)
+    d = out[2][3]
+    ref, _ = oracle.render(d["pos_mass"], rad, d["temp"], np.zeros(s.n, np.int32), np.zeros(s.n), 160, 90)
+    assert np.array_equal(out[2][0], ref)

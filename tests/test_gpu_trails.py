@@ -129,3 +129,31 @@ def test_snapshot_errors(nb, tmp_path):
         assert ei.value.status == _lib.NBODY_EIO
         with pytest.raises(nb.NBodyError):
             e.save_snapshot(p)                                # nothing uploaded
+
+
+def test_visual_system_mirror(nb, oracle):
+    """The page's frame loop through the mirrors (animate(), idx:873-883): physics.integrate x subSteps,
+    then visuals.update -- histories, ribbon vertices and a rendered frame against the oracle."""
+    ph = nb.physics
+    ph.seed_random(77)
+    ps = ph.PhysicsSystem(precision="f64")
+    ph.resetScenario(ps, "galaxy")
+    vis = nb.VisualSystem(ps)
+    hist = None
+    for frame in range(6):
+        ps.integrate(ph.CONFIG.dt / ph.CONFIG.subSteps, nsteps=ph.CONFIG.subSteps)
+        trails = vis.update(ps.bodies, ph.CONFIG.dt)
+        pos = np.array([[*b.pos, b.mass] for b in ps.bodies])
+        hist = oracle.history_push(oracle.history_init(pos, 80), pos) if hist is None else oracle.history_push(hist, pos)
+    radius = np.array([b.radius for b in ps.bodies])
+    assert np.array_equal(vis.histories(), hist)
+    assert np.array_equal(trails, oracle.trail_ribbons(hist, radius, vis.camera_position))
+    img, ids = vis.render(160, 90, ids=True)
+    types = np.array([nb.visuals.TYPE_INDEX[b.type] for b in ps.bodies], dtype=np.int32)
+    seeds = np.array([vis.seeds[b.id] for b in ps.bodies], dtype=np.float32)
+    ref, ref_ids = oracle.render(pos, radius, [b.temperature for b in ps.bodies], types, seeds, 160, 90)
+    assert np.array_equal(ids, ref_ids) and np.array_equal(img, ref)
+    assert (ids == 0).any()                                   # the 1000-degree metal centre is in view (idx:750)
+    vis.garbageCollect(ps.bodies[:10])
+    assert len(vis.seeds) == 10
+    ph.seed_random(None)
