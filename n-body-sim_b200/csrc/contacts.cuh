@@ -59,64 +59,89 @@ __device__ __forceinline__ bool overlap_exact(double xi, double yi, double zi, d
 // grid = (candidate blocks, j-chunks).  cand == nullptr: candidates are i_begin .. i_begin+n_cand-1.
 // BOTH: test every j != i and emit (min, max) -- used for the big bodies, whose partners
 // with a smaller index need not be candidates themselves (the host removes duplicates).
+// Each thread owns kContactPerThread candidates in registers and the j-tile is one 16/32-byte
+// (x, y, z, r) record per body, so a j costs one shared-memory load per kContactPerThread tests.
+constexpr int kContactPerThread = 4;
+
 template <typename Real, bool BOTH>
 __global__ void __launch_bounds__(kContactThreads)
     contact_pairs_kernel(const Real* pos, const Real* radius, const unsigned* cand, unsigned n_cand, size_t i_begin,
                          size_t n, size_t chunk_len, double margin, uint2* pairs, unsigned long long cap,
                          unsigned long long* count)
 {
-    __shared__ Real sx[kContactThreads], sy[kContactThreads], sz[kContactThreads], sr[kContactThreads];
+    using V4 = typename Vec4<Real>::type;
+    constexpr int C = kContactPerThread;
+    __shared__ V4 tile[kContactThreads];
     const int tid = threadIdx.x;
-    const unsigned k = blockIdx.x * kContactThreads + tid;
-    const bool live = k < n_cand;
-    size_t i = 0;
-    Real xi = 0, yi = 0, zi = 0, ri = 0;
-    if (live) {
-        i = cand ? size_t(cand[k]) : i_begin + k;
-        xi = pos[pm_index<Real>(i, 0)];
-        yi = pos[pm_index<Real>(i, 1)];
-        zi = pos[pm_index<Real>(i, 2)];
-        ri = radius[i];
+    size_t ci[C];
+    Real xi[C], yi[C], zi[C], ri[C];
+    size_t i_min = ~size_t(0);
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+        const unsigned k = (blockIdx.x * C + c) * kContactThreads + tid;
+        if (k < n_cand) {
+            ci[c] = cand ? size_t(cand[k]) : i_begin + k;
+            xi[c] = pos[pm_index<Real>(ci[c], 0)];
+            yi[c] = pos[pm_index<Real>(ci[c], 1)];
+            zi[c] = pos[pm_index<Real>(ci[c], 2)];
+            ri[c] = radius[ci[c]];
+            i_min = ci[c] < i_min ? ci[c] : i_min;
+        } else {  // no candidate: parked so far away that every pre-test fails (d2 = inf)
+            ci[c] = ~size_t(0);
+            xi[c] = Real(1e30);
+            yi[c] = zi[c] = ri[c] = Real(0);
+        }
     }
+    // fp32 pre-test: d2 <= ((r_i + margin) * k + r_j * k)^2 with k^2 = 1 + 1e-5 (slack for fp32 rounding), 9 instructions
+    const float kSlack = 1.000005f;
+    float rik[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) rik[c] = (float(ri[c]) + float(margin)) * kSlack;
     const size_t j0 = size_t(blockIdx.y) * chunk_len;
     const size_t j1 = (j0 + chunk_len < n) ? j0 + chunk_len : n;
-    const Real fmargin = Real(margin);
     for (size_t jb = j0; jb < j1; jb += kContactThreads) {
-        const size_t j = jb + tid;
         __syncthreads();
-        if (j < j1) {
-            sx[tid] = pos[pm_index<Real>(j, 0)];
-            sy[tid] = pos[pm_index<Real>(j, 1)];
-            sz[tid] = pos[pm_index<Real>(j, 2)];
-            sr[tid] = radius[j];
+        if (jb + tid < j1) {
+            const size_t j = jb + tid;
+            V4 v;
+            v.x = pos[pm_index<Real>(j, 0)];
+            v.y = pos[pm_index<Real>(j, 1)];
+            v.z = pos[pm_index<Real>(j, 2)];
+            v.w = radius[j];
+            tile[tid] = v;
         }
         __syncthreads();
-        if (!live || (!BOTH && jb + kContactThreads <= i + 1)) continue;  // the tile holds no j > i
+        if (!BOTH && (i_min == ~size_t(0) || jb + kContactThreads <= i_min + 1)) continue;  // the tile holds no j > i for this thread
         const int cnt = static_cast<int>(j1 - jb < size_t(kContactThreads) ? j1 - jb : size_t(kContactThreads));
 #pragma unroll 4
         for (int q = 0; q < cnt; ++q) {
-            bool hit;
-            if (sizeof(Real) == 4) {
-                const float dx = float(sx[q]) - float(xi), dy = float(sy[q]) - float(yi), dz = float(sz[q]) - float(zi);
-                const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-                const float md = float(ri) + float(sr[q]) + float(fmargin);
-                hit = d2 <= md * md * 1.00001f;
-            } else {
-                hit = true;
-            }
-            const size_t j = jb + q;
-            if (!hit || (BOTH ? j == i : j <= i)) continue;
-            // A = the lower index, B = the higher, as the reference's i<j loop has them (idx:306-309)
-            const bool swap = BOTH && j < i;
-            const double ax = swap ? double(sx[q]) : double(xi), ay = swap ? double(sy[q]) : double(yi);
-            const double az = swap ? double(sz[q]) : double(zi), ar = swap ? double(sr[q]) : double(ri);
-            const double bx = swap ? double(xi) : double(sx[q]), by = swap ? double(yi) : double(sy[q]);
-            const double bz = swap ? double(zi) : double(sz[q]), br = swap ? double(ri) : double(sr[q]);
-            if (overlap_exact(ax, ay, az, ar, bx, by, bz, br, margin)) {
-                const unsigned long long at = atomicAdd(count, 1ull);
-                if (at < cap)
-                    pairs[at] = swap ? make_uint2(static_cast<unsigned>(j), static_cast<unsigned>(i))
-                                     : make_uint2(static_cast<unsigned>(i), static_cast<unsigned>(j));
+            const V4 b = tile[q];
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                bool hit;
+                if (sizeof(Real) == 4) {
+                    const float dx = float(b.x) - float(xi[c]), dy = float(b.y) - float(yi[c]), dz = float(b.z) - float(zi[c]);
+                    const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                    const float md = fmaf(float(b.w), kSlack, rik[c]);
+                    hit = d2 <= md * md;
+                } else {
+                    hit = ci[c] != ~size_t(0);
+                }
+                if (!hit) continue;
+                const size_t i = ci[c], j = jb + q;  // rare from here on
+                if (BOTH ? j == i : j <= i) continue;
+                // A = the lower index, B = the higher, as the reference's i<j loop has them (idx:306-309)
+                const bool swap = BOTH && j < i;
+                const double ax = swap ? double(b.x) : double(xi[c]), ay = swap ? double(b.y) : double(yi[c]);
+                const double az = swap ? double(b.z) : double(zi[c]), ar = swap ? double(b.w) : double(ri[c]);
+                const double bx = swap ? double(xi[c]) : double(b.x), by = swap ? double(yi[c]) : double(b.y);
+                const double bz = swap ? double(zi[c]) : double(b.z), br = swap ? double(ri[c]) : double(b.w);
+                if (overlap_exact(ax, ay, az, ar, bx, by, bz, br, margin)) {
+                    const unsigned long long at = atomicAdd(count, 1ull);
+                    if (at < cap)
+                        pairs[at] = swap ? make_uint2(static_cast<unsigned>(j), static_cast<unsigned>(i))
+                                         : make_uint2(static_cast<unsigned>(i), static_cast<unsigned>(j));
+                }
             }
         }
     }

@@ -1084,7 +1084,8 @@ template <typename Real, bool BOTH>
 int launch_pairs(nbody_ctx* c, Shard& s, const unsigned* cand, unsigned n_cand, double margin)
 {
     if (n_cand == 0) return NBODY_OK;
-    const unsigned gx = (n_cand + kContactThreads - 1) / kContactThreads;
+    const unsigned per_cta = kContactThreads * kContactPerThread;
+    const unsigned gx = (n_cand + per_cta - 1) / per_cta;
     // enough CTAs to fill the chip: split the j range when there are few candidate blocks
     size_t jch = (size_t(c->sm_count) * 8 + gx - 1) / gx;
     const size_t max_jch = (c->n + kContactThreads - 1) / kContactThreads;
