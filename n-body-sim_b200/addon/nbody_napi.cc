@@ -21,6 +21,9 @@
 //   historyEnable(ctx, depth) / historyPush(ctx) / historyDownload(ctx, out)      Body.history, idx:540, 564-565
 //   trailRibbons(ctx, camX, camY, camZ, out: Float32Array)  ribbon vertices, idx:567-592
 //   snapshotSave(ctx, path, step, dt, G, softening) / snapshotLoad(ctx, path) -> {step, dt, G, softening}
+//   setMaterials(ctx, type: Int32Array|null, seed: Float32Array|null)   Body.type and the material seed, idx:70-74, 492
+//   render(ctx, width, height, [camX,camY,camZ, tgtX,tgtY,tgtZ, fovDeg] as 7 numbers, rgba: Float32Array w*h*4)
+//                                                          planet shaders idx:83-202, headless
 #include "napi_min.h"
 
 #include <cstdio>
@@ -471,6 +474,58 @@ napi_value SnapshotLoad(napi_env env, napi_callback_info info)
     return obj;
 }
 
+napi_value SetMaterials(napi_env env, napi_callback_info info)  // Body.type + material seed, idx:70-74, 492
+{
+    Args a;
+    if (!get_args(env, info, a, 3, "setMaterials")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "setMaterials");
+    if (!h) return undefined(env);
+    nbody_info inf;
+    nbody_get_info(h->ctx, &inf);
+    void* p[2] = {nullptr, nullptr};
+    const napi_typedarray_type want[2] = {napi_int32_array, napi_float32_array};
+    for (int k = 0; k < 2; ++k) {
+        napi_valuetype t = napi_undefined;
+        napi_typeof(env, a.v[k + 1], &t);
+        if (t == napi_undefined || t == napi_null) continue;
+        size_t len = 0;
+        if (!get_typed(env, a.v[k + 1], want[k], &p[k], &len) || len < inf.n) {
+            napi_throw_error(env, "NBODY", "nbody.setMaterials(ctx, type: Int32Array[n]|null, seed: Float32Array[n]|null)");
+            return undefined(env);
+        }
+    }
+    const int rc = nbody_set_materials(h->ctx, static_cast<const int*>(p[0]), static_cast<const float*>(p[1]));
+    return rc == NBODY_OK ? undefined(env) : fail(env, "setMaterials", rc, h->ctx);
+}
+
+napi_value Render(napi_env env, napi_callback_info info)  // planet shaders, idx:83-202
+{
+    Args a;
+    a.argc = 11;
+    napi_value argv[11] = {};
+    size_t argc = 11;
+    if (napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr) != napi_ok || argc < 11) {
+        napi_throw_error(env, "NBODY", "nbody.render(ctx, width, height, camX, camY, camZ, tgtX, tgtY, tgtZ, fovDeg, rgba: Float32Array)");
+        return undefined(env);
+    }
+    Handle* h = get_handle(env, argv[0], "render");
+    if (!h) return undefined(env);
+    double v[9];
+    for (int k = 0; k < 9; ++k)
+        if (!get_double(env, argv[k + 1], &v[k])) {
+            napi_throw_error(env, "NBODY", "nbody.render: numbers expected");
+            return undefined(env);
+        }
+    void* p = nullptr;
+    size_t len = 0;
+    if (!get_typed(env, argv[10], napi_float32_array, &p, &len) || v[0] < 1 || v[1] < 1 || len < size_t(v[0]) * size_t(v[1]) * 4) {
+        napi_throw_error(env, "NBODY", "nbody.render: rgba must be a Float32Array of width*height*4");
+        return undefined(env);
+    }
+    const int rc = nbody_render(h->ctx, int(v[0]), int(v[1]), &v[2], &v[5], v[8], static_cast<float*>(p), nullptr);
+    return rc == NBODY_OK ? undefined(env) : fail(env, "render", rc, h->ctx);
+}
+
 }  // namespace
 
 // Node loads the addon through this well-known symbol (what NAPI_MODULE_INIT expands to).
@@ -483,7 +538,7 @@ extern "C" __attribute__((visibility("default"))) napi_value napi_register_modul
         {"version", Version}, {"deviceCount", DeviceCount},
         {"setRadius", SetRadius}, {"contacts", Contacts}, {"historyEnable", HistoryEnable}, {"historyPush", HistoryPush},
         {"historyDownload", HistoryDownload}, {"trailRibbons", TrailRibbons}, {"snapshotSave", SnapshotSave},
-        {"snapshotLoad", SnapshotLoad}};
+        {"snapshotLoad", SnapshotLoad}, {"setMaterials", SetMaterials}, {"render", Render}};
     for (const auto& f : fns) {
         napi_value fn = nullptr;
         if (napi_create_function(env, f.name, NAPI_AUTO_LENGTH, f.cb, nullptr, &fn) != napi_ok) return exports;

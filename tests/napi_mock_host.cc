@@ -269,6 +269,22 @@ template <typename T> static void run(bool f64, const char* prec, const std::vec
         std::vector<T> hist(n * depth * 3);
         call("trailRibbons", {ctx, num(0), num(80), num(150), typed_as(napi_float32_array, ribbons.data(), ribbons.size())});
         call("historyDownload", {ctx, typed(f64, hist.data(), hist.size())});
+        {   // a frame of the planet shaders through the addon (idx:83-202): type = k % 3, seed = k * 0.37
+            std::vector<int> type(n);
+            std::vector<float> seed(n), frame(96 * 54 * 4);
+            for (size_t k = 0; k < n; ++k) {
+                type[k] = int(k % 3);
+                seed[k] = float(k) * 0.37f;
+            }
+            call("setMaterials", {ctx, typed_as(napi_int32_array, type.data(), n), typed_as(napi_float32_array, seed.data(), n)});
+            call("render", {ctx, num(96), num(54), num(0), num(80), num(150), num(0), num(0), num(0), num(45),
+                            typed_as(napi_float32_array, frame.data(), frame.size())});
+            call("render", {ctx, num(96), num(54), num(0), num(80), num(150), num(0), num(0), num(0), num(45),
+                            typed_as(napi_float32_array, frame.data(), 16)}, true);  // buffer too small: throws
+            FILE* fr = fopen((g_out_path + ".frame").c_str(), "wb");
+            fwrite(frame.data(), sizeof(float), frame.size(), fr);
+            fclose(fr);
+        }
         call("snapshotSave", {ctx, str((g_out_path + ".nbs").c_str()), num(nsteps), num(dt), num(G), num(eps)});
         napi_value meta = call("snapshotLoad", {ctx, str((g_out_path + ".nbs").c_str())});
         if (meta->props["step"]->num != nsteps || meta->props["dt"]->num != dt) exit(6);

@@ -88,3 +88,7 @@ def test_addon_collision_and_renderer_feed(nb, oracle, tmp_path, prec):
         assert np.array_equal(rib, want)
     else:
         assert np.abs(rib - want).max() < 2e-3 * float(radius.max())
+    frame = np.fromfile(str(fout) + ".frame", dtype=np.float32).reshape(54, 96, 4)
+    k = np.arange(s.n)
+    ref, _ = oracle.render(pm, radius, temp, (k % 3).astype(np.int32), k.astype(np.float32) * np.float32(0.37), 96, 54)
+    assert np.array_equal(frame, ref) and (frame[..., 3] > 0).sum() > 50
