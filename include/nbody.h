@@ -248,7 +248,8 @@ typedef struct {
     int i_tile;          /* bodies per CTA */
     long long kernel_launches; /* kernels launched by this context so far */
     int exchange;        /* position exchange: 0 none (1 GPU), 1 ncclAllGather, 2 fused peer stores over NVLink */
-    int uniform_mass;    /* 1: every uploaded mass is equal and the fp32 force kernel skips the per-pair mass multiply */
+    int uniform_mass;    /* 0: general fp32 force kernel.  1: every uploaded mass is equal and the kernel skips the per-pair
+                            mass multiply.  1+k: all but k (<= 64) bodies share one mass; same kernel, k corrections per body */
 } nbody_info;
 NBODY_API int nbody_get_info(nbody_ctx* ctx, nbody_info* out);
 

@@ -17,8 +17,14 @@ namespace nb {
 
 // fp64 kernel: 8 compute warps + 1 producer warp, one i-body per thread
 constexpr int kThreads = 256;       // compute threads per CTA
-constexpr int kStages = 4;          // j-tile ring depth
-constexpr int kTileBytes = 16384;   // bytes per j-tile stage (512 fp64 bodies)
+#ifndef NB_F64_STAGES
+#define NB_F64_STAGES 4
+#endif
+#ifndef NB_F64_TILE_BYTES
+#define NB_F64_TILE_BYTES 16384
+#endif
+constexpr int kStages = NB_F64_STAGES;          // j-tile ring depth
+constexpr int kTileBytes = NB_F64_TILE_BYTES;   // bytes per j-tile stage (512 fp64 bodies)
 // fp32 kernel (shape chosen by the force_lab sweeps, profiles/r1_force_lab_sweep*.txt):
 // 4 compute warps + 1 producer warp, R i-bodies per thread, 3 CTAs per SM at 128 registers
 constexpr int kF32Threads = 128;    // compute threads per CTA
@@ -55,6 +61,14 @@ template <> __host__ __device__ __forceinline__ size_t pm_index<double>(size_t i
     return 4 * i + c;
 }
 
+// Equal-mass sweep with a few exceptions (force_f32.cuh, UNIFORM): body `index` carries
+// `dm` = its mass minus the common mass, added per i-body after the unit-mass sums.
+struct MassOutlier {
+    unsigned index;
+    float dm;
+};
+constexpr int kMaxOutliers = 64;
+
 enum EpilogueMode : int {
     kForceOnly = 0,        // acc = G * sum                                   (idx:264-291)
     kForceKick2 = 1,       // + vel += acc*h, thermal                         (idx:258-261)
@@ -69,6 +83,9 @@ template <typename Real> struct ForceParams {
     Real* partial;          // [j_chunks][n_local] Real4
     Real* temp;             // local, may be null
     Real* near;             // local; NEAR kernels only: max_j!=i rsqrt(d^2+eps2) (contacts.cuh)
+    const MassOutlier* outliers;  // UNIFORM fp32 kernels only: the bodies whose mass is not the common one
+    int n_outliers;         // 0: `G` already carries the common mass
+    Real bulk_mass;         // n_outliers > 0: the common mass (G stays the plain constant)
     unsigned* tile_counter; // one per local i-tile; zero between launches
     size_t n_j;             // j extent: n rounded up to kJUnit (independent of the GPU count)
     size_t i_begin;         // first global body of this shard (multiple of i-tile)

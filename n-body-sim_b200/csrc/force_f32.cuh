@@ -136,6 +136,34 @@ __device__ __forceinline__ void consume_tile(const float4* __restrict__ tp, cons
     }
 }
 
+// UNIFORM with exceptions (config 3: two mass-500 centres among 131,070 equal disc bodies):
+// the sweep treats every j as the common mass m0; here body i gets the difference,
+//     sum = m0 * (unit-mass sum) + sum_k (m_k - m0) * d_ik / (d_ik^2 + eps^2)^1.5,
+// from the current positions of the few exceptions -- O(N * outliers) scalar work in the
+// CTA that finishes the tile, against the O(N^2) sweep's saved multiply.
+template <bool ZERO_SOFT>
+__device__ __forceinline__ void outlier_correction(const ForceParams<float>& p, float x, float y, float z, float& sx, float& sy,
+                                                   float& sz)
+{
+    float cx = 0.f, cy = 0.f, cz = 0.f;
+    for (int k = 0; k < p.n_outliers; ++k) {
+        const MassOutlier o = p.outliers[k];
+        const float dx = p.pos_cur[pm_index<float>(o.index, 0)] - x;
+        const float dy = p.pos_cur[pm_index<float>(o.index, 1)] - y;
+        const float dz = p.pos_cur[pm_index<float>(o.index, 2)] - z;
+        float r2 = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, p.eps2)));
+        if (ZERO_SOFT) r2 = fmaxf(r2, 1e-20f);
+        const float inv = rsqrt_approx(r2);
+        const float w = inv * (inv * inv);  // the self pair (an exception's own row) is w * 0 = 0 whatever dm is
+        cx = fmaf(o.dm, w * dx, cx);
+        cy = fmaf(o.dm, w * dy, cy);
+        cz = fmaf(o.dm, w * dz, cz);
+    }
+    sx = fmaf(sx, p.bulk_mass, cx);
+    sy = fmaf(sy, p.bulk_mass, cy);
+    sz = fmaf(sz, p.bulk_mass, cz);
+}
+
 template <int R, bool ZERO_SOFT, int U, bool NEAR, bool UNIFORM = false>
 __device__ __forceinline__ void force_f32_body(const ForceParams<float>& p)
 {
@@ -231,6 +259,13 @@ __device__ __forceinline__ void force_f32_body(const ForceParams<float>& p)
     if (p.j_chunks == 1) {
 #pragma unroll
         for (int r = 0; r < R; ++r) {
+            if (UNIFORM && p.n_outliers > 0) {
+                float x, y, z, hi;
+                unpack2(nx[r], x, hi);
+                unpack2(ny[r], y, hi);
+                unpack2(nz[r], z, hi);
+                outlier_correction<ZERO_SOFT>(p, -x, -y, -z, sx[r], sy[r], sz[r]);
+            }
             finish_body<float>(p, il0 + size_t(r) * kF32Threads, sx[r], sy[r], sz[r], p.G);
             if (NEAR) p.near[il0 + size_t(r) * kF32Threads] = nr[r];
         }
@@ -253,6 +288,13 @@ __device__ __forceinline__ void force_f32_body(const ForceParams<float>& p)
             ty += v.y;
             tz += v.z;
             if (NEAR) tn = fmaxf(tn, v.w);
+        }
+        if (UNIFORM && p.n_outliers > 0) {
+            float x, y, z, hi;
+            unpack2(nx[r], x, hi);
+            unpack2(ny[r], y, hi);
+            unpack2(nz[r], z, hi);
+            outlier_correction<ZERO_SOFT>(p, -x, -y, -z, tx, ty, tz);
         }
         finish_body<float>(p, il, tx, ty, tz, p.G);
         if (NEAR) p.near[il] = tn;

@@ -1,11 +1,20 @@
 // fp64 all-pairs force kernel (reference-matching mode), same work decomposition
-// and TMA ring as force_f32.cuh but scalar IEEE double arithmetic in the
-// reference's own association (/root/reference/index.html:277-288):
+// and TMA ring as force_f32.cuh, scalar double arithmetic, one i-body per thread.
+// The reference's statement (/root/reference/index.html:277-288) is
 //   vec = pos_j - pos_i; distSq = (vx*vx + vy*vy) + vz*vz;
 //   f = G / pow(distSq + epsSq, 1.5);  acc_i += (f*m_j)*vec
-// with no multiply-add contraction (JS has none).  pow(s,1.5) is evaluated as
-// s*sqrt(s) with IEEE sqrt and division: <= ~1.5 ulp from the correctly
-// rounded value, i.e. ~2e-16 relative per term against a 1e-12 gate.
+// and the gate is 1e-12 norm-relative per step (north_star), four orders above double
+// rounding, so the kernel is free to pick the cheapest sequence that stays at the
+// 1e-16 level per term.  MATH selects it:
+//   0  IEEE, the reference's association, no contraction: pow(s,1.5) = s*sqrt(s) with
+//      IEEE sqrt and division (<= ~1.5 ulp per term).  33 DP-pipe instructions + 2 MUFU
+//      per interaction, two slow-path branches.  NBODY_F64_MATH=0 selects it.
+//   1  1/pow(s,1.5) = y^3 with y = rsqrt(s): MUFU.RSQ64H seed (2^-26) and one cubically
+//      convergent correction (5 DP ops, y to ~1 ulp); G applied once per body.  Everything
+//      else as in 0.  23 DP instructions + 1 MUFU, no branches.
+//   2  (default) as 1 with the multiply-adds of distSq and of the accumulation contracted
+//      (DFMA: one rounding instead of two).  17 DP instructions + 1 MUFU.
+// Per-step error against the oracle, all three: ~3e-16 (tests/test_gpu_parity.py prints it).
 // For body i with j < i the reference accumulates -(f*m_j)*(pos_i - pos_j),
 // which is bit-identical to +(f*m_j)*(pos_j - pos_i) (negation is exact), so a
 // thread that walks j upward reproduces the reference's summation order when
@@ -19,6 +28,26 @@ namespace nb {
 
 constexpr size_t force_f64_smem_bytes() { return size_t(kStages) * kTileBytes + 2 * kStages * 8; }
 
+// rsqrt(s) to ~1 ulp: e = 1 - s*y0^2 is ~2^-25 after the MUFU seed, and
+// y0 + y0*e*(1/2 + 3/8 e) leaves an O(e^3) term far below the final rounding.
+__device__ __forceinline__ double rsqrt_f64(double s)
+{
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(s));  // MUFU.RSQ64H
+    const double e = __fma_rn(s, -__dmul_rn(y, y), 1.0);
+    const double c = __fma_rn(e, 0.375, 0.5);
+    return __fma_rn(c, __dmul_rn(y, e), y);
+}
+
+#ifndef NB_F64_UNROLL
+#define NB_F64_UNROLL 4  // N=65,536: unroll 1 / 2 / 4 = 830 / 882 / 907 G interactions/s (profiles/r1e_f64_variants.jsonl)
+#endif
+constexpr int kF64Unroll = NB_F64_UNROLL;
+
+// ZERO_SOFT: softening == 0, where the self pair would be 0 * inf and is selected away (the
+// reference never evaluates it, idx:273).  With softening it contributes an exact zero by
+// itself and the select is not compiled in.
+template <int MATH, bool ZERO_SOFT>
 __global__ void __launch_bounds__(kThreads + 32) force_f64_kernel(const ForceParams<double> p)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -75,28 +104,46 @@ __global__ void __launch_bounds__(kThreads + 32) force_f64_kernel(const ForcePar
         const double4* tp = tiles + size_t(slot) * (kTileBytes / 32);
         const size_t off = size_t(t) * kTileBytes;
         const int nj = static_cast<int>((chunk_bytes - off < kTileBytes ? chunk_bytes - off : kTileBytes) / 32);
-        const size_t jg0 = j0 + off / 32;
-#pragma unroll 2
+        const long long self_d = static_cast<long long>(gi) - static_cast<long long>(j0 + off / 32);
+        const int self_q = (self_d >= 0 && self_d < nj) ? static_cast<int>(self_d) : -1;  // this body's slot in the tile
+#pragma unroll kF64Unroll
         for (int q = 0; q < nj; ++q) {
             const double4 b = tp[q];
             const double vx = __dsub_rn(b.x, me.x);
             const double vy = __dsub_rn(b.y, me.y);
             const double vz = __dsub_rn(b.z, me.z);
-            const double distSq =
-                __dadd_rn(__dadd_rn(__dmul_rn(vx, vx), __dmul_rn(vy, vy)), __dmul_rn(vz, vz));
-            const double s = __dadd_rn(distSq, p.eps2);
-            double fm = __dmul_rn(__ddiv_rn(p.G, __dmul_rn(s, __dsqrt_rn(s))), b.w);
-            if (jg0 + q == gi) fm = 0.0;  // the reference never evaluates the self pair (idx:273)
-            ax = __dadd_rn(ax, __dmul_rn(fm, vx));
-            ay = __dadd_rn(ay, __dmul_rn(fm, vy));
-            az = __dadd_rn(az, __dmul_rn(fm, vz));
+            double s;
+            if (MATH == 2) {
+                s = __fma_rn(vz, vz, __fma_rn(vy, vy, __fma_rn(vx, vx, p.eps2)));
+            } else {
+                const double distSq = __dadd_rn(__dadd_rn(__dmul_rn(vx, vx), __dmul_rn(vy, vy)), __dmul_rn(vz, vz));
+                s = __dadd_rn(distSq, p.eps2);
+            }
+            double fm;
+            if (MATH == 0) {
+                fm = __dmul_rn(__ddiv_rn(p.G, __dmul_rn(s, __dsqrt_rn(s))), b.w);
+            } else {
+                const double y = rsqrt_f64(s);
+                fm = __dmul_rn(__dmul_rn(__dmul_rn(y, y), y), b.w);  // G joins in the epilogue
+            }
+            if (ZERO_SOFT && q == self_q) fm = 0.0;
+            if (MATH == 2) {
+                ax = __fma_rn(fm, vx, ax);
+                ay = __fma_rn(fm, vy, ay);
+                az = __fma_rn(fm, vz, az);
+            } else {
+                ax = __dadd_rn(ax, __dmul_rn(fm, vx));
+                ay = __dadd_rn(ay, __dmul_rn(fm, vy));
+                az = __dadd_rn(az, __dmul_rn(fm, vz));
+            }
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[slot]);
     }
 
+    const double scale = MATH == 0 ? 1.0 : p.G;
     if (p.j_chunks == 1) {
-        finish_body<double>(p, il, ax, ay, az, 1.0);
+        finish_body<double>(p, il, ax, ay, az, scale);
         return;
     }
     double4* part = reinterpret_cast<double4*>(p.partial);
@@ -111,7 +158,7 @@ __global__ void __launch_bounds__(kThreads + 32) force_f64_kernel(const ForcePar
         ty = __dadd_rn(ty, xy.y);
         tz = __dadd_rn(tz, zw.x);
     }
-    finish_body<double>(p, il, tx, ty, tz, 1.0);
+    finish_body<double>(p, il, tx, ty, tz, scale);
     if (tid == 0) p.tile_counter[tile_i] = 0;
 }
 

@@ -55,9 +55,14 @@ __global__ void kick2_kernel(Real* vel, const Real* acc, Real* temp, size_t n_lo
 }
 
 // Host AoS (x,y,z,m)[n] staged on the device -> device pos_mass layout.  Pads are massless
-// bodies at the origin, or (pad_x != 0: the equal-mass force kernel ignores masses) bodies far away.
+// bodies parked far away at x = pad_x (1e18): the equal-mass fp32 kernel ignores masses, and a
+// pad at the origin would meet a real body there as 0 * inf when softening is 0.
+// detect != nullptr (fp32): also find the bodies whose mass is not `m0` -- detect[0] counts them
+// (a non-finite mass pushes the count past any limit) and the first kMaxOutliers found are
+// appended to `outliers` in no particular order; the host sorts them (nbody_upload).
 template <typename Real>
-__global__ void pack_pos_kernel(const Real* aos, Real* pos_a, Real* pos_b, size_t n, size_t n_pad, Real pad_x)
+__global__ void pack_pos_kernel(const Real* aos, Real* pos_a, Real* pos_b, size_t n, size_t n_pad, Real pad_x, Real m0,
+                                unsigned* detect, MassOutlier* outliers)
 {
     const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= n_pad) return;
@@ -66,6 +71,11 @@ __global__ void pack_pos_kernel(const Real* aos, Real* pos_a, Real* pos_b, size_
         const Real v = i < n ? aos[4 * i + c] : (c == 0 ? pad_x : Real(0));
         pos_a[pm_index<Real>(i, c)] = v;
         pos_b[pm_index<Real>(i, c)] = v;  // mass is constant: both buffers carry it
+        if (c == 3 && detect != nullptr && i < n && !(v == m0)) {
+            const bool finite = v - v == Real(0);
+            const unsigned k = atomicAdd(detect, finite ? 1u : unsigned(kMaxOutliers) + 1u);
+            if (finite && k < unsigned(kMaxOutliers)) outliers[k] = MassOutlier{unsigned(i), float(v - m0)};
+        }
     }
 }
 

@@ -9,6 +9,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -68,6 +69,8 @@ struct Shard {
     // headless renderer (render.cu), first shard only
     int* mat_type = nullptr;            // Body.type per body (0 rock, 1 metal, 2 ice)
     float* mat_seed = nullptr;          // the `seed` uniform of each body's material (idx:492)
+    MassOutlier* outliers = nullptr;    // fp32: bodies whose mass differs from the common one (force_f32.cuh)
+    unsigned* outlier_count = nullptr;  // how many pack_pos_kernel found
     void* temp_full = nullptr;          // all temperatures gathered on this device (multi-GPU contexts)
     RenderScratch render_scratch;
     float4* image = nullptr;
@@ -105,6 +108,9 @@ struct nbody_ctx {
     bool has_temp = false;
     bool uniform = false;           // fp32: every uploaded mass is the same value -> the 11-op force kernel
     double uniform_mass = 0.0;
+    int f64_math = 2;               // NBODY_F64_MATH at create
+    bool detect_masses = false;     // upload in flight: pack_pos_kernel compares every mass with uniform_mass
+    std::vector<MassOutlier> outliers;  // ... except these few (at most kMaxOutliers), corrected per i-body
     bool has_radius = false;        // nbody_set_radius was called for the current body list
     bool near_valid = false;        // Shard::near describes the CURRENT positions (last launch was a NEAR force pass)
     double near_eps2 = 0.0;         // softening^2 of that pass
@@ -189,7 +195,10 @@ size_t pad_unit(const nbody_ctx* c)
 void choose_chunks(nbody_ctx* c)
 {
     const size_t tiles = (c->n_j + c->i_tile - 1) / c->i_tile;
-    const size_t want_units = size_t(env_int("NBODY_WANT_UNITS", 148 * 3 * 256));
+    // fp64: an interaction costs ~8x the fp32 one, so far fewer units already balance the SMs, and each
+    // unit amortises its ring start-up and its share of the partial-sum pass over more j
+    // (N=16,384: 256 chunks of 64 bodies 374 us/step, 86 chunks of 192 bodies 332 us; profiles/r1e_f64_sweep.jsonl)
+    const size_t want_units = size_t(env_int("NBODY_WANT_UNITS", c->prec == NBODY_F64 ? 148 * 3 * 16 : 148 * 3 * 256));
     const size_t max_chunks = c->n_j / c->j_unit;
     size_t len;
     const int forced = env_int("NBODY_CHUNK_LEN", 0);
@@ -229,6 +238,8 @@ int alloc_shard(nbody_ctx* c, Shard& s)
     s.energy_rows = (local_cap + kEnergyThreads - 1) / kEnergyThreads + 1;
     CU(c, cudaMalloc(&s.energy_out, s.energy_rows * 5 * sizeof(double)));
     CU(c, cudaMalloc(&s.radius, c->cap_pad * c->esz));
+    CU(c, cudaMalloc(&s.outliers, kMaxOutliers * sizeof(MassOutlier)));
+    CU(c, cudaMalloc(&s.outlier_count, sizeof(unsigned)));
     CU(c, cudaMalloc(&s.near, local_cap * sizeof(float)));
     CU(c, cudaMalloc(&s.cand, local_cap * sizeof(unsigned)));
     CU(c, cudaMalloc(&s.cand_count, sizeof(unsigned)));
@@ -250,7 +261,12 @@ int set_kernel_attrs(nbody_ctx* c)
     CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
-    CU(c, cudaFuncSetAttribute(force_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
+    CU(c, cudaFuncSetAttribute(force_f64_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
+    CU(c, cudaFuncSetAttribute(force_f64_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
+    CU(c, cudaFuncSetAttribute(force_f64_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
+    CU(c, cudaFuncSetAttribute(force_f64_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
+    CU(c, cudaFuncSetAttribute(force_f64_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
+    CU(c, cudaFuncSetAttribute(force_f64_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
     return NBODY_OK;
 }
 
@@ -273,6 +289,7 @@ int create_common(nbody_ctx** out, nbody_prec prec, int world, size_t capacity, 
         c->R = 1;
         c->i_tile = kThreads;
         c->j_unit = kJUnitF64;
+        c->f64_math = env_int("NBODY_F64_MATH", 2);
     }
     c->cap_pad = round_up(capacity, pad_unit(c));
     *made = c;
@@ -344,6 +361,8 @@ extern "C" void nbody_destroy(nbody_ctx* c)
         cudaFree(s.ribbons);
         cudaFree(s.mat_type);
         cudaFree(s.mat_seed);
+        cudaFree(s.outliers);
+        cudaFree(s.outlier_count);
         cudaFree(s.temp_full);
         render_scratch_free(s.render_scratch);
         cudaFree(s.image);
@@ -572,7 +591,7 @@ extern "C" int nbody_get_info(nbody_ctx* c, nbody_info* o)
     o->i_tile = c->i_tile;
     o->kernel_launches = c->launches;
     o->exchange = c->world == 1 ? 0 : (c->p2p ? 2 : 1);
-    o->uniform_mass = c->uniform ? 1 : 0;
+    o->uniform_mass = c->uniform ? 1 + int(c->outliers.size()) : 0;
     return NBODY_OK;
 }
 
@@ -594,8 +613,11 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
         // positions + masses: host AoS -> staging -> device layout (both buffers)
         CU(c, cudaMemcpyAsync(s.stage, pm, n * v4, cudaMemcpyHostToDevice, s.stream));
         const unsigned blocks = unsigned((c->n_pad + 255) / 256);
+        const bool detect = c->detect_masses && &s == &c->shards[0];  // every shard packs the same array: one looks
+        if (detect) CU(c, cudaMemsetAsync(s.outlier_count, 0, sizeof(unsigned), s.stream));
         pack_pos_kernel<Real><<<blocks, 256, 0, s.stream>>>(static_cast<const Real*>(s.stage), static_cast<Real*>(s.pos[0]),
-                                                           static_cast<Real*>(s.pos[1]), n, c->n_pad, c->uniform ? Real(1e18) : Real(0));
+                                                           static_cast<Real*>(s.pos[1]), n, c->n_pad, Real(1e18), Real(c->uniform_mass),
+                                                           detect ? s.outlier_count : nullptr, s.outliers);
         c->launches++;
         CU(c, cudaGetLastError());
         CU(c, cudaMemsetAsync(s.vel, 0, s.n_local * v4, s.stream));
@@ -653,6 +675,29 @@ template <typename Real> int download_t(nbody_ctx* c, Real* pm, Real* vel, Real*
     return check_exchange(c);
 }
 
+// After upload_t's final synchronise: what pack_pos_kernel found.  Up to kMaxOutliers exceptions keep
+// the equal-mass sweep (they are corrected per i-body); the list is sorted so that the order of the
+// corrections, and with it every bit of the result, does not depend on the order the atomics landed in.
+int finish_mass_detection(nbody_ctx* c)
+{
+    Shard& s0 = c->shards[0];
+    CU(c, cudaSetDevice(s0.device));
+    unsigned count = 0;
+    CU(c, cudaMemcpy(&count, s0.outlier_count, sizeof(unsigned), cudaMemcpyDeviceToHost));
+    const size_t max_out = std::min<size_t>(size_t(std::max(0, env_int("NBODY_OUTLIERS", kMaxOutliers))), kMaxOutliers);
+    if (count > max_out) return NBODY_OK;  // too many different masses: the general kernel
+    c->uniform = true;
+    if (count == 0) return NBODY_OK;
+    c->outliers.resize(count);
+    CU(c, cudaMemcpy(c->outliers.data(), s0.outliers, count * sizeof(MassOutlier), cudaMemcpyDeviceToHost));
+    std::sort(c->outliers.begin(), c->outliers.end(), [](const MassOutlier& a, const MassOutlier& b) { return a.index < b.index; });
+    for (Shard& s : c->shards) {
+        CU(c, cudaSetDevice(s.device));
+        CU(c, cudaMemcpy(s.outliers, c->outliers.data(), count * sizeof(MassOutlier), cudaMemcpyHostToDevice));
+    }
+    return NBODY_OK;
+}
+
 }  // namespace
 
 extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const void* vel, const void* acc, const void* temp)
@@ -666,22 +711,34 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     c->cur = 0;
     c->has_temp = temp != nullptr;
     c->uniform = false;
+    c->outliers.clear();
+    c->detect_masses = false;
     if (c->prec == NBODY_F32 && c->R == 4 && env_int("NBODY_UNIFORM", 1) != 0) {
+        // Equal-mass sweep (force_f32.cuh, UNIFORM): the mass most bodies share, if there is one, by
+        // majority vote over an evenly spaced sample; pack_pos_kernel then compares every mass with it.
         const float* pm = static_cast<const float*>(pos_mass);
-        const float m0 = pm[3];
-        bool same = m0 > 0.0f;
-        for (size_t i = 1; same && i < n; ++i) same = pm[4 * i + 3] == m0;
-        c->uniform = same;
+        const size_t samples = std::min<size_t>(n, 1024);
+        float m0 = pm[3];
+        size_t votes = 0;
+        for (size_t k = 0; k < samples; ++k) {
+            const float m = pm[4 * (k * n / samples) + 3];
+            if (votes == 0) m0 = m;
+            votes += (m == m0) ? 1 : size_t(-1);
+        }
         c->uniform_mass = m0;
+        c->detect_masses = m0 > 0.0f && std::isfinite(m0);
     }
     c->has_radius = false;  // a new body list: radii must be set again (Body.radius follows mass, idx:221)
     if (c->hist_n != n) c->hist_n = 0;  // history ring: refilled at the next push (trails.cuh)
     c->has_materials = false;
     c->near_valid = false;
     choose_chunks(c);
-    return c->prec == NBODY_F32
-               ? upload_t<float>(c, n, (const float*)pos_mass, (const float*)vel, (const float*)acc, (const float*)temp)
-               : upload_t<double>(c, n, (const double*)pos_mass, (const double*)vel, (const double*)acc, (const double*)temp);
+    int rc = c->prec == NBODY_F32
+                 ? upload_t<float>(c, n, (const float*)pos_mass, (const float*)vel, (const float*)acc, (const float*)temp)
+                 : upload_t<double>(c, n, (const double*)pos_mass, (const double*)vel, (const double*)acc, (const double*)temp);
+    if (rc == NBODY_OK && c->detect_masses) rc = finish_mass_detection(c);
+    c->detect_masses = false;
+    return rc;
 }
 
 extern "C" int nbody_download(nbody_ctx* c, void* pos_mass, void* vel, void* acc, void* temp)
@@ -779,6 +836,9 @@ template <typename Real> ForceParams<Real> make_params(nbody_ctx* c, Shard& s, i
     p.partial = static_cast<Real*>(s.partial);
     p.temp = c->has_temp ? static_cast<Real*>(s.temp) : nullptr;
     p.near = reinterpret_cast<Real*>(s.near);  // written by the fp32 NEAR kernels only
+    p.outliers = s.outliers;
+    p.n_outliers = 0;
+    p.bulk_mass = Real(0);
     p.tile_counter = s.counters;
     p.n_j = c->n_j;
     p.i_begin = s.i_begin;
@@ -824,7 +884,12 @@ int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
         if (c->prec == NBODY_F32) {
             ForceParams<float> p = make_params<float>(c, s, mode, dt, G, eps);
             const bool uniform = c->uniform;
-            if (uniform) p.G = float(G) * float(c->uniform_mass);  // equal masses: the common m joins G (force_f32.cuh, UNIFORM)
+            if (uniform && c->outliers.empty()) {
+                p.G = float(G) * float(c->uniform_mass);  // equal masses: the common m joins G (force_f32.cuh, UNIFORM)
+            } else if (uniform) {
+                p.n_outliers = int(c->outliers.size());   // ... but for a few bodies, corrected per i-body
+                p.bulk_mass = float(c->uniform_mass);
+            }
             const size_t sm = force_f32_smem_bytes();
             const bool z = (eps == 0.0);
             const dim3 blk(kF32Threads + 32);
@@ -846,7 +911,22 @@ int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
             }
         } else {
             const ForceParams<double> p = make_params<double>(c, s, mode, dt, G, eps);
-            force_f64_kernel<<<grid, kThreads + 32, force_f64_smem_bytes(), s.stream>>>(p);
+            const dim3 blk(kThreads + 32);
+            const size_t sm = force_f64_smem_bytes();
+            switch (c->f64_math) {  // force_f64.cuh: 0 IEEE sqrt/div in the reference's association, 1 rsqrt^3, 2 rsqrt^3 + DFMA
+            case 0:
+                if (eps == 0.0) force_f64_kernel<0, true><<<grid, blk, sm, s.stream>>>(p);
+                else force_f64_kernel<0, false><<<grid, blk, sm, s.stream>>>(p);
+                break;
+            case 1:
+                if (eps == 0.0) force_f64_kernel<1, true><<<grid, blk, sm, s.stream>>>(p);
+                else force_f64_kernel<1, false><<<grid, blk, sm, s.stream>>>(p);
+                break;
+            default:
+                if (eps == 0.0) force_f64_kernel<2, true><<<grid, blk, sm, s.stream>>>(p);
+                else force_f64_kernel<2, false><<<grid, blk, sm, s.stream>>>(p);
+                break;
+            }
         }
         c->launches++;
         CU(c, cudaGetLastError());

@@ -114,3 +114,41 @@ def test_multi_gpu_ragged_and_split_api(nb, oracle):
             e.kick2(s.dt, 0.0)
         o = e.download()
     assert norm_rel_err(o["pos_mass"], p) < 1e-12 and norm_rel_err(o["vel"], v) < 1e-12 and norm_rel_err(o["acc"], a) < 1e-12
+
+
+def test_f32_1m_contacts_flagged_equals_full_scan_and_sampled_rows(nb):
+    """Collision broad phase at config 4's full size (N=1,048,576, radii inflated until the
+    cube has a few thousand contacts).  Size-independent properties: the list from the force
+    sweep's nearest-neighbour flags equals the list from scanning every body; it is sorted
+    (i ascending, then j) with i < j; and the rows of sampled bodies equal an O(k*N) restatement
+    of the overlap test of resolveCollisions (idx:301-313) in float64 on the stored fp32 state."""
+    s = nb.scenes.uniform_cube(1048576)
+    pm, vel, _ = s.astype(np.float32)
+    n = s.n
+    rad = np.full(n, 0.02, np.float32)
+    rad[:: 4099] = 0.05                                           # ragged radii, none dominant
+    with nb.Engine(n, precision="f32") as e:
+        e.upload(pm, vel)
+        e.set_radius(rad)
+        e.force(s.G, s.softening)
+        flagged = e.contacts(0.0)
+        st = e.contact_stats()
+        assert st["used_flags"] and st["flagged"] < n // 8
+        e.set_radius(rad)                                         # drops the flags
+        full = e.contacts(0.0)
+        assert not e.contact_stats()["used_flags"]
+    assert len(full) > 1000
+    assert np.array_equal(flagged, full)
+    key = full[:, 0].astype(np.uint64) * np.uint64(n) + full[:, 1].astype(np.uint64)
+    assert (full[:, 0] < full[:, 1]).all() and (np.diff(key.astype(np.int64)) > 0).all()
+    # sampled rows: every body named in the first contacts plus random ones
+    rng = np.random.default_rng(8)
+    rows = np.unique(np.concatenate([full[:40, 0], full[-40:, 0], rng.integers(0, n, 120)]))
+    p64, r64 = pm[:, :3].astype(np.float64), rad.astype(np.float64)
+    for i in rows:
+        d = p64[i + 1:] - p64[i]
+        d2 = (d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]) + d[:, 2] * d[:, 2]
+        rs = r64[i] + r64[i + 1:]
+        ref_j = np.nonzero(d2 < rs * rs)[0] + i + 1               # distSq < minDist * minDist, idx:309-313
+        got_j = full[full[:, 0] == i, 1]
+        assert np.array_equal(got_j, ref_j), i

@@ -101,6 +101,29 @@ def test_f64_golden_fixtures(nb, name):
     np.testing.assert_array_equal(out["temp"], g["temp"])
 
 
+@pytest.mark.parametrize("math", [0, 1, 2])
+@pytest.mark.parametrize("eps", [0.5, 0.0])
+def test_f64_math_variants(nb, oracle, math, eps):
+    """The three arithmetic variants of the fp64 force kernel (csrc/force_f64.cuh; 2 is the
+    default, NBODY_F64_MATH selects): each within the 1e-12 gate of the oracle, with and
+    without softening, ragged N (pads in the j range), one body exactly at the origin."""
+    s = nb.scenes.plummer(3001)
+    pm = s.pos_mass.copy()
+    pm[17, :3] = 0.0
+    ref = oracle.compute_gravity(pm, s.G, eps, mt=True)
+    os.environ["NBODY_F64_MATH"] = str(math)
+    try:
+        with nb.Engine(s.n, precision="f64") as e:
+            e.upload(pm, s.vel)
+            e.force(s.G, eps)
+            acc = e.download()["acc"]
+    finally:
+        del os.environ["NBODY_F64_MATH"]
+    err = norm_rel_err(acc, ref)
+    print(f"f64 math={math} eps={eps}: force norm-rel err {err:.3e}")
+    assert np.isfinite(acc).all() and err < F64_GATE
+
+
 # ---------------------------------------------------------------- fp32 -----------
 # fp32 per-step tolerances (norm-relative): the rsqrt approximation (2 ulp) and fp32
 # accumulation give acc ~1e-6; pos/vel after ONE step from identical state are far tighter.
@@ -270,7 +293,7 @@ def test_physics_system_mirror(nb, oracle):
 def test_f32_uniform_mass_kernel(nb, oracle, n, eps):
     """Equal masses (BASELINE configs 4, 5): the fp32 kernel drops the per-pair mass multiply and
     parks the pad bodies at 1e18.  Same tolerance as the general kernel; NBODY_UNIFORM=0 and a
-    scene with one different mass take the general kernel and agree with it to rounding."""
+    scene with many different masses take the general kernel and agree with it to rounding."""
     rng = np.random.default_rng(n)
     pm = np.concatenate([rng.uniform(-10, 10, (n, 3)), np.full((n, 1), 1.0 / n)], axis=1).astype(np.float32)
     vel = np.zeros((n, 4), np.float32)
@@ -285,6 +308,9 @@ def test_f32_uniform_mass_kernel(nb, oracle, n, eps):
         ke_u = e.energy(1.0, eps)
         pm2 = pm.copy()
         pm2[n // 2, 3] *= 1.5
+        e.upload(pm2, vel)
+        assert e.info()["uniform_mass"] == 2                    # one exception: still the equal-mass sweep (next test)
+        pm2[: n // 4, 3] *= np.linspace(1.1, 2.0, n // 4, dtype=np.float32)
         e.upload(pm2, vel)
         assert e.info()["uniform_mass"] == 0
     assert norm_rel_err(acc_u, ref) < 2e-5
@@ -304,3 +330,51 @@ def test_f32_uniform_mass_kernel(nb, oracle, n, eps):
     assert norm_rel_err(out_u["pos_mass"], out_g["pos_mass"]) < 1e-6
     assert np.isfinite(out_u["vel"]).all()
     assert abs(ke_u[0] - ke_g[0]) <= 1e-4 * abs(ke_g[0]) + 1e-12 and abs(ke_u[1] - ke_g[1]) <= 1e-5 * abs(ke_g[1])
+
+
+@pytest.mark.parametrize("n,eps,k", [(4096, 0.5, 2), (5000, 0.05, 64), (3000, 0.0, 7)])
+def test_f32_uniform_mass_with_outliers(nb, oracle, n, eps, k):
+    """Config 3's shape: all bodies share one mass except a few (the two mass-500 centres).  The
+    equal-mass sweep runs and every body gets sum_k (m_k - m0) * kernel(i, k) added before the
+    integrator.  Same tolerance against the oracle as the general kernel, which it must also
+    match to rounding; body 0 being an exception must not confuse the majority vote."""
+    rng = np.random.default_rng(n + k)
+    pm = np.concatenate([rng.uniform(-10, 10, (n, 3)), np.full((n, 1), 50.0 / n)], axis=1).astype(np.float32)
+    out_idx = np.concatenate([[0], rng.choice(np.arange(1, n), k - 1, replace=False)])
+    pm[out_idx, 3] = rng.uniform(0.0, 500.0, k).astype(np.float32)
+    pm[out_idx[-1], 3] = 0.0                                    # a massless exception: pulls nothing
+    vel = np.zeros((n, 4), np.float32)
+    vel[:, :3] = rng.normal(0, 0.3, (n, 3))
+    ref = oracle.compute_gravity(pm.astype(np.float64), 0.5, eps, mt=True)
+    with nb.Engine(n, precision="f32") as e:
+        e.upload(pm, vel)
+        assert e.info()["uniform_mass"] == 1 + k
+        e.force(0.5, eps)
+        acc_u = e.download()["acc"]
+        e.step(0.004, 0.5, eps, 5)
+        out_u = e.download()
+        pm65 = pm.copy()
+        pm65[rng.choice(np.setdiff1d(np.arange(n), out_idx), 65 - k, replace=False), 3] *= 3.0
+        e.upload(pm65, vel)
+        assert e.info()["uniform_mass"] == 0                    # more than 64 exceptions: the general kernel
+    assert norm_rel_err(acc_u, ref) < 2e-5
+    os.environ["NBODY_UNIFORM"] = "0"
+    try:
+        with nb.Engine(n, precision="f32") as e:
+            e.upload(pm, vel)
+            e.force(0.5, eps)
+            acc_g = e.download()["acc"]
+            e.step(0.004, 0.5, eps, 5)
+            out_g = e.download()
+    finally:
+        del os.environ["NBODY_UNIFORM"]
+    assert norm_rel_err(acc_u, acc_g) < 2e-6
+    # 5 steps among masses up to 500 at small eps amplify last-bit differences, so the two
+    # kernels are each held to the fp64 oracle's step: the corrected sweep may not be worse
+    acc0 = np.zeros((n, 4))
+    acc0[:, :3] = acc_u[:, :3]                                  # the step starts from the force pass above
+    pm_r, vel_r, _, _ = oracle.integrate(pm.astype(np.float64), vel.astype(np.float64), acc0, None, 0.004, 0.5, eps, nsteps=5)
+    err_u = norm_rel_err(out_u["vel"], vel_r), norm_rel_err(out_u["pos_mass"], pm_r)
+    err_g = norm_rel_err(out_g["vel"], vel_r), norm_rel_err(out_g["pos_mass"], pm_r)
+    print(f"outliers k={k}: vel err corrected {err_u[0]:.2e} general {err_g[0]:.2e}; pos {err_u[1]:.2e} / {err_g[1]:.2e}")
+    assert err_u[0] < max(2e-5, 2 * err_g[0]) and err_u[1] < max(1e-6, 2 * err_g[1])
