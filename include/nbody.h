@@ -156,6 +156,14 @@ NBODY_API int nbody_history_enable(nbody_ctx* ctx, int depth);
  * oldest (idx:564-565).  Asynchronous on the context's stream. */
 NBODY_API int nbody_history_push(nbody_ctx* ctx);
 
+/* The body list changed (merge, fracture, spawn: idx:383-389, 835) and was uploaded again, but a
+ * Body object carries its history with it: body i of the current list continues the ring of
+ * body source[i] of the list the ring was last pushed for; source[i] < 0 marks a body the
+ * renderer has not seen, whose ring the next push fills with its position (idx:540).  Without
+ * this call an upload that changes n starts every ring over.  Reads of the history are refused
+ * between a remap and the next push. */
+NBODY_API int nbody_history_remap(nbody_ctx* ctx, const int* source);
+
 /* out[n][depth][3] (context precision) = Body.history of every body, newest first. */
 NBODY_API int nbody_history_download(nbody_ctx* ctx, void* out);
 

@@ -26,7 +26,7 @@ SYMBOLS = (
     "nbody_strerror", "nbody_version", "nbody_device_count", "nbody_set_stream",
     "nbody_enable_timing", "nbody_read_timing", "nbody_get_info",
     "nbody_set_radius", "nbody_contacts", "nbody_contact_stats",
-    "nbody_history_enable", "nbody_history_push", "nbody_history_download", "nbody_trail_ribbons",
+    "nbody_history_enable", "nbody_history_push", "nbody_history_remap", "nbody_history_download", "nbody_trail_ribbons",
     "nbody_snapshot_save", "nbody_snapshot_load", "nbody_set_materials", "nbody_render",
 )
 
@@ -100,6 +100,7 @@ def lib() -> ctypes.CDLL:
     L.nbody_contact_stats.argtypes = [vp, ctypes.POINTER(ctypes.c_longlong)]
     L.nbody_history_enable.argtypes = [vp, i]
     L.nbody_history_push.argtypes = [vp]
+    L.nbody_history_remap.argtypes = [vp, vp]
     L.nbody_history_download.argtypes = [vp, vp]
     L.nbody_trail_ribbons.argtypes = [vp, pd, vp]
     L.nbody_set_materials.argtypes = [vp, vp, vp]

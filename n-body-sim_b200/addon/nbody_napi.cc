@@ -19,6 +19,7 @@
 //   contacts(ctx, margin, pairs: Uint32Array) -> count     overlap search of resolveCollisions, idx:301-313;
 //                                                          count > pairs.length/2: nothing written, call again
 //   historyEnable(ctx, depth) / historyPush(ctx) / historyDownload(ctx, out)      Body.history, idx:540, 564-565
+//   historyRemap(ctx, source: Int32Array[n])               after a list change: body i continues row source[i] (-1: new body)
 //   trailRibbons(ctx, camX, camY, camZ, out: Float32Array)  ribbon vertices, idx:567-592
 //   snapshotSave(ctx, path, step, dt, G, softening) / snapshotLoad(ctx, path) -> {step, dt, G, softening}
 //   setMaterials(ctx, type: Int32Array|null, seed: Float32Array|null)   Body.type and the material seed, idx:70-74, 492
@@ -408,6 +409,24 @@ napi_value HistoryPush(napi_env env, napi_callback_info info)  // history.unshif
     return rc == NBODY_OK ? undefined(env) : fail(env, "historyPush", rc, h->ctx);
 }
 
+napi_value HistoryRemap(napi_env env, napi_callback_info info)  // Body objects carry their history through list changes
+{
+    Args a;
+    if (!get_args(env, info, a, 2, "historyRemap")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "historyRemap");
+    if (!h) return undefined(env);
+    nbody_info inf;
+    nbody_get_info(h->ctx, &inf);
+    void* p = nullptr;
+    size_t len = 0;
+    if (!get_typed(env, a.v[1], napi_int32_array, &p, &len) || len < inf.n) {
+        napi_throw_error(env, "NBODY", "nbody.historyRemap(ctx, source: Int32Array[n])");
+        return undefined(env);
+    }
+    const int rc = nbody_history_remap(h->ctx, static_cast<const int*>(p));
+    return rc == NBODY_OK ? undefined(env) : fail(env, "historyRemap", rc, h->ctx);
+}
+
 napi_value HistoryDownload(napi_env env, napi_callback_info info)
 {
     Args a;
@@ -537,6 +556,7 @@ extern "C" __attribute__((visibility("default"))) napi_value napi_register_modul
         {"setHeatDecay", SetHeatDecay}, {"energy", Energy}, {"sync", Sync}, {"info", Info},
         {"version", Version}, {"deviceCount", DeviceCount},
         {"setRadius", SetRadius}, {"contacts", Contacts}, {"historyEnable", HistoryEnable}, {"historyPush", HistoryPush},
+        {"historyRemap", HistoryRemap},
         {"historyDownload", HistoryDownload}, {"trailRibbons", TrailRibbons}, {"snapshotSave", SnapshotSave},
         {"snapshotLoad", SnapshotLoad}, {"setMaterials", SetMaterials}, {"render", Render}};
     for (const auto& f : fns) {

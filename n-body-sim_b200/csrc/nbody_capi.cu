@@ -64,6 +64,8 @@ struct Shard {
     unsigned long long* pair_count = nullptr;
     // position history ring (trails.cuh), first shard only: every shard holds all positions
     void* hist = nullptr;               // Real4 [depth][hist_stride]
+    void* hist_alt = nullptr;           // second ring, the target of nbody_history_remap (the two swap)
+    int* hist_src = nullptr;            // source index per body of the last remap (< 0: new to the ring)
     float* ribbons = nullptr;           // float [n][depth][6] staging for nbody_trail_ribbons
     size_t ribbons_bytes = 0;
     // headless renderer (render.cu), first shard only
@@ -119,6 +121,8 @@ struct nbody_ctx {
     double r_small_max = 0.0;       // largest radius that is not big
     long long cstat[4] = {0, 0, 0, 0};  // last nbody_contacts: flagged, scanned, pairs, used_flags
     int hist_depth = 0;             // 0: no ring
+    size_t hist_prev_n = 0;         // an upload changed n: the count the ring still describes, until the next push or remap
+    bool hist_fresh_pending = false;  // a remap left rows of new bodies for the next push to fill
     size_t hist_stride = 0;         // bodies per slot (= cap_pad)
     size_t hist_n = 0;              // body count the ring was filled for (0: refill on the next push)
     int hist_head = 0;              // slot of the newest sample
@@ -358,6 +362,8 @@ extern "C" void nbody_destroy(nbody_ctx* c)
         cudaFree(s.pairs);
         cudaFree(s.pair_count);
         cudaFree(s.hist);
+        cudaFree(s.hist_alt);
+        cudaFree(s.hist_src);
         cudaFree(s.ribbons);
         cudaFree(s.mat_type);
         cudaFree(s.mat_seed);
@@ -729,7 +735,10 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
         c->detect_masses = m0 > 0.0f && std::isfinite(m0);
     }
     c->has_radius = false;  // a new body list: radii must be set again (Body.radius follows mass, idx:221)
-    if (c->hist_n != n) c->hist_n = 0;  // history ring: refilled at the next push (trails.cuh)
+    if (c->hist_n != n) {  // history ring: refilled at the next push (trails.cuh) unless nbody_history_remap carries it over
+        if (c->hist_n) c->hist_prev_n = c->hist_n;  // kept over further uploads: the ring itself is not touched
+        c->hist_n = 0;
+    }
     c->has_materials = false;
     c->near_valid = false;
     choose_chunks(c);
@@ -1294,9 +1303,11 @@ extern "C" int nbody_history_enable(nbody_ctx* c, int depth)
     CU(c, cudaSetDevice(s.device));
     CU(c, cudaStreamSynchronize(s.stream));
     cudaFree(s.hist);
-    s.hist = nullptr;
+    cudaFree(s.hist_alt);
+    s.hist = s.hist_alt = nullptr;
     c->hist_depth = 0;
-    c->hist_n = 0;
+    c->hist_n = c->hist_prev_n = 0;
+    c->hist_fresh_pending = false;
     c->hist_head = 0;
     if (depth == 0) return NBODY_OK;
     c->hist_stride = c->cap_pad;
@@ -1316,18 +1327,52 @@ extern "C" int nbody_history_push(nbody_ctx* c)
     Shard& s = c->shards[0];
     CU(c, cudaSetDevice(s.device));
     const int fill = c->hist_n != c->n;
+    const int* fresh = (!fill && c->hist_fresh_pending) ? s.hist_src : nullptr;  // bodies new to a remapped ring
+    c->hist_fresh_pending = false;
+    c->hist_prev_n = 0;
     if (fill) c->hist_head = 0;
     else c->hist_head = (c->hist_head + c->hist_depth - 1) % c->hist_depth;  // unshift: the newest sample moves one slot back
     const unsigned blocks = unsigned((c->n + 255) / 256);
     if (c->prec == NBODY_F32)
         history_push_kernel<float><<<blocks, 256, 0, s.stream>>>((const float*)s.pos[c->cur], (float4*)s.hist, c->n, c->hist_stride, c->hist_head,
-                                                                 c->hist_depth, fill);
+                                                                 c->hist_depth, fill, fresh);
     else
         history_push_kernel<double><<<blocks, 256, 0, s.stream>>>((const double*)s.pos[c->cur], (double4*)s.hist, c->n, c->hist_stride, c->hist_head,
-                                                                  c->hist_depth, fill);
+                                                                  c->hist_depth, fill, fresh);
     c->launches++;
     CU(c, cudaGetLastError());
     c->hist_n = c->n;
+    return NBODY_OK;
+}
+
+extern "C" int nbody_history_remap(nbody_ctx* c, const int* source)
+{
+    int rc = check_ready(c, "history_remap");
+    if (rc != NBODY_OK) return rc;
+    if (!source) return fail(c, NBODY_EINVAL, "history_remap: source is NULL");
+    const size_t old_n = c->hist_n ? c->hist_n : c->hist_prev_n;  // the list the ring was last pushed for
+    if (c->hist_depth == 0 || old_n == 0) return fail(c, NBODY_EINVAL, "history_remap: no history to carry over (enable, then push)");
+    for (size_t i = 0; i < c->n; ++i)
+        if (source[i] >= 0 && size_t(source[i]) >= old_n)
+            return fail(c, NBODY_EINVAL, "history_remap: source[%zu]=%d outside the previous list of %zu bodies", i, source[i], old_n);
+    Shard& s = c->shards[0];
+    CU(c, cudaSetDevice(s.device));
+    const size_t ring_bytes = size_t(c->hist_depth) * c->hist_stride * 4 * c->esz;
+    if (!s.hist_alt) CU(c, cudaMalloc(&s.hist_alt, ring_bytes));
+    if (!s.hist_src) CU(c, cudaMalloc(&s.hist_src, c->cap_pad * sizeof(int)));
+    CU(c, cudaMemcpyAsync(s.hist_src, source, c->n * sizeof(int), cudaMemcpyHostToDevice, s.stream));
+    const unsigned blocks = unsigned((c->n + 255) / 256);
+    if (c->prec == NBODY_F32)
+        history_remap_kernel<float><<<blocks, 256, 0, s.stream>>>((const float4*)s.hist, (float4*)s.hist_alt, s.hist_src, c->n, c->hist_stride, c->hist_depth);
+    else
+        history_remap_kernel<double><<<blocks, 256, 0, s.stream>>>((const double4*)s.hist, (double4*)s.hist_alt, s.hist_src, c->n, c->hist_stride, c->hist_depth);
+    c->launches++;
+    CU(c, cudaGetLastError());
+    CU(c, cudaStreamSynchronize(s.stream));  // `source` is borrowed for the call only
+    std::swap(s.hist, s.hist_alt);
+    c->hist_n = c->n;
+    c->hist_prev_n = 0;
+    c->hist_fresh_pending = true;
     return NBODY_OK;
 }
 
@@ -1336,7 +1381,8 @@ int history_ready(nbody_ctx* c, const char* what)
 {
     int rc = check_ready(c, what);
     if (rc != NBODY_OK) return rc;
-    if (c->hist_depth == 0 || c->hist_n != c->n) return fail(c, NBODY_EINVAL, "%s: no history for the current body list (enable, then push)", what);
+    if (c->hist_depth == 0 || c->hist_n != c->n || c->hist_fresh_pending)
+        return fail(c, NBODY_EINVAL, "%s: no history for the current body list (enable, then push)", what);
     return NBODY_OK;
 }
 }  // namespace

@@ -19,10 +19,11 @@
 namespace nb {
 
 // body.history.unshift(body.pos.clone()) for every body (idx:564); fill_all: a body seen
-// for the first time gets trailLength copies of its position (idx:540).
+// for the first time gets trailLength copies of its position (idx:540).  `source` (nullable,
+// history_remap_kernel below): bodies with source[i] < 0 are new to the ring and are filled alone.
 template <typename Real>
 __global__ void history_push_kernel(const Real* pos, typename Vec4<Real>::type* hist, size_t n, size_t stride,
-                                    int slot, int depth, int fill_all)
+                                    int slot, int depth, int fill_all, const int* source)
 {
     using V4 = typename Vec4<Real>::type;
     const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -32,11 +33,26 @@ __global__ void history_push_kernel(const Real* pos, typename Vec4<Real>::type* 
     v.y = pos[pm_index<Real>(i, 1)];
     v.z = pos[pm_index<Real>(i, 2)];
     v.w = Real(0);
-    if (fill_all) {
+    if (fill_all || (source != nullptr && source[i] < 0)) {
         for (int s = 0; s < depth; ++s) hist[size_t(s) * stride + i] = v;
     } else {
         hist[size_t(slot) * stride + i] = v;
     }
+}
+
+// The body list changed (merge, fracture, spawn; idx:383-389, 835) but Body objects carry their
+// history with them: body i of the new list continues the ring of body source[i] of the old one.
+// Slots keep their meaning (same head), so this is one gather per slot; rows of new bodies
+// (source < 0) are left for the next push to fill.
+template <typename Real>
+__global__ void history_remap_kernel(const typename Vec4<Real>::type* from, typename Vec4<Real>::type* to, const int* source,
+                                     size_t n, size_t stride, int depth)
+{
+    const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int src = source[i];
+    if (src < 0) return;
+    for (int s = 0; s < depth; ++s) to[size_t(s) * stride + i] = from[size_t(s) * stride + size_t(src)];
 }
 
 // out[body][i][0..2] = history[i], newest first (what Body.history holds).

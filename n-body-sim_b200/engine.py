@@ -163,6 +163,15 @@ class Engine:
         """body.history.unshift(pos.clone()); pop the oldest (idx:564-565), for every body."""
         check(self._L.nbody_history_push(self._ctx), self._ctx)
 
+    def history_remap(self, source) -> None:
+        """After the body list changed and was uploaded again: body i continues the ring of body
+        source[i] of the previous list; source[i] < 0 is a body the ring has not seen (filled at the
+        next push, idx:540)."""
+        src = np.ascontiguousarray(source, dtype=np.int32)
+        if src.shape != (self.n,):
+            raise ValueError(f"source must have one entry per body ({self.n})")
+        check(self._L.nbody_history_remap(self._ctx, _ptr(src)), self._ctx)
+
     def history(self) -> np.ndarray:
         """Body.history of every body: [n, depth, 3], newest first."""
         out = np.empty((self.n, self._hist_depth, 3), dtype=self.dtype)

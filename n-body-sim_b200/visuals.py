@@ -9,9 +9,11 @@ idx:83-202.  Here the history ring and the ribbon builder run on the device
 headless (`Engine.render`).  three.js itself -- meshes, particles, flashes, bloom, tone
 mapping -- is not mirrored (no graphics stack on this box).
 
-The array contract has no body identity: when the body list changes length (merge,
-fracture, spawn) the ring starts over, as it does for a body the page sees for the first
-time (idx:540).
+Body identity: the page keys meshes and trails by `body.id` (idx:505-506), and a Body object
+carries its `history` through list changes.  The array contract has no identity, so when the
+list changes (merge, fracture, spawn) `update` tells the engine which row each surviving body
+had before (`Engine.history_remap`); bodies it has not seen start with trailLength copies of
+their position (idx:540).
 """
 from __future__ import annotations
 
@@ -36,6 +38,7 @@ class VisualSystem:
         self.seeds = {}                     # body.id -> material `seed` uniform, drawn at first sight (idx:492)
         self.trails: Optional[np.ndarray] = None   # float32 [n, trailLength, 6]: each trail mesh's `positions` (idx:524)
         self._depth = 0
+        self._ring_ids: Optional[list] = None      # body.id per row of the device ring at the last push
 
     def _sync(self, bodies: List["_ph.Body"]):
         eng = self.physics.engine
@@ -59,7 +62,13 @@ class VisualSystem:
         if self._depth != _ph.CONFIG.trailLength:
             eng.history_enable(_ph.CONFIG.trailLength)
             self._depth = _ph.CONFIG.trailLength
-        eng.history_push()                                           # idx:564-565
+            self._ring_ids = None
+        ids = [b.id for b in bodies]
+        if self._ring_ids is not None and ids != self._ring_ids:     # merge / fracture / spawn since the last frame
+            row = {bid: k for k, bid in enumerate(self._ring_ids)}
+            eng.history_remap([row.get(bid, -1) for bid in ids])
+        eng.history_push()                                           # idx:540, 564-565
+        self._ring_ids = ids
         self.trails = eng.trail_ribbons(self.camera_position)        # idx:567-592
         return self.trails
 

@@ -269,6 +269,20 @@ template <typename T> static void run(bool f64, const char* prec, const std::vec
         std::vector<T> hist(n * depth * 3);
         call("trailRibbons", {ctx, num(0), num(80), num(150), typed_as(napi_float32_array, ribbons.data(), ribbons.size())});
         call("historyDownload", {ctx, typed(f64, hist.data(), hist.size())});
+        {   // historyRemap: the identity map keeps every ring (then one more push shifts it); a short array throws
+            std::vector<int> source(n);
+            for (size_t k = 0; k < n; ++k) source[k] = int(k);
+            call("historyRemap", {ctx, typed_as(napi_int32_array, source.data(), n - 1)}, true);
+            call("historyRemap", {ctx, typed_as(napi_int32_array, source.data(), n)});
+            call("historyDownload", {ctx, typed(f64, hist.data(), hist.size())}, true);  // refused until the next push
+            call("historyPush", {ctx});
+            std::vector<T> hist2(n * depth * 3);
+            call("historyDownload", {ctx, typed(f64, hist2.data(), hist2.size())});
+            for (size_t k = 0; k < n; ++k)
+                for (int i = 1; i < depth; ++i)
+                    for (int c = 0; c < 3; ++c)
+                        if (hist2[(k * depth + i) * 3 + c] != hist[(k * depth + i - 1) * 3 + c]) exit(7);
+        }
         {   // a frame of the planet shaders through the addon (idx:83-202): type = k % 3, seed = k * 0.37
             std::vector<int> type(n);
             std::vector<float> seed(n), frame(96 * 54 * 4);

@@ -157,3 +157,91 @@ def test_visual_system_mirror(nb, oracle):
     vis.garbageCollect(ps.bodies[:10])
     assert len(vis.seeds) == 10
     ph.seed_random(None)
+
+
+@pytest.mark.parametrize("precision", ["f64", "f32"])
+def test_history_remap_follows_bodies(nb, oracle, precision):
+    """A Body object carries its history through list changes (idx:383-389, 835); the device ring
+    follows with nbody_history_remap: survivors keep their samples under their new index, new
+    bodies start with depth copies of their position (idx:540), wrap-around included."""
+    dt = np.float64 if precision == "f64" else np.float32
+    rng = np.random.default_rng(5)
+    n, depth = 300, 12
+    pm = rng.normal(0, 10, (n, 4)).astype(dt)
+    vel = np.zeros((n, 4), dt)
+    vel[:, :3] = rng.normal(0, 1, (n, 3))
+    with nb.Engine(512, precision=precision) as e:
+        e.upload(pm, vel)
+        with pytest.raises(nb.NBodyError):
+            e.history_remap(np.arange(n))                     # no ring yet
+        e.history_enable(depth)
+        hist = None
+        for frame in range(17):                               # past one wrap of the ring
+            e.kick1_drift(0.01)
+            e.history_push()
+            pos = e.download(vel=False, acc=False)["pos_mass"]
+            hist = oracle.history_push(oracle.history_init(pos, depth), pos) if hist is None else oracle.history_push(hist, pos)
+        assert np.array_equal(e.history(), hist)
+        # the list changes twice before the renderer looks again: 40 bodies leave, then 25 new ones join
+        out = e.download()
+        keep = np.sort(rng.choice(n, n - 40, replace=False))
+        e.upload(out["pos_mass"][keep], out["vel"][keep])
+        new_pm = rng.normal(0, 10, (25, 4)).astype(dt)
+        pm2 = np.concatenate([new_pm[:10], out["pos_mass"][keep], new_pm[10:]])
+        vel2 = np.concatenate([np.zeros((10, 4), dt), out["vel"][keep], np.zeros((15, 4), dt)])
+        e.upload(pm2, vel2)
+        source = np.concatenate([np.full(10, -1), keep, np.full(15, -1)])
+        with pytest.raises(nb.NBodyError):
+            e.history_remap(np.where(source < 0, n, source))  # outside the previous list
+        with pytest.raises(ValueError):
+            e.history_remap(source[:-1])
+        e.history_remap(source)
+        with pytest.raises(nb.NBodyError):
+            e.history()                                       # new rows are filled by the next push
+        e.kick1_drift(0.01)
+        e.history_push()
+        pos = e.download(vel=False, acc=False)["pos_mass"]
+        carried = np.where(source[:, None, None] >= 0, hist[np.maximum(source, 0)], oracle.history_init(pos, depth))
+        hist2 = oracle.history_push(carried, pos)
+        assert np.array_equal(e.history(), hist2)
+        # same length, different identity: a permutation
+        perm = rng.permutation(len(source))
+        e.upload(pos[perm], vel2[perm])
+        e.history_remap(perm)
+        e.history_push()
+        assert np.array_equal(e.history(), oracle.history_push(hist2[perm], pos[perm]))
+        # without a remap a changed n starts every ring over, as before
+        e.upload(pos[:50], vel2[:50])
+        e.history_push()
+        assert np.array_equal(e.history(), oracle.history_init(pos[:50], depth))
+
+
+def test_visual_system_keeps_trails_through_merges(nb, oracle):
+    """The page's frame loop with its own collision stage: bodies merge and fracture between
+    frames, and every surviving Body keeps its own history (keyed by body.id like meshMap /
+    trailMap, idx:505-506, 540, 564-565)."""
+    ph = nb.physics
+    ph.seed_random(21)
+    rng = np.random.default_rng(3)
+    ps = ph.PhysicsSystem(precision="f64", collisions=True)
+    for _ in range(90):
+        ps.addBody(ph.Body(float(rng.uniform(0.5, 3.0)), ph.V3(*rng.uniform(-6, 6, 3)), ph.V3(*rng.normal(0, 0.4, 3)), "rock", 0.0))
+    vis = nb.VisualSystem(ps)
+    depth = ph.CONFIG.trailLength
+    ref = {}                                                  # body.id -> history, the way Body objects hold it
+    counts = set()
+    for frame in range(100):
+        ps.integrate(ph.CONFIG.dt / ph.CONFIG.subSteps, nsteps=ph.CONFIG.subSteps)
+        vis.update(ps.bodies, ph.CONFIG.dt)
+        for b in ps.bodies:
+            p = np.array([[*b.pos]])
+            h = ref.get(b.id)
+            ref[b.id] = oracle.history_push(oracle.history_init(p, depth) if h is None else h, p)
+        counts.add(len(ps.bodies))
+        if frame % 9 == 0 or frame == 99:
+            want = np.concatenate([ref[b.id] for b in ps.bodies])
+            assert np.array_equal(vis.histories(), want), frame
+    assert len(counts) > 3 and ps.stats["merge"] > 0          # the list really changed along the way
+    radius = np.array([b.radius for b in ps.bodies])
+    assert np.array_equal(vis.trails, oracle.trail_ribbons(want, radius, vis.camera_position))
+    ph.seed_random(None)
