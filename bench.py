@@ -101,7 +101,7 @@ def run_reference(args, rank):
     if rank != 0:
         return
     import nbody_b200 as nb
-    scene = nb.scenes.uniform_cube(args.n)
+    scene = nb.scenes.SCENES[args.scene](args.n)
     sample_n = min(args.n, args.ref_sample)
     times = []
     from oracle import oracle
@@ -124,7 +124,7 @@ def run_reference(args, rank):
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"uniform cube N={args.n} (configs[3]); each step = one integrate(dt) on the first "
+            "config": {"workload": f"{scene.name} N={args.n} (configs[{scene.meta['config'] - 1}]); each step = one integrate(dt) on the first "
                                    f"{sample_n} bodies (bounded sample)", "n": args.n, "sample_n": sample_n},
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": 1, "kind": "port",
                              "sample": f"first {sample_n} bodies, {args.steps} steps, 1 thread (the reference is "
@@ -140,6 +140,8 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--n", "--bodies", dest="n", type=int, default=1048576)   # --bodies: torchrun's argparse trips over --n
+    ap.add_argument("--scene", default="uniform_cube", choices=["uniform_cube", "cold_collapse"],
+                    help="uniform_cube = BASELINE configs[3] (the metric's workload); cold_collapse = configs[4], with --bodies 4194304 --gpus 8")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--ref-sample", type=int, default=16384)
     ap.add_argument("--cpu-sample", type=int, default=16384)
@@ -166,7 +168,7 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
-    scene = nb.scenes.uniform_cube(args.n)
+    scene = nb.scenes.SCENES[args.scene](args.n)
     pm, vel, _ = scene.astype(np.float32)
     eng = nb.create_rank_engine(args.n, "f32")
     # a real (non-default) stream: the engine, the L2 flush and the timing events all run on it
@@ -283,7 +285,8 @@ def main():
         line = {"metric": METRIC if args.n == 1048576 else METRIC.replace("N=1M", f"N={args.n}"), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": f"uniform cube N={args.n} fp32, G=1 eps=1 dt=0.01 (BASELINE configs[3]); "
+                "config": {"workload": f"{scene.name} N={args.n} fp32, G={scene.G:g} eps={scene.softening:g} dt={scene.dt:g} "
+                                       f"(BASELINE configs[{scene.meta['config'] - 1}]); "
                                        "one step = integrate(dt) = N^2 interactions",
                            "n": args.n, "parallelism": f"i-range shards x{world}, positions exchanged by " + {0: "nothing (1 GPU)", 1: "ncclAllGather",
                                        2: "fused peer stores over NVLink + epoch barrier"}[info["exchange"]],
