@@ -26,6 +26,7 @@
 #include "integrate.cuh"
 #include "nccl_dyn.h"
 #include "render.cuh"
+#include "small.cuh"
 #include "trails.cuh"
 
 using namespace nb;
@@ -111,6 +112,7 @@ struct nbody_ctx {
     bool uniform = false;           // fp32: every uploaded mass is the same value -> the 11-op force kernel
     double uniform_mass = 0.0;
     int f64_math = 2;               // NBODY_F64_MATH at create
+    bool small_path = true;         // NBODY_SMALL at create: one-cluster multi-step kernel for n <= kSmallMaxN (small.cuh)
     bool detect_masses = false;     // upload in flight: pack_pos_kernel compares every mass with uniform_mass
     std::vector<MassOutlier> outliers;  // ... except these few (at most kMaxOutliers), corrected per i-body
     bool has_radius = false;        // nbody_set_radius was called for the current body list
@@ -265,6 +267,8 @@ int set_kernel_attrs(nbody_ctx* c)
     CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
+    CU(c, cudaFuncSetAttribute(small_step_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(small_smem_bytes<float>())));
+    CU(c, cudaFuncSetAttribute(small_step_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(small_smem_bytes<double>())));
     CU(c, cudaFuncSetAttribute(force_f64_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
     CU(c, cudaFuncSetAttribute(force_f64_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
     CU(c, cudaFuncSetAttribute(force_f64_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
@@ -295,6 +299,7 @@ int create_common(nbody_ctx** out, nbody_prec prec, int world, size_t capacity, 
         c->j_unit = kJUnitF64;
         c->f64_math = env_int("NBODY_F64_MATH", 2);
     }
+    c->small_path = env_int("NBODY_SMALL", 1) != 0 && !(prec == NBODY_F64 && c->f64_math == 0);
     c->cap_pad = round_up(capacity, pad_unit(c));
     *made = c;
     return NBODY_OK;
@@ -947,6 +952,37 @@ int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
     return NBODY_OK;
 }
 
+// The whole nsteps x integrate(dt) of a small system in one cluster launch (small.cuh).
+template <typename Real> int launch_small_steps_t(nbody_ctx* c, Shard& s, double dt, double G, double eps, int nsteps)
+{
+    SmallParams<Real> p;
+    p.pos = static_cast<Real*>(s.pos[c->cur]);
+    p.vel = static_cast<Real*>(s.vel);
+    p.acc = static_cast<Real*>(s.acc);
+    p.temp = c->has_temp ? static_cast<Real*>(s.temp) : nullptr;
+    p.n = int(c->n);
+    p.nsteps = nsteps;
+    p.G = Real(G);
+    p.eps2 = Real(eps) * Real(eps);
+    p.r2_floor = eps == 0.0 ? Real(1e-20) : Real(0);
+    p.half_dt = Real(0.5) * Real(dt);
+    p.dt = Real(dt);
+    p.heat_decay = Real(c->heat_decay);
+    small_step_kernel<Real><<<kSmallCluster, kSmallThreads, small_smem_bytes<Real>(), s.stream>>>(p);
+    c->launches++;
+    CU(c, cudaGetLastError());
+    return NBODY_OK;
+}
+
+int launch_small_steps(nbody_ctx* c, double dt, double G, double eps, int nsteps)
+{
+    Shard& s = c->shards[0];
+    CU(c, cudaSetDevice(s.device));
+    c->near_valid = false;  // the bodies move and nobody tracked neighbours: a contact search scans every body
+    return c->prec == NBODY_F32 ? launch_small_steps_t<float>(c, s, dt, G, eps, nsteps)
+                                : launch_small_steps_t<double>(c, s, dt, G, eps, nsteps);
+}
+
 // idx:248-253 for every shard's own range, written to the OTHER buffer of every rank,
 // then the exchange, then the buffers swap (same flow as a fused force step).
 int launch_kick1_drift(nbody_ctx* c, double dt)
@@ -985,6 +1021,7 @@ extern "C" int nbody_step(nbody_ctx* c, double dt, double G, double softening, i
     if (rc != NBODY_OK) return rc;
     if (nsteps < 0 || softening < 0.0) return fail(c, NBODY_EINVAL, "step: nsteps=%d softening=%g", nsteps, softening);
     if (nsteps == 0) return NBODY_OK;
+    if (c->small_path && c->world == 1 && c->n <= size_t(kSmallMaxN) && !c->timing) return launch_small_steps(c, dt, G, softening, nsteps);
     // First loop of integrate() for the first step (idx:250-253); later steps
     // get theirs from the previous force kernel's epilogue, so positions cross
     // HBM once per step.

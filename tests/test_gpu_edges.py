@@ -1,7 +1,11 @@
 """Edge cases of the rows next to the hot path through the C ABI: smallest
 and ragged body counts, extreme ring depths, degenerate geometry, multi-GPU gathers."""
+import os
+
 import numpy as np
 import pytest
+
+from .conftest import norm_rel_err
 
 pytestmark = pytest.mark.gpu
 
@@ -101,17 +105,83 @@ def test_multi_gpu_render_and_trails(nb, oracle):
     rad = (_rad(pm[:, 3]) * 3).astype(np.float32)
     temp = np.linspace(0, 300, s.n).astype(np.float32)
     out = {}
-    for g in (1, 2):
-        with nb.Engine(s.n, precision="f32", n_gpus=g) as e:
-            e.upload(pm, vel, None, temp)
-            e.set_radius(rad)
-            e.history_enable(8)
-            for _ in range(3):
-                e.step(s.dt, s.G, s.softening, 2)
-                e.history_push()
-            out[g] = (e.render(160, 90), e.history(), e.trail_ribbons((0, 80, 150)), e.download(temp=True))
+    os.environ["NBODY_SMALL"] = "0"      # one GPU would take the one-cluster kernel (small.cuh): same step, other sum order
+    try:
+        for g in (1, 2):
+            with nb.Engine(s.n, precision="f32", n_gpus=g) as e:
+                e.upload(pm, vel, None, temp)
+                e.set_radius(rad)
+                e.history_enable(8)
+                for _ in range(3):
+                    e.step(s.dt, s.G, s.softening, 2)
+                    e.history_push()
+                out[g] = (e.render(160, 90), e.history(), e.trail_ribbons((0, 80, 150)), e.download(temp=True))
+    finally:
+        del os.environ["NBODY_SMALL"]
     for a, b in zip(out[1][:3], out[2][:3]):
         assert np.array_equal(a, b)
     d = out[2][3]
     ref, _ = oracle.render(d["pos_mass"], rad, d["temp"], np.zeros(s.n, np.int32), np.zeros(s.n), 160, 90)
     assert np.array_equal(out[2][0], ref)
+
+
+# ---- the one-cluster multi-step kernel for the reference's own sizes (csrc/small.cuh) ----------
+
+@pytest.mark.parametrize("precision,tol", [("f64", 1e-12), ("f32", 3e-5)])
+@pytest.mark.parametrize("n", [1, 2, 7, 8, 9, 151, 300, 512, 513])
+def test_small_system_kernel(nb, oracle, precision, tol, n):
+    """N <= 512 on one GPU: nbody_step is one launch of one thread-block cluster that runs all the
+    steps (N = 513 takes the launch-per-step kernels).  Against the oracle's integrate() and against
+    the launch-per-step path, cluster shares from 1 body per CTA (and idle CTAs) to 64; thermal decay
+    bit-exact; a second call continues from the stored acc."""
+    dt = np.float64 if precision == "f64" else np.float32
+    rng = np.random.default_rng(100 + n)
+    pm = np.concatenate([rng.normal(0, 4, (n, 3)), rng.uniform(0.5, 2.5, (n, 1))], axis=1).astype(dt)
+    vel = np.zeros((n, 4), dt)
+    vel[:, :3] = rng.normal(0, 0.5, (n, 3))
+    temp = rng.uniform(0, 50, n).astype(dt)
+    G, eps, h = 0.5, 0.5, 0.008
+
+    def run(small):
+        os.environ["NBODY_SMALL"] = "1" if small else "0"
+        try:
+            with nb.Engine(600, precision=precision) as e:
+                e.upload(pm, vel, None, temp)
+                l0 = e.info()["kernel_launches"]
+                e.step(h, G, eps, 5)
+                launches = e.info()["kernel_launches"] - l0
+                e.step(h, G, eps, 1)
+                return e.download(temp=True), launches
+        finally:
+            del os.environ["NBODY_SMALL"]
+
+    out, launches = run(True)
+    assert launches == (1 if n <= 512 else 6)                 # kick1_drift + 5 force kernels otherwise
+    p, v, a, t = oracle.integrate(pm, vel, np.zeros_like(vel), temp, h, G, eps, nsteps=6)
+    scale = max(1.0, np.abs(p[:, :3]).max())
+    assert np.abs(out["pos_mass"][:, :3] - p[:, :3]).max() < tol * scale
+    assert np.abs(out["vel"][:, :3] - v[:, :3]).max() < 10 * tol * max(1.0, np.abs(v).max())
+    assert np.abs(out["acc"][:, :3] - a[:, :3]).max() < 10 * tol * max(1e-3, np.abs(a).max())
+    assert np.array_equal(out["pos_mass"][:, 3], pm[:, 3])
+    if precision == "f64":
+        np.testing.assert_array_equal(out["temp"], t)
+    ref, _ = run(False)
+    for k in ("pos_mass", "vel", "acc"):
+        assert np.abs(out[k] - ref[k]).max() < 10 * tol * max(1.0, np.abs(ref[k]).max()), k
+    np.testing.assert_array_equal(out["temp"], ref["temp"])
+
+
+@pytest.mark.parametrize("precision", ["f64", "f32"])
+def test_small_system_kernel_zero_softening(nb, oracle, precision):
+    """eps = 0: the self pair is selected away (fp64) or clamped (fp32), no NaN."""
+    dt = np.float64 if precision == "f64" else np.float32
+    s = nb.scenes.galaxy_default()
+    pm, vel, _ = s.astype(dt)
+    with nb.Engine(s.n, precision=precision) as e:
+        e.upload(pm, vel)
+        e.step(0.002, s.G, 0.0, 3)
+        out = e.download()
+    p, v, a, _ = oracle.integrate(pm, vel, np.zeros_like(vel), None, 0.002, s.G, 0.0, nsteps=3)
+    assert np.isfinite(out["acc"]).all()
+    tol = 1e-12 if precision == "f64" else 2e-5
+    assert norm_rel_err(out["pos_mass"], p) < tol and norm_rel_err(out["acc"], a) < 10 * tol

@@ -280,7 +280,7 @@ def test_physics_system_mirror(nb, oracle):
         ps2.integrate(0.008, collide=lambda sysm, dt: calls.append(dt))
     assert calls == [0.008, 0.008]
     got_p2 = np.array([[b.pos.x, b.pos.y, b.pos.z, b.mass] for b in ps2.bodies])
-    assert np.array_equal(got_p2, got_p)
+    assert norm_rel_err(got_p2, got_p) < 1e-14            # (one-cluster kernel vs split kernels: same step, other sum order)
     # maxBodies cap drops the oldest body (idx:240-242)
     ps3 = nb.PhysicsSystem(precision="f64")
     for k in range(nb.CONFIG.maxBodies + 5):
