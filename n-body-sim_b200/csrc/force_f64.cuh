@@ -43,11 +43,18 @@ __device__ __forceinline__ double rsqrt_f64(double s)
 #define NB_F64_UNROLL 4  // N=65,536: unroll 1 / 2 / 4 = 830 / 882 / 907 G interactions/s (profiles/r1e_f64_variants.jsonl)
 #endif
 constexpr int kF64Unroll = NB_F64_UNROLL;
+#ifndef NB_F64_R
+#define NB_F64_R 1
+#endif
+constexpr int kF64BodiesPerThread = NB_F64_R;  // default i-bodies per thread (NBODY_F64_R overrides at create)
 
 // ZERO_SOFT: softening == 0, where the self pair would be 0 * inf and is selected away (the
 // reference never evaluates it, idx:273).  With softening it contributes an exact zero by
 // itself and the select is not compiled in.
-template <int MATH, bool ZERO_SOFT>
+// UNIFORM (MATH 2 only): every mass is the same value (config 2's Plummer sphere: 1/N), the
+// per-pair multiply by m_j drops out -- 16 DP instructions -- and the common mass joins G; pads sit
+// at x = 1e150, where y^3 underflows to an exact 0.  R: i-bodies per thread (more independent chains).
+template <int MATH, bool ZERO_SOFT, bool UNIFORM = false, int R = 1>
 __global__ void __launch_bounds__(kThreads + 32) force_f64_kernel(const ForceParams<double> p)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -93,10 +100,14 @@ __global__ void __launch_bounds__(kThreads + 32) force_f64_kernel(const ForcePar
         return;
     }
 
-    const size_t il = tile_i * size_t(kThreads) + tid;
-    const size_t gi = p.i_begin + il;
-    const double4 me = reinterpret_cast<const double4*>(p.pos_cur)[gi];
-    double ax = 0.0, ay = 0.0, az = 0.0;
+    const size_t il0 = tile_i * size_t(kThreads * R) + tid;  // body r of this thread: il0 + r * kThreads
+    double4 me[R];
+    double ax[R], ay[R], az[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        me[r] = reinterpret_cast<const double4*>(p.pos_cur)[p.i_begin + il0 + size_t(r) * kThreads];
+        ax[r] = ay[r] = az[r] = 0.0;
+    }
 
     for (int t = 0; t < ntiles; ++t) {
         const int slot = t % kStages;
@@ -104,61 +115,75 @@ __global__ void __launch_bounds__(kThreads + 32) force_f64_kernel(const ForcePar
         const double4* tp = tiles + size_t(slot) * (kTileBytes / 32);
         const size_t off = size_t(t) * kTileBytes;
         const int nj = static_cast<int>((chunk_bytes - off < kTileBytes ? chunk_bytes - off : kTileBytes) / 32);
-        const long long self_d = static_cast<long long>(gi) - static_cast<long long>(j0 + off / 32);
-        const int self_q = (self_d >= 0 && self_d < nj) ? static_cast<int>(self_d) : -1;  // this body's slot in the tile
+        int self_q[R];  // this body's slot in the tile, if it is there
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const long long d = static_cast<long long>(p.i_begin + il0 + size_t(r) * kThreads) - static_cast<long long>(j0 + off / 32);
+            self_q[r] = (d >= 0 && d < nj) ? static_cast<int>(d) : -1;
+        }
 #pragma unroll kF64Unroll
         for (int q = 0; q < nj; ++q) {
             const double4 b = tp[q];
-            const double vx = __dsub_rn(b.x, me.x);
-            const double vy = __dsub_rn(b.y, me.y);
-            const double vz = __dsub_rn(b.z, me.z);
-            double s;
-            if (MATH == 2) {
-                s = __fma_rn(vz, vz, __fma_rn(vy, vy, __fma_rn(vx, vx, p.eps2)));
-            } else {
-                const double distSq = __dadd_rn(__dadd_rn(__dmul_rn(vx, vx), __dmul_rn(vy, vy)), __dmul_rn(vz, vz));
-                s = __dadd_rn(distSq, p.eps2);
-            }
-            double fm;
-            if (MATH == 0) {
-                fm = __dmul_rn(__ddiv_rn(p.G, __dmul_rn(s, __dsqrt_rn(s))), b.w);
-            } else {
-                const double y = rsqrt_f64(s);
-                fm = __dmul_rn(__dmul_rn(__dmul_rn(y, y), y), b.w);  // G joins in the epilogue
-            }
-            if (ZERO_SOFT && q == self_q) fm = 0.0;
-            if (MATH == 2) {
-                ax = __fma_rn(fm, vx, ax);
-                ay = __fma_rn(fm, vy, ay);
-                az = __fma_rn(fm, vz, az);
-            } else {
-                ax = __dadd_rn(ax, __dmul_rn(fm, vx));
-                ay = __dadd_rn(ay, __dmul_rn(fm, vy));
-                az = __dadd_rn(az, __dmul_rn(fm, vz));
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const double vx = __dsub_rn(b.x, me[r].x);
+                const double vy = __dsub_rn(b.y, me[r].y);
+                const double vz = __dsub_rn(b.z, me[r].z);
+                double s;
+                if (MATH == 2) {
+                    s = __fma_rn(vz, vz, __fma_rn(vy, vy, __fma_rn(vx, vx, p.eps2)));
+                } else {
+                    const double distSq = __dadd_rn(__dadd_rn(__dmul_rn(vx, vx), __dmul_rn(vy, vy)), __dmul_rn(vz, vz));
+                    s = __dadd_rn(distSq, p.eps2);
+                }
+                double fm;
+                if (MATH == 0) {
+                    fm = __dmul_rn(__ddiv_rn(p.G, __dmul_rn(s, __dsqrt_rn(s))), b.w);
+                } else {
+                    const double y = rsqrt_f64(s);
+                    fm = __dmul_rn(__dmul_rn(y, y), y);  // G (and the common mass) join in the epilogue
+                    if (!UNIFORM) fm = __dmul_rn(fm, b.w);
+                }
+                if (ZERO_SOFT && q == self_q[r]) fm = 0.0;  // the reference never evaluates the self pair (idx:273)
+                if (MATH == 2) {
+                    ax[r] = __fma_rn(fm, vx, ax[r]);
+                    ay[r] = __fma_rn(fm, vy, ay[r]);
+                    az[r] = __fma_rn(fm, vz, az[r]);
+                } else {
+                    ax[r] = __dadd_rn(ax[r], __dmul_rn(fm, vx));
+                    ay[r] = __dadd_rn(ay[r], __dmul_rn(fm, vy));
+                    az[r] = __dadd_rn(az[r], __dmul_rn(fm, vz));
+                }
             }
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[slot]);
     }
 
-    const double scale = MATH == 0 ? 1.0 : p.G;
+    const double scale = MATH == 0 ? 1.0 : p.G;  // UNIFORM: the host folded the common mass into p.G
     if (p.j_chunks == 1) {
-        finish_body<double>(p, il, ax, ay, az, scale);
+#pragma unroll
+        for (int r = 0; r < R; ++r) finish_body<double>(p, il0 + size_t(r) * kThreads, ax[r], ay[r], az[r], scale);
         return;
     }
     double4* part = reinterpret_cast<double4*>(p.partial);
-    part[size_t(chunk) * p.n_local + il] = make_double4(ax, ay, az, 0.0);
+#pragma unroll
+    for (int r = 0; r < R; ++r) part[size_t(chunk) * p.n_local + il0 + size_t(r) * kThreads] = make_double4(ax[r], ay[r], az[r], 0.0);
     if (!tile_arrive_last(&p.tile_counter[tile_i], p.j_chunks, &s_last, kThreads)) return;
-    double tx = 0.0, ty = 0.0, tz = 0.0;
-    for (int c = 0; c < p.j_chunks; ++c) {
-        const double2* q = reinterpret_cast<const double2*>(&part[size_t(c) * p.n_local + il]);
-        const double2 xy = __ldcg(q);
-        const double2 zw = __ldcg(q + 1);
-        tx = __dadd_rn(tx, xy.x);
-        ty = __dadd_rn(ty, xy.y);
-        tz = __dadd_rn(tz, zw.x);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const size_t il = il0 + size_t(r) * kThreads;
+        double tx = 0.0, ty = 0.0, tz = 0.0;
+        for (int c = 0; c < p.j_chunks; ++c) {
+            const double2* q = reinterpret_cast<const double2*>(&part[size_t(c) * p.n_local + il]);
+            const double2 xy = __ldcg(q);
+            const double2 zw = __ldcg(q + 1);
+            tx = __dadd_rn(tx, xy.x);
+            ty = __dadd_rn(ty, xy.y);
+            tz = __dadd_rn(tz, zw.x);
+        }
+        finish_body<double>(p, il, tx, ty, tz, scale);
     }
-    finish_body<double>(p, il, tx, ty, tz, scale);
     if (tid == 0) p.tile_counter[tile_i] = 0;
 }
 

@@ -55,7 +55,7 @@ __global__ void kick2_kernel(Real* vel, const Real* acc, Real* temp, size_t n_lo
 }
 
 // Host AoS (x,y,z,m)[n] staged on the device -> device pos_mass layout.  Pads are massless
-// bodies parked far away at x = pad_x (1e18): the equal-mass fp32 kernel ignores masses, and a
+// bodies parked far away at x = pad_x (1e18; 1e150 in fp64): the equal-mass kernels ignore masses, and a
 // pad at the origin would meet a real body there as 0 * inf when softening is 0.
 // detect != nullptr (fp32): also find the bodies whose mass is not `m0` -- detect[0] counts them
 // (a non-finite mass pushes the count past any limit) and the first kMaxOutliers found are

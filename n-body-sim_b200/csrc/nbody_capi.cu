@@ -112,6 +112,7 @@ struct nbody_ctx {
     bool uniform = false;           // fp32: every uploaded mass is the same value -> the 11-op force kernel
     double uniform_mass = 0.0;
     int f64_math = 2;               // NBODY_F64_MATH at create
+    int f64_R_forced = 0;          // NBODY_F64_R at create: 1 or 2 i-bodies per thread in the fp64 kernel, 0 = by body count
     bool small_path = true;         // NBODY_SMALL at create: one-cluster multi-step kernel for n <= kSmallMaxN (small.cuh)
     bool detect_masses = false;     // upload in flight: pack_pos_kernel compares every mass with uniform_mass
     std::vector<MassOutlier> outliers;  // ... except these few (at most kMaxOutliers), corrected per i-body
@@ -186,6 +187,16 @@ int env_int(const char* name, int dflt)
 
 size_t gcd_sz(size_t a, size_t b) { return b ? gcd_sz(b, a % b) : a; }
 
+// fp64 force kernel: two i-bodies per thread pay from ~32k bodies up (N=65,536: 961 -> 974 G interactions/s with
+// equal masses, 906 -> 948 without) and cost below (N=16,384: 304 -> 326 us/step): profiles/r1e_f64_r_uniform.jsonl
+constexpr size_t kF64TwoBodyMinN = 32768;
+int f64_bodies_per_thread(const nbody_ctx* c, size_t n)
+{
+    if (c->f64_math != 2) return 1;
+    if (c->f64_R_forced == 1 || c->f64_R_forced == 2) return c->f64_R_forced;
+    return n >= kF64TwoBodyMinN ? 2 : 1;
+}
+
 // n is padded to whole i-tiles per shard AND to whole j units: lcm(i_tile * world, j_unit)
 size_t pad_unit(const nbody_ctx* c)
 {
@@ -253,6 +264,32 @@ int alloc_shard(nbody_ctx* c, Shard& s)
     return NBODY_OK;
 }
 
+// The fp64 force kernel's variants (force_f64.cuh): MATH 0/1 exist for one body per thread and general masses only.
+template <typename F> void pick_f64_kernel(int math, bool zero_soft, bool uniform, int R, F&& f)
+{
+    if (math == 0) return zero_soft ? f(force_f64_kernel<0, true>) : f(force_f64_kernel<0, false>);
+    if (math == 1) return zero_soft ? f(force_f64_kernel<1, true>) : f(force_f64_kernel<1, false>);
+    if (R == 2) {
+        if (uniform) return zero_soft ? f(force_f64_kernel<2, true, true, 2>) : f(force_f64_kernel<2, false, true, 2>);
+        return zero_soft ? f(force_f64_kernel<2, true, false, 2>) : f(force_f64_kernel<2, false, false, 2>);
+    }
+    if (uniform) return zero_soft ? f(force_f64_kernel<2, true, true, 1>) : f(force_f64_kernel<2, false, true, 1>);
+    return zero_soft ? f(force_f64_kernel<2, true, false, 1>) : f(force_f64_kernel<2, false, false, 1>);
+}
+
+template <typename F> int for_each_f64_kernel(F&& f, nbody_ctx* c)
+{
+    for (int math = 0; math < 3; ++math)
+        for (int z = 0; z < 2; ++z)
+            for (int u = 0; u < 2; ++u)
+                for (int R = 1; R <= 2; ++R) {
+                    cudaError_t e = cudaSuccess;
+                    pick_f64_kernel(math, z != 0, u != 0, R, [&](auto kernel) { e = f(kernel); });
+                    if (e != cudaSuccess) return fail(c, NBODY_ECUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+                }
+    return NBODY_OK;
+}
+
 int set_kernel_attrs(nbody_ctx* c)
 {
     const int sm32 = int(force_f32_smem_bytes());
@@ -269,13 +306,7 @@ int set_kernel_attrs(nbody_ctx* c)
     CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
     CU(c, cudaFuncSetAttribute(small_step_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(small_smem_bytes<float>())));
     CU(c, cudaFuncSetAttribute(small_step_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(small_smem_bytes<double>())));
-    CU(c, cudaFuncSetAttribute(force_f64_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
-    CU(c, cudaFuncSetAttribute(force_f64_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
-    CU(c, cudaFuncSetAttribute(force_f64_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
-    CU(c, cudaFuncSetAttribute(force_f64_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
-    CU(c, cudaFuncSetAttribute(force_f64_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
-    CU(c, cudaFuncSetAttribute(force_f64_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64));
-    return NBODY_OK;
+    return for_each_f64_kernel([&](auto kernel) { return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64); }, c);
 }
 
 int create_common(nbody_ctx** out, nbody_prec prec, int world, size_t capacity, nbody_ctx** made)
@@ -294,10 +325,11 @@ int create_common(nbody_ctx** out, nbody_prec prec, int world, size_t capacity, 
         if (c->R != 2 && c->R != 4) c->R = 4;
         c->i_tile = kF32Threads * c->R;
     } else {
-        c->R = 1;
-        c->i_tile = kThreads;
-        c->j_unit = kJUnitF64;
         c->f64_math = env_int("NBODY_F64_MATH", 2);
+        c->f64_R_forced = env_int("NBODY_F64_R", 0);
+        c->R = f64_bodies_per_thread(c, capacity);  // for cap_pad: the largest i-tile an upload may pick
+        c->i_tile = kThreads * c->R;
+        c->j_unit = kJUnitF64;
     }
     c->small_path = env_int("NBODY_SMALL", 1) != 0 && !(prec == NBODY_F64 && c->f64_math == 0);
     c->cap_pad = round_up(capacity, pad_unit(c));
@@ -627,7 +659,7 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
         const bool detect = c->detect_masses && &s == &c->shards[0];  // every shard packs the same array: one looks
         if (detect) CU(c, cudaMemsetAsync(s.outlier_count, 0, sizeof(unsigned), s.stream));
         pack_pos_kernel<Real><<<blocks, 256, 0, s.stream>>>(static_cast<const Real*>(s.stage), static_cast<Real*>(s.pos[0]),
-                                                           static_cast<Real*>(s.pos[1]), n, c->n_pad, Real(1e18), Real(c->uniform_mass),
+                                                           static_cast<Real*>(s.pos[1]), n, c->n_pad, Real(sizeof(Real) == 8 ? 1e150 : 1e18), Real(c->uniform_mass),
                                                            detect ? s.outlier_count : nullptr, s.outliers);
         c->launches++;
         CU(c, cudaGetLastError());
@@ -695,7 +727,8 @@ int finish_mass_detection(nbody_ctx* c)
     CU(c, cudaSetDevice(s0.device));
     unsigned count = 0;
     CU(c, cudaMemcpy(&count, s0.outlier_count, sizeof(unsigned), cudaMemcpyDeviceToHost));
-    const size_t max_out = std::min<size_t>(size_t(std::max(0, env_int("NBODY_OUTLIERS", kMaxOutliers))), kMaxOutliers);
+    // (exceptions are corrected in the fp32 epilogue only: an fp64 context takes the sweep for exactly equal masses)
+    const size_t max_out = c->prec == NBODY_F64 ? 0 : std::min<size_t>(size_t(std::max(0, env_int("NBODY_OUTLIERS", kMaxOutliers))), kMaxOutliers);
     if (count > max_out) return NBODY_OK;  // too many different masses: the general kernel
     c->uniform = true;
     if (count == 0) return NBODY_OK;
@@ -717,6 +750,10 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     if (n == 0 || n > c->capacity) return fail(c, NBODY_EINVAL, "upload: n=%zu outside 1..capacity=%zu", n, c->capacity);
     if (!pos_mass || !vel) return fail(c, NBODY_EINVAL, "upload: pos_mass and vel are required");
     c->n = n;
+    if (c->prec == NBODY_F64) {
+        c->R = f64_bodies_per_thread(c, n);
+        c->i_tile = kThreads * c->R;
+    }
     c->n_pad = round_up(n, pad_unit(c));
     c->n_j = round_up(n, size_t(c->j_unit));
     c->cur = 0;
@@ -724,20 +761,21 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     c->uniform = false;
     c->outliers.clear();
     c->detect_masses = false;
-    if (c->prec == NBODY_F32 && c->R == 4 && env_int("NBODY_UNIFORM", 1) != 0) {
-        // Equal-mass sweep (force_f32.cuh, UNIFORM): the mass most bodies share, if there is one, by
-        // majority vote over an evenly spaced sample; pack_pos_kernel then compares every mass with it.
-        const float* pm = static_cast<const float*>(pos_mass);
+    const bool f32_sweep = c->prec == NBODY_F32 && c->R == 4, f64_sweep = c->prec == NBODY_F64 && c->f64_math == 2;
+    if ((f32_sweep || f64_sweep) && env_int("NBODY_UNIFORM", 1) != 0) {
+        // Equal-mass sweep (force_f32.cuh / force_f64.cuh, UNIFORM): the mass most bodies share, if there is one,
+        // by majority vote over an evenly spaced sample; pack_pos_kernel then compares every mass with it.
         const size_t samples = std::min<size_t>(n, 1024);
-        float m0 = pm[3];
+        double m0 = 0.0;
         size_t votes = 0;
         for (size_t k = 0; k < samples; ++k) {
-            const float m = pm[4 * (k * n / samples) + 3];
+            const size_t at = 4 * (k * n / samples) + 3;
+            const double m = f32_sweep ? double(static_cast<const float*>(pos_mass)[at]) : static_cast<const double*>(pos_mass)[at];
             if (votes == 0) m0 = m;
             votes += (m == m0) ? 1 : size_t(-1);
         }
         c->uniform_mass = m0;
-        c->detect_masses = m0 > 0.0f && std::isfinite(m0);
+        c->detect_masses = m0 > 0.0 && std::isfinite(m0);
     }
     c->has_radius = false;  // a new body list: radii must be set again (Body.radius follows mass, idx:221)
     if (c->hist_n != n) {  // history ring: refilled at the next push (trails.cuh) unless nbody_history_remap carries it over
@@ -927,20 +965,10 @@ int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
             const ForceParams<double> p = make_params<double>(c, s, mode, dt, G, eps);
             const dim3 blk(kThreads + 32);
             const size_t sm = force_f64_smem_bytes();
-            switch (c->f64_math) {  // force_f64.cuh: 0 IEEE sqrt/div in the reference's association, 1 rsqrt^3, 2 rsqrt^3 + DFMA
-            case 0:
-                if (eps == 0.0) force_f64_kernel<0, true><<<grid, blk, sm, s.stream>>>(p);
-                else force_f64_kernel<0, false><<<grid, blk, sm, s.stream>>>(p);
-                break;
-            case 1:
-                if (eps == 0.0) force_f64_kernel<1, true><<<grid, blk, sm, s.stream>>>(p);
-                else force_f64_kernel<1, false><<<grid, blk, sm, s.stream>>>(p);
-                break;
-            default:
-                if (eps == 0.0) force_f64_kernel<2, true><<<grid, blk, sm, s.stream>>>(p);
-                else force_f64_kernel<2, false><<<grid, blk, sm, s.stream>>>(p);
-                break;
-            }
+            ForceParams<double> q = p;
+            const bool uni = c->uniform && c->f64_math == 2;
+            if (uni) q.G = G * c->uniform_mass;  // equal masses: the common m joins G (force_f64.cuh, UNIFORM)
+            pick_f64_kernel(c->f64_math, eps == 0.0, uni, c->R, [&](auto kernel) { kernel<<<grid, blk, sm, s.stream>>>(q); });
         }
         c->launches++;
         CU(c, cudaGetLastError());

@@ -26,6 +26,7 @@ def main():
     ap.add_argument("--sizes", default="4096,16384,65536")
     ap.add_argument("--units", default="0,28416,7104,3552,1776")
     ap.add_argument("--math", default="0,1,2")
+    ap.add_argument("--tag", default="")
     a = ap.parse_args()
     s4 = nb.scenes.plummer(4096)
     ref4 = oracle.compute_gravity(s4.pos_mass, s4.G, s4.softening, mt=True)
@@ -53,7 +54,8 @@ def main():
                     e.sync()
                     dt = (time.perf_counter() - t0) / k
                     info = e.info()
-                rows.append({"lib": os.path.basename(os.environ.get("NBODY_LIB", "default")), "math": math, "want_units": units or "default", "n": n, "us_per_step": dt * 1e6,
+                rows.append({"lib": os.path.basename(os.environ.get("NBODY_LIB", "default")), "tag": a.tag, "uniform_kernel": info["uniform_mass"],
+                             "i_tile": info["i_tile"], "math": math, "want_units": units or "default", "n": n, "us_per_step": dt * 1e6,
                              "g_int_per_s": float(n) ** 2 / dt * 1e-9, "j_chunks": info["j_chunks"], "force_err_n4096": e4})
                 print(json.dumps(rows[-1]), flush=True)
     os.makedirs(os.path.dirname(a.out), exist_ok=True)

@@ -152,3 +152,29 @@ def test_f32_1m_contacts_flagged_equals_full_scan_and_sampled_rows(nb):
         ref_j = np.nonzero(d2 < rs * rs)[0] + i + 1               # distSq < minDist * minDist, idx:309-313
         got_j = full[full[:, 0] == i, 1]
         assert np.array_equal(got_j, ref_j), i
+
+
+@pytest.mark.parametrize("scene", ["plummer", "two_galaxies"])
+def test_f64_32768_two_bodies_per_thread_sampled(nb, oracle, scene):
+    """From 32,768 bodies up the fp64 kernel gives each thread two i-bodies; the Plummer sphere
+    (masses 1/N) also takes its equal-mass variant, the two-galaxy scene (two heavy centres) the
+    general one.  Sampled bodies against the oracle at the fp64 gate, and the one-body-per-thread
+    shape must agree to rounding."""
+    s = nb.scenes.SCENES[scene](32768)
+    idx = np.unique(np.concatenate([[0, 1, 255, 256, 511, 512, 16384, s.n - 1], np.random.default_rng(9).integers(0, s.n, 56)]))
+    ref = oracle.acc_subset(s.pos_mass, idx, s.G, s.softening)
+    accs = {}
+    for forced in ("0", "1"):
+        os.environ["NBODY_F64_R"] = forced
+        try:
+            with nb.Engine(s.n, precision="f64") as e:
+                e.upload(s.pos_mass, s.vel)
+                info = e.info()
+                assert info["i_tile"] == (512 if forced == "0" else 256)
+                assert info["uniform_mass"] == (1 if scene == "plummer" else 0)
+                e.force(s.G, s.softening)
+                accs[forced] = e.download()["acc"]
+        finally:
+            del os.environ["NBODY_F64_R"]
+    assert norm_rel_err(accs["0"][idx], ref) < 1e-12
+    assert norm_rel_err(accs["0"], accs["1"]) < 1e-14

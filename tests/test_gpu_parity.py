@@ -115,13 +115,21 @@ def test_f64_math_variants(nb, oracle, math, eps):
     try:
         with nb.Engine(s.n, precision="f64") as e:
             e.upload(pm, s.vel)
+            assert e.info()["uniform_mass"] == (1 if math == 2 else 0)   # Plummer masses are all 1/N: equal-mass variant
             e.force(s.G, eps)
             acc = e.download()["acc"]
+            pm2 = pm.copy()
+            pm2[5, 3] *= 2.0                                             # one different mass: the general variant
+            e.upload(pm2, s.vel)
+            assert e.info()["uniform_mass"] == 0
+            e.force(s.G, eps)
+            acc2 = e.download()["acc"]
     finally:
         del os.environ["NBODY_F64_MATH"]
     err = norm_rel_err(acc, ref)
-    print(f"f64 math={math} eps={eps}: force norm-rel err {err:.3e}")
-    assert np.isfinite(acc).all() and err < F64_GATE
+    err2 = norm_rel_err(acc2, oracle.compute_gravity(pm2, s.G, eps, mt=True))
+    print(f"f64 math={math} eps={eps}: force norm-rel err {err:.3e} (one different mass: {err2:.3e})")
+    assert np.isfinite(acc).all() and err < F64_GATE and err2 < F64_GATE
 
 
 # ---------------------------------------------------------------- fp32 -----------
