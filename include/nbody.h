@@ -138,7 +138,8 @@ NBODY_API int nbody_contacts(nbody_ctx* ctx, double margin, unsigned* pairs /* 2
 
 /* What the last nbody_contacts did: out = {bodies flagged by the force sweep's
  * nearest-neighbour tracking, bodies scanned by the pair kernel, pairs found,
- * 1 if the flags were used (0: every body was scanned)}. */
+ * how: 0 every body was scanned against every other, 1 the flagged bodies against
+ * every other, 2 the flagged bodies against each other (under half the bodies flagged)}. */
 NBODY_API int nbody_contact_stats(nbody_ctx* ctx, long long out[4]);
 
 /* ---- renderer feed: position history and ribbon trails ---- */

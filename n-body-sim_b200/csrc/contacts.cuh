@@ -147,4 +147,86 @@ __global__ void __launch_bounds__(kContactThreads)
     }
 }
 
+// ---- candidate x candidate -----------------------------------------------------------------
+// When two ordinary (not "big") bodies overlap, EACH of them has the other within its reach, so
+// both are candidates: the partners of a candidate need only be looked for among the candidates.
+// With F candidates of N bodies that is F^2 tests instead of F*N (N=1M, F=64k: 16x fewer).  The
+// candidates of all devices, concatenated, are first gathered into dense (x, y, z, r) records.
+template <typename Real>
+__global__ void gather_candidates_kernel(const Real* pos, const Real* radius, const unsigned* cand, unsigned n_cand,
+                                         typename Vec4<Real>::type* rec)
+{
+    const unsigned k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_cand) return;
+    const size_t i = cand[k];
+    typename Vec4<Real>::type v;
+    v.x = pos[pm_index<Real>(i, 0)];
+    v.y = pos[pm_index<Real>(i, 1)];
+    v.z = pos[pm_index<Real>(i, 2)];
+    v.w = radius[i];
+    rec[k] = v;
+}
+
+// grid = (blocks of this device's own candidates [i_off, i_off + n_i), chunks of the whole list [0, n_all)).
+// The list is in no particular order, so every (i, j) is visited from both sides and kept where
+// index(i) < index(j).
+template <typename Real>
+__global__ void __launch_bounds__(kContactThreads)
+    contact_pairs_compact_kernel(const typename Vec4<Real>::type* rec, const unsigned* cand, unsigned i_off, unsigned n_i,
+                                 unsigned n_all, unsigned chunk_len, double margin, uint2* pairs, unsigned long long cap,
+                                 unsigned long long* count)
+{
+    using V4 = typename Vec4<Real>::type;
+    constexpr int C = kContactPerThread;
+    __shared__ V4 tile[kContactThreads];
+    __shared__ unsigned tile_idx[kContactThreads];
+    const int tid = threadIdx.x;
+    unsigned ci[C];
+    V4 me[C];
+    float rik[C];
+    const float kSlack = 1.000005f;  // see contact_pairs_kernel
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+        const unsigned k = (blockIdx.x * C + c) * kContactThreads + tid;
+        if (k < n_i) {
+            ci[c] = cand[i_off + k];
+            me[c] = rec[i_off + k];
+        } else {  // parked so far away that every pre-test fails
+            ci[c] = 0xffffffffu;
+            me[c].x = Real(1e30);
+            me[c].y = me[c].z = me[c].w = Real(0);
+        }
+        rik[c] = (float(me[c].w) + float(margin)) * kSlack;
+    }
+    const unsigned j0 = blockIdx.y * chunk_len;
+    const unsigned j1 = (j0 + chunk_len < n_all) ? j0 + chunk_len : n_all;
+    for (unsigned jb = j0; jb < j1; jb += kContactThreads) {
+        __syncthreads();
+        if (jb + tid < j1) {
+            tile[tid] = rec[jb + tid];
+            tile_idx[tid] = cand[jb + tid];
+        }
+        __syncthreads();
+        const int cnt = static_cast<int>(j1 - jb < unsigned(kContactThreads) ? j1 - jb : unsigned(kContactThreads));
+#pragma unroll 4
+        for (int q = 0; q < cnt; ++q) {
+            const V4 b = tile[q];
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                const float dx = float(b.x) - float(me[c].x), dy = float(b.y) - float(me[c].y), dz = float(b.z) - float(me[c].z);
+                const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                const float md = fmaf(float(b.w), kSlack, rik[c]);
+                if (!(d2 <= md * md)) continue;
+                const unsigned i = ci[c], j = tile_idx[q];  // rare from here on
+                if (j <= i) continue;                        // (also drops the parked slots: i = 0xffffffff)
+                if (overlap_exact(double(me[c].x), double(me[c].y), double(me[c].z), double(me[c].w), double(b.x), double(b.y),
+                                  double(b.z), double(b.w), margin)) {
+                    const unsigned long long at = atomicAdd(count, 1ull);
+                    if (at < cap) pairs[at] = make_uint2(i, j);
+                }
+            }
+        }
+    }
+}
+
 }  // namespace nb

@@ -58,6 +58,9 @@ struct Shard {
     float* near = nullptr;              // local: nearest-neighbour rsqrt from the NEAR force kernel
     unsigned* cand = nullptr;           // local: candidate body indices
     unsigned* cand_count = nullptr;
+    unsigned* cand_all = nullptr;       // several devices: the candidates of all of them, concatenated in shard order
+    float4* cand_rec = nullptr;         // dense (x, y, z, r) records of those candidates (contacts.cuh, candidate x candidate)
+    size_t cand_rec_cap = 0;
     unsigned* big = nullptr;            // the big bodies of this shard's own range (global indices)
     unsigned n_big = 0;
     uint2* pairs = nullptr;
@@ -122,7 +125,7 @@ struct nbody_ctx {
     double r_max = 0.0;             // largest radius
     double r_split = 0.0;           // bodies with a larger radius are "big": scanned against everybody (contacts.cuh)
     double r_small_max = 0.0;       // largest radius that is not big
-    long long cstat[4] = {0, 0, 0, 0};  // last nbody_contacts: flagged, scanned, pairs, used_flags
+    long long cstat[4] = {0, 0, 0, 0};  // last nbody_contacts: flagged, scanned, pairs, 0 full scan / 1 candidates x all / 2 candidates x candidates
     int hist_depth = 0;             // 0: no ring
     size_t hist_prev_n = 0;         // an upload changed n: the count the ring still describes, until the next push or remap
     bool hist_fresh_pending = false;  // a remap left rows of new bodies for the next push to fill
@@ -395,6 +398,8 @@ extern "C" void nbody_destroy(nbody_ctx* c)
         cudaFree(s.near);
         cudaFree(s.cand);
         cudaFree(s.cand_count);
+        cudaFree(s.cand_all);
+        cudaFree(s.cand_rec);
         cudaFree(s.big);
         cudaFree(s.pairs);
         cudaFree(s.pair_count);
@@ -1255,43 +1260,105 @@ int launch_pairs(nbody_ctx* c, Shard& s, const unsigned* cand, unsigned n_cand, 
     return NBODY_OK;
 }
 
-// One shard's pairs appended to `keys` as (i << 32 | j): the pairs whose lower index lies in
-// the shard's own range, plus the lower-index partners of its big bodies.
-int shard_contacts(nbody_ctx* c, Shard& s, double margin, bool use_flags, std::vector<unsigned long long>& keys)
+// Stage 1 on one shard: the nearest-neighbour values of the last force sweep -> candidate list
+// (device, s.cand) and its length.
+int shard_flag(nbody_ctx* c, Shard& s, double margin, unsigned* n_cand)
 {
+    *n_cand = 0;
     CU(c, cudaSetDevice(s.device));
     if (s.n_local_real == 0) return NBODY_OK;
-    unsigned n_cand = unsigned(s.n_local_real);
-    if (use_flags) {
-        CU(c, cudaMemsetAsync(s.cand_count, 0, sizeof(unsigned), s.stream));
-        const unsigned blocks = unsigned((s.n_local_real + 255) / 256);
-        flag_near_kernel<<<blocks, 256, 0, s.stream>>>(s.near, static_cast<const float*>(s.radius), s.i_begin, s.n_local_real,
-                                                       float(c->r_small_max + margin) * 1.000001f, float(c->r_split), float(c->near_eps2),
-                                                       s.cand, s.cand_count);
+    CU(c, cudaMemsetAsync(s.cand_count, 0, sizeof(unsigned), s.stream));
+    const unsigned blocks = unsigned((s.n_local_real + 255) / 256);
+    flag_near_kernel<<<blocks, 256, 0, s.stream>>>(s.near, static_cast<const float*>(s.radius), s.i_begin, s.n_local_real,
+                                                   float(c->r_small_max + margin) * 1.000001f, float(c->r_split), float(c->near_eps2), s.cand,
+                                                   s.cand_count);
+    c->launches++;
+    CU(c, cudaGetLastError());
+    CU(c, cudaMemcpyAsync(n_cand, s.cand_count, sizeof *n_cand, cudaMemcpyDeviceToHost, s.stream));
+    CU(c, cudaStreamSynchronize(s.stream));
+    return NBODY_OK;
+}
+
+// Candidate x candidate (contacts.cuh): every device gets the candidates of all devices, concatenated in
+// shard order (offsets[k] = where shard k's own begin), and dense (x, y, z, r) records of them.
+int build_candidate_records(nbody_ctx* c, const std::vector<unsigned>& n_cand, std::vector<unsigned>& offsets, unsigned* total)
+{
+    offsets.assign(c->shards.size(), 0);
+    unsigned F = 0;
+    for (size_t k = 0; k < c->shards.size(); ++k) {
+        offsets[k] = F;
+        F += n_cand[k];
+    }
+    *total = F;
+    std::vector<unsigned> all;
+    if (c->shards.size() > 1) {
+        all.resize(F);
+        for (size_t k = 0; k < c->shards.size(); ++k) {
+            Shard& s = c->shards[k];
+            if (n_cand[k] == 0) continue;
+            CU(c, cudaSetDevice(s.device));
+            CU(c, cudaMemcpy(all.data() + offsets[k], s.cand, n_cand[k] * sizeof(unsigned), cudaMemcpyDeviceToHost));
+        }
+    }
+    for (Shard& s : c->shards) {
+        CU(c, cudaSetDevice(s.device));
+        if (c->shards.size() > 1) {
+            if (!s.cand_all) CU(c, cudaMalloc(&s.cand_all, c->cap_pad * sizeof(unsigned)));
+            CU(c, cudaMemcpyAsync(s.cand_all, all.data(), F * sizeof(unsigned), cudaMemcpyHostToDevice, s.stream));
+        }
+        if (F > s.cand_rec_cap) {
+            CU(c, cudaStreamSynchronize(s.stream));
+            cudaFree(s.cand_rec);
+            s.cand_rec = nullptr;
+            s.cand_rec_cap = 0;
+            const size_t want = std::min<size_t>(c->cap_pad, size_t(F) + F / 4 + 1024);
+            CU(c, cudaMalloc(&s.cand_rec, want * sizeof(float4)));
+            s.cand_rec_cap = want;
+        }
+        const unsigned* list = c->shards.size() > 1 ? s.cand_all : s.cand;
+        gather_candidates_kernel<float><<<(F + 255) / 256, 256, 0, s.stream>>>(static_cast<const float*>(s.pos[c->cur]), static_cast<const float*>(s.radius),
+                                                                               list, F, s.cand_rec);
         c->launches++;
         CU(c, cudaGetLastError());
-        CU(c, cudaMemcpyAsync(&n_cand, s.cand_count, sizeof n_cand, cudaMemcpyDeviceToHost, s.stream));
-        CU(c, cudaStreamSynchronize(s.stream));
-        c->cstat[0] += n_cand + s.n_big;
     }
-    const unsigned n_big = use_flags ? s.n_big : 0;
-    c->cstat[1] += n_cand + n_big;
-    if (n_cand + n_big == 0) return NBODY_OK;
+    if (c->shards.size() > 1)  // `all` is borrowed by the copies above
+        for (Shard& s : c->shards) {
+            CU(c, cudaSetDevice(s.device));
+            CU(c, cudaStreamSynchronize(s.stream));
+        }
+    return NBODY_OK;
+}
+
+int launch_pairs_compact(nbody_ctx* c, Shard& s, unsigned i_off, unsigned n_i, unsigned n_all, double margin)
+{
+    if (n_i == 0) return NBODY_OK;
+    const unsigned per_cta = kContactThreads * kContactPerThread;
+    const unsigned gx = (n_i + per_cta - 1) / per_cta;
+    size_t jch = (size_t(c->sm_count) * 8 + gx - 1) / gx;  // enough CTAs to fill the chip
+    const size_t max_jch = (n_all + kContactThreads - 1) / kContactThreads;
+    jch = std::max<size_t>(1, std::min(jch, std::min<size_t>(max_jch, 65535)));
+    const unsigned chunk_len = unsigned(round_up((n_all + jch - 1) / jch, size_t(kContactThreads)));
+    jch = (n_all + chunk_len - 1) / chunk_len;
+    const unsigned* list = c->shards.size() > 1 ? s.cand_all : s.cand;
+    contact_pairs_compact_kernel<float><<<dim3(gx, unsigned(jch)), kContactThreads, 0, s.stream>>>(s.cand_rec, list, i_off, n_i, n_all, chunk_len, margin,
+                                                                                                    s.pairs, s.pair_cap, s.pair_count);
+    c->launches++;
+    CU(c, cudaGetLastError());
+    return NBODY_OK;
+}
+
+// Stage 2 on one shard: `launch` queues its pair kernels; they run again with a larger buffer until every
+// pair fits, then the pairs join `keys` as (i << 32 | j).
+template <typename L> int shard_collect(nbody_ctx* c, Shard& s, L&& launch, std::vector<unsigned long long>& keys)
+{
+    CU(c, cudaSetDevice(s.device));
     if (s.pair_cap == 0) {
         s.pair_cap = 1 << 16;
         CU(c, cudaMalloc(&s.pairs, s.pair_cap * sizeof(uint2)));
     }
     for (;;) {
         CU(c, cudaMemsetAsync(s.pair_count, 0, sizeof(unsigned long long), s.stream));
-        const unsigned* cand = use_flags ? s.cand : nullptr;
-        int rc;
-        if (c->prec == NBODY_F32) {
-            rc = launch_pairs<float, false>(c, s, cand, n_cand, margin);
-            if (rc == NBODY_OK) rc = launch_pairs<float, true>(c, s, s.big, n_big, margin);
-        } else {
-            rc = launch_pairs<double, false>(c, s, cand, n_cand, margin);
-            if (rc == NBODY_OK) rc = launch_pairs<double, true>(c, s, s.big, n_big, margin);
-        }
+        const int rc = launch();
         if (rc != NBODY_OK) return rc;
         unsigned long long found = 0;
         CU(c, cudaMemcpyAsync(&found, s.pair_count, sizeof found, cudaMemcpyDeviceToHost, s.stream));
@@ -1313,6 +1380,53 @@ int shard_contacts(nbody_ctx* c, Shard& s, double margin, bool use_flags, std::v
     }
 }
 
+// Every shard's pairs: those whose lower index lies in the shard's own range, plus the lower-index
+// partners of its big bodies.
+int all_contacts(nbody_ctx* c, double margin, bool use_flags, std::vector<unsigned long long>& keys)
+{
+    const size_t ns = c->shards.size();
+    std::vector<unsigned> n_cand(ns, 0), offsets(ns, 0);
+    unsigned total = 0;
+    bool compact = false;
+    if (use_flags) {
+        size_t flagged = 0;
+        for (size_t k = 0; k < ns; ++k) {
+            int rc = shard_flag(c, c->shards[k], margin, &n_cand[k]);
+            if (rc != NBODY_OK) return rc;
+            flagged += n_cand[k];
+            c->cstat[0] += n_cand[k] + c->shards[k].n_big;
+        }
+        // F^2 tests among the candidates against F*N/2 of candidates x everybody (contacts.cuh)
+        compact = flagged > 0 && 2 * flagged < c->n && env_int("NBODY_CONTACTS_COMPACT", 1) != 0;
+        if (compact) {
+            int rc = build_candidate_records(c, n_cand, offsets, &total);
+            if (rc != NBODY_OK) return rc;
+        }
+    }
+    if (compact) c->cstat[3] = 2;
+    for (size_t k = 0; k < ns; ++k) {
+        Shard& s = c->shards[k];
+        if (s.n_local_real == 0) continue;
+        const unsigned nc = use_flags ? n_cand[k] : unsigned(s.n_local_real);
+        const unsigned n_big = use_flags ? s.n_big : 0;
+        c->cstat[1] += nc + n_big;
+        if (nc + n_big == 0) continue;
+        int rc = shard_collect(c, s, [&]() -> int {
+            int r;
+            if (c->prec == NBODY_F32) {
+                r = compact ? launch_pairs_compact(c, s, offsets[k], nc, total, margin)
+                            : launch_pairs<float, false>(c, s, use_flags ? s.cand : nullptr, nc, margin);
+                if (r == NBODY_OK) r = launch_pairs<float, true>(c, s, s.big, n_big, margin);
+            } else {
+                r = launch_pairs<double, false>(c, s, nullptr, nc, margin);  // fp64 contexts have no flags: every body is scanned
+            }
+            return r;
+        }, keys);
+        if (rc != NBODY_OK) return rc;
+    }
+    return NBODY_OK;
+}
+
 }  // namespace
 
 extern "C" int nbody_contacts(nbody_ctx* c, double margin, unsigned* pairs, size_t cap, size_t* count)
@@ -1329,10 +1443,8 @@ extern "C" int nbody_contacts(nbody_ctx* c, double margin, unsigned* pairs, size
     c->cstat[3] = use_flags;
     std::vector<unsigned long long> keys;
     try {
-        for (Shard& s : c->shards) {
-            rc = shard_contacts(c, s, margin, use_flags, keys);
-            if (rc != NBODY_OK) return rc;
-        }
+        rc = all_contacts(c, margin, use_flags, keys);
+        if (rc != NBODY_OK) return rc;
         std::sort(keys.begin(), keys.end());  // the reference's visiting order: ascending i, then j (idx:301-305)
         keys.erase(std::unique(keys.begin(), keys.end()), keys.end());  // a big body's scan repeats pairs its partner also found
     } catch (const std::bad_alloc&) {

@@ -151,7 +151,7 @@ class Engine:
         nearest-neighbour tracking, bodies scanned by the pair kernel, pairs found."""
         st = (ctypes.c_longlong * 4)()
         check(self._L.nbody_contact_stats(self._ctx, st), self._ctx)
-        return {"flagged": st[0], "scanned": st[1], "pairs": st[2], "used_flags": bool(st[3])}
+        return {"flagged": st[0], "scanned": st[1], "pairs": st[2], "used_flags": bool(st[3]), "candidates_only": st[3] == 2}
 
     # -- renderer feed: Body.history and ribbon trails (SURVEY.md 8f row 3) -----------------
     def history_enable(self, depth: int = 80) -> None:

@@ -6,6 +6,7 @@ of the overlap loop of resolveCollisions (idx:301-313), and the complete referen
 Pair lists are index work: the bar is bit-exact (same pairs, same order).
 """
 import math
+import os
 
 import numpy as np
 import pytest
@@ -67,7 +68,13 @@ def test_f32_pairs_exact_with_and_without_flags(nb, oracle, n, box, eps, mass):
             b = e.contacts(margin)
             st = e.contact_stats()
             assert st["used_flags"] and st["flagged"] < n
+            assert st["candidates_only"] == (2 * st["flagged"] < n)      # partners sought among the candidates only
             assert np.array_equal(b, oracle.overlap_pairs(*ref_in, margin)), margin
+            os.environ["NBODY_CONTACTS_COMPACT"] = "0"                   # candidates against every body: same list
+            try:
+                assert np.array_equal(e.contacts(margin), b) and not e.contact_stats()["candidates_only"]
+            finally:
+                del os.environ["NBODY_CONTACTS_COMPACT"]
         acc_near = e.download()["acc"]
         # the flags go stale when bodies move
         e.kick1_drift(0.01)
@@ -93,7 +100,7 @@ def test_f32_two_galaxies_131072_pairs_exact(nb, oracle):
         st = e.contact_stats()
         out = e.download()
     ref = oracle.overlap_pairs(out["pos_mass"].astype(np.float64), rad.astype(np.float64), 0.0)
-    assert st["used_flags"] and st["flagged"] < s.n // 2
+    assert st["used_flags"] and st["flagged"] < s.n // 2 and st["candidates_only"]   # candidates x candidates
     assert len(ref) > 0
     assert np.array_equal(got, ref)
 

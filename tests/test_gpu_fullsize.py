@@ -134,6 +134,7 @@ def test_f32_1m_contacts_flagged_equals_full_scan_and_sampled_rows(nb):
         flagged = e.contacts(0.0)
         st = e.contact_stats()
         assert st["used_flags"] and st["flagged"] < n // 4         # reach = r_i + largest ordinary radius
+        assert st["candidates_only"]                                # 178k flagged: F^2 tests instead of F*N
         e.set_radius(rad)                                         # drops the flags
         full = e.contacts(0.0)
         assert not e.contact_stats()["used_flags"]
