@@ -261,14 +261,15 @@ def main():
         # dominant kernel: the force kernel; its launch processes (N/world) x N interactions
         k_inter = inter_step / world
         achieved = k_inter / (k_ms_max * 1e-3) * 1e-9
-        traffic = None
+        traffic = traffic_source = None
         tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")
         if os.path.exists(tp):                      # dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture
             t = json.load(open(tp))
             if t.get("n") == args.n and t.get("world") == world:
-                traffic = {"bytes_per_launch": t["dram_bytes_read"] + t["dram_bytes_write"], "source": t["source"]}
+                traffic = t["dram_bytes_read"] + t["dram_bytes_write"]   # bytes per launch
+                traffic_source = t["source"]
         roof = {"bound": "fp32_issue", "achieved": achieved, "peak": peak_max, "unit": UNIT + " per GPU",
-                "frac": achieved / peak_max, "traffic": traffic,
+                "frac": achieved / peak_max, "traffic": traffic, "traffic_source": traffic_source,
                 "kernel": "force_f32_kernel", "kernel_ms": k_ms_max, "kernel_launches": k_launches,
                 "peak_def": f"{sms} SMs x 128 FP32 lanes x {pk['sm_max_mhz']:.0f} MHz ({pk['src']} sm_max_mhz) / 13 issue slots per interaction",
                 "frac_fp32_pipe_only": achieved / (peak_max * 13 / 12),

@@ -334,7 +334,7 @@ int create_common(nbody_ctx** out, nbody_prec prec, int world, size_t capacity, 
         c->i_tile = kThreads * c->R;
         c->j_unit = kJUnitF64;
     }
-    c->small_path = env_int("NBODY_SMALL", 1) != 0 && !(prec == NBODY_F64 && c->f64_math == 0);
+    c->small_path = env_int("NBODY_SMALL", 1) != 0 && !(prec == NBODY_F64 && c->f64_math != 2);  // (its pair arithmetic is MATH 2's)
     c->cap_pad = round_up(capacity, pad_unit(c));
     *made = c;
     return NBODY_OK;
