@@ -46,6 +46,11 @@ template <typename Real> struct PosOut {
     int n;
 };
 
+// Epoch flags of the peer-store exchange barrier (exchange.cuh).
+struct PeerFlags {
+    unsigned long long* flags[kMaxPeers];  // flags[r] = rank r's flag array (kMaxPeers entries), as mapped here
+};
+
 template <typename Real> struct Vec4;
 template <> struct Vec4<float> { using type = float4; };
 template <> struct Vec4<double> { using type = double4; };

@@ -22,10 +22,6 @@
 
 namespace nb {
 
-struct PeerFlags {
-    unsigned long long* flags[kMaxPeers];  // flags[r] = rank r's flag array (kMaxPeers entries), as mapped here
-};
-
 __device__ __forceinline__ unsigned long long globaltimer_ns()
 {
     unsigned long long t;

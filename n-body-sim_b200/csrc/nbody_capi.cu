@@ -4,32 +4,14 @@
 // world of processes; otherwise it holds n_gpus Shards (ranks 0..n_gpus-1 of a
 // world inside this process).  Both run the same per-step schedule; only the
 // NCCL communicator construction differs.
-#include "../../include/nbody.h"
+#include "capi_ctx.cuh"
 
-#include <cuda_runtime.h>
-
-#include <algorithm>
-#include <cmath>
-#include <cstdarg>
-#include <cstdio>
-#include <cstdlib>
-#include <cstring>
-#include <new>
-#include <string>
-#include <vector>
-
-#include "common.cuh"
-#include "contacts.cuh"
 #include "exchange.cuh"
 #include "force_f32.cuh"
 #include "force_f64.cuh"
 #include "integrate.cuh"
-#include "nccl_dyn.h"
-#include "render.cuh"
 #include "small.cuh"
-#include "trails.cuh"
 
-using namespace nb;
 
 #ifndef NB_UNIFORM_UNROLL
 #define NB_UNIFORM_UNROLL 16
@@ -38,157 +20,7 @@ constexpr int kUniUnroll = NB_UNIFORM_UNROLL;  // inner-loop unroll of the equal
 
 namespace {
 
-struct Shard {
-    int device = 0;
-    int rank = 0;
-    cudaStream_t own_stream = nullptr;
-    cudaStream_t stream = nullptr;
-    void* pos[2] = {nullptr, nullptr};  // full padded pos_mass, double-buffered
-    void* vel = nullptr;                // local range
-    void* acc = nullptr;
-    void* temp = nullptr;
-    void* partial = nullptr;
-    size_t partial_bytes = 0;
-    unsigned* counters = nullptr;
-    void* stage = nullptr;              // AoS staging for upload/download (4*cap_pad elements)
-    double* energy_out = nullptr;
-    size_t energy_rows = 0;
-    // collision broad phase (contacts.cuh)
-    void* radius = nullptr;             // full padded array, Real, replicated like the masses
-    float* near = nullptr;              // local: nearest-neighbour rsqrt from the NEAR force kernel
-    unsigned* cand = nullptr;           // local: candidate body indices
-    unsigned* cand_count = nullptr;
-    unsigned* cand_all = nullptr;       // several devices: the candidates of all of them, concatenated in shard order
-    float4* cand_rec = nullptr;         // dense (x, y, z, r) records of those candidates (contacts.cuh, candidate x candidate)
-    size_t cand_rec_cap = 0;
-    unsigned* big = nullptr;            // the big bodies of this shard's own range (global indices)
-    unsigned n_big = 0;
-    uint2* pairs = nullptr;
-    size_t pair_cap = 0;
-    unsigned long long* pair_count = nullptr;
-    // position history ring (trails.cuh), first shard only: every shard holds all positions
-    void* hist = nullptr;               // Real4 [depth][hist_stride]
-    void* hist_alt = nullptr;           // second ring, the target of nbody_history_remap (the two swap)
-    int* hist_src = nullptr;            // source index per body of the last remap (< 0: new to the ring)
-    float* ribbons = nullptr;           // float [n][depth][6] staging for nbody_trail_ribbons
-    size_t ribbons_bytes = 0;
-    // headless renderer (render.cu), first shard only
-    int* mat_type = nullptr;            // Body.type per body (0 rock, 1 metal, 2 ice)
-    float* mat_seed = nullptr;          // the `seed` uniform of each body's material (idx:492)
-    MassOutlier* outliers = nullptr;    // fp32: bodies whose mass differs from the common one (force_f32.cuh)
-    unsigned* outlier_count = nullptr;  // how many pack_pos_kernel found
-    void* temp_full = nullptr;          // all temperatures gathered on this device (multi-GPU contexts)
-    RenderScratch render_scratch;
-    float4* image = nullptr;
-    int* image_ids = nullptr;
-    size_t image_pixels = 0;
-    ncclComm_t comm = nullptr;
-    // peer-store exchange (exchange.cuh): every rank's two position buffers and flag array as mapped on this device
-    void* peer_pos[kMaxPeers][2] = {};
-    PeerFlags peer_flags = {};
-    unsigned long long* flags = nullptr; // this rank's flag array (kMaxPeers entries)
-    unsigned* xerr = nullptr;            // exchange timeout flag
-    std::vector<void*> ipc_opened;       // IPC mappings to close (rank mode)
-    size_t i_begin = 0;                 // set by upload
-    size_t n_local = 0;                 // padded
-    size_t n_local_real = 0;            // bodies of [i_begin, i_begin+n_local) that are < n
-    // force-kernel timing (shard 0 only)
-    std::vector<cudaEvent_t> ev;
-    size_t ev_used = 0;
-};
-
-}  // namespace
-
-struct nbody_ctx {
-    nbody_prec prec = NBODY_F32;
-    size_t esz = 4;
-    size_t capacity = 0;
-    size_t cap_pad = 0;
-    size_t n = 0, n_pad = 0;   // bodies uploaded; padded for even i-sharding (pads have mass 0)
-    size_t n_j = 0;            // j extent = n rounded up to kJUnit: independent of the GPU count
-    int cur = 0;
-    int world = 1;       // total ranks (devices across all processes)
-    bool rank_mode = false;
-    int my_rank = 0;     // rank of shards[0] in rank mode
-    std::vector<Shard> shards;
-    bool has_temp = false;
-    bool uniform = false;           // fp32: every uploaded mass is the same value -> the 11-op force kernel
-    double uniform_mass = 0.0;
-    int f64_math = 2;               // NBODY_F64_MATH at create
-    int f64_R_forced = 0;          // NBODY_F64_R at create: 1 or 2 i-bodies per thread in the fp64 kernel, 0 = by body count
-    bool small_path = true;         // NBODY_SMALL at create: one-cluster multi-step kernel for n <= kSmallMaxN (small.cuh)
-    bool detect_masses = false;     // upload in flight: pack_pos_kernel compares every mass with uniform_mass
-    std::vector<MassOutlier> outliers;  // ... except these few (at most kMaxOutliers), corrected per i-body
-    bool has_radius = false;        // nbody_set_radius was called for the current body list
-    bool near_valid = false;        // Shard::near describes the CURRENT positions (last launch was a NEAR force pass)
-    double near_eps2 = 0.0;         // softening^2 of that pass
-    double r_max = 0.0;             // largest radius
-    double r_split = 0.0;           // bodies with a larger radius are "big": scanned against everybody (contacts.cuh)
-    double r_small_max = 0.0;       // largest radius that is not big
-    long long cstat[4] = {0, 0, 0, 0};  // last nbody_contacts: flagged, scanned, pairs, 0 full scan / 1 candidates x all / 2 candidates x candidates
-    int hist_depth = 0;             // 0: no ring
-    size_t hist_prev_n = 0;         // an upload changed n: the count the ring still describes, until the next push or remap
-    bool hist_fresh_pending = false;  // a remap left rows of new bodies for the next push to fill
-    size_t hist_stride = 0;         // bodies per slot (= cap_pad)
-    size_t hist_n = 0;              // body count the ring was filled for (0: refill on the next push)
-    int hist_head = 0;              // slot of the newest sample
-    bool has_materials = false;     // nbody_set_materials was called for the current body list
-    bool p2p = false;               // peer-store exchange instead of ncclAllGather
-    unsigned long long epoch = 0;   // exchange barrier epoch (same sequence on every rank)
-    double heat_decay = 0.998;  // CONFIG.heatDecay, /root/reference/index.html:67
-    int R = 4;           // i-bodies per thread (fp32)
-    int i_tile = 512;
-    int j_unit = kJUnit;  // bodies; granularity of the j extent and of the j-chunks
-    int j_chunks = 1;
-    size_t chunk_len = 0;
-    int sm_count = 0;
-    long long launches = 0;
-    bool timing = false;
-    long long t_launches = 0;
-    double t_ms = 0.0;
-    std::string err;
-};
-
-namespace {
-
 int check_exchange(nbody_ctx* c);  // defined with the exchange code below
-
-int fail(nbody_ctx* c, int code, const char* fmt, ...)
-{
-    char buf[512];
-    va_list ap;
-    va_start(ap, fmt);
-    vsnprintf(buf, sizeof buf, fmt, ap);
-    va_end(ap);
-    if (c) c->err = buf;
-    return code;
-}
-
-#define CU(ctx, call)                                                                         \
-    do {                                                                                      \
-        cudaError_t e_ = (call);                                                              \
-        if (e_ != cudaSuccess)                                                                \
-            return fail(ctx, e_ == cudaErrorMemoryAllocation ? NBODY_ENOMEM : NBODY_ECUDA,    \
-                        "%s: %s", #call, cudaGetErrorString(e_));                             \
-    } while (0)
-
-#define NC(ctx, call)                                                                         \
-    do {                                                                                      \
-        ncclResult_t r_ = (call);                                                             \
-        if (r_ != 0)                                                                          \
-            return fail(ctx, NBODY_ENCCL, "%s: %s", #call,                                    \
-                        nccl().GetErrorString ? nccl().GetErrorString(r_) : "nccl error");    \
-    } while (0)
-
-size_t round_up(size_t a, size_t b) { return (a + b - 1) / b * b; }
-
-int env_int(const char* name, int dflt)
-{
-    const char* s = getenv(name);
-    return (s && *s) ? atoi(s) : dflt;
-}
-
-size_t gcd_sz(size_t a, size_t b) { return b ? gcd_sz(b, a % b) : a; }
 
 // fp64 force kernel: two i-bodies per thread pay from ~32k bodies up (N=65,536: 961 -> 974 G interactions/s with
 // equal masses, 906 -> 948 without) and cost below (N=16,384: 304 -> 326 us/step): profiles/r1e_f64_r_uniform.jsonl
@@ -1039,12 +871,6 @@ int launch_kick1_drift(nbody_ctx* c, double dt)
     return rc;
 }
 
-int check_ready(nbody_ctx* c, const char* what)
-{
-    if (!c) return NBODY_EINVAL;
-    if (c->n == 0) return fail(c, NBODY_EINVAL, "%s before upload", what);
-    return NBODY_OK;
-}
 
 }  // namespace
 
@@ -1174,679 +1000,5 @@ extern "C" int nbody_energy(nbody_ctx* c, double G, double softening, double* ki
         momentum[1] = tot[3];
         momentum[2] = tot[4];
     }
-    return NBODY_OK;
-}
-
-// ============================================================================
-// collision broad phase (contacts.cuh)
-// ============================================================================
-
-extern "C" int nbody_set_radius(nbody_ctx* c, const void* radius)
-{
-    int rc = check_ready(c, "set_radius");
-    if (rc != NBODY_OK) return rc;
-    if (!radius) {
-        c->has_radius = false;
-        c->near_valid = false;
-        return NBODY_OK;
-    }
-    std::vector<double> r(c->n);
-    double rmax = 0.0;
-    for (size_t i = 0; i < c->n; ++i) {
-        r[i] = c->prec == NBODY_F32 ? double(static_cast<const float*>(radius)[i]) : static_cast<const double*>(radius)[i];
-        if (!(r[i] >= 0.0)) return fail(c, NBODY_EINVAL, "set_radius: radius[%zu] = %g", i, r[i]);
-        rmax = std::max(rmax, r[i]);
-    }
-    // A few dominant bodies (a galaxy's central mass, idx:750) would make every body a
-    // candidate of the nearest-neighbour test; split them off when they are few.
-    std::vector<double> sorted(r);
-    std::nth_element(sorted.begin(), sorted.begin() + sorted.size() / 2, sorted.end());
-    const double split = 4.0 * sorted[sorted.size() / 2];
-    size_t n_big = 0;
-    double small_max = 0.0;
-    for (double v : r) {
-        if (v > split) n_big++;
-        else small_max = std::max(small_max, v);
-    }
-    const bool use_split = n_big > 0 && n_big <= std::max<size_t>(64, c->n / 256);
-    c->r_split = use_split ? split : rmax;
-    c->r_small_max = use_split ? small_max : rmax;
-    for (Shard& s : c->shards) {
-        CU(c, cudaSetDevice(s.device));
-        CU(c, cudaMemsetAsync(s.radius, 0, c->n_pad * c->esz, s.stream));
-        CU(c, cudaMemcpyAsync(s.radius, radius, c->n * c->esz, cudaMemcpyHostToDevice, s.stream));
-        std::vector<unsigned> big;
-        if (use_split)
-            for (size_t i = s.i_begin; i < std::min(s.i_begin + s.n_local, c->n); ++i)
-                if (r[i] > split) big.push_back(unsigned(i));
-        cudaFree(s.big);
-        s.big = nullptr;
-        s.n_big = unsigned(big.size());
-        if (s.n_big) {
-            CU(c, cudaMalloc(&s.big, big.size() * sizeof(unsigned)));
-            CU(c, cudaMemcpy(s.big, big.data(), big.size() * sizeof(unsigned), cudaMemcpyHostToDevice));
-        }
-    }
-    for (Shard& s : c->shards) {
-        CU(c, cudaSetDevice(s.device));
-        CU(c, cudaStreamSynchronize(s.stream));
-    }
-    c->r_max = rmax;
-    c->has_radius = true;
-    c->near_valid = false;
-    return NBODY_OK;
-}
-
-namespace {
-
-template <typename Real, bool BOTH>
-int launch_pairs(nbody_ctx* c, Shard& s, const unsigned* cand, unsigned n_cand, double margin)
-{
-    if (n_cand == 0) return NBODY_OK;
-    const unsigned per_cta = kContactThreads * kContactPerThread;
-    const unsigned gx = (n_cand + per_cta - 1) / per_cta;
-    // enough CTAs to fill the chip: split the j range when there are few candidate blocks
-    size_t jch = (size_t(c->sm_count) * 8 + gx - 1) / gx;
-    const size_t max_jch = (c->n + kContactThreads - 1) / kContactThreads;
-    jch = std::max<size_t>(1, std::min(jch, std::min<size_t>(max_jch, 65535)));
-    const size_t chunk_len = round_up((c->n + jch - 1) / jch, size_t(kContactThreads));
-    jch = (c->n + chunk_len - 1) / chunk_len;
-    const dim3 grid(gx, unsigned(jch));
-    contact_pairs_kernel<Real, BOTH><<<grid, kContactThreads, 0, s.stream>>>(static_cast<const Real*>(s.pos[c->cur]), static_cast<const Real*>(s.radius),
-                                                                             cand, n_cand, s.i_begin, c->n, chunk_len, margin, s.pairs, s.pair_cap,
-                                                                             s.pair_count);
-    c->launches++;
-    CU(c, cudaGetLastError());
-    return NBODY_OK;
-}
-
-// Stage 1 on one shard: the nearest-neighbour values of the last force sweep -> candidate list
-// (device, s.cand) and its length.
-int shard_flag(nbody_ctx* c, Shard& s, double margin, unsigned* n_cand)
-{
-    *n_cand = 0;
-    CU(c, cudaSetDevice(s.device));
-    if (s.n_local_real == 0) return NBODY_OK;
-    CU(c, cudaMemsetAsync(s.cand_count, 0, sizeof(unsigned), s.stream));
-    const unsigned blocks = unsigned((s.n_local_real + 255) / 256);
-    flag_near_kernel<<<blocks, 256, 0, s.stream>>>(s.near, static_cast<const float*>(s.radius), s.i_begin, s.n_local_real,
-                                                   float(c->r_small_max + margin) * 1.000001f, float(c->r_split), float(c->near_eps2), s.cand,
-                                                   s.cand_count);
-    c->launches++;
-    CU(c, cudaGetLastError());
-    CU(c, cudaMemcpyAsync(n_cand, s.cand_count, sizeof *n_cand, cudaMemcpyDeviceToHost, s.stream));
-    CU(c, cudaStreamSynchronize(s.stream));
-    return NBODY_OK;
-}
-
-// Candidate x candidate (contacts.cuh): every device gets the candidates of all devices, concatenated in
-// shard order (offsets[k] = where shard k's own begin), and dense (x, y, z, r) records of them.
-int build_candidate_records(nbody_ctx* c, const std::vector<unsigned>& n_cand, std::vector<unsigned>& offsets, unsigned* total)
-{
-    offsets.assign(c->shards.size(), 0);
-    unsigned F = 0;
-    for (size_t k = 0; k < c->shards.size(); ++k) {
-        offsets[k] = F;
-        F += n_cand[k];
-    }
-    *total = F;
-    std::vector<unsigned> all;
-    if (c->shards.size() > 1) {
-        all.resize(F);
-        for (size_t k = 0; k < c->shards.size(); ++k) {
-            Shard& s = c->shards[k];
-            if (n_cand[k] == 0) continue;
-            CU(c, cudaSetDevice(s.device));
-            CU(c, cudaMemcpy(all.data() + offsets[k], s.cand, n_cand[k] * sizeof(unsigned), cudaMemcpyDeviceToHost));
-        }
-    }
-    for (Shard& s : c->shards) {
-        CU(c, cudaSetDevice(s.device));
-        if (c->shards.size() > 1) {
-            if (!s.cand_all) CU(c, cudaMalloc(&s.cand_all, c->cap_pad * sizeof(unsigned)));
-            CU(c, cudaMemcpyAsync(s.cand_all, all.data(), F * sizeof(unsigned), cudaMemcpyHostToDevice, s.stream));
-        }
-        if (F > s.cand_rec_cap) {
-            CU(c, cudaStreamSynchronize(s.stream));
-            cudaFree(s.cand_rec);
-            s.cand_rec = nullptr;
-            s.cand_rec_cap = 0;
-            const size_t want = std::min<size_t>(c->cap_pad, size_t(F) + F / 4 + 1024);
-            CU(c, cudaMalloc(&s.cand_rec, want * sizeof(float4)));
-            s.cand_rec_cap = want;
-        }
-        const unsigned* list = c->shards.size() > 1 ? s.cand_all : s.cand;
-        gather_candidates_kernel<float><<<(F + 255) / 256, 256, 0, s.stream>>>(static_cast<const float*>(s.pos[c->cur]), static_cast<const float*>(s.radius),
-                                                                               list, F, s.cand_rec);
-        c->launches++;
-        CU(c, cudaGetLastError());
-    }
-    if (c->shards.size() > 1)  // `all` is borrowed by the copies above
-        for (Shard& s : c->shards) {
-            CU(c, cudaSetDevice(s.device));
-            CU(c, cudaStreamSynchronize(s.stream));
-        }
-    return NBODY_OK;
-}
-
-int launch_pairs_compact(nbody_ctx* c, Shard& s, unsigned i_off, unsigned n_i, unsigned n_all, double margin)
-{
-    if (n_i == 0) return NBODY_OK;
-    const unsigned per_cta = kContactThreads * kContactPerThread;
-    const unsigned gx = (n_i + per_cta - 1) / per_cta;
-    size_t jch = (size_t(c->sm_count) * 8 + gx - 1) / gx;  // enough CTAs to fill the chip
-    const size_t max_jch = (n_all + kContactThreads - 1) / kContactThreads;
-    jch = std::max<size_t>(1, std::min(jch, std::min<size_t>(max_jch, 65535)));
-    const unsigned chunk_len = unsigned(round_up((n_all + jch - 1) / jch, size_t(kContactThreads)));
-    jch = (n_all + chunk_len - 1) / chunk_len;
-    const unsigned* list = c->shards.size() > 1 ? s.cand_all : s.cand;
-    contact_pairs_compact_kernel<float><<<dim3(gx, unsigned(jch)), kContactThreads, 0, s.stream>>>(s.cand_rec, list, i_off, n_i, n_all, chunk_len, margin,
-                                                                                                    s.pairs, s.pair_cap, s.pair_count);
-    c->launches++;
-    CU(c, cudaGetLastError());
-    return NBODY_OK;
-}
-
-// Stage 2 on one shard: `launch` queues its pair kernels; they run again with a larger buffer until every
-// pair fits, then the pairs join `keys` as (i << 32 | j).
-template <typename L> int shard_collect(nbody_ctx* c, Shard& s, L&& launch, std::vector<unsigned long long>& keys)
-{
-    CU(c, cudaSetDevice(s.device));
-    if (s.pair_cap == 0) {
-        s.pair_cap = 1 << 16;
-        CU(c, cudaMalloc(&s.pairs, s.pair_cap * sizeof(uint2)));
-    }
-    for (;;) {
-        CU(c, cudaMemsetAsync(s.pair_count, 0, sizeof(unsigned long long), s.stream));
-        const int rc = launch();
-        if (rc != NBODY_OK) return rc;
-        unsigned long long found = 0;
-        CU(c, cudaMemcpyAsync(&found, s.pair_count, sizeof found, cudaMemcpyDeviceToHost, s.stream));
-        CU(c, cudaStreamSynchronize(s.stream));
-        if (found > s.pair_cap) {  // grow and search again
-            cudaFree(s.pairs);
-            s.pairs = nullptr;
-            s.pair_cap = size_t(found + found / 4 + 1024);
-            CU(c, cudaMalloc(&s.pairs, s.pair_cap * sizeof(uint2)));
-            continue;
-        }
-        if (found) {
-            std::vector<uint2> host(found);
-            CU(c, cudaMemcpyAsync(host.data(), s.pairs, found * sizeof(uint2), cudaMemcpyDeviceToHost, s.stream));
-            CU(c, cudaStreamSynchronize(s.stream));
-            for (const uint2& q : host) keys.push_back((unsigned long long)q.x << 32 | q.y);
-        }
-        return NBODY_OK;
-    }
-}
-
-// Every shard's pairs: those whose lower index lies in the shard's own range, plus the lower-index
-// partners of its big bodies.
-int all_contacts(nbody_ctx* c, double margin, bool use_flags, std::vector<unsigned long long>& keys)
-{
-    const size_t ns = c->shards.size();
-    std::vector<unsigned> n_cand(ns, 0), offsets(ns, 0);
-    unsigned total = 0;
-    bool compact = false;
-    if (use_flags) {
-        size_t flagged = 0;
-        for (size_t k = 0; k < ns; ++k) {
-            int rc = shard_flag(c, c->shards[k], margin, &n_cand[k]);
-            if (rc != NBODY_OK) return rc;
-            flagged += n_cand[k];
-            c->cstat[0] += n_cand[k] + c->shards[k].n_big;
-        }
-        // F^2 tests among the candidates against F*N/2 of candidates x everybody (contacts.cuh)
-        compact = flagged > 0 && 2 * flagged < c->n && env_int("NBODY_CONTACTS_COMPACT", 1) != 0;
-        if (compact) {
-            int rc = build_candidate_records(c, n_cand, offsets, &total);
-            if (rc != NBODY_OK) return rc;
-        }
-    }
-    if (compact) c->cstat[3] = 2;
-    for (size_t k = 0; k < ns; ++k) {
-        Shard& s = c->shards[k];
-        if (s.n_local_real == 0) continue;
-        const unsigned nc = use_flags ? n_cand[k] : unsigned(s.n_local_real);
-        const unsigned n_big = use_flags ? s.n_big : 0;
-        c->cstat[1] += nc + n_big;
-        if (nc + n_big == 0) continue;
-        int rc = shard_collect(c, s, [&]() -> int {
-            int r;
-            if (c->prec == NBODY_F32) {
-                r = compact ? launch_pairs_compact(c, s, offsets[k], nc, total, margin)
-                            : launch_pairs<float, false>(c, s, use_flags ? s.cand : nullptr, nc, margin);
-                if (r == NBODY_OK) r = launch_pairs<float, true>(c, s, s.big, n_big, margin);
-            } else {
-                r = launch_pairs<double, false>(c, s, nullptr, nc, margin);  // fp64 contexts have no flags: every body is scanned
-            }
-            return r;
-        }, keys);
-        if (rc != NBODY_OK) return rc;
-    }
-    return NBODY_OK;
-}
-
-}  // namespace
-
-extern "C" int nbody_contacts(nbody_ctx* c, double margin, unsigned* pairs, size_t cap, size_t* count)
-{
-    int rc = check_ready(c, "contacts");
-    if (rc != NBODY_OK) return rc;
-    if (!count) return fail(c, NBODY_EINVAL, "contacts: count is required");
-    *count = 0;
-    if (!c->has_radius) return fail(c, NBODY_EINVAL, "contacts before set_radius");
-    if (!(margin >= 0.0)) return fail(c, NBODY_EINVAL, "contacts: margin=%g", margin);
-    if (c->n > 0xffffffffull) return fail(c, NBODY_EINVAL, "contacts: n exceeds 32-bit pair indices");
-    const bool use_flags = c->near_valid;
-    c->cstat[0] = c->cstat[1] = c->cstat[2] = 0;
-    c->cstat[3] = use_flags;
-    std::vector<unsigned long long> keys;
-    try {
-        rc = all_contacts(c, margin, use_flags, keys);
-        if (rc != NBODY_OK) return rc;
-        std::sort(keys.begin(), keys.end());  // the reference's visiting order: ascending i, then j (idx:301-305)
-        keys.erase(std::unique(keys.begin(), keys.end()), keys.end());  // a big body's scan repeats pairs its partner also found
-    } catch (const std::bad_alloc&) {
-        return fail(c, NBODY_ENOMEM, "contacts: host allocation failed");
-    }
-    c->cstat[2] = (long long)keys.size();
-    *count = keys.size();
-    if (keys.size() > cap) return fail(c, NBODY_ENOMEM, "contacts: %zu pairs found, room for %zu", keys.size(), cap);
-    if (!pairs && !keys.empty()) return fail(c, NBODY_EINVAL, "contacts: pairs is NULL");
-    for (size_t k = 0; k < keys.size(); ++k) {
-        pairs[2 * k] = unsigned(keys[k] >> 32);
-        pairs[2 * k + 1] = unsigned(keys[k] & 0xffffffffull);
-    }
-    return NBODY_OK;
-}
-
-extern "C" int nbody_contact_stats(nbody_ctx* c, long long out[4])
-{
-    if (!c || !out) return NBODY_EINVAL;
-    for (int k = 0; k < 4; ++k) out[k] = c->cstat[k];
-    return NBODY_OK;
-}
-
-// ============================================================================
-// renderer feed: position history ring + ribbon trails (trails.cuh)
-// ============================================================================
-
-extern "C" int nbody_history_enable(nbody_ctx* c, int depth)
-{
-    if (!c) return NBODY_EINVAL;
-    if (depth != 0 && (depth < 2 || depth > 256)) return fail(c, NBODY_EINVAL, "history_enable: depth=%d outside 2..256", depth);
-    Shard& s = c->shards[0];
-    CU(c, cudaSetDevice(s.device));
-    CU(c, cudaStreamSynchronize(s.stream));
-    cudaFree(s.hist);
-    cudaFree(s.hist_alt);
-    s.hist = s.hist_alt = nullptr;
-    c->hist_depth = 0;
-    c->hist_n = c->hist_prev_n = 0;
-    c->hist_fresh_pending = false;
-    c->hist_head = 0;
-    if (depth == 0) return NBODY_OK;
-    c->hist_stride = c->cap_pad;
-    CU(c, cudaMalloc(&s.hist, size_t(depth) * c->hist_stride * 4 * c->esz));
-    c->hist_depth = depth;
-    const int smem = (depth + 1) * 512;  // trail_bodies() x sizeof(Real4) = 512 B per sample in either precision, one padding element per body
-    if (c->prec == NBODY_F32) CU(c, cudaFuncSetAttribute(trail_ribbons_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    else CU(c, cudaFuncSetAttribute(trail_ribbons_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    return NBODY_OK;
-}
-
-extern "C" int nbody_history_push(nbody_ctx* c)
-{
-    int rc = check_ready(c, "history_push");
-    if (rc != NBODY_OK) return rc;
-    if (c->hist_depth == 0) return fail(c, NBODY_EINVAL, "history_push before history_enable");
-    Shard& s = c->shards[0];
-    CU(c, cudaSetDevice(s.device));
-    const int fill = c->hist_n != c->n;
-    const int* fresh = (!fill && c->hist_fresh_pending) ? s.hist_src : nullptr;  // bodies new to a remapped ring
-    c->hist_fresh_pending = false;
-    c->hist_prev_n = 0;
-    if (fill) c->hist_head = 0;
-    else c->hist_head = (c->hist_head + c->hist_depth - 1) % c->hist_depth;  // unshift: the newest sample moves one slot back
-    const unsigned blocks = unsigned((c->n + 255) / 256);
-    if (c->prec == NBODY_F32)
-        history_push_kernel<float><<<blocks, 256, 0, s.stream>>>((const float*)s.pos[c->cur], (float4*)s.hist, c->n, c->hist_stride, c->hist_head,
-                                                                 c->hist_depth, fill, fresh);
-    else
-        history_push_kernel<double><<<blocks, 256, 0, s.stream>>>((const double*)s.pos[c->cur], (double4*)s.hist, c->n, c->hist_stride, c->hist_head,
-                                                                  c->hist_depth, fill, fresh);
-    c->launches++;
-    CU(c, cudaGetLastError());
-    c->hist_n = c->n;
-    return NBODY_OK;
-}
-
-extern "C" int nbody_history_remap(nbody_ctx* c, const int* source)
-{
-    int rc = check_ready(c, "history_remap");
-    if (rc != NBODY_OK) return rc;
-    if (!source) return fail(c, NBODY_EINVAL, "history_remap: source is NULL");
-    const size_t old_n = c->hist_n ? c->hist_n : c->hist_prev_n;  // the list the ring was last pushed for
-    if (c->hist_depth == 0 || old_n == 0) return fail(c, NBODY_EINVAL, "history_remap: no history to carry over (enable, then push)");
-    for (size_t i = 0; i < c->n; ++i)
-        if (source[i] >= 0 && size_t(source[i]) >= old_n)
-            return fail(c, NBODY_EINVAL, "history_remap: source[%zu]=%d outside the previous list of %zu bodies", i, source[i], old_n);
-    Shard& s = c->shards[0];
-    CU(c, cudaSetDevice(s.device));
-    const size_t ring_bytes = size_t(c->hist_depth) * c->hist_stride * 4 * c->esz;
-    if (!s.hist_alt) CU(c, cudaMalloc(&s.hist_alt, ring_bytes));
-    if (!s.hist_src) CU(c, cudaMalloc(&s.hist_src, c->cap_pad * sizeof(int)));
-    CU(c, cudaMemcpyAsync(s.hist_src, source, c->n * sizeof(int), cudaMemcpyHostToDevice, s.stream));
-    const unsigned blocks = unsigned((c->n + 255) / 256);
-    if (c->prec == NBODY_F32)
-        history_remap_kernel<float><<<blocks, 256, 0, s.stream>>>((const float4*)s.hist, (float4*)s.hist_alt, s.hist_src, c->n, c->hist_stride, c->hist_depth);
-    else
-        history_remap_kernel<double><<<blocks, 256, 0, s.stream>>>((const double4*)s.hist, (double4*)s.hist_alt, s.hist_src, c->n, c->hist_stride, c->hist_depth);
-    c->launches++;
-    CU(c, cudaGetLastError());
-    CU(c, cudaStreamSynchronize(s.stream));  // `source` is borrowed for the call only
-    std::swap(s.hist, s.hist_alt);
-    c->hist_n = c->n;
-    c->hist_prev_n = 0;
-    c->hist_fresh_pending = true;
-    return NBODY_OK;
-}
-
-namespace {
-int history_ready(nbody_ctx* c, const char* what)
-{
-    int rc = check_ready(c, what);
-    if (rc != NBODY_OK) return rc;
-    if (c->hist_depth == 0 || c->hist_n != c->n || c->hist_fresh_pending)
-        return fail(c, NBODY_EINVAL, "%s: no history for the current body list (enable, then push)", what);
-    return NBODY_OK;
-}
-}  // namespace
-
-extern "C" int nbody_history_download(nbody_ctx* c, void* out)
-{
-    int rc = history_ready(c, "history_download");
-    if (rc != NBODY_OK) return rc;
-    if (!out) return fail(c, NBODY_EINVAL, "history_download: out is NULL");
-    Shard& s = c->shards[0];
-    CU(c, cudaSetDevice(s.device));
-    const size_t elems = c->n * size_t(c->hist_depth) * 3;
-    const size_t bytes = elems * c->esz;
-    if (bytes > s.ribbons_bytes) {
-        CU(c, cudaStreamSynchronize(s.stream));
-        cudaFree(s.ribbons);
-        s.ribbons = nullptr;
-        s.ribbons_bytes = 0;
-        CU(c, cudaMalloc(&s.ribbons, bytes));
-        s.ribbons_bytes = bytes;
-    }
-    const unsigned blocks = unsigned((c->n * size_t(c->hist_depth) + 255) / 256);
-    if (c->prec == NBODY_F32)
-        history_gather_kernel<float><<<blocks, 256, 0, s.stream>>>((const float4*)s.hist, (float*)s.ribbons, c->n, c->hist_stride, c->hist_head, c->hist_depth);
-    else
-        history_gather_kernel<double><<<blocks, 256, 0, s.stream>>>((const double4*)s.hist, (double*)s.ribbons, c->n, c->hist_stride, c->hist_head, c->hist_depth);
-    c->launches++;
-    CU(c, cudaGetLastError());
-    CU(c, cudaMemcpyAsync(out, s.ribbons, bytes, cudaMemcpyDeviceToHost, s.stream));
-    CU(c, cudaStreamSynchronize(s.stream));
-    return NBODY_OK;
-}
-
-namespace {
-// Builds the ribbons into Shard::ribbons (device); shared by the download call and the timing hook.
-int build_ribbons(nbody_ctx* c, const double camera[3])
-{
-    Shard& s = c->shards[0];
-    CU(c, cudaSetDevice(s.device));
-    const size_t bytes = c->n * size_t(c->hist_depth) * 6 * sizeof(float);
-    if (bytes > s.ribbons_bytes) {
-        CU(c, cudaStreamSynchronize(s.stream));
-        cudaFree(s.ribbons);
-        s.ribbons = nullptr;
-        s.ribbons_bytes = 0;
-        CU(c, cudaMalloc(&s.ribbons, bytes));
-        s.ribbons_bytes = bytes;
-    }
-    const size_t bpb = c->prec == NBODY_F32 ? trail_bodies<float>() : trail_bodies<double>();
-    const unsigned blocks = unsigned((c->n + bpb - 1) / bpb);
-    const size_t smem = size_t(c->hist_depth + 1) * 512;
-    if (c->prec == NBODY_F32)
-        trail_ribbons_kernel<float><<<blocks, kTrailThreads, smem, s.stream>>>((const float4*)s.hist, (const float*)s.radius, s.ribbons, c->n, c->hist_stride,
-                                                                               c->hist_head, c->hist_depth, c->hist_depth, float(camera[0]),
-                                                                               float(camera[1]), float(camera[2]));
-    else
-        trail_ribbons_kernel<double><<<blocks, kTrailThreads, smem, s.stream>>>((const double4*)s.hist, (const double*)s.radius, s.ribbons, c->n,
-                                                                                c->hist_stride, c->hist_head, c->hist_depth, c->hist_depth, camera[0],
-                                                                                camera[1], camera[2]);
-    c->launches++;
-    CU(c, cudaGetLastError());
-    return NBODY_OK;
-}
-}  // namespace
-
-extern "C" int nbody_trail_ribbons(nbody_ctx* c, const double camera[3], float* out)
-{
-    int rc = history_ready(c, "trail_ribbons");
-    if (rc != NBODY_OK) return rc;
-    if (!camera) return fail(c, NBODY_EINVAL, "trail_ribbons: camera is NULL");
-    if (!c->has_radius) return fail(c, NBODY_EINVAL, "trail_ribbons before set_radius");
-    rc = build_ribbons(c, camera);
-    if (rc != NBODY_OK) return rc;
-    Shard& s = c->shards[0];
-    if (out) {  // out == NULL: build on the device only (timing)
-        CU(c, cudaMemcpyAsync(out, s.ribbons, c->n * size_t(c->hist_depth) * 6 * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
-        CU(c, cudaStreamSynchronize(s.stream));
-    }
-    return NBODY_OK;
-}
-
-// ============================================================================
-// snapshots
-// ============================================================================
-
-namespace {
-struct SnapHeader {
-    char magic[8];
-    unsigned long long n, step;
-    double dt, G, softening;
-    unsigned prec, flags;
-    unsigned long long reserved;
-};
-static_assert(sizeof(SnapHeader) == 64, "snapshot header is 64 bytes");
-const char kSnapMagic[8] = {'N', 'B', 'O', 'D', 'Y', 'S', 'N', '1'};
-}  // namespace
-
-extern "C" int nbody_snapshot_save(nbody_ctx* c, const char* path, unsigned long long step, double dt, double G, double softening)
-{
-    int rc = check_ready(c, "snapshot_save");
-    if (rc != NBODY_OK) return rc;
-    if (!path) return fail(c, NBODY_EINVAL, "snapshot_save: path is NULL");
-    if (c->rank_mode && c->world > 1) return fail(c, NBODY_EINVAL, "snapshot_save: a rank holds only its own vel/acc; gather on the host instead");
-    const size_t n = c->n, esz = c->esz;
-    std::vector<char> pm, vel, acc, temp, rad;
-    try {
-        pm.resize(4 * n * esz);
-        vel.resize(4 * n * esz);
-        acc.resize(4 * n * esz);
-        if (c->has_temp) temp.resize(n * esz);
-        if (c->has_radius) rad.resize(n * esz);
-    } catch (const std::bad_alloc&) {
-        return fail(c, NBODY_ENOMEM, "snapshot_save: host allocation failed");
-    }
-    rc = nbody_download(c, pm.data(), vel.data(), acc.data(), c->has_temp ? temp.data() : nullptr);
-    if (rc != NBODY_OK) return rc;
-    if (c->has_radius) {
-        Shard& s = c->shards[0];
-        CU(c, cudaSetDevice(s.device));
-        CU(c, cudaMemcpy(rad.data(), s.radius, n * esz, cudaMemcpyDeviceToHost));
-    }
-    SnapHeader h;
-    memset(&h, 0, sizeof h);
-    memcpy(h.magic, kSnapMagic, 8);
-    h.n = n;
-    h.step = step;
-    h.dt = dt;
-    h.G = G;
-    h.softening = softening;
-    h.prec = unsigned(c->prec);
-    h.flags = (c->has_temp ? 1u : 0u) | (c->has_radius ? 2u : 0u);
-    FILE* f = fopen(path, "wb");
-    if (!f) return fail(c, NBODY_EIO, "snapshot_save: cannot open %s", path);
-    bool ok = fwrite(&h, sizeof h, 1, f) == 1;
-    for (const std::vector<char>* a : {&pm, &vel, &acc, &temp, &rad})
-        if (ok && !a->empty()) ok = fwrite(a->data(), 1, a->size(), f) == a->size();
-    ok = (fclose(f) == 0) && ok;
-    return ok ? NBODY_OK : fail(c, NBODY_EIO, "snapshot_save: short write to %s", path);
-}
-
-extern "C" int nbody_snapshot_load(nbody_ctx* c, const char* path, unsigned long long* step, double* dt, double* G, double* softening)
-{
-    if (!c) return NBODY_EINVAL;
-    if (!path) return fail(c, NBODY_EINVAL, "snapshot_load: path is NULL");
-    FILE* f = fopen(path, "rb");
-    if (!f) return fail(c, NBODY_EIO, "snapshot_load: cannot open %s", path);
-    SnapHeader h;
-    if (fread(&h, sizeof h, 1, f) != 1 || memcmp(h.magic, kSnapMagic, 8) != 0) {
-        fclose(f);
-        return fail(c, NBODY_EIO, "snapshot_load: %s is not an NBODYSN1 snapshot", path);
-    }
-    if (h.prec != unsigned(c->prec) || h.n == 0 || h.n > c->capacity || (h.flags & ~3u)) {
-        fclose(f);
-        return fail(c, NBODY_EINVAL, "snapshot_load: n=%llu precision=%u flags=%u do not fit this context (capacity %zu, precision %d)", h.n, h.prec,
-                    h.flags, c->capacity, int(c->prec));
-    }
-    const size_t n = size_t(h.n), esz = c->esz;
-    std::vector<char> pm, vel, acc, temp, rad;
-    try {
-        pm.resize(4 * n * esz);
-        vel.resize(4 * n * esz);
-        acc.resize(4 * n * esz);
-        if (h.flags & 1u) temp.resize(n * esz);
-        if (h.flags & 2u) rad.resize(n * esz);
-    } catch (const std::bad_alloc&) {
-        fclose(f);
-        return fail(c, NBODY_ENOMEM, "snapshot_load: host allocation failed");
-    }
-    bool ok = true;
-    for (std::vector<char>* a : {&pm, &vel, &acc, &temp, &rad})
-        if (ok && !a->empty()) ok = fread(a->data(), 1, a->size(), f) == a->size();
-    char extra;
-    ok = ok && fread(&extra, 1, 1, f) == 0;  // nothing may follow
-    fclose(f);
-    if (!ok) return fail(c, NBODY_EIO, "snapshot_load: %s is truncated or has trailing bytes", path);
-    int rc = nbody_upload(c, n, pm.data(), vel.data(), acc.data(), (h.flags & 1u) ? temp.data() : nullptr);
-    if (rc != NBODY_OK) return rc;
-    if (h.flags & 2u) {
-        rc = nbody_set_radius(c, rad.data());
-        if (rc != NBODY_OK) return rc;
-    }
-    if (step) *step = h.step;
-    if (dt) *dt = h.dt;
-    if (G) *G = h.G;
-    if (softening) *softening = h.softening;
-    return NBODY_OK;
-}
-
-// ============================================================================
-// headless body renderer (render.cu)
-// ============================================================================
-
-extern "C" int nbody_set_materials(nbody_ctx* c, const int* type, const float* seed)
-{
-    int rc = check_ready(c, "set_materials");
-    if (rc != NBODY_OK) return rc;
-    Shard& s = c->shards[0];
-    CU(c, cudaSetDevice(s.device));
-    if (type)
-        for (size_t i = 0; i < c->n; ++i)
-            if (type[i] < 0 || type[i] > 2) return fail(c, NBODY_EINVAL, "set_materials: type[%zu] = %d (0 rock, 1 metal, 2 ice)", i, type[i]);
-    if (!s.mat_type) {
-        CU(c, cudaMalloc(&s.mat_type, c->cap_pad * sizeof(int)));
-        CU(c, cudaMalloc(&s.mat_seed, c->cap_pad * sizeof(float)));
-    }
-    CU(c, cudaMemsetAsync(s.mat_type, 0, c->n * sizeof(int), s.stream));
-    CU(c, cudaMemsetAsync(s.mat_seed, 0, c->n * sizeof(float), s.stream));
-    if (type) CU(c, cudaMemcpyAsync(s.mat_type, type, c->n * sizeof(int), cudaMemcpyHostToDevice, s.stream));
-    if (seed) CU(c, cudaMemcpyAsync(s.mat_seed, seed, c->n * sizeof(float), cudaMemcpyHostToDevice, s.stream));
-    CU(c, cudaStreamSynchronize(s.stream));
-    c->has_materials = true;
-    return NBODY_OK;
-}
-
-extern "C" int nbody_render(nbody_ctx* c, int width, int height, const double cam_position[3], const double cam_target[3],
-                            double fov_deg, float* rgba, int* ids)
-{
-    int rc = check_ready(c, "render");
-    if (rc != NBODY_OK) return rc;
-    if (width < 1 || height < 1 || size_t(width) * size_t(height) > (size_t(1) << 28))
-        return fail(c, NBODY_EINVAL, "render: %d x %d", width, height);
-    if (!cam_position || !cam_target || !(fov_deg > 0.0 && fov_deg < 180.0)) return fail(c, NBODY_EINVAL, "render: camera");
-    if (!c->has_radius) return fail(c, NBODY_EINVAL, "render before set_radius");
-    if (c->rank_mode && c->world > 1) return fail(c, NBODY_EINVAL, "render: a rank holds only its own temperatures; render from a single-process context");
-    if (c->n > 0xffffffffull) return fail(c, NBODY_EINVAL, "render: n exceeds the 32-bit body id of the depth buffer");
-    // Matrix4.lookAt(position, target, up = +y) in double, stored as float (render.cuh)
-    RenderCamera cam;
-    double z[3] = {cam_position[0] - cam_target[0], cam_position[1] - cam_target[1], cam_position[2] - cam_target[2]};
-    double l = sqrt(z[0] * z[0] + z[1] * z[1] + z[2] * z[2]);
-    if (!(l > 0.0)) return fail(c, NBODY_EINVAL, "render: camera position equals its target");
-    for (double& v : z) v /= l;
-    double x[3] = {1.0 * z[2] - 0.0 * z[1], 0.0 * z[0] - 0.0 * z[2], 0.0 * z[1] - 1.0 * z[0]};
-    l = sqrt(x[0] * x[0] + x[1] * x[1] + x[2] * x[2]);
-    if (!(l > 0.0)) return fail(c, NBODY_EINVAL, "render: the camera looks along its up axis");
-    for (double& v : x) v /= l;
-    const double y[3] = {z[1] * x[2] - z[2] * x[1], z[2] * x[0] - z[0] * x[2], z[0] * x[1] - z[1] * x[0]};
-    for (int k = 0; k < 3; ++k) {
-        cam.pos[k] = float(cam_position[k]);
-        cam.xa[k] = float(x[k]);
-        cam.ya[k] = float(y[k]);
-        cam.za[k] = float(z[k]);
-    }
-    cam.tan_half = float(tan(fov_deg * 3.14159265358979323846 / 360.0));
-    cam.aspect = float(width) / float(height);
-    cam.near = 0.1f;  // PerspectiveCamera(45, aspect, 0.1, 3000), idx:704
-
-    Shard& s = c->shards[0];
-    CU(c, cudaSetDevice(s.device));
-    const size_t pixels = size_t(width) * size_t(height);
-    if (pixels > s.image_pixels) {
-        CU(c, cudaStreamSynchronize(s.stream));
-        render_scratch_free(s.render_scratch);
-        cudaFree(s.image);
-        cudaFree(s.image_ids);
-        s.image = nullptr;
-        s.image_ids = nullptr;
-        s.image_pixels = 0;
-        CU(c, cudaMalloc(&s.image, pixels * sizeof(float4)));
-        CU(c, cudaMalloc(&s.image_ids, pixels * sizeof(int)));
-        s.image_pixels = pixels;
-    }
-    // temperatures: the renderer's `temperature` uniform (idx:553); sharded state is gathered on this device
-    const void* temp = c->has_temp ? s.temp : nullptr;
-    if (c->has_temp && c->shards.size() > 1) {
-        if (!s.temp_full) CU(c, cudaMalloc(&s.temp_full, c->cap_pad * c->esz));
-        for (Shard& o : c->shards) {
-            if (o.n_local_real == 0) continue;
-            CU(c, cudaSetDevice(o.device));
-            CU(c, cudaStreamSynchronize(o.stream));
-            CU(c, cudaMemcpy(static_cast<char*>(s.temp_full) + std::min(o.i_begin, c->n) * c->esz, o.temp, o.n_local_real * c->esz, cudaMemcpyDefault));
-        }
-        CU(c, cudaSetDevice(s.device));
-        temp = s.temp_full;
-    }
-    const int* type = c->has_materials ? s.mat_type : nullptr;
-    const float* seed = c->has_materials ? s.mat_seed : nullptr;
-    cudaError_t e;
-    if (c->prec == NBODY_F32)
-        e = render_launch<float>((const float*)s.pos[c->cur], (const float*)s.radius, (const float*)temp, type, seed, c->n, cam, width, height, s.render_scratch,
-                                 s.image, ids ? s.image_ids : nullptr, s.stream);
-    else
-        e = render_launch<double>((const double*)s.pos[c->cur], (const double*)s.radius, (const double*)temp, type, seed, c->n, cam, width, height,
-                                  s.render_scratch, s.image, ids ? s.image_ids : nullptr, s.stream);
-    c->launches += 4;  // bin count, scan, bin fill, tile render
-    if (e != cudaSuccess) return fail(c, NBODY_ECUDA, "render: %s", cudaGetErrorString(e));
-    if (rgba) CU(c, cudaMemcpyAsync(rgba, s.image, pixels * sizeof(float4), cudaMemcpyDeviceToHost, s.stream));
-    if (ids) CU(c, cudaMemcpyAsync(ids, s.image_ids, pixels * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
-    if (rgba || ids) CU(c, cudaStreamSynchronize(s.stream));  // rgba == NULL: the frame stays on the device (timing)
     return NBODY_OK;
 }

@@ -13,9 +13,14 @@ from typing import Tuple
 import math
 
 I_TILE_F32 = 512   # kF32Threads * R (128 x 4), csrc/common.cuh
-I_TILE_F64 = 256   # kThreads
+I_TILE_F64 = 256   # kThreads; 512 from 32,768 bodies up (two i-bodies per thread, nbody_capi.cu f64_bodies_per_thread)
 J_UNIT_F32 = 512   # kJUnit: one ring stage of the fp32 kernel
 J_UNIT_F64 = 64    # kJUnitF64
+
+
+def i_tile_f64(n: int) -> int:
+    """The fp64 kernel's i-tile for n bodies (nbody_info.i_tile reports the same)."""
+    return 512 if n >= 32768 else I_TILE_F64
 
 
 def padded_n(n: int, world: int, i_tile: int, j_unit: int = J_UNIT_F32) -> int:
