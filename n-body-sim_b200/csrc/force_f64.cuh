@@ -12,8 +12,9 @@
 //   1  1/pow(s,1.5) = y^3 with y = rsqrt(s): MUFU.RSQ64H seed (2^-26) and one cubically
 //      convergent correction (5 DP ops, y to ~1 ulp); G applied once per body.  Everything
 //      else as in 0.  23 DP instructions + 1 MUFU, no branches.
-//   2  (default) as 1 with the multiply-adds of distSq and of the accumulation contracted
-//      (DFMA: one rounding instead of two).  17 DP instructions + 1 MUFU.
+//   2  (default) the multiply-adds of distSq and of the accumulation contracted (DFMA: one
+//      rounding instead of two) and s^-1.5 taken directly from the seed (inv_cube_f64: 6 DP ops
+//      instead of 5 + 2, and closer to the exact value).  16 DP instructions + 1 MUFU.
 // Per-step error against the oracle, all three: ~3e-16 (tests/test_gpu_parity.py prints it).
 // For body i with j < i the reference accumulates -(f*m_j)*(pos_i - pos_j),
 // which is bit-identical to +(f*m_j)*(pos_j - pos_i) (negation is exact), so a
@@ -39,6 +40,21 @@ __device__ __forceinline__ double rsqrt_f64(double s)
     return __fma_rn(c, __dmul_rn(y, e), y);
 }
 
+// s^-1.5 to ~2 ulp in 6 DP instructions: with c = y0^2 and e = 1 - s*c,
+//   s^-1.5 = y0^3 * (1 - e)^-1.5 = y0^3 * (1 + e*(3/2 + 15/8 e) + O(e^3)).
+// Measured on the host against quad precision with a seed truncated to the high word (2^-21, worse
+// than MUFU.RSQ64H's): max 2.1 x 2^-53 relative, against 4.9 x 2^-53 for rsqrt_f64(s)^3 (7 instructions).
+__device__ __forceinline__ double inv_cube_f64(double s)
+{
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(s));  // MUFU.RSQ64H
+    const double c = __dmul_rn(y, y);
+    const double e = __fma_rn(s, -c, 1.0);
+    const double c3 = __dmul_rn(c, y);
+    const double p = __fma_rn(e, 1.875, 1.5);
+    return __fma_rn(c3, __dmul_rn(p, e), c3);
+}
+
 #ifndef NB_F64_UNROLL
 #define NB_F64_UNROLL 4  // N=65,536: unroll 1 / 2 / 4 = 830 / 882 / 907 G interactions/s (profiles/r1e_f64_variants.jsonl)
 #endif
@@ -52,7 +68,7 @@ constexpr int kF64BodiesPerThread = NB_F64_R;  // default i-bodies per thread (N
 // reference never evaluates it, idx:273).  With softening it contributes an exact zero by
 // itself and the select is not compiled in.
 // UNIFORM (MATH 2 only): every mass is the same value (config 2's Plummer sphere: 1/N), the
-// per-pair multiply by m_j drops out -- 16 DP instructions -- and the common mass joins G; pads sit
+// per-pair multiply by m_j drops out -- 15 DP instructions -- and the common mass joins G; pads sit
 // at x = 1e150, where y^3 underflows to an exact 0.  R: i-bodies per thread (more independent chains).
 template <int MATH, bool ZERO_SOFT, bool UNIFORM = false, int R = 1>
 __global__ void __launch_bounds__(kThreads + 32) force_f64_kernel(const ForceParams<double> p)
@@ -140,8 +156,12 @@ __global__ void __launch_bounds__(kThreads + 32) force_f64_kernel(const ForcePar
                 if (MATH == 0) {
                     fm = __dmul_rn(__ddiv_rn(p.G, __dmul_rn(s, __dsqrt_rn(s))), b.w);
                 } else {
-                    const double y = rsqrt_f64(s);
-                    fm = __dmul_rn(__dmul_rn(y, y), y);  // G (and the common mass) join in the epilogue
+                    if (MATH == 2) {
+                        fm = inv_cube_f64(s);  // G (and the common mass) join in the epilogue
+                    } else {
+                        const double y = rsqrt_f64(s);
+                        fm = __dmul_rn(__dmul_rn(y, y), y);
+                    }
                     if (!UNIFORM) fm = __dmul_rn(fm, b.w);
                 }
                 if (ZERO_SOFT && q == self_q[r]) fm = 0.0;  // the reference never evaluates the self pair (idx:273)

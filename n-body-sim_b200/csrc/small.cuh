@@ -62,8 +62,7 @@ __device__ __forceinline__ void small_pair(const double4& me, const double4& b, 
 {
     const double vx = __dsub_rn(b.x, me.x), vy = __dsub_rn(b.y, me.y), vz = __dsub_rn(b.z, me.z);
     const double s = __fma_rn(vz, vz, __fma_rn(vy, vy, __fma_rn(vx, vx, eps2)));
-    const double y = rsqrt_f64(s);
-    double fm = __dmul_rn(__dmul_rn(__dmul_rn(y, y), y), b.w);
+    double fm = __dmul_rn(inv_cube_f64(s), b.w);
     if (self) fm = 0.0;  // the reference never evaluates the self pair (idx:273); with eps = 0 it would be 0 * inf
     ax = __fma_rn(fm, vx, ax);
     ay = __fma_rn(fm, vy, ay);
@@ -108,8 +107,7 @@ __device__ __forceinline__ void small_pair4(const double4& me, const double4& b0
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         const double s = __fma_rn(vz[k], vz[k], __fma_rn(vy[k], vy[k], __fma_rn(vx[k], vx[k], eps2)));
-        const double y = rsqrt_f64(s);
-        fm[k] = __dmul_rn(__dmul_rn(__dmul_rn(y, y), y), b[k].w);
+        fm[k] = __dmul_rn(inv_cube_f64(s), b[k].w);
         if (k == self) fm[k] = 0.0;
     }
 #pragma unroll
