@@ -13,7 +13,7 @@
 // per interaction of the roofline in 7 issue slots instead of 13.
 // G is applied once per body.
 //
-// Shape (4 compute warps, R = 4, unroll 4, 128 registers, 3 CTAs/SM) is the best of
+// Shape (4 compute warps, R = 4, unroll 16, 128 registers, 3 CTAs/SM) is the best of
 // the force_lab sweeps (profiles/r1_force_lab_sweep*.txt): 9.2 interactions/clk/SM.
 // The plateau is insensitive to ring depth, unroll and occupancy, and an 11-op
 // formulation (mass-scaled coordinates) does not move it: the packed FP32
