@@ -259,6 +259,8 @@ typedef struct {
     int exchange;        /* position exchange: 0 none (1 GPU), 1 ncclAllGather, 2 fused peer stores over NVLink */
     int uniform_mass;    /* 0: general fp32 force kernel.  1: every uploaded mass is equal and the kernel skips the per-pair
                             mass multiply.  1+k: all but k (<= 64) bodies share one mass; same kernel, k corrections per body */
+    int f64_symmetric;   /* fp64, one GPU: > 0 when the force pass evaluates every pair once and applies it to both bodies,
+                            as the reference's i<j loop does (idx:272-288); the value is the j-blocks per CTA.  0: one-sided */
 } nbody_info;
 NBODY_API int nbody_get_info(nbody_ctx* ctx, nbody_info* out);
 

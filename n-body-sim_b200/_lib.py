@@ -43,7 +43,7 @@ class Info(ctypes.Structure):
         ("i_end", ctypes.c_size_t), ("n_gpus", ctypes.c_int), ("world", ctypes.c_int),
         ("rank", ctypes.c_int), ("sm_count", ctypes.c_int), ("j_chunks", ctypes.c_int),
         ("i_tile", ctypes.c_int), ("kernel_launches", ctypes.c_longlong), ("exchange", ctypes.c_int),
-        ("uniform_mass", ctypes.c_int),
+        ("uniform_mass", ctypes.c_int), ("f64_symmetric", ctypes.c_int),
     ]
 
 

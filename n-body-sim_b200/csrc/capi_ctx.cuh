@@ -34,6 +34,9 @@ struct Shard {
     void* partial = nullptr;
     size_t partial_bytes = 0;
     unsigned* counters = nullptr;
+    double* sym_part_i = nullptr;       // fp64 pairs-once pass (force_f64_sym.cuh): per-chunk i-side sums
+    double* sym_part_j = nullptr;       // ... and per-i-block j-side sums
+    size_t sym_bytes_i = 0, sym_bytes_j = 0;
     void* stage = nullptr;              // AoS staging for upload/download (4*cap_pad elements)
     double* energy_out = nullptr;
     size_t energy_rows = 0;
@@ -98,6 +101,8 @@ struct nbody_ctx {
     bool uniform = false;           // fp32: every uploaded mass is the same value -> the 11-op force kernel
     double uniform_mass = 0.0;
     int f64_math = 2;               // NBODY_F64_MATH at create
+    bool f64_sym_allowed = false;   // NBODY_F64_SYM at create (one GPU, MATH 2): pairs evaluated once (force_f64_sym.cuh)
+    int f64_sym_k = 0;              // j-blocks per CTA of that pass for the current upload; 0: the one-sided kernel
     int f64_R_forced = 0;          // NBODY_F64_R at create: 1 or 2 i-bodies per thread in the fp64 kernel, 0 = by body count
     bool small_path = true;         // NBODY_SMALL at create: one-cluster multi-step kernel for n <= kSmallMaxN (small.cuh)
     bool detect_masses = false;     // upload in flight: pack_pos_kernel compares every mass with uniform_mass

@@ -56,7 +56,10 @@ __global__ void kick2_kernel(Real* vel, const Real* acc, Real* temp, size_t n_lo
 
 // Host AoS (x,y,z,m)[n] staged on the device -> device pos_mass layout.  Pads are massless
 // bodies parked far away at x = pad_x (1e18; 1e150 in fp64): the equal-mass kernels ignore masses, and a
-// pad at the origin would meet a real body there as 0 * inf when softening is 0.
+// pad at the origin would meet a real body there as 0 * inf when softening is 0.  In fp64 pad k sits at
+// pad_x * (1 + k), every pad somewhere else: two pads at one point are 0 * inf for each other when softening
+// is 0 (only the self pair is selected away), and a NaN acceleration would move the pad onto the bodies'
+// sums at the next fused step.  (fp32 clamps r^2 instead: force_f32.cuh, ZERO_SOFT.)
 // detect != nullptr (fp32): also find the bodies whose mass is not `m0` -- detect[0] counts them
 // (a non-finite mass pushes the count past any limit) and the first kMaxOutliers found are
 // appended to `outliers` in no particular order; the host sorts them (nbody_upload).
@@ -68,7 +71,7 @@ __global__ void pack_pos_kernel(const Real* aos, Real* pos_a, Real* pos_b, size_
     if (i >= n_pad) return;
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
-        const Real v = i < n ? aos[4 * i + c] : (c == 0 ? pad_x : Real(0));
+        const Real v = i < n ? aos[4 * i + c] : (c == 0 ? (sizeof(Real) == 8 ? pad_x * Real(1 + (i - n)) : pad_x) : Real(0));
         pos_a[pm_index<Real>(i, c)] = v;
         pos_b[pm_index<Real>(i, c)] = v;  // mass is constant: both buffers carry it
         if (c == 3 && detect != nullptr && i < n && !(v == m0)) {

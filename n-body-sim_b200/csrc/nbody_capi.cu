@@ -9,6 +9,7 @@
 #include "exchange.cuh"
 #include "force_f32.cuh"
 #include "force_f64.cuh"
+#include "force_f64_sym.cuh"
 #include "integrate.cuh"
 #include "small.cuh"
 
@@ -25,9 +26,48 @@ int check_exchange(nbody_ctx* c);  // defined with the exchange code below
 // fp64 force kernel: two i-bodies per thread pay from ~32k bodies up (N=65,536: 961 -> 974 G interactions/s with
 // equal masses, 906 -> 948 without) and cost below (N=16,384: 304 -> 326 us/step): profiles/r1e_f64_r_uniform.jsonl
 constexpr size_t kF64TwoBodyMinN = 32768;
+// The pairs-once pass (force_f64_sym.cuh) serves one-GPU MATH 2 contexts from 1,024 bodies up, while its partial
+// sums fit NBODY_F64_SYM_MAX_MB (default 4 GiB: N ~ 300k).  N=16,384: see DESIGN.md 4.2.
+constexpr size_t kSymMinN = 1024;
+size_t sym_partial_bytes(size_t n_pad, int k, size_t* bytes_i, size_t* bytes_j)
+{
+    const size_t nib = n_pad / kSymIBlock;
+    const size_t bi = size_t(sym_chunks_of_row(int(nib), k, 0)) * 3 * n_pad * sizeof(double);
+    const size_t bj = nib * 3 * n_pad * sizeof(double);
+    if (bytes_i) *bytes_i = bi;
+    if (bytes_j) *bytes_j = bj;
+    return bi + bj;
+}
+// j-blocks per CTA: as many as still leave ~48 CTAs per SM (NBODY_F64_SYM_K overrides); 0 = not this pass.
+// Measured (profiles/r1f_f64_sym.jsonl): N=65,536 runs at 1,599 / 1,617 / 1,622 / 1,504 G interactions/s with
+// k = 1 / 2 / 4 / 19, N=16,384 at 192 / 204 / 262 us per step with k = 1 / 2 / 4.
+int sym_pick_k(const nbody_ctx* c, size_t n)
+{
+    if (!c->f64_sym_allowed || n < kSymMinN) return 0;
+    const size_t n_pad = round_up(n, size_t(kSymIBlock));
+    const int nib = int(n_pad / kSymIBlock);
+    const int forced = env_int("NBODY_F64_SYM_K", 0);
+    int k = 1;
+    if (forced > 0) {
+        k = forced;
+    } else {
+        const long long want = 48LL * std::max(c->sm_count, 1);
+        for (int t = 2; t <= 64; ++t) {
+            long long ctas = 0;
+            for (int I = 0; I < nib; ++I) ctas += sym_chunks_of_row(nib, t, I);
+            if (ctas < want) break;
+            k = t;
+        }
+    }
+    const size_t budget = size_t(std::max(1, env_int("NBODY_F64_SYM_MAX_MB", 4096))) << 20;
+    while (k < 64 && sym_partial_bytes(n_pad, k, nullptr, nullptr) > budget) ++k;
+    return sym_partial_bytes(n_pad, k, nullptr, nullptr) > budget ? 0 : k;
+}
+
 int f64_bodies_per_thread(const nbody_ctx* c, size_t n)
 {
     if (c->f64_math != 2) return 1;
+    if (c->f64_sym_allowed && n >= kSymMinN) return kSymIBlock / kThreads;  // its 512-body i-blocks set the padding
     if (c->f64_R_forced == 1 || c->f64_R_forced == 2) return c->f64_R_forced;
     return n >= kF64TwoBodyMinN ? 2 : 1;
 }
@@ -162,6 +202,8 @@ int create_common(nbody_ctx** out, nbody_prec prec, int world, size_t capacity, 
     } else {
         c->f64_math = env_int("NBODY_F64_MATH", 2);
         c->f64_R_forced = env_int("NBODY_F64_R", 0);
+        // (forcing the one-sided kernel's shape, or another arithmetic, selects the one-sided kernel)
+        c->f64_sym_allowed = env_int("NBODY_F64_SYM", 1) != 0 && world == 1 && c->f64_math == 2 && c->f64_R_forced == 0;
         c->R = f64_bodies_per_thread(c, capacity);  // for cap_pad: the largest i-tile an upload may pick
         c->i_tile = kThreads * c->R;
         c->j_unit = kJUnitF64;
@@ -224,6 +266,8 @@ extern "C" void nbody_destroy(nbody_ctx* c)
         cudaFree(s.acc);
         cudaFree(s.temp);
         cudaFree(s.partial);
+        cudaFree(s.sym_part_i);
+        cudaFree(s.sym_part_j);
         cudaFree(s.counters);
         cudaFree(s.energy_out);
         cudaFree(s.radius);
@@ -472,6 +516,7 @@ extern "C" int nbody_get_info(nbody_ctx* c, nbody_info* o)
     o->kernel_launches = c->launches;
     o->exchange = c->world == 1 ? 0 : (c->p2p ? 2 : 1);
     o->uniform_mass = c->uniform ? 1 + int(c->outliers.size()) : 0;
+    o->f64_symmetric = c->f64_sym_k;
     return NBODY_OK;
 }
 
@@ -555,6 +600,30 @@ template <typename Real> int download_t(nbody_ctx* c, Real* pm, Real* vel, Real*
     return check_exchange(c);
 }
 
+// Partial-sum arrays of the fp64 pairs-once pass (force_f64_sym.cuh) for the current n_pad; they only grow.
+int ensure_sym_buffers(nbody_ctx* c)
+{
+    Shard& s = c->shards[0];
+    CU(c, cudaSetDevice(s.device));
+    size_t bi = 0, bj = 0;
+    sym_partial_bytes(c->n_pad, c->f64_sym_k, &bi, &bj);
+    if (bi > s.sym_bytes_i) {
+        cudaFree(s.sym_part_i);
+        s.sym_part_i = nullptr;
+        s.sym_bytes_i = 0;
+        CU(c, cudaMalloc(&s.sym_part_i, bi));
+        s.sym_bytes_i = bi;
+    }
+    if (bj > s.sym_bytes_j) {
+        cudaFree(s.sym_part_j);
+        s.sym_part_j = nullptr;
+        s.sym_bytes_j = 0;
+        CU(c, cudaMalloc(&s.sym_part_j, bj));
+        s.sym_bytes_j = bj;
+    }
+    return NBODY_OK;
+}
+
 // After upload_t's final synchronise: what pack_pos_kernel found.  Up to kMaxOutliers exceptions keep
 // the equal-mass sweep (they are corrected per i-body); the list is sorted so that the order of the
 // corrections, and with it every bit of the result, does not depend on the order the atomics landed in.
@@ -587,9 +656,11 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     if (n == 0 || n > c->capacity) return fail(c, NBODY_EINVAL, "upload: n=%zu outside 1..capacity=%zu", n, c->capacity);
     if (!pos_mass || !vel) return fail(c, NBODY_EINVAL, "upload: pos_mass and vel are required");
     c->n = n;
+    c->f64_sym_k = 0;
     if (c->prec == NBODY_F64) {
         c->R = f64_bodies_per_thread(c, n);
         c->i_tile = kThreads * c->R;
+        c->f64_sym_k = sym_pick_k(c, n);
     }
     c->n_pad = round_up(n, pad_unit(c));
     c->n_j = round_up(n, size_t(c->j_unit));
@@ -627,6 +698,7 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
                  : upload_t<double>(c, n, (const double*)pos_mass, (const double*)vel, (const double*)acc, (const double*)temp);
     if (rc == NBODY_OK && c->detect_masses) rc = finish_mass_detection(c);
     c->detect_masses = false;
+    if (rc == NBODY_OK && c->f64_sym_k > 0) rc = ensure_sym_buffers(c);
     return rc;
 }
 
@@ -805,7 +877,31 @@ int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
             ForceParams<double> q = p;
             const bool uni = c->uniform && c->f64_math == 2;
             if (uni) q.G = G * c->uniform_mass;  // equal masses: the common m joins G (force_f64.cuh, UNIFORM)
-            pick_f64_kernel(c->f64_math, eps == 0.0, uni, c->R, [&](auto kernel) { kernel<<<grid, blk, sm, s.stream>>>(q); });
+            if (c->f64_sym_k > 0) {
+                // every pair once, then one pass that adds the partial sums and runs the epilogue (force_f64_sym.cuh)
+                SymParams sp;
+                sp.pos = q.pos_cur;
+                sp.part_i = s.sym_part_i;
+                sp.part_j = s.sym_part_j;
+                sp.n_pad = c->n_pad;
+                sp.n_iblocks = int(c->n_pad / kSymIBlock);
+                sp.k = c->f64_sym_k;
+                sp.eps2 = q.eps2;
+                const dim3 sgrid(unsigned(sym_chunks_of_row(sp.n_iblocks, sp.k, 0)), unsigned(sp.n_iblocks));
+                const bool z = eps == 0.0;
+                if (uni) {
+                    if (z) force_f64_sym_kernel<true, true><<<sgrid, kSymThreads, 0, s.stream>>>(sp);
+                    else force_f64_sym_kernel<false, true><<<sgrid, kSymThreads, 0, s.stream>>>(sp);
+                } else {
+                    if (z) force_f64_sym_kernel<true, false><<<sgrid, kSymThreads, 0, s.stream>>>(sp);
+                    else force_f64_sym_kernel<false, false><<<sgrid, kSymThreads, 0, s.stream>>>(sp);
+                }
+                c->launches++;
+                CU(c, cudaGetLastError());
+                f64_sym_finish_kernel<<<unsigned(c->n_pad / 32), kSymFinishWarps * 32, 0, s.stream>>>(q, sp, q.G);
+            } else {
+                pick_f64_kernel(c->f64_math, eps == 0.0, uni, c->R, [&](auto kernel) { kernel<<<grid, blk, sm, s.stream>>>(q); });
+            }
         }
         c->launches++;
         CU(c, cudaGetLastError());

@@ -54,7 +54,7 @@ def main():
                     e.sync()
                     dt = (time.perf_counter() - t0) / k
                     info = e.info()
-                rows.append({"lib": os.path.basename(os.environ.get("NBODY_LIB", "default")), "tag": a.tag, "uniform_kernel": info["uniform_mass"],
+                rows.append({"lib": os.path.basename(os.environ.get("NBODY_LIB", "default")), "tag": a.tag, "uniform_kernel": info["uniform_mass"], "pairs_once_k": info["f64_symmetric"],
                              "i_tile": info["i_tile"], "math": math, "want_units": units or "default", "n": n, "us_per_step": dt * 1e6,
                              "g_int_per_s": float(n) ** 2 / dt * 1e-9, "j_chunks": info["j_chunks"], "force_err_n4096": e4})
                 print(json.dumps(rows[-1]), flush=True)

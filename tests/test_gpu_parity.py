@@ -132,6 +132,70 @@ def test_f64_math_variants(nb, oracle, math, eps):
     assert np.isfinite(acc).all() and err < F64_GATE and err2 < F64_GATE
 
 
+@pytest.mark.parametrize("n,eps,general", [(1024, 0.5, False), (1500, 0.01, True), (4096, 0.0, False), (5000, 0.0, True),
+                                           (3001, 0.3, True)])
+def test_f64_pairs_once_pass(nb, oracle, n, eps, general):
+    """The fp64 pass that evaluates every pair once and applies it to both bodies, as the reference's
+    i<j loop does (csrc/force_f64_sym.cuh; one GPU, from 1,024 bodies up): the force and three fused
+    steps within the 1e-12 gate of the oracle, for equal and for general masses, with and without
+    softening, ragged N (pads inside the last blocks); the same terms as the one-sided kernel
+    (NBODY_F64_SYM=0) in another order; two runs and two chunkings agree (bit for bit / to rounding)."""
+    s = nb.scenes.plummer(n)
+    pm = s.pos_mass.copy()
+    pm[n // 3, :3] = 0.0                                             # one body exactly at the origin
+    if general:
+        pm[:, 3] *= np.random.default_rng(n).uniform(0.5, 2.0, n)
+    ref = oracle.compute_gravity(pm, s.G, eps, mt=True)
+    p3, v3, a3, _ = oracle.integrate(pm, s.vel, np.zeros_like(s.vel), None, s.dt, s.G, eps, nsteps=3)
+
+    def run(**env):
+        os.environ.update({k: str(v) for k, v in env.items()})
+        try:
+            with nb.Engine(n, precision="f64") as e:
+                e.upload(pm, s.vel)
+                info = e.info()
+                e.force(s.G, eps)
+                acc = e.download()["acc"]
+                e.upload(pm, s.vel)
+                e.step(s.dt, s.G, eps, 3)
+                return info, acc, e.download()
+        finally:
+            for k in env:
+                del os.environ[k]
+
+    info, acc, out = run()
+    assert info["f64_symmetric"] > 0 and info["uniform_mass"] == (0 if general else 1)
+    info1, acc1, out1 = run(NBODY_F64_SYM=0)
+    assert info1["f64_symmetric"] == 0
+    _, acc_b, out_b = run()
+    _, acc_k, _ = run(NBODY_F64_SYM_K=3)
+    err, err1 = norm_rel_err(acc, ref), norm_rel_err(acc1, ref)
+    print(f"f64 pairs-once n={n} eps={eps} general={general}: force err {err:.3e} (one-sided {err1:.3e}), "
+          f"3 steps pos {norm_rel_err(out['pos_mass'], p3):.3e} vel {norm_rel_err(out['vel'], v3):.3e}")
+    assert np.isfinite(acc).all() and err < F64_GATE and err1 < F64_GATE
+    assert norm_rel_err(acc, acc1) < 1e-13 and norm_rel_err(acc_k, acc) < 1e-13
+    for k, r in (("pos_mass", p3), ("vel", v3), ("acc", a3)):
+        assert norm_rel_err(out[k], r) < F64_GATE and norm_rel_err(out1[k], r) < F64_GATE
+        np.testing.assert_array_equal(out[k], out_b[k])
+    np.testing.assert_array_equal(acc, acc_b)
+
+
+@pytest.mark.parametrize("n", [700, 1100])
+def test_f64_zero_softening_fused_steps_with_pads(nb, oracle, n):
+    """softening = 0 over several fused steps with pad bodies in the last tile: two pads at one point
+    would be 0 * inf for each other, and the NaN would reach every body at the next step (fp64 pads
+    are spread out for that reason, csrc/integrate.cuh pack_pos_kernel).  n = 700: one-sided kernel."""
+    s = nb.scenes.uniform_cube(n)
+    p, v, a, _ = oracle.integrate(s.pos_mass, s.vel, np.zeros_like(s.vel), None, 1e-3, 1.0, 0.0, nsteps=4)
+    with nb.Engine(n, precision="f64") as e:
+        e.upload(s.pos_mass, s.vel)
+        e.step(1e-3, 1.0, 0.0, 4)
+        out = e.download()
+    for k, r in (("pos_mass", p), ("vel", v), ("acc", a)):
+        assert np.isfinite(out[k]).all()
+        assert norm_rel_err(out[k], r) < F64_GATE
+
+
 # ---------------------------------------------------------------- fp32 -----------
 # fp32 per-step tolerances (norm-relative): the rsqrt approximation (2 ulp) and fp32
 # accumulation give acc ~1e-6; pos/vel after ONE step from identical state are far tighter.
