@@ -14,6 +14,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "common.cuh"
@@ -102,6 +103,7 @@ struct nbody_ctx {
     double uniform_mass = 0.0;
     int f64_math = 2;               // NBODY_F64_MATH at create
     bool f64_sym_allowed = false;   // NBODY_F64_SYM at create (one GPU, MATH 2): pairs evaluated once (force_f64_sym.cuh)
+    int f64_sym_r = 4;              // i-bodies per thread of that pass (fewer for small systems)
     int f64_sym_k = 0;              // j-blocks per CTA of that pass for the current upload; 0: the one-sided kernel
     int f64_R_forced = 0;          // NBODY_F64_R at create: 1 or 2 i-bodies per thread in the fp64 kernel, 0 = by body count
     bool small_path = true;         // NBODY_SMALL at create: one-cluster multi-step kernel for n <= kSmallMaxN (small.cuh)

@@ -8,7 +8,7 @@
 // instructions -- is the same for both bodies.  Evaluated once, a pair costs 18 DP instructions
 // (20 with general masses) for TWO interactions: 9-10 per interaction instead of 15-16.
 //
-// Decomposition.  Bodies are cut into i-blocks of 512 (4 per thread, 128 threads) and j-blocks
+// Decomposition.  Bodies are cut into i-blocks of 512 (R = 4 per thread, 128 threads) and j-blocks
 // of 128.  CTA (I, c) takes i-block I against the c-th run of `k` j-blocks at or above I's
 // own; j-blocks below I belong to the rows of lower i-blocks (they reach I through the
 // j-side sums).  A j-block inside I's own range is walked the ordinary one-sided way (every
@@ -33,18 +33,14 @@
 
 namespace nb {
 
-#ifndef NB_SYM_R
-#define NB_SYM_R 4
-#endif
 #ifndef NB_SYM_UNROLL
 #define NB_SYM_UNROLL 2
 #endif
 constexpr int kSymUnroll = NB_SYM_UNROLL;            // steps per inner-loop iteration
 constexpr int kSymThreads = 128;
-constexpr int kSymR = NB_SYM_R;                   // i-bodies per thread
-constexpr int kSymIBlock = kSymThreads * kSymR;   // 512
+constexpr int kSymMaxR = 4;                       // i-bodies per thread: 4 (2 and 1 for small systems: more CTAs)
+constexpr int kSymIBlock = kSymThreads * kSymMaxR;  // 512: the padding granularity whatever R is
 constexpr int kSymJBlock = kSymThreads;           // 128: one 32-body segment per warp and phase
-constexpr int kSymJPerI = kSymIBlock / kSymJBlock;
 constexpr int kSymFinishWarps = 8;
 
 struct SymParams {
@@ -52,14 +48,15 @@ struct SymParams {
     double* part_i;      // [chunks_max][3][n_pad]
     double* part_j;      // [n_iblocks][3][n_pad]; row I is written for bodies above i-block I only
     size_t n_pad;        // multiple of kSymIBlock
-    int n_iblocks;
+    int r;               // i-bodies per thread: an i-block is r j-blocks long
+    int n_iblocks;       // n_pad / (kSymThreads * r)
     int k;               // j-blocks per CTA
     double eps2;
 };
 
-__host__ __device__ inline int sym_chunks_of_row(int n_iblocks, int k, int I)
+__host__ __device__ inline int sym_chunks_of_row(int n_iblocks, int r, int k, int I)
 {
-    return ((n_iblocks - I) * kSymJPerI + k - 1) / k;
+    return ((n_iblocks - I) * r + k - 1) / k;
 }
 
 // (distSq + epsSq)^-1.5 of one pair, MATH 2's arithmetic (force_f64.cuh)
@@ -68,21 +65,23 @@ __device__ __forceinline__ double sym_pair_weight(double dx, double dy, double d
     return inv_cube_f64(__fma_rn(dz, dz, __fma_rn(dy, dy, __fma_rn(dx, dx, eps2))));
 }
 
-template <bool ZERO_SOFT, bool UNIFORM>
+template <bool ZERO_SOFT, bool UNIFORM, int kSymR>
 __global__ void __launch_bounds__(kSymThreads) force_f64_sym_kernel(const SymParams p)
 {
+    constexpr int kSymJPerI = kSymR;
+    constexpr int kIBlock = kSymThreads * kSymR;
     __shared__ double sx[kSymJBlock], sy[kSymJBlock], sz[kSymJBlock], sm[kSymJBlock];
     __shared__ double fx[kSymJBlock], fy[kSymJBlock], fz[kSymJBlock];
 
     const int I = blockIdx.y, c = blockIdx.x;
-    if (c >= sym_chunks_of_row(p.n_iblocks, p.k, I)) return;
+    if (c >= sym_chunks_of_row(p.n_iblocks, kSymR, p.k, I)) return;
     const int jb0 = I * kSymJPerI + c * p.k;
     const int jb_end = p.n_iblocks * kSymJPerI;
     const int jb1 = jb0 + p.k < jb_end ? jb0 + p.k : jb_end;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const double4* pos4 = reinterpret_cast<const double4*>(p.pos);
-    const size_t i0 = size_t(I) * kSymIBlock + tid;  // body r of this thread: i0 + r * kSymThreads
+    const size_t i0 = size_t(I) * kIBlock + tid;  // body r of this thread: i0 + r * kSymThreads
 
     double xi[kSymR], yi[kSymR], zi[kSymR], mi[kSymR], ax[kSymR], ay[kSymR], az[kSymR];
 #pragma unroll
@@ -184,8 +183,8 @@ __global__ void __launch_bounds__(kSymFinishWarps * 32) f64_sym_finish_kernel(co
     __shared__ double red[kSymFinishWarps][3][32];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const size_t b = size_t(blockIdx.x) * 32 + lane;
-    const int I = int(b / kSymIBlock);  // the same for all 32 bodies
-    const int nj = I, ni = sym_chunks_of_row(s.n_iblocks, s.k, I);
+    const int I = int(b / (size_t(kSymThreads) * s.r));  // the same for all 32 bodies
+    const int nj = I, ni = sym_chunks_of_row(s.n_iblocks, s.r, s.k, I);
     double tx = 0.0, ty = 0.0, tz = 0.0;
 #pragma unroll 4
     for (int k = w; k < nj + ni; k += kSymFinishWarps) {

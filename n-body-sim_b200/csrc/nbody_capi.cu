@@ -26,13 +26,15 @@ int check_exchange(nbody_ctx* c);  // defined with the exchange code below
 // fp64 force kernel: two i-bodies per thread pay from ~32k bodies up (N=65,536: 961 -> 974 G interactions/s with
 // equal masses, 906 -> 948 without) and cost below (N=16,384: 304 -> 326 us/step): profiles/r1e_f64_r_uniform.jsonl
 constexpr size_t kF64TwoBodyMinN = 32768;
-// The pairs-once pass (force_f64_sym.cuh) serves one-GPU MATH 2 contexts from 1,024 bodies up, while its partial
-// sums fit NBODY_F64_SYM_MAX_MB (default 4 GiB: N ~ 300k).  N=16,384: see DESIGN.md 4.2.
-constexpr size_t kSymMinN = 1024;
-size_t sym_partial_bytes(size_t n_pad, int k, size_t* bytes_i, size_t* bytes_j)
+// The pairs-once pass (force_f64_sym.cuh) serves one-GPU MATH 2 contexts from 3,072 bodies up, while its partial
+// sums fit NBODY_F64_SYM_MAX_MB (default 4 GiB: N ~ 300k).  Below, its two launches and few CTAs lose to the
+// one-sided kernel (us/step one-sided vs pairs-once: N=2,048 16.8 / 20.5, N=4,096 38.1 / 30.9, N=16,384 291 / 190;
+// profiles/r1f_f64_sym_r.jsonl).
+constexpr size_t kSymMinN = 3072;
+size_t sym_partial_bytes(size_t n_pad, int r, int k, size_t* bytes_i, size_t* bytes_j)
 {
-    const size_t nib = n_pad / kSymIBlock;
-    const size_t bi = size_t(sym_chunks_of_row(int(nib), k, 0)) * 3 * n_pad * sizeof(double);
+    const size_t nib = n_pad / (size_t(kSymThreads) * r);
+    const size_t bi = size_t(sym_chunks_of_row(int(nib), r, k, 0)) * 3 * n_pad * sizeof(double);
     const size_t bj = nib * 3 * n_pad * sizeof(double);
     if (bytes_i) *bytes_i = bi;
     if (bytes_j) *bytes_j = bj;
@@ -41,27 +43,41 @@ size_t sym_partial_bytes(size_t n_pad, int k, size_t* bytes_i, size_t* bytes_j)
 // j-blocks per CTA: as many as still leave ~48 CTAs per SM (NBODY_F64_SYM_K overrides); 0 = not this pass.
 // Measured (profiles/r1f_f64_sym.jsonl): N=65,536 runs at 1,599 / 1,617 / 1,622 / 1,504 G interactions/s with
 // k = 1 / 2 / 4 / 19, N=16,384 at 192 / 204 / 262 us per step with k = 1 / 2 / 4.
-int sym_pick_k(const nbody_ctx* c, size_t n)
+long long sym_cta_count(size_t n_pad, int r, int k)
 {
+    const int nib = int(n_pad / (size_t(kSymThreads) * r));
+    long long ctas = 0;
+    for (int I = 0; I < nib; ++I) ctas += sym_chunks_of_row(nib, r, k, I);
+    return ctas;
+}
+// Shape of the pass for n bodies: i-bodies per thread (*r_out) and j-blocks per CTA (returned; 0 = not this pass).
+// Small systems take fewer bodies per thread so that every SM still gets several CTAs (NBODY_F64_SYM_R overrides;
+// measured best: R = 1 at N=4,096, 2 at 8,192, 4 from 12,288 up).
+int sym_pick_k(const nbody_ctx* c, size_t n, int* r_out)
+{
+    *r_out = kSymMaxR;
     if (!c->f64_sym_allowed || n < kSymMinN) return 0;
     const size_t n_pad = round_up(n, size_t(kSymIBlock));
-    const int nib = int(n_pad / kSymIBlock);
+    const long long sms = std::max(c->sm_count, 1);
+    int r = env_int("NBODY_F64_SYM_R", 0);
+    if (r != 1 && r != 2 && r != 4) {
+        r = 4;
+        while (r > 1 && sym_cta_count(n_pad, r, 1) < 6 * sms) r /= 2;
+    }
+    *r_out = r;
     const int forced = env_int("NBODY_F64_SYM_K", 0);
     int k = 1;
     if (forced > 0) {
         k = forced;
     } else {
-        const long long want = 48LL * std::max(c->sm_count, 1);
         for (int t = 2; t <= 64; ++t) {
-            long long ctas = 0;
-            for (int I = 0; I < nib; ++I) ctas += sym_chunks_of_row(nib, t, I);
-            if (ctas < want) break;
+            if (sym_cta_count(n_pad, r, t) < 48 * sms) break;
             k = t;
         }
     }
     const size_t budget = size_t(std::max(1, env_int("NBODY_F64_SYM_MAX_MB", 4096))) << 20;
-    while (k < 64 && sym_partial_bytes(n_pad, k, nullptr, nullptr) > budget) ++k;
-    return sym_partial_bytes(n_pad, k, nullptr, nullptr) > budget ? 0 : k;
+    while (k < 64 && sym_partial_bytes(n_pad, r, k, nullptr, nullptr) > budget) ++k;
+    return sym_partial_bytes(n_pad, r, k, nullptr, nullptr) > budget ? 0 : k;
 }
 
 int f64_bodies_per_thread(const nbody_ctx* c, size_t n)
@@ -150,6 +166,18 @@ template <typename F> void pick_f64_kernel(int math, bool zero_soft, bool unifor
     }
     if (uniform) return zero_soft ? f(force_f64_kernel<2, true, true, 1>) : f(force_f64_kernel<2, false, true, 1>);
     return zero_soft ? f(force_f64_kernel<2, true, false, 1>) : f(force_f64_kernel<2, false, false, 1>);
+}
+
+template <typename F> void pick_f64_sym_kernel(bool zero_soft, bool uniform, int r, F&& f)
+{
+    auto by_r = [&](auto zs, auto un) {
+        constexpr bool Z = decltype(zs)::value, U = decltype(un)::value;
+        if (r == 1) return f(force_f64_sym_kernel<Z, U, 1>);
+        if (r == 2) return f(force_f64_sym_kernel<Z, U, 2>);
+        return f(force_f64_sym_kernel<Z, U, 4>);
+    };
+    if (zero_soft) return uniform ? by_r(std::true_type{}, std::true_type{}) : by_r(std::true_type{}, std::false_type{});
+    return uniform ? by_r(std::false_type{}, std::true_type{}) : by_r(std::false_type{}, std::false_type{});
 }
 
 template <typename F> int for_each_f64_kernel(F&& f, nbody_ctx* c)
@@ -606,7 +634,7 @@ int ensure_sym_buffers(nbody_ctx* c)
     Shard& s = c->shards[0];
     CU(c, cudaSetDevice(s.device));
     size_t bi = 0, bj = 0;
-    sym_partial_bytes(c->n_pad, c->f64_sym_k, &bi, &bj);
+    sym_partial_bytes(c->n_pad, c->f64_sym_r, c->f64_sym_k, &bi, &bj);
     if (bi > s.sym_bytes_i) {
         cudaFree(s.sym_part_i);
         s.sym_part_i = nullptr;
@@ -660,7 +688,7 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     if (c->prec == NBODY_F64) {
         c->R = f64_bodies_per_thread(c, n);
         c->i_tile = kThreads * c->R;
-        c->f64_sym_k = sym_pick_k(c, n);
+        c->f64_sym_k = sym_pick_k(c, n, &c->f64_sym_r);
     }
     c->n_pad = round_up(n, pad_unit(c));
     c->n_j = round_up(n, size_t(c->j_unit));
@@ -884,18 +912,12 @@ int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
                 sp.part_i = s.sym_part_i;
                 sp.part_j = s.sym_part_j;
                 sp.n_pad = c->n_pad;
-                sp.n_iblocks = int(c->n_pad / kSymIBlock);
+                sp.r = c->f64_sym_r;
+                sp.n_iblocks = int(c->n_pad / (size_t(kSymThreads) * sp.r));
                 sp.k = c->f64_sym_k;
                 sp.eps2 = q.eps2;
-                const dim3 sgrid(unsigned(sym_chunks_of_row(sp.n_iblocks, sp.k, 0)), unsigned(sp.n_iblocks));
-                const bool z = eps == 0.0;
-                if (uni) {
-                    if (z) force_f64_sym_kernel<true, true><<<sgrid, kSymThreads, 0, s.stream>>>(sp);
-                    else force_f64_sym_kernel<false, true><<<sgrid, kSymThreads, 0, s.stream>>>(sp);
-                } else {
-                    if (z) force_f64_sym_kernel<true, false><<<sgrid, kSymThreads, 0, s.stream>>>(sp);
-                    else force_f64_sym_kernel<false, false><<<sgrid, kSymThreads, 0, s.stream>>>(sp);
-                }
+                const dim3 sgrid(unsigned(sym_chunks_of_row(sp.n_iblocks, sp.r, sp.k, 0)), unsigned(sp.n_iblocks));
+                pick_f64_sym_kernel(eps == 0.0, uni, sp.r, [&](auto kernel) { kernel<<<sgrid, kSymThreads, 0, s.stream>>>(sp); });
                 c->launches++;
                 CU(c, cudaGetLastError());
                 f64_sym_finish_kernel<<<unsigned(c->n_pad / 32), kSymFinishWarps * 32, 0, s.stream>>>(q, sp, q.G);

@@ -127,6 +127,60 @@ template <int CH> __global__ void k_mix1(float* out, int iters, long long* clk)
     if (threadIdx.x == 0 && blockIdx.x == 0) *clk = t1 - t0;
 }
 
+// FP64 pipe: dependent DFMA chains (U per thread), and the pairs-once interaction mix of force_f64_sym.cuh with register
+// operands (per chain and iteration: 3 DADD + 3 DFMA + MUFU.RSQ64H + 3 DMUL + 3 DFMA + 6 DFMA = 18 DP instructions).
+__global__ void k_dfma(float* out, int iters, long long* clk)
+{
+    double a[U], b = 1.0001 + threadIdx.x * 1e-9, c = 0.5;
+    for (int u = 0; u < U; ++u) a[u] = u + threadIdx.x;
+    long long t0 = clock64();
+    for (int i = 0; i < iters; ++i)
+#pragma unroll
+        for (int u = 0; u < U; ++u) asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(a[u]) : "d"(b), "d"(c));
+    long long t1 = clock64();
+    double s = 0;
+    for (int u = 0; u < U; ++u) s += a[u];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = float(s);
+    if (threadIdx.x == 0 && blockIdx.x == 0) *clk = t1 - t0;
+}
+
+template <int CH, int SEED> __global__ void k_dmix(float* out, int iters, long long* clk)
+{
+    double ax[CH], ay[CH], az[CH], gx = 0, gy = 0, gz = 0, jx[CH], jy[CH], jz[CH];
+    const double xi = 0.1 * threadIdx.x, yi = 0.3, zi = -0.7, e2 = 0.01;
+    for (int u = 0; u < CH; ++u) { ax[u] = ay[u] = az[u] = 0.0; jx[u] = 1.0 + u; jy[u] = 0.5 * u; jz[u] = 3.0; }
+    long long t0 = clock64();
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < CH; ++u) {
+            jx[u] = __longlong_as_double(__double_as_longlong(jx[u]) ^ (long long)(i & 0xff));  // loop-variant operands
+            const double dx = __dsub_rn(jx[u], xi), dy = __dsub_rn(jy[u], yi), dz = __dsub_rn(jz[u], zi);
+            const double s = __fma_rn(dz, dz, __fma_rn(dy, dy, __fma_rn(dx, dx, e2)));
+            double y;
+            if (SEED == 0) {
+                asm volatile("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(s));   // MUFU.RSQ64H
+            } else if (SEED == 1) {
+                float sf, yf;                                                        // F2F + MUFU.RSQ + F2F
+                asm volatile("cvt.rn.f32.f64 %0, %1;" : "=f"(sf) : "d"(s));
+                asm volatile("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(yf) : "f"(sf));
+                asm volatile("cvt.f64.f32 %0, %1;" : "=d"(y) : "f"(yf));
+            } else {
+                // no MUFU at all (how much of the DP peak the rest of the mix reaches): integer seed
+                y = __longlong_as_double(0x5FE6EB50C7B537A9ll - (__double_as_longlong(s) >> 1));
+            }
+            const double c = __dmul_rn(y, y), e = __fma_rn(s, -c, 1.0), c3 = __dmul_rn(c, y), p = __fma_rn(e, 1.875, 1.5);
+            const double w = __fma_rn(c3, __dmul_rn(p, e), c3);
+            ax[u] = __fma_rn(w, dx, ax[u]); ay[u] = __fma_rn(w, dy, ay[u]); az[u] = __fma_rn(w, dz, az[u]);
+            gx = __fma_rn(w, dx, gx); gy = __fma_rn(w, dy, gy); gz = __fma_rn(w, dz, gz);
+        }
+    }
+    long long t1 = clock64();
+    double s = gx + gy + gz;
+    for (int u = 0; u < CH; ++u) s += ax[u] + ay[u] + az[u];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = float(s);
+    if (threadIdx.x == 0 && blockIdx.x == 0) *clk = t1 - t0;
+}
+
 template <typename K> void run(const char* name, K kernel, int threads, int ctas_per_sm, int sms, int iters, double lanes_per_thread_iter, const char* unit)
 {
     float* out;
@@ -171,6 +225,13 @@ int main()
         run("mix packed 12x2+2MUFU CH=2", k_mix2<2>, 256, cps, sms, it / 4, 4, "int");
         run("mix packed 12x2+2MUFU CH=4", k_mix2<4>, 256, cps, sms, it / 4, 8, "int");
     }
+    for (int cps : {1, 2, 4}) {
+        run("DFMA (lanes=DP instr)", k_dfma, 256, cps, sms, it / 4, U, "dfma");
+        run("fp64 pairs-once mix 18DP+1MUFU CH=4", k_dmix<4, 0>, 128, cps, sms, it / 16, 4 * 18, "dp");
+    }
+    run("fp64 pairs-once mix CH=4, 5 CTAs x 128", k_dmix<4, 0>, 128, 5, sms, it / 16, 4 * 18, "dp");
+    run("  ... seed by F2F+MUFU.RSQ+F2F", k_dmix<4, 1>, 128, 5, sms, it / 16, 4 * 18, "dp");
+    run("  ... integer seed, no MUFU", k_dmix<4, 2>, 128, 5, sms, it / 16, 4 * 18, "dp");
     run("mix packed CH=4 thr=512", k_mix2<4>, 512, 2, sms, it / 4, 8, "int");
     run("mix packed CH=4 thr=1024", k_mix2<4>, 1024, 1, sms, it / 4, 8, "int");
     return 0;

@@ -132,11 +132,11 @@ def test_f64_math_variants(nb, oracle, math, eps):
     assert np.isfinite(acc).all() and err < F64_GATE and err2 < F64_GATE
 
 
-@pytest.mark.parametrize("n,eps,general", [(1024, 0.5, False), (1500, 0.01, True), (4096, 0.0, False), (5000, 0.0, True),
-                                           (3001, 0.3, True)])
+@pytest.mark.parametrize("n,eps,general", [(3072, 0.5, False), (3500, 0.01, True), (4096, 0.0, False), (5000, 0.0, True),
+                                           (9001, 0.3, True)])
 def test_f64_pairs_once_pass(nb, oracle, n, eps, general):
     """The fp64 pass that evaluates every pair once and applies it to both bodies, as the reference's
-    i<j loop does (csrc/force_f64_sym.cuh; one GPU, from 1,024 bodies up): the force and three fused
+    i<j loop does (csrc/force_f64_sym.cuh; one GPU, from 3,072 bodies up): the force and three fused
     steps within the 1e-12 gate of the oracle, for equal and for general masses, with and without
     softening, ragged N (pads inside the last blocks); the same terms as the one-sided kernel
     (NBODY_F64_SYM=0) in another order; two runs and two chunkings agree (bit for bit / to rounding)."""
@@ -169,6 +169,7 @@ def test_f64_pairs_once_pass(nb, oracle, n, eps, general):
     assert info1["f64_symmetric"] == 0
     _, acc_b, out_b = run()
     _, acc_k, _ = run(NBODY_F64_SYM_K=3)
+    shapes = [run(NBODY_F64_SYM_R=r) for r in (1, 2, 4)]             # i-bodies per thread (small systems take fewer)
     err, err1 = norm_rel_err(acc, ref), norm_rel_err(acc1, ref)
     print(f"f64 pairs-once n={n} eps={eps} general={general}: force err {err:.3e} (one-sided {err1:.3e}), "
           f"3 steps pos {norm_rel_err(out['pos_mass'], p3):.3e} vel {norm_rel_err(out['vel'], v3):.3e}")
@@ -178,9 +179,11 @@ def test_f64_pairs_once_pass(nb, oracle, n, eps, general):
         assert norm_rel_err(out[k], r) < F64_GATE and norm_rel_err(out1[k], r) < F64_GATE
         np.testing.assert_array_equal(out[k], out_b[k])
     np.testing.assert_array_equal(acc, acc_b)
+    for _, acc_r, out_r in shapes:
+        assert norm_rel_err(acc_r, acc) < 1e-13 and norm_rel_err(out_r["pos_mass"], p3) < F64_GATE
 
 
-@pytest.mark.parametrize("n", [700, 1100])
+@pytest.mark.parametrize("n", [700, 3100])
 def test_f64_zero_softening_fused_steps_with_pads(nb, oracle, n):
     """softening = 0 over several fused steps with pad bodies in the last tile: two pads at one point
     would be 0 * inf for each other, and the NaN would reach every body at the next step (fp64 pads
