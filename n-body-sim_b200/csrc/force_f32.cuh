@@ -67,8 +67,12 @@ __device__ __forceinline__ float rsqrt_approx(float x)
 #define NB_F32_UNROLL 16
 #endif
 constexpr int kF32Unroll = NB_F32_UNROLL;  // j-pairs per inner-loop iteration
-constexpr int kF32TileBytes = kF32TilePairs * 32;
-constexpr size_t force_f32_smem_bytes() { return size_t(kF32Stages) * kF32TileBytes + 2 * kF32Stages * 8; }
+// TP = j-PAIRS per ring stage: kF32TilePairs (512 bodies, 8 KiB) for large systems, kF32SmallTilePairs (128 bodies,
+// 2 KiB) for systems of up to 4,096 bodies, where a CTA's 512 x 512 interactions are a ~20 us dependent chain whatever
+// the SM count and four times as many, four times shorter CTAs fill the chip instead: N=1,024 24.5 -> 13.1 us/step,
+// N=4,096 24.6 -> 20.4 (nbody_capi.cu picks by body count; from 8,192 bodies up the large tile wins).
+constexpr int kF32SmallTilePairs = 64;
+template <int TP = kF32TilePairs> constexpr size_t force_f32_smem_bytes() { return size_t(kF32Stages) * TP * 32 + 2 * kF32Stages * 8; }
 
 // ZERO_SOFT: softening == 0.  The reference never evaluates the self pair
 // (idx:273, j starts at i+1); an all-pairs sweep does, and with eps = 0 it
@@ -88,13 +92,13 @@ constexpr size_t force_f32_smem_bytes() { return size_t(kF32Stages) * kF32TileBy
 // of carrying zero mass: inv^3 underflows to an exact 0 there.  Measured at N=1M: 2,829 G
 // interactions/s against 2,651 for the general kernel (+6.7 %); unroll 16 (166 registers,
 // 2 CTAs/SM) beats unroll 8 (2,809), 32 (2,741) and 4 (2,724); profiles/r1d_uniform_variants.txt.
-template <int R, bool ZERO_SOFT, int U, bool NEAR, bool DIAG, bool UNIFORM>
+template <int R, bool ZERO_SOFT, int U, bool NEAR, bool DIAG, bool UNIFORM, int TP>
 __device__ __forceinline__ void consume_tile(const float4* __restrict__ tp, const f32x2 (&nx)[R], const f32x2 (&ny)[R],
                                              const f32x2 (&nz)[R], f32x2 (&ax)[R], f32x2 (&ay)[R], f32x2 (&az)[R],
                                              float (&nr)[R], const f32x2 eps2, const int self0)
 {
 #pragma unroll U
-    for (int q = 0; q < kF32TilePairs; ++q) {
+    for (int q = 0; q < TP; ++q) {
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             // (the loads are re-stated per i-body and merged by the compiler: this form
@@ -119,7 +123,7 @@ __device__ __forceinline__ void consume_tile(const float4* __restrict__ tp, cons
             if (NEAR) {
                 float ma = ia, mb = ib;
                 if (DIAG) {
-                    const int s = self0 + r * kF32Threads;  // this body's index inside the tile
+                    const int s = self0 + r * kF32Threads;  // this body's index inside the tile (outside [0, 2 TP): not in it)
                     ma = (2 * q == s) ? 0.f : ia;
                     mb = (2 * q + 1 == s) ? 0.f : ib;
                 }
@@ -164,10 +168,12 @@ __device__ __forceinline__ void outlier_correction(const ForceParams<float>& p, 
     sz = fmaf(sz, p.bulk_mass, cz);
 }
 
-template <int R, bool ZERO_SOFT, int U, bool NEAR, bool UNIFORM = false>
+template <int R, bool ZERO_SOFT, int U, bool NEAR, bool UNIFORM = false, int TP = kF32TilePairs>
 __device__ __forceinline__ void force_f32_body(const ForceParams<float>& p)
 {
     constexpr int kWarps = kF32Threads / 32;
+    constexpr int kF32TileBytes = TP * 32;
+    constexpr int kTileBodies = 2 * TP;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + size_t(kF32Stages) * kF32TileBytes);
     uint64_t* empty = full + kF32Stages;
@@ -179,10 +185,10 @@ __device__ __forceinline__ void force_f32_body(const ForceParams<float>& p)
     const int chunk = blockIdx.x % p.j_chunks;
     const size_t tile_i = blockIdx.x / p.j_chunks;
 
-    // chunk_len and n_j are multiples of kJUnit = one tile: every tile is full
+    // chunk_len and n_j are multiples of the j unit = one tile: every tile is full
     const size_t j0 = size_t(chunk) * p.chunk_len;
     const size_t j1 = (j0 + p.chunk_len < p.n_j) ? j0 + p.chunk_len : p.n_j;
-    const int ntiles = static_cast<int>((j1 - j0) / (2 * kF32TilePairs));
+    const int ntiles = static_cast<int>((j1 - j0) / kTileBodies);
     const unsigned char* src = reinterpret_cast<const unsigned char*>(p.pos_cur) + j0 * 16;
 
     if (tid == 0) {
@@ -226,20 +232,18 @@ __device__ __forceinline__ void force_f32_body(const ForceParams<float>& p)
     float nr[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) nr[r] = 0.f;
-    // NEAR: the j-tile (512 bodies, 512-aligned) that contains this CTA's i-bodies
-    const size_t i0 = p.i_begin + tile_i * size_t(kF32Threads * R);
-    const size_t diag_start = i0 / size_t(2 * kF32TilePairs) * size_t(2 * kF32TilePairs);
-    const int diag_t = (NEAR && diag_start >= j0 && diag_start < j1) ? int((diag_start - j0) / (2 * kF32TilePairs)) : -1;
-    const int self0 = int(i0 - diag_start) + tid;
+    // NEAR: the j-tiles that hold this CTA's own i-bodies (one 512-body tile, or four 128-body ones) mask the self pair
+    const long long i0 = static_cast<long long>(p.i_begin + tile_i * size_t(kF32Threads * R));
 
     for (int t = 0; t < ntiles; ++t) {
         const int slot = t % kF32Stages;
         mbar_wait(&full[slot], (t / kF32Stages) & 1);
         const float4* tp = reinterpret_cast<const float4*>(smem_raw + size_t(slot) * kF32TileBytes);
-        if (NEAR && t == diag_t)
-            consume_tile<R, ZERO_SOFT, U, NEAR, true, UNIFORM>(tp, nx, ny, nz, ax, ay, az, nr, eps2, self0);
+        const long long off = i0 - (static_cast<long long>(j0) + static_cast<long long>(t) * kTileBodies);  // first own body, relative to the tile
+        if (NEAR && off > -static_cast<long long>(kF32Threads * R) && off < kTileBodies)
+            consume_tile<R, ZERO_SOFT, U, NEAR, true, UNIFORM, TP>(tp, nx, ny, nz, ax, ay, az, nr, eps2, static_cast<int>(off) + tid);
         else
-            consume_tile<R, ZERO_SOFT, U, NEAR, false, UNIFORM>(tp, nx, ny, nz, ax, ay, az, nr, eps2, self0);
+            consume_tile<R, ZERO_SOFT, U, NEAR, false, UNIFORM, TP>(tp, nx, ny, nz, ax, ay, az, nr, eps2, 0);
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[slot]);
     }
@@ -302,10 +306,10 @@ __device__ __forceinline__ void force_f32_body(const ForceParams<float>& p)
     if (tid == 0) p.tile_counter[tile_i] = 0;  // ready for the next launch
 }
 
-template <int R, bool ZERO_SOFT, int U = kF32Unroll, bool UNIFORM = false>
+template <int R, bool ZERO_SOFT, int U = kF32Unroll, bool UNIFORM = false, int TP = kF32TilePairs>
 __global__ void __launch_bounds__(kF32Threads + 32) force_f32_kernel(const ForceParams<float> p)
 {
-    force_f32_body<R, ZERO_SOFT, U, false, UNIFORM>(p);
+    force_f32_body<R, ZERO_SOFT, U, false, UNIFORM, TP>(p);
 }
 
 // The NEAR variant keeps 4 more live values per thread and a second (masked) copy of the
@@ -317,10 +321,10 @@ __global__ void __launch_bounds__(kF32Threads + 32) force_f32_kernel(const Force
 #ifndef NB_NEAR_UNROLL
 #define NB_NEAR_UNROLL 4  // measured (profiles/r1c_near_variants.jsonl): U=4 @2 CTAs/SM +6.0 % over the plain sweep; U=8 +15 %, U=4 @3 CTAs +11 %
 #endif
-template <int R, bool ZERO_SOFT, bool UNIFORM = false, int U = NB_NEAR_UNROLL>
+template <int R, bool ZERO_SOFT, bool UNIFORM = false, int U = NB_NEAR_UNROLL, int TP = kF32TilePairs>
 __global__ void __launch_bounds__(kF32Threads + 32, NB_NEAR_MIN_CTAS) force_f32_near_kernel(const ForceParams<float> p)
 {
-    force_f32_body<R, ZERO_SOFT, U, true, UNIFORM>(p);
+    force_f32_body<R, ZERO_SOFT, U, true, UNIFORM, TP>(p);
 }
 
 }  // namespace nb

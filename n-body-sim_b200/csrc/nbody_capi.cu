@@ -26,6 +26,11 @@ int check_exchange(nbody_ctx* c);  // defined with the exchange code below
 // fp64 force kernel: two i-bodies per thread pay from ~32k bodies up (N=65,536: 961 -> 974 G interactions/s with
 // equal masses, 906 -> 948 without) and cost below (N=16,384: 304 -> 326 us/step): profiles/r1e_f64_r_uniform.jsonl
 constexpr size_t kF64TwoBodyMinN = 32768;
+// fp32: 128-body j tiles up to this many bodies.  Measured us/step with 512- / 128-body tiles (scripts/gpu_25.sh,
+// profiles/r1f_f32_tile_sweep.jsonl): N=600 24.5 / 12.3, 1,024 24.5 / 13.1, 2,048 24.6 / 14.3, 4,096 24.6 / 20.4,
+// 8,192 41.0 / 42.9, 16,384 116 / 128.  (Two i-bodies per thread change nothing there: the 512 x 512 CTA is a
+// dependent chain, not an issue-bound one; profiles/r1f_f32_midsize_r.jsonl.)
+constexpr size_t kF32SmallTileMaxN = 4096;
 // The pairs-once pass (force_f64_sym.cuh) serves one-GPU MATH 2 contexts from 3,072 bodies up, while its partial
 // sums fit NBODY_F64_SYM_MAX_MB (default 4 GiB: N ~ 300k).  Below, its two launches and few CTAs lose to the
 // one-sided kernel (us/step one-sided vs pairs-once: N=2,048 16.8 / 20.5, N=4,096 38.1 / 30.9, N=16,384 291 / 190;
@@ -155,6 +160,27 @@ int alloc_shard(nbody_ctx* c, Shard& s)
     return NBODY_OK;
 }
 
+// The fp32 force kernel's variants (force_f32.cuh): nearest-neighbour tracking, equal-mass sweep, softening == 0, and the
+// ring-stage size `tp` (j-pairs: 512- or 128-body tiles).  Two i-bodies per thread (NBODY_R=2) exist for the plain general
+// sweep on 512-body tiles only; every other request with R = 2 gets the R = 4 kernel's nearest relative and must not
+// happen (create/upload keep R = 4 whenever tracking, equal masses or small tiles are in play).
+template <typename F> void pick_f32_kernel(bool near, bool uniform, bool z, int R, int tp, F&& f)
+{
+    auto by_tile = [&](auto nr, auto un, auto zs) {
+        constexpr bool N = decltype(nr)::value, U = decltype(un)::value, Z = decltype(zs)::value;
+        if (tp == kF32SmallTilePairs) {
+            if (N) return f(force_f32_near_kernel<4, Z, U, NB_NEAR_UNROLL, kF32SmallTilePairs>);
+            return f(force_f32_kernel<4, Z, U ? kUniUnroll : kF32Unroll, U, kF32SmallTilePairs>);
+        }
+        if (N) return f(force_f32_near_kernel<4, Z, U>);
+        if (!U && R == 2) return f(force_f32_kernel<2, Z>);
+        return f(force_f32_kernel<4, Z, U ? kUniUnroll : kF32Unroll, U>);
+    };
+    auto by_z = [&](auto nr, auto un) { return z ? by_tile(nr, un, std::true_type{}) : by_tile(nr, un, std::false_type{}); };
+    auto by_u = [&](auto nr) { return uniform ? by_z(nr, std::true_type{}) : by_z(nr, std::false_type{}); };
+    return near ? by_u(std::true_type{}) : by_u(std::false_type{});
+}
+
 // The fp64 force kernel's variants (force_f64.cuh): MATH 0/1 exist for one body per thread and general masses only.
 template <typename F> void pick_f64_kernel(int math, bool zero_soft, bool uniform, int R, F&& f)
 {
@@ -197,16 +223,15 @@ int set_kernel_attrs(nbody_ctx* c)
 {
     const int sm32 = int(force_f32_smem_bytes());
     const int sm64 = int(force_f64_smem_bytes());
-    CU(c, cudaFuncSetAttribute(force_f32_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
-    CU(c, cudaFuncSetAttribute(force_f32_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
-    CU(c, cudaFuncSetAttribute(force_f32_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
-    CU(c, cudaFuncSetAttribute(force_f32_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
-    CU(c, cudaFuncSetAttribute(force_f32_kernel<4, false, kUniUnroll, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
-    CU(c, cudaFuncSetAttribute(force_f32_kernel<4, true, kUniUnroll, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
-    CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
-    CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
-    CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
-    CU(c, cudaFuncSetAttribute(force_f32_near_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32));
+    for (int near = 0; near < 2; ++near)
+        for (int uni = 0; uni < 2; ++uni)
+            for (int z = 0; z < 2; ++z)
+                for (int R : {2, 4}) {  // (the 2 KiB-tile variants stay below the 48 KiB default)
+                    cudaError_t e = cudaSuccess;
+                    pick_f32_kernel(near != 0, uni != 0, z != 0, R, kF32TilePairs,
+                                    [&](auto kernel) { e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32); });
+                    if (e != cudaSuccess) return fail(c, NBODY_ECUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+                }
     CU(c, cudaFuncSetAttribute(small_step_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(small_smem_bytes<float>())));
     CU(c, cudaFuncSetAttribute(small_step_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(small_smem_bytes<double>())));
     return for_each_f64_kernel([&](auto kernel) { return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64); }, c);
@@ -685,6 +710,12 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     if (!pos_mass || !vel) return fail(c, NBODY_EINVAL, "upload: pos_mass and vel are required");
     c->n = n;
     c->f64_sym_k = 0;
+    if (c->prec == NBODY_F32) {
+        // small systems: 128-body j tiles, four times as many and four times shorter CTAs (force_f32.cuh)
+        const int forced = env_int("NBODY_F32_TILE", 0);  // bodies per tile: 128 or 512; 0 = by body count
+        const bool small_tile = c->R == 4 && (forced == 2 * kF32SmallTilePairs || (forced != 2 * kF32TilePairs && n <= kF32SmallTileMaxN));
+        c->j_unit = small_tile ? 2 * kF32SmallTilePairs : kJUnit;
+    }
     if (c->prec == NBODY_F64) {
         c->R = f64_bodies_per_thread(c, n);
         c->i_tile = kThreads * c->R;
@@ -879,25 +910,10 @@ int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
                 p.n_outliers = int(c->outliers.size());   // ... but for a few bodies, corrected per i-body
                 p.bulk_mass = float(c->uniform_mass);
             }
-            const size_t sm = force_f32_smem_bytes();
-            const bool z = (eps == 0.0);
+            const int tp = c->j_unit / 2;  // j-pairs per ring stage: the j unit is one tile
+            const size_t sm = tp == kF32SmallTilePairs ? force_f32_smem_bytes<kF32SmallTilePairs>() : force_f32_smem_bytes();
             const dim3 blk(kF32Threads + 32);
-            if (track_near && uniform) {
-                if (z) force_f32_near_kernel<4, true, true><<<grid, blk, sm, s.stream>>>(p);
-                else force_f32_near_kernel<4, false, true><<<grid, blk, sm, s.stream>>>(p);
-            } else if (track_near) {
-                if (z) force_f32_near_kernel<4, true><<<grid, blk, sm, s.stream>>>(p);
-                else force_f32_near_kernel<4, false><<<grid, blk, sm, s.stream>>>(p);
-            } else if (uniform) {
-                if (z) force_f32_kernel<4, true, kUniUnroll, true><<<grid, blk, sm, s.stream>>>(p);
-                else force_f32_kernel<4, false, kUniUnroll, true><<<grid, blk, sm, s.stream>>>(p);
-            } else if (c->R == 2) {
-                if (z) force_f32_kernel<2, true><<<grid, blk, sm, s.stream>>>(p);
-                else force_f32_kernel<2, false><<<grid, blk, sm, s.stream>>>(p);
-            } else {
-                if (z) force_f32_kernel<4, true><<<grid, blk, sm, s.stream>>>(p);
-                else force_f32_kernel<4, false><<<grid, blk, sm, s.stream>>>(p);
-            }
+            pick_f32_kernel(track_near, uniform, eps == 0.0, c->R, tp, [&](auto kernel) { kernel<<<grid, blk, sm, s.stream>>>(p); });
         } else {
             const ForceParams<double> p = make_params<double>(c, s, mode, dt, G, eps);
             const dim3 blk(kThreads + 32);
