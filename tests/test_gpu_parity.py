@@ -363,6 +363,39 @@ def test_physics_system_mirror(nb, oracle):
     assert len(ps3.bodies) == nb.CONFIG.maxBodies and ps3.bodies[0].pos.x == 5
 
 
+@pytest.mark.parametrize("n,eps", [(1000, 0.05), (5000, 0.0)])
+def test_f32_tile_sizes(nb, oracle, n, eps):
+    """The fp32 kernel's ring stage is 512 bodies, or 128 for systems of up to 4,096 bodies (more, shorter
+    CTAs; csrc/force_f32.cuh).  NBODY_F32_TILE forces either: both within the fp32 tolerance of the
+    oracle, general and equal masses, and a complete step agrees between them to fp32 rounding."""
+    s = nb.scenes.plummer(n)
+    pm, vel, _ = s.astype(np.float32)
+    pm_g = pm.copy()
+    pm_g[:, 3] *= np.random.default_rng(n).uniform(0.5, 2.0, n).astype(np.float32)
+    outs = {}
+    for tile in (128, 512):
+        os.environ["NBODY_F32_TILE"] = str(tile)
+        try:
+            for name, masses in (("equal", pm), ("general", pm_g)):
+                with nb.Engine(n, precision="f32") as e:
+                    e.upload(masses, vel)
+                    assert e.info()["uniform_mass"] == (1 if name == "equal" else 0)
+                    e.force(s.G, eps)
+                    acc = e.download()["acc"]
+                    e.step(s.dt, s.G, eps, 3)
+                    outs[tile, name] = (acc, e.download(), e.info()["j_chunks"])
+        finally:
+            del os.environ["NBODY_F32_TILE"]
+    for name, masses in (("equal", pm), ("general", pm_g)):
+        ref = oracle.compute_gravity(masses.astype(np.float64), s.G, eps, mt=True)
+        a128, o128, c128 = outs[128, name]
+        a512, o512, c512 = outs[512, name]
+        assert c128 > c512                                            # the j range really is cut finer
+        assert norm_rel_err(a128, ref) < F32_ACC_TOL and norm_rel_err(a512, ref) < F32_ACC_TOL
+        assert norm_rel_err(o128["pos_mass"], o512["pos_mass"]) < F32_POS_TOL
+        assert norm_rel_err(o128["vel"], o512["vel"]) < 1e-5
+
+
 # ---------------------------------------------------------------- equal-mass fast path -----------
 @pytest.mark.parametrize("n,eps", [(4096, 0.3), (5000, 0.05), (3000, 0.0)])
 def test_f32_uniform_mass_kernel(nb, oracle, n, eps):
