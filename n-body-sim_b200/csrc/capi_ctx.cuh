@@ -35,6 +35,7 @@ struct Shard {
     void* partial = nullptr;
     size_t partial_bytes = 0;
     unsigned* counters = nullptr;
+    unsigned* medium_arrivals = nullptr; // grid-barrier counter of medium_step_kernel (medium.cuh)
     double* sym_part_i = nullptr;       // fp64 pairs-once pass (force_f64_sym.cuh): per-chunk i-side sums
     double* sym_part_j = nullptr;       // ... and per-i-block j-side sums
     size_t sym_bytes_i = 0, sym_bytes_j = 0;
@@ -106,6 +107,10 @@ struct nbody_ctx {
     int f64_sym_r = 4;              // i-bodies per thread of that pass (fewer for small systems)
     int f64_sym_k = 0;              // j-blocks per CTA of that pass for the current upload; 0: the one-sided kernel
     int f64_R_forced = 0;          // NBODY_F64_R at create: 1 or 2 i-bodies per thread in the fp64 kernel, 0 = by body count
+    size_t medium_max_n = 0;        // largest system that kernel takes (fp32 5,120, fp64 4,096; NBODY_MEDIUM_MAX lowers it)
+    int medium_ctas = 0;            // > 0: systems of up to medium_max_n bodies run all steps of a call in one cooperative launch
+                                    // of this many CTAs (medium.cuh; NBODY_MEDIUM at create, one GPU, needs cooperative launch)
+    size_t small_max_n = 512;       // largest system the one-cluster kernel takes (NBODY_SMALL_MAX at create, <= kSmallMaxN)
     bool small_path = true;         // NBODY_SMALL at create: one-cluster multi-step kernel for n <= kSmallMaxN (small.cuh)
     bool detect_masses = false;     // upload in flight: pack_pos_kernel compares every mass with uniform_mass
     std::vector<MassOutlier> outliers;  // ... except these few (at most kMaxOutliers), corrected per i-body

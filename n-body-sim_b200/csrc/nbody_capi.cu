@@ -12,6 +12,7 @@
 #include "force_f64_sym.cuh"
 #include "integrate.cuh"
 #include "small.cuh"
+#include "medium.cuh"
 
 
 #ifndef NB_UNIFORM_UNROLL
@@ -146,6 +147,7 @@ int alloc_shard(nbody_ctx* c, Shard& s)
     CU(c, cudaMemset(s.counters, 0, ntiles * sizeof(unsigned)));
     CU(c, cudaMalloc(&s.flags, kMaxPeers * sizeof(unsigned long long)));
     CU(c, cudaMemset(s.flags, 0, kMaxPeers * sizeof(unsigned long long)));
+    CU(c, cudaMalloc(&s.medium_arrivals, sizeof(unsigned)));
     CU(c, cudaMalloc(&s.xerr, sizeof(unsigned)));
     CU(c, cudaMemset(s.xerr, 0, sizeof(unsigned)));
     s.energy_rows = (local_cap + kEnergyThreads - 1) / kEnergyThreads + 1;
@@ -234,6 +236,8 @@ int set_kernel_attrs(nbody_ctx* c)
                 }
     CU(c, cudaFuncSetAttribute(small_step_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(small_smem_bytes<float>())));
     CU(c, cudaFuncSetAttribute(small_step_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(small_smem_bytes<double>())));
+    CU(c, cudaFuncSetAttribute(medium_step_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(medium_smem_bytes<float>())));
+    CU(c, cudaFuncSetAttribute(medium_step_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(medium_smem_bytes<double>())));
     return for_each_f64_kernel([&](auto kernel) { return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm64); }, c);
 }
 
@@ -261,6 +265,10 @@ int create_common(nbody_ctx** out, nbody_prec prec, int world, size_t capacity, 
         c->i_tile = kThreads * c->R;
         c->j_unit = kJUnitF64;
     }
+    // one cluster up to here, all SMs above (measured crossover, profiles/r1f_small_vs_medium_crossover.jsonl: fp64 2.33 / 3.06 us
+    // per step at 151 bodies and 4.26 / 3.49 at 300; fp32 2.17 / 2.57 at 300 and 3.64 / 2.66 at 512)
+    const int small_default = prec == NBODY_F64 ? kSmallDefaultMaxN64 : kSmallDefaultMaxN32;
+    c->small_max_n = size_t(std::min(std::max(env_int("NBODY_SMALL_MAX", small_default), 0), kSmallMaxN));
     c->small_path = env_int("NBODY_SMALL", 1) != 0 && !(prec == NBODY_F64 && c->f64_math != 2);  // (its pair arithmetic is MATH 2's)
     c->cap_pad = round_up(capacity, pad_unit(c));
     *made = c;
@@ -312,6 +320,7 @@ extern "C" void nbody_destroy(nbody_ctx* c)
         for (void* m : s.ipc_opened) cudaIpcCloseMemHandle(m);
         cudaFree(s.flags);
         cudaFree(s.xerr);
+        cudaFree(s.medium_arrivals);
         cudaFree(s.pos[0]);
         cudaFree(s.pos[1]);
         cudaFree(s.stage);
@@ -471,6 +480,19 @@ static int create_body(nbody_ctx* c, const int* devs, int n_local_shards, const 
         rc = set_kernel_attrs(c);
         if (rc != NBODY_OK) return rc;
     }
+    if (c->world == 1 && c->small_path && env_int("NBODY_MEDIUM", 1) != 0) {
+        // one CTA per SM, all co-resident (the kernel's grid barrier needs that: cooperative launch)
+        int coop = 0, per_sm = 0;
+        CU(c, cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->shards[0].device));
+        if (c->prec == NBODY_F32)
+            CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, medium_step_kernel<float>, kMediumThreads, medium_smem_bytes<float>()));
+        else
+            CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, medium_step_kernel<double>, kMediumThreads, medium_smem_bytes<double>()));
+        c->medium_max_n = size_t(c->prec == NBODY_F32 ? medium_max_n<float>() : medium_max_n<double>());
+        c->medium_max_n = std::min(c->medium_max_n, size_t(std::max(env_int("NBODY_MEDIUM_MAX", int(c->medium_max_n)), 0)));
+        if (coop && per_sm >= 1 && size_t(c->sm_count) * kMediumThreads >= c->medium_max_n) c->medium_ctas = c->sm_count;
+    }
+    if (c->medium_ctas == 0 && !getenv("NBODY_SMALL_MAX")) c->small_max_n = kSmallMaxN;  // nobody else runs all steps in one launch
     if (c->world > 1) {
         if (!nccl().ok()) return fail(c, NBODY_ENCCL, "%s", nccl().error.c_str());
         if (c->rank_mode) {
@@ -973,6 +995,42 @@ template <typename Real> int launch_small_steps_t(nbody_ctx* c, Shard& s, double
     return NBODY_OK;
 }
 
+// ... and of a system of up to medium_max_n bodies in one cooperative launch over all SMs (medium.cuh).
+template <typename Real> int launch_medium_steps_t(nbody_ctx* c, Shard& s, double dt, double G, double eps, int nsteps)
+{
+    MediumParams<Real> p;
+    p.pos[0] = static_cast<Real*>(s.pos[c->cur]);
+    p.pos[1] = static_cast<Real*>(s.pos[c->cur ^ 1]);
+    p.vel = static_cast<Real*>(s.vel);
+    p.acc = static_cast<Real*>(s.acc);
+    p.temp = c->has_temp ? static_cast<Real*>(s.temp) : nullptr;
+    p.arrivals = s.medium_arrivals;
+    p.n = int(c->n);
+    p.nsteps = nsteps;
+    p.G = Real(G);
+    p.eps2 = Real(eps) * Real(eps);
+    p.r2_floor = eps == 0.0 ? Real(1e-20) : Real(0);
+    p.half_dt = Real(0.5) * Real(dt);
+    p.dt = Real(dt);
+    p.heat_decay = Real(c->heat_decay);
+    CU(c, cudaMemsetAsync(s.medium_arrivals, 0, sizeof(unsigned), s.stream));
+    void* args[] = {&p};
+    CU(c, cudaLaunchCooperativeKernel(reinterpret_cast<void*>(medium_step_kernel<Real>), dim3(unsigned(c->medium_ctas)), dim3(kMediumThreads), args,
+                                      medium_smem_bytes<Real>(), s.stream));
+    c->launches++;
+    c->cur ^= nsteps & 1;  // step s drifts into the other buffer
+    return NBODY_OK;
+}
+
+int launch_medium_steps(nbody_ctx* c, double dt, double G, double eps, int nsteps)
+{
+    Shard& s = c->shards[0];
+    CU(c, cudaSetDevice(s.device));
+    c->near_valid = false;
+    return c->prec == NBODY_F32 ? launch_medium_steps_t<float>(c, s, dt, G, eps, nsteps)
+                                : launch_medium_steps_t<double>(c, s, dt, G, eps, nsteps);
+}
+
 int launch_small_steps(nbody_ctx* c, double dt, double G, double eps, int nsteps)
 {
     Shard& s = c->shards[0];
@@ -1014,7 +1072,8 @@ extern "C" int nbody_step(nbody_ctx* c, double dt, double G, double softening, i
     if (rc != NBODY_OK) return rc;
     if (nsteps < 0 || softening < 0.0) return fail(c, NBODY_EINVAL, "step: nsteps=%d softening=%g", nsteps, softening);
     if (nsteps == 0) return NBODY_OK;
-    if (c->small_path && c->world == 1 && c->n <= size_t(kSmallMaxN) && !c->timing) return launch_small_steps(c, dt, G, softening, nsteps);
+    if (c->small_path && c->world == 1 && c->n <= c->small_max_n && !c->timing) return launch_small_steps(c, dt, G, softening, nsteps);
+    if (c->medium_ctas > 0 && c->n <= c->medium_max_n && !c->timing) return launch_medium_steps(c, dt, G, softening, nsteps);
     // First loop of integrate() for the first step (idx:250-253); later steps
     // get theirs from the previous force kernel's epilogue, so positions cross
     // HBM once per step.

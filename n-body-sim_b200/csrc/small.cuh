@@ -30,7 +30,8 @@ namespace cg = cooperative_groups;
 
 constexpr int kSmallCluster = 8;    // portable cluster size
 constexpr int kSmallThreads = 1024;  // 8 warps per scheduler: the per-pair dependency chain (~13 ops) hides behind other warps
-constexpr int kSmallMaxN = 512;     // above this the launch-per-step kernels on all 148 SMs win
+constexpr int kSmallMaxN = 512;     // what the kernel's shared memory holds
+constexpr int kSmallDefaultMaxN64 = 224, kSmallDefaultMaxN32 = 384;  // above this the all-SM one-launch kernel (medium.cuh) takes over
 
 template <typename Real> constexpr size_t small_smem_bytes() { return (2 * size_t(kSmallMaxN) + kSmallThreads) * 4 * sizeof(Real); }
 

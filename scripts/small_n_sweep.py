@@ -12,10 +12,10 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import nbody_b200 as nb  # noqa: E402
 
 for prec in ("f64", "f32"):
-    for n in (151, 300, 512, 1024, 2048, 4096):
+    for n in (151, 300, 512, 768, 1024, 2048, 3072, 4096, 6144, 8192):
         s = nb.scenes.galaxy_default() if n == 151 else nb.scenes.plummer(n)
         pm, vel, _ = s.astype(np.float32 if prec == "f32" else np.float64)
-        with nb.Engine(max(n, 1024), precision=prec) as e:
+        with nb.Engine(max(n, 1024), precision=prec) as e:  # (k = 2000 steps per call; fewer for the larger systems)
             e.upload(pm, vel)
             e.step(s.dt, s.G, s.softening, 10)
             e.sync()

@@ -131,7 +131,7 @@ def test_multi_gpu_render_and_trails(nb, oracle):
 @pytest.mark.parametrize("n", [1, 2, 7, 8, 9, 151, 300, 512, 513])
 def test_small_system_kernel(nb, oracle, precision, tol, n):
     """N <= 512 on one GPU: nbody_step is one launch of one thread-block cluster that runs all the
-    steps (N = 513 takes the launch-per-step kernels).  Against the oracle's integrate() and against
+    steps (N = 513 takes the cooperative all-SM kernel, medium.cuh).  Against the oracle's integrate() and against
     the launch-per-step path, cluster shares from 1 body per CTA (and idle CTAs) to 64; thermal decay
     bit-exact; a second call continues from the stored acc."""
     dt = np.float64 if precision == "f64" else np.float32
@@ -156,7 +156,7 @@ def test_small_system_kernel(nb, oracle, precision, tol, n):
             del os.environ["NBODY_SMALL"]
 
     out, launches = run(True)
-    assert launches == (1 if n <= 512 else 6)                 # kick1_drift + 5 force kernels otherwise
+    assert launches == 1                                      # (513 bodies: the all-SM form of the same idea, medium.cuh)
     p, v, a, t = oracle.integrate(pm, vel, np.zeros_like(vel), temp, h, G, eps, nsteps=6)
     scale = max(1.0, np.abs(p[:, :3]).max())
     assert np.abs(out["pos_mass"][:, :3] - p[:, :3]).max() < tol * scale
@@ -185,3 +185,78 @@ def test_small_system_kernel_zero_softening(nb, oracle, precision):
     assert np.isfinite(out["acc"]).all()
     tol = 1e-12 if precision == "f64" else 2e-5
     assert norm_rel_err(out["pos_mass"], p) < tol and norm_rel_err(out["acc"], a) < 10 * tol
+
+
+# ---- 513 .. 4,096 bodies: all steps of a call in one cooperative launch over all SMs (csrc/medium.cuh) ----------
+
+@pytest.mark.parametrize("precision,tol", [("f64", 1e-12), ("f32", 3e-5)])
+@pytest.mark.parametrize("n,eps", [(513, 0.5), (600, 0.0), (1000, 0.05), (2049, 0.5), (4096, 0.05)])
+def test_medium_system_kernel(nb, oracle, precision, tol, n, eps):
+    """One launch runs every step of the call, positions exchanged through the context's two position
+    buffers with one grid barrier per step.  Against the oracle's integrate() and against the
+    launch-per-step path (NBODY_MEDIUM=0); odd and even step counts (the current buffer flips), a second
+    call continues from the stored acc, thermal decay bit-exact, a force pass afterwards reads the
+    right buffer, two runs agree bit for bit."""
+    dt = np.float64 if precision == "f64" else np.float32
+    rng = np.random.default_rng(200 + n)
+    pm = np.concatenate([rng.normal(0, 6, (n, 3)), rng.uniform(0.5, 2.5, (n, 1))], axis=1).astype(dt)
+    vel = np.zeros((n, 4), dt)
+    vel[:, :3] = rng.normal(0, 0.3, (n, 3))
+    temp = rng.uniform(0, 50, n).astype(dt)
+    G, h = 0.5, 0.004
+
+    def run(medium, cap=n):
+        os.environ["NBODY_MEDIUM"] = "1" if medium else "0"
+        try:
+            with nb.Engine(cap, precision=precision) as e:
+                e.upload(pm[:cap] if cap < n else pm, vel, None, temp)
+                l0 = e.info()["kernel_launches"]
+                e.step(h, G, eps, 3)
+                launches = e.info()["kernel_launches"] - l0
+                e.step(h, G, eps, 2)
+                out = e.download(temp=True)
+                e.force(G, eps)
+                return out, launches, e.download()["acc"]
+        finally:
+            del os.environ["NBODY_MEDIUM"]
+
+    out, launches, acc_again = run(True)
+    assert launches == 1
+    p, v, a, t = oracle.integrate(pm, vel, np.zeros_like(vel), temp, h, G, eps, nsteps=5)
+    scale = max(1.0, np.abs(p[:, :3]).max())
+    assert np.abs(out["pos_mass"][:, :3] - p[:, :3]).max() < tol * scale
+    assert np.abs(out["vel"][:, :3] - v[:, :3]).max() < 10 * tol * max(1.0, np.abs(v).max())
+    assert np.abs(out["acc"][:, :3] - a[:, :3]).max() < 10 * tol * max(1e-3, np.abs(a).max())
+    assert np.array_equal(out["pos_mass"][:, 3], pm[:, 3])
+    if precision == "f64":
+        np.testing.assert_array_equal(out["temp"], t)
+    assert np.abs(acc_again[:, :3] - a[:, :3]).max() < 10 * tol * max(1e-3, np.abs(a).max())   # same positions, other kernel
+    ref, ref_launches, _ = run(False)
+    assert ref_launches >= 4                                   # kick1_drift + 3 force passes (two kernels each in the fp64 pairs-once pass)
+    for k in ("pos_mass", "vel", "acc"):
+        assert np.abs(out[k] - ref[k]).max() < 10 * tol * max(1.0, np.abs(ref[k]).max()), k
+    np.testing.assert_array_equal(out["temp"], ref["temp"])
+    again, _, _ = run(True)
+    for k in ("pos_mass", "vel", "acc", "temp"):
+        np.testing.assert_array_equal(out[k], again[k])
+
+
+@pytest.mark.parametrize("precision,n_max", [("f32", 5120), ("f64", 4096)])
+def test_medium_system_kernel_upper_bound(nb, oracle, precision, n_max):
+    """The largest system of each precision (where the launch-per-step kernels catch up) against the oracle; one body more
+    takes the launch-per-step kernels."""
+    dt = np.float32 if precision == "f32" else np.float64
+    for n in (n_max, n_max + 1):
+        s = nb.scenes.plummer(n)
+        pm, vel, _ = s.astype(dt)
+        with nb.Engine(s.n, precision=precision) as e:
+            e.upload(pm, vel)
+            l0 = e.info()["kernel_launches"]
+            e.step(s.dt, s.G, s.softening, 3)
+            launches = e.info()["kernel_launches"] - l0
+            out = e.download()
+        assert (launches == 1) if n == n_max else (launches >= 4)
+        if n == n_max:
+            p, v, a, _ = oracle.integrate(pm, vel, np.zeros_like(vel), None, s.dt, s.G, s.softening, nsteps=3)
+            tol = 1e-12 if precision == "f64" else 1e-6
+            assert norm_rel_err(out["pos_mass"], p) < tol and norm_rel_err(out["acc"], a) < (1e-12 if precision == "f64" else 2e-5)
