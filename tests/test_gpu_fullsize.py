@@ -85,6 +85,9 @@ def test_multi_gpu_bit_identical(nb, precision, exchange):
     pm, vel, t = s.astype(dt)
     outs = []
     os.environ["NBODY_EXCHANGE"] = exchange
+    # (fp64 on ONE GPU would take the pairs-once pass, force_f64_sym.cuh: the same terms added in another order,
+    # 1e-15 away; the property tested here is the sharded one-sided kernels')
+    os.environ["NBODY_F64_SYM"] = "0"
     try:
         for g in sorted({1, 2, min(ng, 4), min(ng, 8)}):
             with nb.Engine(s.n, precision=precision, n_gpus=g) as e:
@@ -95,6 +98,7 @@ def test_multi_gpu_bit_identical(nb, precision, exchange):
                 outs.append((g, e.download(temp=True), e.energy(s.G, s.softening)))
     finally:
         os.environ.pop("NBODY_EXCHANGE", None)
+        os.environ.pop("NBODY_F64_SYM", None)
     for g, o, en in outs[1:]:
         for k in ("pos_mass", "vel", "acc", "temp"):
             assert np.array_equal(o[k], outs[0][1][k]), (g, k)
