@@ -101,6 +101,34 @@ def test_f64_golden_fixtures(nb, name):
     np.testing.assert_array_equal(out["temp"], g["temp"])
 
 
+@pytest.mark.parametrize("name", ["ref_js_galaxy151_gravity", "ref_js_plummer256_gravity"])
+def test_f64_reference_source_vectors(nb, name):
+    """fp64 mode against vectors produced by the reference's OWN source text (tests/golden/
+    make_reference_golden.py executes index.html's integrate/computeGravity through oracle/js_reference.py).
+    Gate: 1e-12 norm-relative after one and after two calls (one animate() frame, idx:877-879); the later
+    checkpoints (100, 1000 calls of a chaotic system) amplify the 1e-16 per-step differences."""
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    gates = {1: F64_GATE, 2: F64_GATE, 10: 1e-11, 100: 1e-11, 1000: 1e-9}
+    with nb.Engine(g["pos_mass0"].shape[0], precision="f64") as e:
+        e.upload(g["pos_mass0"], g["vel0"], None, g["temp0"])
+        done = 0
+        for k, c in enumerate(g["checkpoints"]):
+            e.step(float(g["dt"]), float(g["G"]), float(g["softening"]), int(c) - done)
+            done = int(c)
+            out = e.download(temp=True)
+            for key in ("pos_mass", "vel", "acc"):
+                assert norm_rel_err(out[key], g[key][k]) < gates[int(c)], (name, int(c), key)
+            np.testing.assert_array_equal(out["temp"], g["temp"][k])
+        # the per-step gate restarted from the reference's own state (non-zero acc going into kick-1, idx:251)
+        assert list(g["checkpoints"][:2]) == [1, 2]
+        e.upload(g["pos_mass"][0], g["vel"][0], g["acc"][0], g["temp"][0])
+        e.step(float(g["dt"]), float(g["G"]), float(g["softening"]), 1)
+        out = e.download(temp=True)
+        assert np.array_equal(out["pos_mass"], g["pos_mass"][1])          # kick-1 + drift: the same rounded operations
+        for key in ("vel", "acc"):
+            assert norm_rel_err(out[key], g[key][1]) < F64_GATE, (name, "restart", key)
+
+
 @pytest.mark.parametrize("math", [0, 1, 2])
 @pytest.mark.parametrize("eps", [0.5, 0.0])
 def test_f64_math_variants(nb, oracle, math, eps):
