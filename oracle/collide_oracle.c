@@ -7,8 +7,12 @@
  * together with the Body constructor (idx:208-225), addBody (idx:239-245) and
  * the full integrate(dt) that calls them (idx:247-262).  SURVEY.md 8(f) row 1.
  *
- * PARITY UNPINNED (see nbody_oracle.c): the reference has no tests or golden
- * vectors for this stage and its JS cannot be run here.  The restatement is
+ * PARITY PINNED TO THE REFERENCE'S SOURCE TEXT, NOT TO V8 (see nbody_oracle.c):
+ * the reference has no tests or golden vectors for this stage and no JS engine
+ * exists here; oracle/js_reference.py executes the reference's own
+ * resolveCollisions / mergeBodies / fractureBodies text and this restatement
+ * equals it bit for bit through merges and fractures, new ids and random draws
+ * included (tests/test_reference_source.py).  The restatement is
  * statement by statement, in the reference's association, with the
  * THREE.Vector3 members it calls written out (three@0.160.0, un-vendored):
  *   normalize()       = multiplyScalar(1 / (length() || 1))

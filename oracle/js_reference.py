@@ -200,9 +200,14 @@ class Parser:
         self.eat("++")
         self.eat(")")
         body = self.statement()
-        if bound[0] not in ("id", "num") or (bound[0] == "id" and _assigns(body, bound[1])) or _assigns(body, var):
-            raise SyntaxError("js subset: counted for needs a loop-invariant bound (a name or a literal) and an unmodified counter")
-        return ("forrange", var, start, bound, body)
+        if _assigns(body, var):
+            raise SyntaxError("js subset: counted for must not modify its counter")
+        if bound[0] == "num" or (bound[0] == "id" and not _assigns(body, bound[1])):
+            return ("forrange", var, start, bound, body)
+        # any other bound (idx:519 `trailLen - 1`, idx:567 `body.history.length`) is re-evaluated every pass, as in JS
+        if _own_continue(body):
+            raise SyntaxError("js subset: `continue` in a counted for with a computed bound is not supported")
+        return ("forwhile", var, start, bound, body)
 
     # expressions
     def expr(self):
@@ -286,6 +291,17 @@ class Parser:
                     return self.t[j + 1] == ("op", "=>")
             j += 1
 
+    def _arrow_body(self, ps):
+        if not self.at("{"):
+            return ("arrow", ps, self.assign())
+        body = self.block()
+        outer = _assigned_names(body) - _declared_names(body) - set(ps)
+        if outer:   # Python closures cannot rebind an enclosing local without `nonlocal`
+            raise SyntaxError(f"js subset: arrow function assigns to enclosing variable(s) {sorted(outer)}")
+        if _has(body, "return"):
+            raise SyntaxError("js subset: `return` inside a block-bodied arrow function is not supported")
+        return ("arrowblock", ps, body)
+
     def primary(self):
         k, v = self.peek()
         if k == "num":
@@ -306,15 +322,13 @@ class Parser:
             self.i += 1
             if self.at("=>"):
                 self.i += 1
-                return ("arrow", [v], self.assign())
+                return self._arrow_body([v])
             return ("id", v)
         if v == "(":
             if self._arrow_ahead():
                 ps = [p for p, d in self.params()]
                 self.eat("=>")
-                if self.at("{"):
-                    raise SyntaxError("js subset: block-bodied arrow functions are not supported")
-                return ("arrow", ps, self.assign())
+                return self._arrow_body(ps)
             self.i += 1
             e = self.expr()
             self.eat(")")
@@ -358,6 +372,47 @@ def _assigns(node, name) -> bool:
     return False
 
 
+def _walk(node):
+    if isinstance(node, tuple):
+        yield node
+        for c in node[1:]:
+            yield from _walk(c)
+    elif isinstance(node, list):
+        for c in node:
+            yield from _walk(c)
+
+
+def _has(node, kind) -> bool:
+    return any(n and n[0] == kind for n in _walk(node))
+
+
+def _assigned_names(node) -> set:
+    return {n[2][1] for n in _walk(node) if n and n[0] in ("assign", "update") and isinstance(n[2], tuple) and n[2][0] == "id"}
+
+
+def _declared_names(node) -> set:
+    out = set()
+    for n in _walk(node):
+        if n and n[0] == "decl":
+            out |= {name for name, _ in n[1]}
+        elif n and n[0] in ("forrange", "forwhile", "forof"):
+            out.add(n[1])
+    return out
+
+
+def _own_continue(node) -> bool:
+    """A `continue` that belongs to the loop whose body `node` is (not to a loop nested inside it)."""
+    if isinstance(node, tuple):
+        if node and node[0] == "continue":
+            return True
+        if node and node[0] in ("forrange", "forwhile", "forof", "arrowblock"):
+            return False
+        return any(_own_continue(c) for c in node[1:])
+    if isinstance(node, list):
+        return any(_own_continue(c) for c in node)
+    return False
+
+
 # ---------------------------------------------------------------- Python emitter
 
 _CONSTANTS = {"true": "True", "false": "False", "null": "None", "undefined": "None"}
@@ -371,8 +426,24 @@ def _name(n: str) -> str:
     return n + "_" if keyword.iskeyword(n) else n
 
 
+_HOIST = []      # block-bodied arrow functions met while emitting a statement's expressions: (name, params, block)
+_COUNTER = [0]
+
+
+def _flush_hoisted(ind: int, out: list):
+    while _HOIST:
+        name, params, block = _HOIST.pop(0)
+        out.append(f"{'    ' * ind}def {name}({', '.join(_name(p) for p in params)}):")
+        emit_body(block, ind + 1, out)
+
+
 def emit_expr(e) -> str:
     k = e[0]
+    if k == "arrowblock":
+        _COUNTER[0] += 1
+        name = f"_arrow_{_COUNTER[0]}"
+        _HOIST.append((name, e[1], e[2]))
+        return name
     if k == "num":
         return e[1]
     if k == "str":
@@ -406,6 +477,11 @@ def emit_expr(e) -> str:
 def emit_stmt(s, ind: int, out: list):
     pad = "    " * ind
     k = s[0]
+
+    def line(text):          # the statement's own expressions are emitted first, so hoisted defs land above it
+        _flush_hoisted(ind, out)
+        out.append(pad + text)
+
     if k == "block":
         if not s[1]:
             out.append(pad + "pass")
@@ -413,38 +489,43 @@ def emit_stmt(s, ind: int, out: list):
             emit_stmt(c, ind, out)
     elif k == "func":
         ps = [_name(p) + (f"={emit_expr(d)}" if d is not None else "") for p, d in s[2]]
-        out.append(f"{pad}def {_name(s[1])}({', '.join(ps)}):")
+        line(f"def {_name(s[1])}({', '.join(ps)}):")
         emit_body(s[3], ind + 1, out)
     elif k == "decl":
         for name, value in s[1]:
-            out.append(f"{pad}{_name(name)} = {emit_expr(value) if value is not None else 'None'}")
+            line(f"{_name(name)} = {emit_expr(value) if value is not None else 'None'}")
     elif k == "if":
-        out.append(f"{pad}if {emit_expr(s[1])}:")
+        line(f"if {emit_expr(s[1])}:")
         emit_body(s[2], ind + 1, out)
         if s[3] is not None:
             out.append(pad + "else:")
             emit_body(s[3], ind + 1, out)
     elif k == "forof":
-        out.append(f"{pad}for {_name(s[1])} in {emit_expr(s[2])}:")
+        line(f"for {_name(s[1])} in {emit_expr(s[2])}:")
         emit_body(s[3], ind + 1, out)
     elif k == "forrange":
-        out.append(f"{pad}for {_name(s[1])} in range({emit_expr(s[2])}, {emit_expr(s[3])}):")
+        line(f"for {_name(s[1])} in range({emit_expr(s[2])}, {emit_expr(s[3])}):")
         emit_body(s[4], ind + 1, out)
+    elif k == "forwhile":
+        line(f"{_name(s[1])} = {emit_expr(s[2])}")
+        line(f"while ({_name(s[1])} < {emit_expr(s[3])}):")
+        emit_body(s[4], ind + 1, out)
+        out.append(f"{pad}    {_name(s[1])} += 1")
     elif k == "return":
-        out.append(f"{pad}return {emit_expr(s[1]) if s[1] is not None else ''}".rstrip())
+        line(f"return {emit_expr(s[1]) if s[1] is not None else ''}".rstrip())
     elif k in ("continue", "break"):
         out.append(pad + k)
     elif k == "expr":
         e = s[1]
         if e[0] == "assign":
             if e[1] == "/=":
-                out.append(f"{pad}{emit_expr(e[2])} = _div({emit_expr(e[2])}, {emit_expr(e[3])})")
+                line(f"{emit_expr(e[2])} = _div({emit_expr(e[2])}, {emit_expr(e[3])})")
             else:
-                out.append(f"{pad}{emit_expr(e[2])} {e[1]} {emit_expr(e[3])}")
+                line(f"{emit_expr(e[2])} {e[1]} {emit_expr(e[3])}")
         elif e[0] == "update":
-            out.append(f"{pad}{emit_expr(e[2])} {'+=' if e[1] == '++' else '-='} 1")
+            line(f"{emit_expr(e[2])} {'+=' if e[1] == '++' else '-='} 1")
         else:
-            out.append(pad + emit_expr(e))
+            line(emit_expr(e))
     else:
         raise SyntaxError(f"js subset: cannot emit {k}")
 
@@ -501,6 +582,19 @@ class JSArray(list):
 
     def filter(self, fn):
         return JSArray(x for i, x in enumerate(self) if fn(x, i))
+
+    def forEach(self, fn):
+        i = 0
+        while i < len(self):                 # live length, like Array.prototype.forEach over a dense array
+            fn(self[i])
+            i += 1
+
+    def map(self, fn):
+        return JSArray(fn(x) for x in self)
+
+    def unshift(self, *items):
+        self[0:0] = items
+        return len(self)
 
     def sort(self, cmp=None):                # ids are numbers here (see module docstring): numeric order
         assert cmp is None
@@ -629,6 +723,17 @@ class Vector3:
     def normalize(self):
         return self.divideScalar(self.length() or 1)
 
+    def crossVectors(self, a, b):
+        ax, ay, az, bx, by, bz = a.x, a.y, a.z, b.x, b.y, b.z
+        self.x = ay * bz - az * by
+        self.y = az * bx - ax * bz
+        self.z = ax * by - ay * bx
+        return self
+
+    def setScalar(self, s):
+        self.x = self.y = self.z = s
+        return self
+
 
 class _Color:
     def __init__(self, *rgb):
@@ -749,6 +854,99 @@ class Reference:
             st["temp"][i], st["radius"][i], st["id"][i] = b.temperature, b.radius, b.id
             st["type"][i] = TYPES.index(b.type)
         return st
+
+
+# ---------------------------------------------------------------- the renderer feed: VisualSystem.update (idx:500-597)
+
+class _Bag:
+    """A plain JS object / three.js object whose members the page only stores."""
+
+    def __init__(self, *args, **kw):
+        self.args = args
+        self.__dict__.update(kw)
+
+
+class _BufferGeometry(_Bag):
+    def __init__(self):
+        self.attributes = _Bag()
+        self.index = None
+
+    def setIndex(self, indices):
+        self.index = indices
+
+    def setAttribute(self, name, attr):
+        setattr(self.attributes, name, attr)
+
+
+class _BufferAttribute(_Bag):
+    def __init__(self, array, itemSize):
+        self.array, self.itemSize, self.needsUpdate = array, itemSize, False
+
+
+class _Mesh(_Bag):
+    def __init__(self, geometry, material):
+        self.geometry, self.material = geometry, material
+        self.position, self.scale, self.rotation = Vector3(), Vector3(1, 1, 1), Vector3()
+        self.frustumCulled = True
+
+
+class _ThreeVisual(_Three):
+    Mesh = _Mesh
+    BufferGeometry = _BufferGeometry
+    BufferAttribute = _BufferAttribute
+    MeshBasicMaterial = _Bag
+    AdditiveBlending = 2
+    DoubleSide = 2
+
+
+def _float32_array(n):
+    import numpy as np
+    return np.zeros(int(n), dtype=np.float32)      # stores round to binary32, like a JS Float32Array
+
+
+class ReferenceVisuals:
+    """`VisualSystem.update(bodies, dt)` executed from the page's source (idx:500-597): per body the
+    `history` unshift/pop (idx:540, 564-565) and the camera-facing ribbon vertices (idx:567-592) written
+    into a Float32Array.  The method is sliced out on its own: the constructor, materials, particles and
+    flashes (WebGL objects, `Math.random`-driven, no effect on the ribbons) are stand-ins, and the scene
+    graph objects it creates are inert records."""
+
+    def __init__(self, reference: "Reference", camera=(0.0, 80.0, 150.0), html=REFERENCE_HTML):
+        with open(html, encoding="utf-8") as f:
+            page = f.read()
+        body = _slice(page, "update(bodies, dt) {", "garbageCollect(activeBodies) {")
+        self.python_source = transliterate("class VisualUpdate {\n" + body + "\n}")
+        self.Math = _Math(0xC0FFEE)                 # its own stream: idx:557 draws only for bodies hotter than 50
+        self.clock = 0.0
+        ns = {"THREE": _ThreeVisual, "Math": self.Math, "CONFIG": reference.CONFIG, "JSArray": JSArray, "JSObject": _Bag_from_dict,
+              "Map": JSMap, "Set": JSSet, "_div": _div, "Float32Array": _float32_array,
+              "performance": _Bag(now=lambda: self.clock)}
+        exec(compile(self.python_source, "<index.html idx:500-597 transliterated>", "exec"), ns)
+        v = self.v = ns["VisualUpdate"]()
+        v.scene, v.camera = _Bag(add=lambda obj: None), _Bag(position=Vector3(*map(float, camera)))
+        v.meshMap, v.trailMap, v.geo = JSMap(), JSMap(), _Bag()                       # idx:454-458
+        v.vecToCam, v.vecDir, v.vecPerp = Vector3(), Vector3(), Vector3()            # idx:480-482
+        v.createPlanetMaterial = lambda type: _Bag(uniforms=_Bag(time=_Bag(value=0), temperature=_Bag(value=0)))
+        v.spawnTrail = lambda body: None
+        v.updateParticles = lambda dt: None
+        self.reference = reference
+
+    def update(self, dt):
+        self.clock += 1000.0 * dt
+        self.v.update(self.reference.physics.bodies, dt)
+
+    def ribbons(self):
+        """float32 [n, trailLength, 6] in body order: the `position` arrays the page hands to WebGL."""
+        import numpy as np
+        return np.stack([self.v.trailMap.get(b.id).positions.reshape(-1, 6) for b in self.reference.physics.bodies])
+
+    def histories(self):
+        import numpy as np
+        return np.array([[(p.x, p.y, p.z) for p in b.history] for b in self.reference.physics.bodies])
+
+
+def _Bag_from_dict(d):
+    return _Bag(**d)
 
 
 def available(html=REFERENCE_HTML) -> bool:

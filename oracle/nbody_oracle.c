@@ -6,11 +6,15 @@
  * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
  * may load this library; the product path (libnbody.so) never does.
  *
- * PARITY UNPINNED: the reference ships no tests, fixtures or golden vectors
- * (SURVEY.md section 4), and no JavaScript engine exists in the build
- * container or can be installed, so this restatement could not be run against
- * the reference's own JS.  It follows the reference statement by statement;
- * the pins that do exist are the analytic known answers in tests/.
+ * PARITY PINNED TO THE REFERENCE'S SOURCE TEXT, NOT TO V8: the reference ships
+ * no tests, fixtures or golden vectors and no JavaScript
+ * engine exists in the build container or on the GPU box.  oracle/js_reference.py
+ * slices the reference's own statements out of index.html at run time and
+ * executes them through a JavaScript-subset transliterator (IEEE binary64
+ * arithmetic, libm pow); this restatement equals that execution BIT FOR BIT
+ * (tests/test_reference_source.py, committed vectors tests/golden/ref_js_*.npz).
+ * What stays unpinned is V8 itself: its Math.pow may differ from libm's by an
+ * ulp on rare inputs (1e-16 relative, four orders below the 1e-12 gate).
  *
  * Arithmetic rules (so that the result equals V8's wherever pow() agrees):
  *   - double everywhere, compiled with -O2 -ffp-contract=off -fno-fast-math

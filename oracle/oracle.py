@@ -2,8 +2,8 @@
 
 TEST INFRASTRUCTURE ONLY.  Importers allowed: tests/, __graft_entry__.smoke(),
 and bench.py's cpu_baseline / --impl reference legs.  The product package
-(n-body-sim_b200/) never imports this module.  PARITY UNPINNED: see the header
-of nbody_oracle.c.
+(n-body-sim_b200/) never imports this module.  Parity: pinned to the reference's source text
+(oracle/js_reference.py), not to V8 -- see the header of nbody_oracle.c.
 
 All arrays are float64, C-contiguous, in the host layout of include/nbody.h:
 pos_mass[n,4] = x,y,z,m; vel[n,4]; acc[n,4]; temp[n].

@@ -4,7 +4,10 @@
  * CPU fp64 restatement of the arithmetic parts of the reference's VisualSystem that
  * the B200 path reproduces headless (/root/reference/index.html, "idx:NNN"):
  *   - the ribbon-trail vertex loop of VisualSystem.update, idx:563-592;
- * PARITY UNPINNED: the reference has no tests and needs a browser + WebGL to run.
+ *     PINNED TO THE REFERENCE'S SOURCE TEXT: oracle/js_reference.py executes the page's own
+ *     VisualSystem.update and this loop equals its Float32Array bit for bit
+ *     (tests/test_reference_source.py, tests/golden/ref_js_page_galaxy_ribbons.npz);
+ *   - the planet shaders, idx:83-202 (GLSL: PARITY UNPINNED, needs a browser + WebGL to run).
  * THREE.Vector3 members written out (three@0.160.0): subVectors, crossVectors
  * (x = ay*bz - az*by, y = az*bx - ax*bz, z = ax*by - ay*bx), normalize =
  * multiplyScalar(1 / (length() || 1)), multiplyScalar.

@@ -4,7 +4,7 @@ The reference (/root/reference/index.html) is a browser page with no tests and
 no runnable engine in this image, so these vectors are produced by the oracle
 restatement itself: they pin the oracle against regressions and give the GPU
 tests fixed bytes to compare with; they do NOT pin the oracle against the
-reference (parity unpinned).   Run:  python tests/golden/make_golden.py
+reference (make_reference_golden.py's vectors do).   Run:  python tests/golden/make_golden.py
 """
 import os
 import sys

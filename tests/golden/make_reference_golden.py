@@ -74,6 +74,26 @@ def collision_fixture(name, bodies, seed, nsteps, dt=0.008, reseed=None, referen
     print(name, len(bodies), "->", len(r.physics.bodies), "bodies;", r.visuals.flash, "flashes,", r.visuals.explosion, "fragments")
 
 
+def ribbons_fixture(name, frames, keep_every=5):
+    """animate() (idx:873-883): subSteps x integrate(dt/subSteps) then visuals.update(bodies, dt), complete step
+    with collisions, the page's own default scene.  Stores every `keep_every`-th body's history and ribbon
+    vertices (the Float32Array the page hands to WebGL, idx:583-589) after the last frame."""
+    r = jr.Reference(seed=5, collisions=True)
+    r.resetScenario("galaxy")
+    r.Math.state = 1234
+    vis = jr.ReferenceVisuals(r)
+    c = r.CONFIG
+    for _ in range(frames):
+        r.integrate(c.dt / c.subSteps, c.subSteps)
+        vis.update(c.dt)
+    st = r.state()
+    keep = np.arange(0, len(st["temp"]), keep_every)
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), frames=frames, camera=np.array([0.0, 80.0, 150.0]),
+                        n_bodies=len(st["temp"]), kept=keep, radius=st["radius"][keep], history=vis.histories()[keep],
+                        ribbons=vis.ribbons()[keep], trail_length=c.trailLength)
+    print(name, frames, "frames,", len(st["temp"]), "bodies,", len(keep), "kept")
+
+
 if __name__ == "__main__":
     if not jr.available():
         sys.exit("needs /root/reference/index.html")
@@ -88,3 +108,4 @@ if __name__ == "__main__":
     page = [(s0["pos_mass"][i, 3], tuple(s0["pos_mass"][i, :3]), tuple(s0["vel"][i, :3]), jr.TYPES[s0["type"][i]], s0["temp"][i])
             for i in range(len(s0["temp"]))]
     collision_fixture("ref_js_page_galaxy_collisions", page, seed=5, nsteps=200, reseed=1234, reference=r)
+    ribbons_fixture("ref_js_page_galaxy_ribbons", frames=100)

@@ -48,6 +48,29 @@ def test_history_ring_and_ribbons_f64_bit_exact(nb, oracle):
         assert np.array_equal(e.history(), oracle.history_init(out["pos_mass"][:100], 80))
 
 
+def test_ribbons_equal_reference_source_vectors(nb):
+    """The ribbon kernel against vertices produced by the page's OWN VisualSystem.update (idx:563-592, executed
+    by oracle/js_reference.py; tests/golden/make_reference_golden.py): the reference's histories are replayed
+    into the device ring oldest first, then one nbody_trail_ribbons call must reproduce the page's Float32Array."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_js_page_galaxy_ribbons.npz"))
+    hist, rad = g["history"], g["radius"]
+    n, depth, _ = hist.shape
+    pm = np.zeros((n, 4))
+    pm[:, 3] = 1.0
+    with nb.Engine(n, precision="f64") as e:
+        e.upload(np.concatenate([hist[:, depth - 1], pm[:, 3:]], axis=1), np.zeros((n, 4)))
+        e.set_radius(rad)
+        e.history_enable(depth)
+        for k in range(depth - 1, -1, -1):
+            pm[:, :3] = hist[:, k]
+            e.upload(pm, np.zeros((n, 4)))
+            e.set_radius(rad)
+            e.history_push()
+        assert np.array_equal(e.history(), hist)
+        assert np.array_equal(e.trail_ribbons(tuple(g["camera"])), g["ribbons"])
+
+
 def test_ribbons_f32_close(nb, oracle):
     s = nb.scenes.two_galaxies(4096)
     pm, vel, _ = s.astype(np.float32)

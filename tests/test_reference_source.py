@@ -72,7 +72,7 @@ def test_subset_loops_collections_and_arrows():
 
 @pytest.mark.parametrize("js", [
     "function f() { while (true) {} }", "function f(a) { a = b = 1; return a; }", "function f(n) { for (let i = 0; i < n; i += 2) {} }",
-    "function f(n) { for (let i = 0; i < n; i++) { n = 3; } }", "function f() { return x => { return 1; }; }", "function f(a) { return `t${a}`; }",
+    "function f(n) { for (let i = 0; i < n - 1; i++) { if (i) continue; } }", "function f() { return x => { return 1; }; }", "function f(xs) { let t = 0; xs.forEach(x => { t += x; }); return t; }", "function f(a) { return `t${a}`; }",
 ])
 def test_subset_rejects_what_it_does_not_cover(js):
     with pytest.raises(SyntaxError):
@@ -176,7 +176,45 @@ def test_live_committed_vectors_rederive(tmp_path, nb):
             assert np.array_equal(a[k], b[k]), (name, k)
 
 
+@live
+def test_live_visual_update_ribbons_bit_exact(oracle):
+    """VisualSystem.update (idx:500-597) executed from the page: the history unshift/pop and the ribbon vertex
+    loop equal oracle/visual_oracle.c bit for bit, every frame, through merges (bodies appearing and leaving)."""
+    r = jr.Reference(seed=5, collisions=True)
+    r.resetScenario("galaxy")
+    r.Math.state = 1234
+    vis = jr.ReferenceVisuals(r)
+    chains, sizes = {}, set()
+    for frame in range(60):
+        r.integrate(0.008, 2)
+        vis.update(0.016)
+        st, H = r.state(), vis.histories()
+        sizes.add(len(st["temp"]))
+        assert np.array_equal(vis.ribbons(), oracle.trail_ribbons(H, st["radius"], (0.0, 80.0, 150.0))), frame
+        for i, ident in enumerate(st["id"]):           # Body.history against history_init/history_push, per identity
+            pos = st["pos_mass"][i:i + 1]
+            chains[ident] = oracle.history_push(chains[ident] if ident in chains else oracle.history_init(pos, 80), pos)
+            assert np.array_equal(chains[ident][0], H[i]), (frame, i)
+    assert len(sizes) > 1                               # the body list did change
+
+
+def test_subset_block_arrows_and_computed_bounds():
+    js = """
+    function f(xs) {
+        const out = [];
+        xs.forEach(x => { const y = x * 2; if (y > 2) { out.push(y); } });
+        for (let i = 0; i < out.length - 1; i++) { out[i] = out[i] + out[i + 1]; }
+        return out;
+    }"""
+    assert list(_run(js, "f", jr.JSArray([1, 2, 3, 4]))) == [10, 14, 8]
+
+
 # ---------------------------------------------------------------- fixtures: run anywhere
+
+def test_oracle_equals_reference_vectors_ribbons(oracle):
+    g = np.load(os.path.join(GOLD, "ref_js_page_galaxy_ribbons.npz"))
+    rib = oracle.trail_ribbons(g["history"], g["radius"], g["camera"], trail_length=int(g["trail_length"]))
+    assert rib.dtype == np.float32 and np.array_equal(rib, g["ribbons"])
 
 @pytest.mark.parametrize("name", ["ref_js_galaxy151_gravity", "ref_js_plummer256_gravity"])
 def test_oracle_equals_reference_vectors_gravity(oracle, name):
