@@ -103,6 +103,14 @@ NBODY_API int nbody_download(nbody_ctx* ctx, void* pos_mass, void* vel, void* ac
  * a temp array was uploaded (idx:227-230, 260); see nbody_set_heat_decay. */
 NBODY_API int nbody_step(nbody_ctx* ctx, double dt, double G, double softening, int nsteps);
 
+/* One frame of the JS shim in one call (animate(), idx:877-881): upload the caller's arrays
+ * (as nbody_upload: a new body list), nsteps x integrate(dt), and write pos_mass, vel, acc (and temp, when not
+ * NULL) back in place for visuals.update -- the state ALSO stays on the device for nbody_contacts,
+ * nbody_history_push, nbody_render.  Same results as the three calls; for systems of up to 4,096 bodies on one
+ * device the arrays travel as one pinned record each way and the call synchronises once. */
+NBODY_API int nbody_step_host(nbody_ctx* ctx, size_t n, void* pos_mass, void* vel, void* acc, void* temp,
+                              double dt, double G, double softening, int nsteps);
+
 /* Split form, so a host can keep the reference's own collision stage between
  * force evaluation and kick-2 (idx:255-259). */
 NBODY_API int nbody_kick1_drift(nbody_ctx* ctx, double dt);             /* idx:248-253 */

@@ -21,7 +21,7 @@ NCCL_ID_BYTES = 128
 # every symbol include/nbody.h declares (tests check the library exports them all)
 SYMBOLS = (
     "nbody_create", "nbody_create_rank", "nbody_nccl_unique_id", "nbody_destroy",
-    "nbody_upload", "nbody_download", "nbody_step", "nbody_kick1_drift", "nbody_force",
+    "nbody_upload", "nbody_download", "nbody_step", "nbody_step_host", "nbody_kick1_drift", "nbody_force",
     "nbody_kick2", "nbody_set_heat_decay", "nbody_energy", "nbody_sync", "nbody_last_error",
     "nbody_strerror", "nbody_version", "nbody_device_count", "nbody_set_stream",
     "nbody_enable_timing", "nbody_read_timing", "nbody_get_info",
@@ -79,6 +79,7 @@ def lib() -> ctypes.CDLL:
     L.nbody_upload.argtypes = [vp, sz, vp, vp, vp, vp]
     L.nbody_download.argtypes = [vp, vp, vp, vp, vp]
     L.nbody_step.argtypes = [vp, d, d, d, i]
+    L.nbody_step_host.argtypes = [vp, sz, vp, vp, vp, vp, d, d, d, i]
     L.nbody_kick1_drift.argtypes = [vp, d]
     L.nbody_force.argtypes = [vp, d, d]
     L.nbody_kick2.argtypes = [vp, d, d]

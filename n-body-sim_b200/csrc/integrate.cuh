@@ -82,6 +82,51 @@ __global__ void pack_pos_kernel(const Real* aos, Real* pos_a, Real* pos_b, size_
     }
 }
 
+// Small systems (nbody_upload / nbody_download with at most kSmallIoMaxN bodies on one device): the host arrays travel as
+// ONE record [pos_mass 4n | vel 4n | acc 4n | temp n] through pinned memory, so a call is one copy + one kernel instead of
+// four copies, three memsets and a kernel -- the per-frame flow of the JS shim (upload, step, download every frame at the
+// reference's N <= 300, idx:57) is bound by exactly those driver calls.  pack_state_kernel = pack_pos_kernel + the local
+// arrays with their pads zeroed; unpack_state_kernel is its inverse.
+constexpr size_t kSmallIoMaxN = 4096;
+
+template <typename Real> __host__ __device__ constexpr size_t small_io_elems(size_t n) { return 13 * n; }
+
+template <typename Real>
+__global__ void pack_state_kernel(const Real* rec, Real* pos_a, Real* pos_b, Real* vel, Real* acc, Real* temp, size_t n, size_t n_pad,
+                                  Real pad_x, Real m0, unsigned* detect, MassOutlier* outliers)
+{
+    const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n_pad) return;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        const Real v = i < n ? rec[4 * i + c] : (c == 0 ? (sizeof(Real) == 8 ? pad_x * Real(1 + (i - n)) : pad_x) : Real(0));
+        pos_a[pm_index<Real>(i, c)] = v;
+        pos_b[pm_index<Real>(i, c)] = v;
+        if (c == 3 && detect != nullptr && i < n && !(v == m0)) {
+            const bool finite = v - v == Real(0);
+            const unsigned k = atomicAdd(detect, finite ? 1u : unsigned(kMaxOutliers) + 1u);
+            if (finite && k < unsigned(kMaxOutliers)) outliers[k] = MassOutlier{unsigned(i), float(v - m0)};
+        }
+        vel[4 * i + c] = i < n ? rec[4 * n + 4 * i + c] : Real(0);
+        acc[4 * i + c] = i < n ? rec[8 * n + 4 * i + c] : Real(0);
+    }
+    temp[i] = i < n ? rec[12 * n + i] : Real(0);
+}
+
+template <typename Real>
+__global__ void unpack_state_kernel(const Real* pos, const Real* vel, const Real* acc, const Real* temp, Real* rec, size_t n)
+{
+    const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        rec[4 * i + c] = pos[pm_index<Real>(i, c)];
+        rec[4 * n + 4 * i + c] = vel[4 * i + c];
+        rec[8 * n + 4 * i + c] = acc[4 * i + c];
+    }
+    rec[12 * n + i] = temp[i];
+}
+
 template <typename Real>
 __global__ void unpack_pos_kernel(const Real* pos, Real* aos, size_t n)
 {

@@ -23,6 +23,7 @@ constexpr int kUniUnroll = NB_UNIFORM_UNROLL;  // inner-loop unroll of the equal
 namespace {
 
 int check_exchange(nbody_ctx* c);  // defined with the exchange code below
+int resolve_mass_detection(nbody_ctx* c);  // defined with the upload code below
 
 // fp64 force kernel: two i-bodies per thread pay from ~32k bodies up (N=65,536: 961 -> 974 G interactions/s with
 // equal masses, 906 -> 948 without) and cost below (N=16,384: 304 -> 326 us/step): profiles/r1e_f64_r_uniform.jsonl
@@ -159,6 +160,12 @@ int alloc_shard(nbody_ctx* c, Shard& s)
     CU(c, cudaMalloc(&s.cand, local_cap * sizeof(unsigned)));
     CU(c, cudaMalloc(&s.cand_count, sizeof(unsigned)));
     CU(c, cudaMalloc(&s.pair_count, sizeof(unsigned long long)));
+    if (c->world == 1 && env_int("NBODY_SMALL_IO", 1) != 0) {  // one device: small systems travel as one record (integrate.cuh)
+        const size_t bytes = 13 * std::min(c->cap_pad, kSmallIoMaxN) * c->esz + 16;
+        CU(c, cudaMalloc(&s.io_dev, bytes));
+        CU(c, cudaMallocHost(&s.io_host, bytes));
+        CU(c, cudaEventCreateWithFlags(&s.io_done, cudaEventDisableTiming));
+    }
     return NBODY_OK;
 }
 
@@ -324,6 +331,9 @@ extern "C" void nbody_destroy(nbody_ctx* c)
         cudaFree(s.pos[0]);
         cudaFree(s.pos[1]);
         cudaFree(s.stage);
+        cudaFree(s.io_dev);
+        if (s.io_host) cudaFreeHost(s.io_host);
+        if (s.io_done) cudaEventDestroy(s.io_done);
         cudaFree(s.vel);
         cudaFree(s.acc);
         cudaFree(s.temp);
@@ -577,6 +587,10 @@ extern "C" int nbody_get_info(nbody_ctx* c, nbody_info* o)
 {
     if (!c || !o) return NBODY_EINVAL;
     memset(o, 0, sizeof *o);
+    if (c->detect_pending) {
+        const int rcd = resolve_mass_detection(c);
+        if (rcd != NBODY_OK) return rcd;
+    }
     o->n = c->n;
     o->n_padded = c->n_pad;
     o->i_begin = std::min(c->shards[0].i_begin, c->n);
@@ -604,12 +618,36 @@ namespace {
 template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, const Real* vel, const Real* acc, const Real* temp)
 {
     const size_t v4 = 4 * sizeof(Real);
+    bool small_io = false;
     for (Shard& s : c->shards) {
         CU(c, cudaSetDevice(s.device));
         s.n_local = c->n_pad / c->world;
         s.i_begin = size_t(s.rank) * s.n_local;
         const size_t lo = std::min(s.i_begin, n), hi = std::min(s.i_begin + s.n_local, n);
         s.n_local_real = hi - lo;
+        if (s.io_host && n <= kSmallIoMaxN) {
+            // small system on one device: one pinned record, one copy, one kernel (pack_state_kernel), one synchronise
+            Real* rec = static_cast<Real*>(s.io_host);
+            unsigned* count_host = reinterpret_cast<unsigned*>(static_cast<char*>(s.io_host) + 13 * std::min(c->cap_pad, kSmallIoMaxN) * sizeof(Real));
+            CU(c, cudaEventSynchronize(s.io_done));  // the previous upload's copy out of the record (long done, as a rule)
+            memcpy(rec, pm, n * v4);
+            memcpy(rec + 4 * n, vel, n * v4);
+            if (acc) memcpy(rec + 8 * n, acc, n * v4); else memset(rec + 8 * n, 0, n * v4);
+            if (temp) memcpy(rec + 12 * n, temp, n * sizeof(Real)); else memset(rec + 12 * n, 0, n * sizeof(Real));
+            CU(c, cudaMemcpyAsync(s.io_dev, rec, 13 * n * sizeof(Real), cudaMemcpyHostToDevice, s.stream));
+            CU(c, cudaEventRecord(s.io_done, s.stream));
+            if (c->detect_masses) CU(c, cudaMemsetAsync(s.outlier_count, 0, sizeof(unsigned), s.stream));
+            pack_state_kernel<Real><<<unsigned((c->n_pad + 255) / 256), 256, 0, s.stream>>>(
+                static_cast<const Real*>(s.io_dev), static_cast<Real*>(s.pos[0]), static_cast<Real*>(s.pos[1]), static_cast<Real*>(s.vel),
+                static_cast<Real*>(s.acc), static_cast<Real*>(s.temp), n, c->n_pad, Real(sizeof(Real) == 8 ? 1e150 : 1e18), Real(c->uniform_mass),
+                c->detect_masses ? s.outlier_count : nullptr, s.outliers);
+            c->launches++;
+            CU(c, cudaGetLastError());
+            if (c->detect_masses) CU(c, cudaMemcpyAsync(count_host, s.outlier_count, sizeof(unsigned), cudaMemcpyDeviceToHost, s.stream));
+            c->detect_count_host = c->detect_masses ? count_host : nullptr;
+            small_io = true;
+        } else {
+        c->detect_count_host = nullptr;
         // positions + masses: host AoS -> staging -> device layout (both buffers)
         CU(c, cudaMemcpyAsync(s.stage, pm, n * v4, cudaMemcpyHostToDevice, s.stream));
         const unsigned blocks = unsigned((c->n_pad + 255) / 256);
@@ -628,6 +666,7 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
             if (acc) CU(c, cudaMemcpyAsync(s.acc, acc + 4 * lo, s.n_local_real * v4, cudaMemcpyHostToDevice, s.stream));
             if (temp) CU(c, cudaMemcpyAsync(s.temp, temp + lo, s.n_local_real * sizeof(Real), cudaMemcpyHostToDevice, s.stream));
         }
+        }
         // per-chunk partial sums
         const size_t need = c->j_chunks > 1 ? size_t(c->j_chunks) * s.n_local * v4 : 0;
         if (need > s.partial_bytes) {
@@ -639,7 +678,8 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
             s.partial_bytes = need;
         }
     }
-    // host buffers are borrowed for the duration of the call only
+    // host buffers are borrowed for the duration of the call only (the small-system path has copied them already)
+    if (small_io) return NBODY_OK;
     for (Shard& s : c->shards) {
         CU(c, cudaSetDevice(s.device));
         CU(c, cudaStreamSynchronize(s.stream));
@@ -650,6 +690,25 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
 template <typename Real> int download_t(nbody_ctx* c, Real* pm, Real* vel, Real* acc, Real* temp)
 {
     const size_t v4 = 4 * sizeof(Real);
+    if (c->shards[0].io_host && c->n <= kSmallIoMaxN) {
+        // small system on one device: one kernel gathers the state into a record, one copy, one synchronise (integrate.cuh)
+        Shard& s = c->shards[0];
+        const size_t n = c->n;
+        CU(c, cudaSetDevice(s.device));
+        unpack_state_kernel<Real><<<unsigned((n + 255) / 256), 256, 0, s.stream>>>(static_cast<const Real*>(s.pos[c->cur]), static_cast<const Real*>(s.vel),
+                                                                               static_cast<const Real*>(s.acc), static_cast<const Real*>(s.temp),
+                                                                               static_cast<Real*>(s.io_dev), n);
+        c->launches++;
+        CU(c, cudaGetLastError());
+        const Real* rec = static_cast<const Real*>(s.io_host);
+        CU(c, cudaMemcpyAsync(s.io_host, s.io_dev, 13 * n * sizeof(Real), cudaMemcpyDeviceToHost, s.stream));
+        CU(c, cudaStreamSynchronize(s.stream));
+        if (pm) memcpy(pm, rec, n * v4);
+        if (vel) memcpy(vel, rec + 4 * n, n * v4);
+        if (acc) memcpy(acc, rec + 8 * n, n * v4);
+        if (temp) memcpy(temp, rec + 12 * n, n * sizeof(Real));
+        return check_exchange(c);
+    }
     if (pm && c->n) {
         Shard& s = c->shards[0];  // every shard holds the complete position array
         CU(c, cudaSetDevice(s.device));
@@ -707,7 +766,8 @@ int finish_mass_detection(nbody_ctx* c)
     Shard& s0 = c->shards[0];
     CU(c, cudaSetDevice(s0.device));
     unsigned count = 0;
-    CU(c, cudaMemcpy(&count, s0.outlier_count, sizeof(unsigned), cudaMemcpyDeviceToHost));
+    if (c->detect_count_host) count = *c->detect_count_host;  // the small-system upload brought it back with its own synchronise
+    else CU(c, cudaMemcpy(&count, s0.outlier_count, sizeof(unsigned), cudaMemcpyDeviceToHost));
     // (exceptions are corrected in the fp32 epilogue only: an fp64 context takes the sweep for exactly equal masses)
     const size_t max_out = c->prec == NBODY_F64 ? 0 : std::min<size_t>(size_t(std::max(0, env_int("NBODY_OUTLIERS", kMaxOutliers))), kMaxOutliers);
     if (count > max_out) return NBODY_OK;  // too many different masses: the general kernel
@@ -721,6 +781,17 @@ int finish_mass_detection(nbody_ctx* c)
         CU(c, cudaMemcpy(s.outliers, c->outliers.data(), count * sizeof(MassOutlier), cudaMemcpyHostToDevice));
     }
     return NBODY_OK;
+}
+
+// The small-system upload leaves the mass-detection count in flight; whoever needs `uniform` first waits for it.
+int resolve_mass_detection(nbody_ctx* c)
+{
+    if (!c->detect_pending) return NBODY_OK;
+    c->detect_pending = false;
+    Shard& s0 = c->shards[0];
+    CU(c, cudaSetDevice(s0.device));
+    CU(c, cudaStreamSynchronize(s0.stream));
+    return finish_mass_detection(c);
 }
 
 }  // namespace
@@ -750,6 +821,7 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     c->uniform = false;
     c->outliers.clear();
     c->detect_masses = false;
+    c->detect_pending = false;
     const bool f32_sweep = c->prec == NBODY_F32 && c->R == 4, f64_sweep = c->prec == NBODY_F64 && c->f64_math == 2;
     if ((f32_sweep || f64_sweep) && env_int("NBODY_UNIFORM", 1) != 0) {
         // Equal-mass sweep (force_f32.cuh / force_f64.cuh, UNIFORM): the mass most bodies share, if there is one,
@@ -777,7 +849,8 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     int rc = c->prec == NBODY_F32
                  ? upload_t<float>(c, n, (const float*)pos_mass, (const float*)vel, (const float*)acc, (const float*)temp)
                  : upload_t<double>(c, n, (const double*)pos_mass, (const double*)vel, (const double*)acc, (const double*)temp);
-    if (rc == NBODY_OK && c->detect_masses) rc = finish_mass_detection(c);
+    c->detect_pending = rc == NBODY_OK && c->detect_masses && c->detect_count_host != nullptr;
+    if (rc == NBODY_OK && c->detect_masses && !c->detect_pending) rc = finish_mass_detection(c);
     c->detect_masses = false;
     if (rc == NBODY_OK && c->f64_sym_k > 0) rc = ensure_sym_buffers(c);
     return rc;
@@ -898,6 +971,10 @@ template <typename Real> ForceParams<Real> make_params(nbody_ctx* c, Shard& s, i
 
 int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
 {
+    if (c->detect_pending) {
+        const int rcd = resolve_mass_detection(c);
+        if (rcd != NBODY_OK) return rcd;
+    }
     // With radii set, the fp32 sweep also tracks each body's nearest neighbour for the
     // collision broad phase (contacts.cuh).  The result describes the positions the
     // sweep READ, so it stays valid only when the epilogue does not drift them.
@@ -1090,6 +1167,19 @@ extern "C" int nbody_step(nbody_ctx* c, double dt, double G, double softening, i
         }
     }
     return NBODY_OK;
+}
+
+extern "C" int nbody_step_host(nbody_ctx* c, size_t n, void* pos_mass, void* vel, void* acc, void* temp, double dt, double G, double softening,
+                               int nsteps)
+{
+    // The JS shim's frame: typed arrays in, nsteps x integrate(dt), typed arrays out.  For a small
+    // system on one device this is one copy in, pack, the step kernel(s), unpack, one copy out and ONE synchronise.
+    if (!c) return NBODY_EINVAL;
+    if (!pos_mass || !vel || !acc) return fail(c, NBODY_EINVAL, "step_host: pos_mass, vel and acc are required (in and out)");
+    int rc = nbody_upload(c, n, pos_mass, vel, acc, temp);
+    if (rc == NBODY_OK) rc = nbody_step(c, dt, G, softening, nsteps);
+    if (rc == NBODY_OK) rc = nbody_download(c, pos_mass, vel, acc, temp);
+    return rc;
 }
 
 extern "C" int nbody_kick1_drift(nbody_ctx* c, double dt)

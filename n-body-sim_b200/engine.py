@@ -113,6 +113,19 @@ class Engine:
     def step(self, dt: float, G: float, softening: float, nsteps: int = 1) -> None:
         check(self._L.nbody_step(self._ctx, dt, G, softening, nsteps), self._ctx)
 
+    def step_host(self, pos_mass, vel, acc, temp, dt: float, G: float, softening: float, nsteps: int = 1) -> None:
+        """One frame of the JS shim in one call (nbody_step_host): the arrays (contiguous, the engine's dtype;
+        `temp` may be None) are uploaded as a new body list, advanced by nsteps x integrate(dt) and overwritten
+        IN PLACE with the new state; the state also stays on the device."""
+        n = pos_mass.shape[0]
+        for name, a, shape in (("pos_mass", pos_mass, (n, 4)), ("vel", vel, (n, 4)), ("acc", acc, (n, 4)), ("temp", temp, (n,))):
+            if a is None and name == "temp":
+                continue
+            if not isinstance(a, np.ndarray) or a.dtype != self.dtype or not a.flags.c_contiguous or a.shape != shape or not a.flags.writeable:
+                raise ValueError(f"{name} must be a writable contiguous {np.dtype(self.dtype).name} array of shape {shape}")
+        check(self._L.nbody_step_host(self._ctx, n, _ptr(pos_mass), _ptr(vel), _ptr(acc), _ptr(temp), dt, G, softening, nsteps), self._ctx)
+        self.n = n
+
     def kick1_drift(self, dt: float) -> None:
         check(self._L.nbody_kick1_drift(self._ctx, dt), self._ctx)
 
