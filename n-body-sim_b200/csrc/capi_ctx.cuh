@@ -41,8 +41,8 @@ struct Shard {
     size_t sym_bytes_i = 0, sym_bytes_j = 0;
     void* stage = nullptr;              // AoS staging for upload/download (4*cap_pad elements)
     void* io_dev = nullptr;             // small systems on one device: the whole state as one record, [pos_mass 4n | vel 4n | acc 4n | temp n]
-    void* io_host = nullptr;            // ... its pinned host twin (+ one word for the mass-detection count): one copy each way per call
-    cudaEvent_t io_done = nullptr;      // the last host-to-device copy out of io_host (an upload may return before it has run)
+    void* io_host = nullptr;            // ... its pinned, device-mapped host twin: one copy each way per call, none at all for the smallest systems
+    cudaEvent_t io_done = nullptr;      // the last device-side read of io_host (an upload returns before it has run)
     double* energy_out = nullptr;
     size_t energy_rows = 0;
     // collision broad phase (contacts.cuh)
@@ -116,8 +116,8 @@ struct nbody_ctx {
     size_t small_max_n = 512;       // largest system the one-cluster kernel takes (NBODY_SMALL_MAX at create, <= kSmallMaxN)
     bool small_path = true;         // NBODY_SMALL at create: one-cluster multi-step kernel for n <= kSmallMaxN (small.cuh)
     bool detect_masses = false;     // upload in flight: pack_pos_kernel compares every mass with uniform_mass
-    const unsigned* detect_count_host = nullptr;  // small-system upload: where the count lands (pinned), else null
-    bool detect_pending = false;    // small-system upload returned without waiting for that count: resolve_mass_detection() reads it
+    bool upload_deferred = false;   // the last upload took the small-system path and returned without a synchronise
+    bool detect_pending = false;    // ... so nobody has read the detection count yet: resolve_mass_detection() does
                                     // before the first consumer of `uniform` (a force launch of the large kernels, nbody_get_info)
     std::vector<MassOutlier> outliers;  // ... except these few (at most kMaxOutliers), corrected per i-body
     bool has_radius = false;        // nbody_set_radius was called for the current body list

@@ -88,6 +88,7 @@ __global__ void pack_pos_kernel(const Real* aos, Real* pos_a, Real* pos_b, size_
 // reference's N <= 300, idx:57) is bound by exactly those driver calls.  pack_state_kernel = pack_pos_kernel + the local
 // arrays with their pads zeroed; unpack_state_kernel is its inverse.
 constexpr size_t kSmallIoMaxN = 4096;
+constexpr size_t kSmallIoZeroCopyMaxN = 1024;  // up to here the two kernels read / write the pinned record in place (<= 104 KiB over PCIe)
 
 template <typename Real> __host__ __device__ constexpr size_t small_io_elems(size_t n) { return 13 * n; }
 

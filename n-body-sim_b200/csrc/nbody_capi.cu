@@ -163,7 +163,7 @@ int alloc_shard(nbody_ctx* c, Shard& s)
     if (c->world == 1 && env_int("NBODY_SMALL_IO", 1) != 0) {  // one device: small systems travel as one record (integrate.cuh)
         const size_t bytes = 13 * std::min(c->cap_pad, kSmallIoMaxN) * c->esz + 16;
         CU(c, cudaMalloc(&s.io_dev, bytes));
-        CU(c, cudaMallocHost(&s.io_host, bytes));
+        CU(c, cudaHostAlloc(&s.io_host, bytes, cudaHostAllocMapped | cudaHostAllocPortable));
         CU(c, cudaEventCreateWithFlags(&s.io_done, cudaEventDisableTiming));
     }
     return NBODY_OK;
@@ -626,28 +626,27 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
         const size_t lo = std::min(s.i_begin, n), hi = std::min(s.i_begin + s.n_local, n);
         s.n_local_real = hi - lo;
         if (s.io_host && n <= kSmallIoMaxN) {
-            // small system on one device: one pinned record, one copy, one kernel (pack_state_kernel), one synchronise
+            // small system on one device: one pinned record and one kernel (pack_state_kernel), no synchronise.  Up to
+            // kSmallIoZeroCopyMaxN bodies the kernel reads the record where it lies (mapped pinned memory, a few us over
+            // PCIe) and no copy operation enters the stream at all; above, one copy brings it to the device first.
             Real* rec = static_cast<Real*>(s.io_host);
-            unsigned* count_host = reinterpret_cast<unsigned*>(static_cast<char*>(s.io_host) + 13 * std::min(c->cap_pad, kSmallIoMaxN) * sizeof(Real));
-            CU(c, cudaEventSynchronize(s.io_done));  // the previous upload's copy out of the record (long done, as a rule)
+            const bool zero_copy = n <= kSmallIoZeroCopyMaxN;
+            CU(c, cudaEventSynchronize(s.io_done));  // the previous upload's last read of the record (long done, as a rule)
             memcpy(rec, pm, n * v4);
             memcpy(rec + 4 * n, vel, n * v4);
             if (acc) memcpy(rec + 8 * n, acc, n * v4); else memset(rec + 8 * n, 0, n * v4);
             if (temp) memcpy(rec + 12 * n, temp, n * sizeof(Real)); else memset(rec + 12 * n, 0, n * sizeof(Real));
-            CU(c, cudaMemcpyAsync(s.io_dev, rec, 13 * n * sizeof(Real), cudaMemcpyHostToDevice, s.stream));
-            CU(c, cudaEventRecord(s.io_done, s.stream));
+            if (!zero_copy) CU(c, cudaMemcpyAsync(s.io_dev, rec, 13 * n * sizeof(Real), cudaMemcpyHostToDevice, s.stream));
             if (c->detect_masses) CU(c, cudaMemsetAsync(s.outlier_count, 0, sizeof(unsigned), s.stream));
             pack_state_kernel<Real><<<unsigned((c->n_pad + 255) / 256), 256, 0, s.stream>>>(
-                static_cast<const Real*>(s.io_dev), static_cast<Real*>(s.pos[0]), static_cast<Real*>(s.pos[1]), static_cast<Real*>(s.vel),
+                zero_copy ? rec : static_cast<const Real*>(s.io_dev), static_cast<Real*>(s.pos[0]), static_cast<Real*>(s.pos[1]), static_cast<Real*>(s.vel),
                 static_cast<Real*>(s.acc), static_cast<Real*>(s.temp), n, c->n_pad, Real(sizeof(Real) == 8 ? 1e150 : 1e18), Real(c->uniform_mass),
                 c->detect_masses ? s.outlier_count : nullptr, s.outliers);
             c->launches++;
             CU(c, cudaGetLastError());
-            if (c->detect_masses) CU(c, cudaMemcpyAsync(count_host, s.outlier_count, sizeof(unsigned), cudaMemcpyDeviceToHost, s.stream));
-            c->detect_count_host = c->detect_masses ? count_host : nullptr;
+            CU(c, cudaEventRecord(s.io_done, s.stream));
             small_io = true;
         } else {
-        c->detect_count_host = nullptr;
         // positions + masses: host AoS -> staging -> device layout (both buffers)
         CU(c, cudaMemcpyAsync(s.stage, pm, n * v4, cudaMemcpyHostToDevice, s.stream));
         const unsigned blocks = unsigned((c->n_pad + 255) / 256);
@@ -679,6 +678,7 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
         }
     }
     // host buffers are borrowed for the duration of the call only (the small-system path has copied them already)
+    c->upload_deferred = small_io;
     if (small_io) return NBODY_OK;
     for (Shard& s : c->shards) {
         CU(c, cudaSetDevice(s.device));
@@ -694,14 +694,15 @@ template <typename Real> int download_t(nbody_ctx* c, Real* pm, Real* vel, Real*
         // small system on one device: one kernel gathers the state into a record, one copy, one synchronise (integrate.cuh)
         Shard& s = c->shards[0];
         const size_t n = c->n;
+        const bool zero_copy = n <= kSmallIoZeroCopyMaxN;  // the kernel stores straight into the pinned record
         CU(c, cudaSetDevice(s.device));
         unpack_state_kernel<Real><<<unsigned((n + 255) / 256), 256, 0, s.stream>>>(static_cast<const Real*>(s.pos[c->cur]), static_cast<const Real*>(s.vel),
                                                                                static_cast<const Real*>(s.acc), static_cast<const Real*>(s.temp),
-                                                                               static_cast<Real*>(s.io_dev), n);
+                                                                               static_cast<Real*>(zero_copy ? s.io_host : s.io_dev), n);
         c->launches++;
         CU(c, cudaGetLastError());
         const Real* rec = static_cast<const Real*>(s.io_host);
-        CU(c, cudaMemcpyAsync(s.io_host, s.io_dev, 13 * n * sizeof(Real), cudaMemcpyDeviceToHost, s.stream));
+        if (!zero_copy) CU(c, cudaMemcpyAsync(s.io_host, s.io_dev, 13 * n * sizeof(Real), cudaMemcpyDeviceToHost, s.stream));
         CU(c, cudaStreamSynchronize(s.stream));
         if (pm) memcpy(pm, rec, n * v4);
         if (vel) memcpy(vel, rec + 4 * n, n * v4);
@@ -766,8 +767,7 @@ int finish_mass_detection(nbody_ctx* c)
     Shard& s0 = c->shards[0];
     CU(c, cudaSetDevice(s0.device));
     unsigned count = 0;
-    if (c->detect_count_host) count = *c->detect_count_host;  // the small-system upload brought it back with its own synchronise
-    else CU(c, cudaMemcpy(&count, s0.outlier_count, sizeof(unsigned), cudaMemcpyDeviceToHost));
+    CU(c, cudaMemcpy(&count, s0.outlier_count, sizeof(unsigned), cudaMemcpyDeviceToHost));
     // (exceptions are corrected in the fp32 epilogue only: an fp64 context takes the sweep for exactly equal masses)
     const size_t max_out = c->prec == NBODY_F64 ? 0 : std::min<size_t>(size_t(std::max(0, env_int("NBODY_OUTLIERS", kMaxOutliers))), kMaxOutliers);
     if (count > max_out) return NBODY_OK;  // too many different masses: the general kernel
@@ -849,7 +849,7 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     int rc = c->prec == NBODY_F32
                  ? upload_t<float>(c, n, (const float*)pos_mass, (const float*)vel, (const float*)acc, (const float*)temp)
                  : upload_t<double>(c, n, (const double*)pos_mass, (const double*)vel, (const double*)acc, (const double*)temp);
-    c->detect_pending = rc == NBODY_OK && c->detect_masses && c->detect_count_host != nullptr;
+    c->detect_pending = rc == NBODY_OK && c->detect_masses && c->upload_deferred;
     if (rc == NBODY_OK && c->detect_masses && !c->detect_pending) rc = finish_mass_detection(c);
     c->detect_masses = false;
     if (rc == NBODY_OK && c->f64_sym_k > 0) rc = ensure_sym_buffers(c);
