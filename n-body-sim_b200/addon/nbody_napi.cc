@@ -56,8 +56,8 @@ napi_value fail(napi_env env, const char* what, int status, const nbody_ctx* ctx
 }
 
 struct Args {
-    size_t argc = 8;
-    napi_value v[8] = {};
+    size_t argc = 12;
+    napi_value v[12] = {};
 };
 
 bool get_args(napi_env env, napi_callback_info info, Args& a, size_t need, const char* what)
@@ -214,6 +214,34 @@ napi_value Step(napi_env env, napi_callback_info info)
     }
     const int rc = nbody_step(h->ctx, dt, G, eps, nsteps);
     return rc == NBODY_OK ? undefined(env) : fail(env, "step", rc, h->ctx);
+}
+
+// stepHost(ctx, posMass, vel, acc, temp|null, dt, G, softening, nsteps): one frame of the shim in one call -- the
+// typed arrays are uploaded as the body list, advanced by nsteps x integrate(dt) and overwritten in place (nbody_step_host)
+napi_value StepHost(napi_env env, napi_callback_info info)
+{
+    Args a;
+    if (!get_args(env, info, a, 9, "stepHost")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "stepHost");
+    if (!h) return undefined(env);
+    void* p[4] = {};
+    size_t len[4] = {};
+    for (int k = 0; k < 4; ++k)
+        if (!get_array(env, a.v[k + 1], h->prec, &p[k], &len[k], "stepHost")) return undefined(env);
+    const size_t n = len[0] / 4;
+    if (!p[0] || !p[1] || !p[2] || len[0] % 4 || len[1] != len[0] || len[2] != len[0] || (p[3] && len[3] != n)) {
+        napi_throw_error(env, "NBODY", "nbody.stepHost: posMass[4n], vel[4n], acc[4n], temp[n]|null");
+        return undefined(env);
+    }
+    double dt, G, eps;
+    int32_t nsteps = 1;
+    if (!get_double(env, a.v[5], &dt) || !get_double(env, a.v[6], &G) || !get_double(env, a.v[7], &eps) ||
+        napi_get_value_int32(env, a.v[8], &nsteps) != napi_ok) {
+        napi_throw_error(env, "NBODY", "nbody.stepHost(ctx, posMass, vel, acc, temp, dt, G, softening, nsteps): numbers expected");
+        return undefined(env);
+    }
+    const int rc = nbody_step_host(h->ctx, n, p[0], p[1], p[2], p[3], dt, G, eps, nsteps);
+    return rc == NBODY_OK ? undefined(env) : fail(env, "stepHost", rc, h->ctx);
 }
 
 napi_value Kick1Drift(napi_env env, napi_callback_info info)  // idx:248-253
@@ -552,7 +580,7 @@ extern "C" __attribute__((visibility("default"))) napi_value napi_register_modul
 {
     const struct { const char* name; napi_callback cb; } fns[] = {
         {"create", Create}, {"destroy", Destroy}, {"upload", Upload}, {"download", Download},
-        {"step", Step}, {"kick1Drift", Kick1Drift}, {"force", Force}, {"kick2", Kick2},
+        {"step", Step}, {"stepHost", StepHost}, {"kick1Drift", Kick1Drift}, {"force", Force}, {"kick2", Kick2},
         {"setHeatDecay", SetHeatDecay}, {"energy", Energy}, {"sync", Sync}, {"info", Info},
         {"version", Version}, {"deviceCount", DeviceCount},
         {"setRadius", SetRadius}, {"contacts", Contacts}, {"historyEnable", HistoryEnable}, {"historyPush", HistoryPush},

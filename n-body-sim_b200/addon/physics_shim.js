@@ -42,7 +42,7 @@ function installGpuIntegrate(physics, CONFIG, addon, opts = {}) {
     pm = new Arr(4 * capacity); vel = new Arr(4 * capacity); acc = new Arr(4 * capacity); temp = new Arr(capacity);
   }
 
-  function pack(bodies) {
+  function pack(bodies, upload = true) {
     const n = bodies.length;
     for (let i = 0; i < n; i++) {
       const b = bodies[i], o = 4 * i;
@@ -51,12 +51,12 @@ function installGpuIntegrate(physics, CONFIG, addon, opts = {}) {
       acc[o] = b.acc.x; acc[o + 1] = b.acc.y; acc[o + 2] = b.acc.z;
       temp[i] = b.temperature;
     }
-    addon.upload(ctx, pm.subarray(0, 4 * n), vel.subarray(0, 4 * n), acc.subarray(0, 4 * n), temp.subarray(0, n));
+    if (upload) addon.upload(ctx, pm.subarray(0, 4 * n), vel.subarray(0, 4 * n), acc.subarray(0, 4 * n), temp.subarray(0, n));
   }
 
-  function unpack(bodies, what) {
+  function unpack(bodies, what, download = true) {
     const n = bodies.length;
-    addon.download(ctx, what.pos ? pm.subarray(0, 4 * n) : null, what.vel ? vel.subarray(0, 4 * n) : null,
+    if (download) addon.download(ctx, what.pos ? pm.subarray(0, 4 * n) : null, what.vel ? vel.subarray(0, 4 * n) : null,
                    what.acc ? acc.subarray(0, 4 * n) : null, what.temp ? temp.subarray(0, n) : null);
     for (let i = 0; i < n; i++) {
       const b = bodies[i], o = 4 * i;
@@ -74,12 +74,16 @@ function installGpuIntegrate(physics, CONFIG, addon, opts = {}) {
     if (bodies.length === 0) return;
     ensure(bodies.length);
     addon.setHeatDecay(ctx, CONFIG.heatDecay);           // idx:67, read at call time like G and softening
-    pack(bodies);
     if (opts.collisions === false) {
-      addon.step(ctx, dt, CONFIG.G, CONFIG.softening, 1);  // idx:250-261 minus idx:256
-      unpack(bodies, ALL);
+      // the whole frame in one addon call: arrays in, integrate(dt), arrays out in place (nbody_step_host)
+      const n = bodies.length;
+      pack(bodies, false);
+      addon.stepHost(ctx, pm.subarray(0, 4 * n), vel.subarray(0, 4 * n), acc.subarray(0, 4 * n), temp.subarray(0, n),
+                     dt, CONFIG.G, CONFIG.softening, 1);   // idx:250-261 minus idx:256
+      unpack(bodies, ALL, false);
       return;
     }
+    pack(bodies);
     addon.kick1Drift(ctx, dt);                           // idx:250-253
     if (opts.collisions === 'gpu-broad-phase') {
       const n = bodies.length;

@@ -221,6 +221,7 @@ static napi_value call(const char* name, std::vector<napi_value> args, bool expe
 
 static std::string g_out_path;  // collide mode writes <out>.pairs, <out>.ribbons and <out>.nbs next to the state
 static bool g_collide = false;
+static bool g_host = false;     // "host" mode: the frame as ONE addon call (stepHost), arrays in and out in place
 
 template <typename T> static void run(bool f64, const char* prec, const std::vector<double>& in, size_t n, double dt, double G,
                                       double eps, int nsteps, bool split, std::vector<double>& out)
@@ -315,6 +316,16 @@ template <typename T> static void run(bool f64, const char* prec, const std::vec
             fwrite(&d, 8, 1, fp);
         }
         fclose(fp);
+    } else if (g_host) {
+        // the arrays uploaded above are handed over again and come back advanced; a bad array must throw, not crash
+        call("stepHost", {ctx, typed(f64, pm.data(), 4 * n), typed(f64, vel.data(), 4 * n - 4), typed(f64, acc.data(), 4 * n),
+                          typed(f64, temp.data(), n), num(dt), num(G), num(eps), num(nsteps)}, true);
+        call("stepHost", {ctx, typed(f64, pm.data(), 4 * n), typed(f64, vel.data(), 4 * n), typed(f64, acc.data(), 4 * n),
+                          typed(f64, temp.data(), n), num(dt), num(G), num(eps), num(nsteps)});
+        std::vector<T> pm2 = pm, vel2 = vel, acc2 = acc, temp2 = temp;  // what stepHost wrote must equal what download reads
+        call("download", {ctx, typed(f64, pm2.data(), 4 * n), typed(f64, vel2.data(), 4 * n), typed(f64, acc2.data(), 4 * n),
+                          typed(f64, temp2.data(), n)});
+        if (pm2 != pm || vel2 != vel || acc2 != acc || temp2 != temp) exit(7);
     } else if (!split) {
         call("step", {ctx, num(dt), num(G), num(eps), num(nsteps)});
     } else {
@@ -379,6 +390,7 @@ int main(int argc, char** argv)
     const int nsteps = atoi(argv[4]);
     const bool split = strcmp(argv[5], "split") == 0;
     g_collide = strcmp(argv[5], "collide") == 0;
+    g_host = strcmp(argv[5], "host") == 0;
     g_out_path = argv[3];
     const bool f64 = strcmp(argv[6], "f64") == 0;
     std::vector<double> out;

@@ -38,7 +38,7 @@ def test_addon_exports_and_imports():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("mode", ["step", "split"])
+@pytest.mark.parametrize("mode", ["step", "split", "host"])
 @pytest.mark.parametrize("prec,tol", [("f64", 1e-12), ("f32", 2e-5)])
 def test_addon_matches_oracle(nb, oracle, tmp_path, mode, prec, tol):
     s = nb.scenes.galaxy_default()                    # the reference's own default scene
