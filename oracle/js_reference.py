@@ -294,13 +294,7 @@ class Parser:
     def _arrow_body(self, ps):
         if not self.at("{"):
             return ("arrow", ps, self.assign())
-        body = self.block()
-        outer = _assigned_names(body) - _declared_names(body) - set(ps)
-        if outer:   # Python closures cannot rebind an enclosing local without `nonlocal`
-            raise SyntaxError(f"js subset: arrow function assigns to enclosing variable(s) {sorted(outer)}")
-        if _has(body, "return"):
-            raise SyntaxError("js subset: `return` inside a block-bodied arrow function is not supported")
-        return ("arrowblock", ps, body)
+        return ("arrowblock", ps, self.block())
 
     def primary(self):
         k, v = self.peek()
@@ -318,7 +312,10 @@ class Parser:
                     callee = ("member", callee, self.eat(kind="id"))
                 return ("new", callee, self.args())
             if v == "function":
-                raise SyntaxError("js subset: function expressions are not supported")
+                self.i += 1
+                name = self.eat(kind="id") if self.peek()[0] == "id" else None
+                params = self.params()
+                return ("funcexpr", name, params, self.block())
             self.i += 1
             if self.at("=>"):
                 self.i += 1
@@ -349,8 +346,18 @@ class Parser:
                 if kk not in ("id", "str"):
                     raise SyntaxError(f"js subset: bad property key {key!r}")
                 self.i += 1
-                self.eat(":")
-                props.append((key[1:-1] if kk == "str" else key, self.assign()))
+                if kk == "id" and key == "get" and self.peek()[0] == "id":      # { get name() { ... } }
+                    gname = self.eat(kind="id")
+                    params = self.params()
+                    props.append((gname, ("getter", ("funcexpr", gname, params, self.block()))))
+                elif kk == "id" and self.at("("):                              # { name(params) { ... } }
+                    params = self.params()
+                    props.append((key, ("funcexpr", key, params, self.block())))
+                elif kk == "id" and (self.at(",") or self.at("}")):                # { name }  =  { name: name }
+                    props.append((key, ("id", key)))
+                else:
+                    self.eat(":")
+                    props.append((key[1:-1] if kk == "str" else key, self.assign()))
                 if not self.at("}"):
                     self.eat(",")
             return ("object", props)
@@ -380,6 +387,43 @@ def _walk(node):
     elif isinstance(node, list):
         for c in node:
             yield from _walk(c)
+
+
+_FUNCTION_NODES = ("func", "funcexpr", "arrowblock", "arrow")
+
+
+def _walk_shallow(node, top=True):
+    """Like _walk, but does not enter nested functions (their names are their own)."""
+    if isinstance(node, tuple):
+        if not top and node and node[0] in _FUNCTION_NODES:
+            if node[0] == "func":
+                yield ("decl", [(node[1], None)])      # a nested function declaration binds its name here
+            return
+        yield node
+        for c in node[1:]:
+            yield from _walk_shallow(c, False)
+    elif isinstance(node, list):
+        for c in node:
+            yield from _walk_shallow(c, False)
+
+
+def _scope_names(params, body):
+    """(declared, assigned) plain identifiers of one function body, nested functions excluded."""
+    declared, assigned = {p if isinstance(p, str) else p[0] for p in params}, set()
+    for n in _walk_shallow(body, False):
+        if not n:
+            continue
+        if n[0] == "decl":
+            declared |= {name for name, _ in n[1]}
+        elif n[0] in ("forrange", "forwhile", "forof"):
+            declared.add(n[1])
+        elif n[0] in ("assign", "update") and isinstance(n[2], tuple) and n[2][0] == "id":
+            assigned.add(n[2][1])
+    return declared, assigned
+
+
+def _uses_this(body) -> bool:
+    return any(n == ("id", "this") for n in _walk_shallow(body, False))
 
 
 def _has(node, kind) -> bool:
@@ -426,15 +470,36 @@ def _name(n: str) -> str:
     return n + "_" if keyword.iskeyword(n) else n
 
 
-_HOIST = []      # block-bodied arrow functions met while emitting a statement's expressions: (name, params, block)
+_HOIST = []      # function-valued expressions met while emitting a statement's expressions: (name, params, block, takes_self)
 _COUNTER = [0]
+_SCOPES = []     # declared names of the enclosing functions, innermost last
+_THIS_FN_OK = [False]
+
+
+def _emit_function(name, params, block, ind, out, takes_self=False):
+    """def name(params): body -- with `nonlocal` for the enclosing functions' variables it assigns (JS closures rebind freely)."""
+    ps = (["self"] if takes_self else []) + [_name(p) if isinstance(p, str) else _name(p[0]) + (f"={emit_expr(p[1])}" if p[1] is not None else "")
+                                             for p in params]
+    declared, assigned = _scope_names(params, block)
+    outer = sorted(x for x in assigned - declared if any(x in sc for sc in _SCOPES))
+    free = sorted(x for x in assigned - declared if not any(x in sc for sc in _SCOPES))
+    if free:
+        raise SyntaxError(f"js subset: function {name} assigns to undeclared or module-level name(s) {free}")
+    out.append(f"{'    ' * ind}def {name}({', '.join(ps)}):")
+    if outer:
+        out.append(f"{'    ' * (ind + 1)}nonlocal {', '.join(_name(x) for x in outer)}")
+    _SCOPES.append(declared)
+    try:
+        emit_body(block, ind + 1, out)
+    finally:
+        _SCOPES.pop()
 
 
 def _flush_hoisted(ind: int, out: list):
-    while _HOIST:
-        name, params, block = _HOIST.pop(0)
-        out.append(f"{'    ' * ind}def {name}({', '.join(_name(p) for p in params)}):")
-        emit_body(block, ind + 1, out)
+    pending = _HOIST[:]          # (functions hoisted while THESE bodies are emitted flush inside them, at their own statements)
+    del _HOIST[:]
+    for name, params, block, takes_self in pending:
+        _emit_function(name, params, block, ind, out, takes_self)
 
 
 def emit_expr(e) -> str:
@@ -442,8 +507,17 @@ def emit_expr(e) -> str:
     if k == "arrowblock":
         _COUNTER[0] += 1
         name = f"_arrow_{_COUNTER[0]}"
-        _HOIST.append((name, e[1], e[2]))
+        _HOIST.append((name, e[1], e[2], False))
         return name
+    if k == "funcexpr":      # `this` inside is the object the function is assigned to: bound where it is assigned (emit_stmt)
+        if _uses_this(e[3]) and not _THIS_FN_OK[0]:
+            raise SyntaxError("js subset: a function expression using `this` is only supported as `obj.member = function ...`")
+        _COUNTER[0] += 1
+        name = f"_fn_{_COUNTER[0]}_{_name(e[1] or 'anonymous')}"
+        _HOIST.append((name, e[2], e[3], _uses_this(e[3])))
+        return name
+    if k == "getter":
+        return f"JSGetter({emit_expr(e[1])})"
     if k == "num":
         return e[1]
     if k == "str":
@@ -488,9 +562,8 @@ def emit_stmt(s, ind: int, out: list):
         for c in s[1]:
             emit_stmt(c, ind, out)
     elif k == "func":
-        ps = [_name(p) + (f"={emit_expr(d)}" if d is not None else "") for p, d in s[2]]
-        line(f"def {_name(s[1])}({', '.join(ps)}):")
-        emit_body(s[3], ind + 1, out)
+        _flush_hoisted(ind, out)
+        _emit_function(_name(s[1]), s[2], s[3], ind, out)
     elif k == "decl":
         for name, value in s[1]:
             line(f"{_name(name)} = {emit_expr(value) if value is not None else 'None'}")
@@ -517,7 +590,16 @@ def emit_stmt(s, ind: int, out: list):
         out.append(pad + k)
     elif k == "expr":
         e = s[1]
-        if e[0] == "assign":
+        if e[0] == "assign" and e[3][0] == "funcexpr" and _uses_this(e[3][3]):
+            if e[1] != "=" or e[2][0] != "member":
+                raise SyntaxError("js subset: a function using `this` must be assigned to an object member")
+            _THIS_FN_OK[0] = True
+            try:
+                fn = emit_expr(e[3])
+            finally:
+                _THIS_FN_OK[0] = False
+            line(f"{emit_expr(e[2])} = _bind({fn}, {emit_expr(e[2][1])})")
+        elif e[0] == "assign":
             if e[1] == "/=":
                 line(f"{emit_expr(e[2])} = _div({emit_expr(e[2])}, {emit_expr(e[3])})")
             else:
@@ -543,9 +625,7 @@ def emit_program(prog) -> str:
         if node[0] == "class":
             out.append(f"class {_name(node[1])}:")
             for mname, params, body in node[2]:
-                ps = ["self"] + [_name(p) + (f"={emit_expr(d)}" if d is not None else "") for p, d in params]
-                out.append(f"    def {'__init__' if mname == 'constructor' else _name(mname)}({', '.join(ps)}):")
-                emit_body(body, 2, out)
+                _emit_function("__init__" if mname == "constructor" else _name(mname), params, body, 1, out, takes_self=True)
             out.append("")
         else:
             emit_stmt(node, 0, out)
@@ -605,15 +685,55 @@ class JSArray(list):
         return tuple(self)
 
 
+class JSGetter:
+    def __init__(self, fn):
+        self.fn = fn
+
+
 class JSObject:
     def __init__(self, d):
-        self.__dict__.update(d)
+        getters = {k: v.fn for k, v in d.items() if isinstance(v, JSGetter)}
+        self.__dict__.update({k: v for k, v in d.items() if k not in getters})
+        self.__dict__["_getters"] = getters
+
+    def __getattr__(self, key):              # only reached for names not in __dict__: a getter, else `undefined`
+        getters = self.__dict__.get("_getters", {})
+        return getters[key]() if key in getters else None
 
     def __getitem__(self, key):
         return self.__dict__[key]
 
     def __setitem__(self, key, value):
         self.__dict__[key] = value
+
+
+def _bind(fn, obj):
+    """`obj.name = function () { ... this ... }`: calls through obj see it as `this`."""
+    import types
+    return types.MethodType(fn, obj)
+
+
+def typed_array(dtype):
+    """Float64Array / Float32Array / Uint32Array: numpy storage (stores round like the JS typed array), `length`, `subarray`."""
+    import numpy as np
+
+    class TypedArray(np.ndarray):
+        def __new__(cls, n):
+            return np.zeros(int(n), dtype=dtype).view(cls)
+
+        @property
+        def length(self):
+            return self.shape[0]
+
+        def subarray(self, begin, end=None):
+            return self[int(begin):None if end is None else int(end)]
+
+        def __getitem__(self, key):          # an element read is a JS Number (binary64), whatever the storage type
+            v = np.ndarray.__getitem__(self, key)
+            return v.item() if isinstance(v, np.generic) else v
+
+    TypedArray.__name__ = np.dtype(dtype).name
+    return TypedArray
 
 
 class JSMap:
@@ -947,6 +1067,28 @@ class ReferenceVisuals:
 
 def _Bag_from_dict(d):
     return _Bag(**d)
+
+
+# ---------------------------------------------------------------- the drop-in: the page with its integrate() replaced by the shim
+
+SHIM_JS = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "n-body-sim_b200", "addon", "physics_shim.js")
+
+
+def install_shim(reference: "Reference", addon, **opts):
+    """Executes n-body-sim_b200/addon/physics_shim.js (this repository's JS, transliterated like the page) against the
+    page's own `physics` and `CONFIG`: `installGpuIntegrate(physics, CONFIG, addon, opts)` replaces
+    `PhysicsSystem.integrate` (idx:247-262) and `computeGravity` on that one object; Body, addBody, resolveCollisions,
+    mergeBodies, fractureBodies stay the page's.  `addon` is any object with the N-API addon's methods
+    (create/destroy/upload/download/step/stepHost/kick1Drift/force/kick2/setHeatDecay/setRadius/contacts).
+    Returns the shim's handle (`dispose()`, `ctx`)."""
+    with open(SHIM_JS, encoding="utf-8") as f:
+        src = f.read()
+    module = JSObject({})
+    ns = {"JSArray": JSArray, "JSObject": JSObject, "JSGetter": JSGetter, "_bind": _bind, "_div": _div, "Math": reference.Math,
+          "Float64Array": typed_array("float64"), "Float32Array": typed_array("float32"), "Uint32Array": typed_array("uint32"),
+          "module": module}
+    exec(compile(transliterate(src), "<physics_shim.js transliterated>", "exec"), ns)
+    return module.exports.installGpuIntegrate(reference.physics, reference.CONFIG, addon, JSObject(opts))
 
 
 def available(html=REFERENCE_HTML) -> bool:

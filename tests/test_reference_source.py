@@ -32,7 +32,8 @@ def _make_golden():
 
 
 def _run(js, entry="f", *args):
-    ns = {"JSArray": jr.JSArray, "JSObject": jr.JSObject, "Map": jr.JSMap, "Set": jr.JSSet, "_div": jr._div, "Math": jr._Math(1)}
+    ns = {"JSArray": jr.JSArray, "JSObject": jr.JSObject, "JSGetter": jr.JSGetter, "_bind": jr._bind, "Map": jr.JSMap, "Set": jr.JSSet,
+          "_div": jr._div, "Math": jr._Math(1)}
     exec(jr.transliterate(js), ns)
     return ns[entry](*args)
 
@@ -72,7 +73,7 @@ def test_subset_loops_collections_and_arrows():
 
 @pytest.mark.parametrize("js", [
     "function f() { while (true) {} }", "function f(a) { a = b = 1; return a; }", "function f(n) { for (let i = 0; i < n; i += 2) {} }",
-    "function f(n) { for (let i = 0; i < n - 1; i++) { if (i) continue; } }", "function f() { return x => { return 1; }; }", "function f(xs) { let t = 0; xs.forEach(x => { t += x; }); return t; }", "function f(a) { return `t${a}`; }",
+    "function f(n) { for (let i = 0; i < n - 1; i++) { if (i) continue; } }", "function f(a) { a.x = function () { return this.y; }.bind(a); }", "function f() { g = 1; }", "function f(a) { return `t${a}`; }",
 ])
 def test_subset_rejects_what_it_does_not_cover(js):
     with pytest.raises(SyntaxError):
@@ -196,6 +197,37 @@ def test_live_visual_update_ribbons_bit_exact(oracle):
             chains[ident] = oracle.history_push(chains[ident] if ident in chains else oracle.history_init(pos, 80), pos)
             assert np.array_equal(chains[ident][0], H[i]), (frame, i)
     assert len(sizes) > 1                               # the body list did change
+
+
+def test_subset_closures_function_expressions_and_objects():
+    # closures rebind enclosing variables (nonlocal), `this` of a function assigned to a member is that object,
+    # object literals carry methods, getters and shorthand properties, missing members are undefined
+    js = """
+    function f(obj, xs) {
+        let t = 0, calls = 0;
+        function bump(k = 2) { calls++; t += k; }
+        xs.forEach(x => { t += x; });
+        bump(); bump(5);
+        obj.twice = function twice(a) { return this.base * 2 + a; };
+        const g = x => { return x + 1; };
+        const shorthand = 7;
+        return { t, calls, shorthand, plus: g(1), get total() { return t + calls; }, inc() { t++; }, missing: obj.nope || 'undefined' };
+    }"""
+    obj = jr.JSObject({"base": 10})
+    r = _run(js, "f", obj, jr.JSArray([1, 2, 3]))
+    assert (r.t, r.calls, r.shorthand, r.plus, r.missing) == (13, 2, 7, 2, "undefined")
+    assert obj.twice(1) == 21 and r.total == 15
+    r.inc()
+    assert r.total == 16 and r.undefined_member is None
+
+
+def test_subset_typed_arrays():
+    F32 = jr.typed_array("float32")
+    a = F32(8)
+    a[1] = 0.1
+    assert a.length == 8 and a.subarray(0, 4).length == 4 and isinstance(a[1], float) and a[1] == float(np.float32(0.1))
+    a.subarray(4, 8)[0] = 2.0                             # a view, like TypedArray.prototype.subarray
+    assert a[4] == 2.0
 
 
 def test_subset_block_arrows_and_computed_bounds():
