@@ -1058,6 +1058,8 @@ template <typename Real> int launch_small_steps_t(nbody_ctx* c, Shard& s, double
     p.vel = static_cast<Real*>(s.vel);
     p.acc = static_cast<Real*>(s.acc);
     p.temp = c->has_temp ? static_cast<Real*>(s.temp) : nullptr;
+    p.rec_out = static_cast<Real*>(c->step_rec_out);  // nbody_step_host: the kernel writes the caller's record itself
+    c->step_rec_out = nullptr;
     p.n = int(c->n);
     p.nsteps = nsteps;
     p.G = Real(G);
@@ -1177,9 +1179,30 @@ extern "C" int nbody_step_host(nbody_ctx* c, size_t n, void* pos_mass, void* vel
     if (!c) return NBODY_EINVAL;
     if (!pos_mass || !vel || !acc) return fail(c, NBODY_EINVAL, "step_host: pos_mass, vel and acc are required (in and out)");
     int rc = nbody_upload(c, n, pos_mass, vel, acc, temp);
-    if (rc == NBODY_OK) rc = nbody_step(c, dt, G, softening, nsteps);
-    if (rc == NBODY_OK) rc = nbody_download(c, pos_mass, vel, acc, temp);
-    return rc;
+    if (rc != NBODY_OK) return rc;
+    Shard& s = c->shards[0];
+    // the page's own sizes: the cluster kernel (small.cuh) also writes the record the caller reads, so the frame is
+    // count reset + pack + ONE step kernel + one synchronise
+    const bool fused_out = s.io_host && c->upload_deferred && n <= kSmallIoZeroCopyMaxN && c->small_path && c->world == 1 &&
+                           n <= c->small_max_n && !c->timing && nsteps > 0 && softening >= 0.0;
+    if (!fused_out) {
+        rc = nbody_step(c, dt, G, softening, nsteps);
+        if (rc == NBODY_OK) rc = nbody_download(c, pos_mass, vel, acc, temp);
+        return rc;
+    }
+    c->step_rec_out = s.io_host;
+    rc = nbody_step(c, dt, G, softening, nsteps);
+    c->step_rec_out = nullptr;
+    if (rc != NBODY_OK) return rc;
+    CU(c, cudaSetDevice(s.device));
+    CU(c, cudaStreamSynchronize(s.stream));
+    const size_t bytes4 = 4 * n * c->esz;
+    const char* rec = static_cast<const char*>(s.io_host);
+    memcpy(pos_mass, rec, bytes4);
+    memcpy(vel, rec + bytes4, bytes4);
+    memcpy(acc, rec + 2 * bytes4, bytes4);
+    if (temp) memcpy(temp, rec + 3 * bytes4, n * c->esz);
+    return check_exchange(c);
 }
 
 extern "C" int nbody_kick1_drift(nbody_ctx* c, double dt)

@@ -40,6 +40,8 @@ template <typename Real> struct SmallParams {
     Real* vel;    // Real4 per body
     Real* acc;    // Real4 per body: acc of the previous step on entry (first kick-1), of the last step on exit
     Real* temp;   // may be null
+    Real* rec_out;  // may be null; else the final state also goes out as one record [pos_mass 4n | vel 4n | acc 4n | temp n]
+                    // (integrate.cuh) -- nbody_step_host points it at the mapped pinned record, so no unpack kernel follows
     int n;
     int nsteps;
     Real G, eps2, r2_floor, half_dt, dt, heat_decay;  // r2_floor: 1e-20 when eps == 0 (fp32 self pair), else 0
@@ -162,7 +164,7 @@ __global__ void __cluster_dims__(kSmallCluster, 1, 1) __launch_bounds__(kSmallTh
     if (owner) {
         v = reinterpret_cast<const V4*>(p.vel)[gi];
         a = reinterpret_cast<const V4*>(p.acc)[gi];
-        if (thermal_on) t = p.temp[gi];
+        if (p.temp != nullptr) t = p.temp[gi];
     }
     cluster_barrier();  // every CTA is resident and has its copy before anyone stores into a peer
 
@@ -231,6 +233,13 @@ __global__ void __cluster_dims__(kSmallCluster, 1, 1) __launch_bounds__(kSmallTh
         reinterpret_cast<V4*>(p.vel)[gi] = v;
         reinterpret_cast<V4*>(p.acc)[gi] = a;
         if (thermal_on) p.temp[gi] = t;
+        if (p.rec_out != nullptr) {
+            V4* rec = reinterpret_cast<V4*>(p.rec_out);
+            rec[gi] = b;
+            rec[n + gi] = v;
+            rec[2 * n + gi] = a;
+            if (p.temp != nullptr) p.rec_out[12 * size_t(n) + gi] = t;
+        }
     }
 }
 
