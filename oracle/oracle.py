@@ -85,6 +85,10 @@ def lib() -> ctypes.CDLL:
         L.oracle_render.argtypes = [sz, _fp, _fp, _fp, ctypes.POINTER(ctypes.c_int), _fp, i, i, _dp, _dp, d, _fp,
                                     ctypes.POINTER(ctypes.c_int32)]
         L.oracle_render.restype = None
+        L.oracle_planet_fragment.argtypes = [_fp, _fp, _fp, i, ctypes.c_float, ctypes.c_float, _fp, _fp]
+        L.oracle_planet_fragment.restype = None
+        L.oracle_snoise.argtypes = [_fp]
+        L.oracle_snoise.restype = ctypes.c_float
         for f in ("oracle_overlap_pairs", "oracle_overlap_pairs_mt"):
             getattr(L, f).argtypes = [sz, _dp, _dp, d, _u32p, sz]
             getattr(L, f).restype = sz
@@ -279,3 +283,19 @@ def render(pos_mass, radius, temp, type, seed, width, height, camera=(0.0, 80.0,
                         ty.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), sd.ctypes.data_as(fp), int(width), int(height),
                         _p(cam), _p(tgt), float(fov_deg), rgba.ctypes.data_as(fp), ids.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)))
     return rgba, ids
+
+
+def planet_fragment(vpos, vnormal, vview, type, temperature, seed, sun=(50.0, 50.0, 50.0)):
+    """gl_FragColor of planetFragmentShader (idx:164-201) for one fragment, float32[4]."""
+    fp = ctypes.POINTER(ctypes.c_float)
+    a = [np.ascontiguousarray(x, dtype=np.float32) for x in (vpos, vnormal, vview, sun)]
+    rgba = np.zeros(4, dtype=np.float32)
+    lib().oracle_planet_fragment(a[0].ctypes.data_as(fp), a[1].ctypes.data_as(fp), a[2].ctypes.data_as(fp), int(type), float(temperature),
+                                 float(seed), a[3].ctypes.data_as(fp), rgba.ctypes.data_as(fp))
+    return rgba
+
+
+def snoise(v):
+    """snoise(vec3) of the planet shader (idx:114-162), float32."""
+    a = np.ascontiguousarray(v, dtype=np.float32)
+    return np.float32(lib().oracle_snoise(a.ctypes.data_as(ctypes.POINTER(ctypes.c_float))))

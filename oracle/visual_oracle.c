@@ -7,7 +7,11 @@
  *     PINNED TO THE REFERENCE'S SOURCE TEXT: oracle/js_reference.py executes the page's own
  *     VisualSystem.update and this loop equals its Float32Array bit for bit
  *     (tests/test_reference_source.py, tests/golden/ref_js_page_galaxy_ribbons.npz);
- *   - the planet shaders, idx:83-202 (GLSL: PARITY UNPINNED, needs a browser + WebGL to run).
+ *   - the planet shaders, idx:83-202.  The fragment shader's arithmetic is PINNED TO ITS GLSL TEXT:
+ *     oracle/glsl_reference.py executes planetFragmentShader from the page, one binary32 operation per
+ *     GLSL operation, and planet_fragment / snoise below equal it bit for bit
+ *     (tests/test_reference_source.py, tests/golden/ref_glsl_planet_fragments.npz).  Parity against a
+ *     real WebGL driver (its own pow/normalize precision, rasterised varyings) stays unpinned.
  * THREE.Vector3 members written out (three@0.160.0): subVectors, crossVectors
  * (x = ay*bz - az*by, y = az*bx - ax*bz, z = ax*by - ay*bx), normalize =
  * multiplyScalar(1 / (length() || 1)), multiplyScalar.
@@ -180,6 +184,17 @@ static void planet_fragment(v3 vPosition, v3 vNormal, v3 vViewPosition, int type
     }
     rgba[3] = 1.0f;
 }
+
+/* One fragment of planetFragmentShader and one noise sample, exported so that the restatement can be compared with the
+ * shader's own text executed by oracle/glsl_reference.py (tests/test_reference_source.py). */
+ORACLE_API void oracle_planet_fragment(const float *vpos, const float *vnormal, const float *vview, int type, float temperature,
+                                       float seed, const float *sun, float *rgba)
+{
+    planet_fragment((v3){vpos[0], vpos[1], vpos[2]}, (v3){vnormal[0], vnormal[1], vnormal[2]}, (v3){vview[0], vview[1], vview[2]}, type,
+                    temperature, seed, (v3){sun[0], sun[1], sun[2]}, rgba);
+}
+
+ORACLE_API float oracle_snoise(const float *v) { return snoise((v3){v[0], v[1], v[2]}); }
 
 typedef struct {
     v3 pos, xa, ya, za; /* camera position and basis (za points from the target to the camera) */

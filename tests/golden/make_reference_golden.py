@@ -94,6 +94,35 @@ def ribbons_fixture(name, frames, keep_every=5):
     print(name, frames, "frames,", len(st["temp"]), "bodies,", len(keep), "kept")
 
 
+def fragments(count, seed):
+    """Varyings and uniforms of `count` fragments on random spheres seen from the page's camera (0, 80, 150), idx:705."""
+    rng = np.random.default_rng(seed)
+    out = dict(vpos=[], vnormal=[], vview=[], type=[], temperature=[], seed=[])
+    for _ in range(count):
+        nrm = rng.normal(0, 1, 3)
+        nrm /= np.linalg.norm(nrm)
+        vpos = (rng.uniform(-80, 80, 3) + rng.uniform(0.4, 4.0) * nrm).astype(np.float32)
+        out["vpos"].append(vpos)
+        out["vnormal"].append((nrm * rng.uniform(0.5, 1.5)).astype(np.float32))        # un-normalised, as interpolation leaves it
+        out["vview"].append((np.array([0.0, 80.0, 150.0]) - vpos).astype(np.float32))
+        out["type"].append(int(rng.integers(0, 3)))
+        out["temperature"].append(np.float32(rng.choice([0.0, 10.0, 30.0, 49.0, 60.0, 120.0, 1000.0])))
+        out["seed"].append(np.float32(rng.uniform(0, 100)))                             # Math.random() * 100, idx:492
+    return {k: np.array(v) for k, v in out.items()}
+
+
+def shader_fixture(name, count=256):
+    """gl_FragColor of the page's planetFragmentShader (idx:99-202), executed from its GLSL text (oracle/glsl_reference.py)."""
+    from oracle import glsl_reference as gr
+    sh, cfg = gr.PlanetShader(), jr.Reference().CONFIG
+    f = fragments(count, 7)
+    rgba = np.stack([sh.fragment(f["vpos"][k], f["vnormal"][k], f["vview"][k], cfg.materials[jr.TYPES[f["type"][k]]].color1.rgb,
+                                 cfg.materials[jr.TYPES[f["type"][k]]].color2.rgb, f["temperature"][k], f["seed"][k]) for k in range(count)])
+    noise = np.array([sh.snoise(f["vpos"][k]) for k in range(count)], dtype=np.float32)
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), rgba=rgba, snoise=noise, **f)
+    print(name, count, "fragments")
+
+
 if __name__ == "__main__":
     if not jr.available():
         sys.exit("needs /root/reference/index.html")
@@ -109,3 +138,4 @@ if __name__ == "__main__":
             for i in range(len(s0["temp"]))]
     collision_fixture("ref_js_page_galaxy_collisions", page, seed=5, nsteps=200, reseed=1234, reference=r)
     ribbons_fixture("ref_js_page_galaxy_ribbons", frames=100)
+    shader_fixture("ref_glsl_planet_fragments")

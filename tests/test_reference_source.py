@@ -230,6 +230,32 @@ def test_subset_typed_arrays():
     assert a[4] == 2.0
 
 
+@live
+def test_live_planet_shader_text_equals_restatement(oracle):
+    """planetFragmentShader (GLSL, idx:99-202) executed from its text, one binary32 operation per GLSL operation
+    (oracle/glsl_reference.py), against visual_oracle.c's planet_fragment / snoise: every bit of every channel."""
+    from oracle import glsl_reference as gr
+    sh, cfg = gr.PlanetShader(), jr.Reference().CONFIG
+    f = _make_golden().fragments(200, 11)
+    for k in range(200):
+        m = cfg.materials[jr.TYPES[f["type"][k]]]
+        a = sh.fragment(f["vpos"][k], f["vnormal"][k], f["vview"][k], m.color1.rgb, m.color2.rgb, f["temperature"][k], f["seed"][k])
+        b = oracle.planet_fragment(f["vpos"][k], f["vnormal"][k], f["vview"][k], f["type"][k], f["temperature"][k], f["seed"][k])
+        assert np.array_equal(a, b), (k, a, b)
+        assert sh.snoise(f["vpos"][k] * np.float32(2.0)) == oracle.snoise(f["vpos"][k] * np.float32(2.0))
+    # the shader declares the six uniforms and four varyings the renderer feeds (idx:100-110)
+    assert all(("uniform %s;" % u) in " ".join(sh.glsl.split()) for u in ("vec3 color1", "vec3 color2", "float temperature", "float seed", "vec3 sunPosition"))
+
+
+def test_glsl_subset_rejects_control_flow():
+    from oracle import glsl_reference as gr
+    assert "def f(x):" in gr.transliterate("float f(float x) { float y = x * 2.0; y *= x; return y - 1.0; }")
+    for bad in ("float f(float x) { if (x > 0.0) return x; return 0.0; }", "float f(float x) { for (int i = 0; i < 3; i++) x += 1.0; return x; }",
+                "vec3 f(vec3 x) { x.xy = x.yx; return x; }", "float f(float x) { return 1.0; }\nfloat f(float x) { return 2.0; }"):
+        with pytest.raises(SyntaxError):
+            gr.transliterate(bad)
+
+
 def test_subset_block_arrows_and_computed_bounds():
     js = """
     function f(xs) {
@@ -258,6 +284,15 @@ def test_oracle_equals_reference_vectors_gravity(oracle, name):
         done = int(c)
         for key, x in zip(STATE_KEYS, (p, v, a, t)):
             assert np.array_equal(x, g[key][k]), (name, int(c), key)
+
+
+def test_oracle_equals_shader_text_vectors(oracle):
+    g = np.load(os.path.join(GOLD, "ref_glsl_planet_fragments.npz"))
+    for k in range(len(g["seed"])):
+        b = oracle.planet_fragment(g["vpos"][k], g["vnormal"][k], g["vview"][k], g["type"][k], g["temperature"][k], g["seed"][k])
+        assert np.array_equal(b, g["rgba"][k]), k
+        assert oracle.snoise(g["vpos"][k]) == g["snoise"][k], k
+    assert np.isfinite(g["rgba"]).all() and (g["rgba"][:, 3] == 1).all() and g["rgba"][:, :3].std() > 0.05
 
 
 def _world_from_fixture(oracle, g):
