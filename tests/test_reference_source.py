@@ -135,6 +135,55 @@ def test_live_complete_step_bit_exact(oracle, speed, nsteps):
     assert (c["merge"] if speed < 1 else c["fracture"]) > 0
 
 
+_EDGE_CASES = {
+    # name: (bodies (mass, pos, vel, type, temp), steps, softening, collisions, maxBodies)
+    "empty": ([], 2, 0.5, True, 300),
+    "single": ([(1.0, (0, 0, 0), (1, 0, 0), "rock", 60.0)], 3, 0.5, True, 300),
+    "coincident": ([(1.0, (0, 0, 0), (0, 0, 0), "rock", 0.0), (2.0, (0, 0, 0), (0, 0, 0), "ice", 0.0)], 3, 0.5, True, 300),
+    "coincident_zero_softening_nan": ([(1.0, (0, 0, 0), (0, 0, 0), "rock", 0.0), (2.0, (0, 0, 0), (0, 0, 0), "ice", 0.0),
+                                       (1.0, (3, 0, 0), (0, 0, 0), "rock", 0.0)], 2, 0.0, False, 300),      # G / pow(0, 1.5) = Infinity, 0 * Infinity = NaN
+    "massless_pair": ([(0.0, (0, 0, 0), (0.1, 0, 0), "rock", 0.0), (0.0, (0, 0, 0), (-0.1, 0, 0), "rock", 0.0),
+                       (1.0, (5, 0, 0), (0, 0, 0), "metal", 0.0)], 3, 0.5, True, 300),                       # invMass = 0 (idx:212): x / 0 in the impulse
+    "massless_on_massive": ([(0.0, (0, 0, 0), (1, 0, 0), "rock", 0.0), (5.0, (0.5, 0, 0), (-1, 0, 0), "metal", 10.0)], 5, 0.5, True, 300),
+    "thermal_floor": ([(1.0, (0, 0, 0), (0, 0, 0), "rock", 0.11), (1.0, (9, 0, 0), (0, 0, 0), "rock", 0.1)], 60, 0.5, False, 300),  # T < 0.1 -> 0 (idx:229)
+    "fracture": ([(3.0, (-0.4, 0, 0), (40, 0, 0), "rock", 0.0), (3.0, (0.4, 0, 0), (-40, 0, 0), "metal", 0.0)], 4, 0.5, True, 300),
+    "fracture_below_min_fragment_mass": ([(0.15, (-0.1, 0, 0), (40, 0, 0), "rock", 0.0), (0.15, (0.1, 0, 0), (-40, 0, 0), "ice", 0.0)], 4, 0.5, True, 300),
+    "pile_of_four_merging": ([(1.0, (0, 0, 0), (0, 0, 0), "rock", 0.0), (1.0, (0.3, 0, 0), (-1, 0, 0), "rock", 0.0),
+                              (1.0, (0.1, 0.2, 0), (0, -1, 0), "ice", 0.0), (1.0, (-0.2, 0.1, 0.1), (1, 0, 0), "metal", 0.0)], 80, 0.5, True, 300),
+    "fracture_into_a_full_list": ([(3.0, (-0.4, 0, 0), (40, 0, 0), "rock", 0.0), (3.0, (0.4, 0, 0), (-40, 0, 0), "metal", 0.0)] +
+                                  [(1.0, (20.0 + 5 * k, 0, 0), (0, 0, 0), "ice", 0.0) for k in range(5)], 4, 0.5, True, 7),   # addBody shifts the oldest out (idx:240-242)
+}
+
+
+@live
+@pytest.mark.parametrize("name", sorted(_EDGE_CASES))
+def test_live_edge_cases_bit_exact(oracle, name):
+    """Empty and single-body lists, coincident bodies, NaN/Infinity propagation (the page signals nothing),
+    massless bodies, the thermal floor, fractures that fall below minFragmentMass, a full body list: page == oracle."""
+    bodies, steps, eps, collisions, cap = _EDGE_CASES[name]
+    r = jr.Reference(seed=3, collisions=collisions)
+    r.CONFIG.softening, r.CONFIG.maxBodies = eps, cap
+    w = oracle.World(seed=3, max_bodies=cap)
+    for (m, p, v, ty, t) in bodies:
+        r.add(m, p, v, ty, t)
+        w.add(m, p, v, ty, t)
+    sizes = {len(bodies)}
+    for step in range(steps):
+        r.integrate(0.008)
+        w.integrate(0.008, 0.5, eps, collisions, 1)
+        a, b = r.state(), w.state()
+        sizes.add(len(a["temp"]))
+        for k in a:
+            assert np.array_equal(a[k], b[k], equal_nan=True), (name, step, k)
+    assert r.Math.draws >= len(bodies) and r.physics.contactPairs.size == w.n_contacts
+    if name == "coincident_zero_softening_nan":
+        assert np.isnan(a["acc"]).any()
+    if name in ("fracture", "pile_of_four_merging"):
+        assert len(sizes) > 1
+    if name == "fracture_into_a_full_list":   # two bodies out, the fragments in, the oldest bodies pushed out: full again
+        assert sizes == {cap} and w.counters()["fracture"] == 1 and not np.array_equal(a["pos_mass"][0, :3], [20.0, 0, 0])
+
+
 @live
 def test_live_reset_scenario_equals_mirror(nb):
     """The page's scene generator (idx:744-759) and the host mirror's, same Math.random stream."""
