@@ -426,24 +426,6 @@ def _uses_this(body) -> bool:
     return any(n == ("id", "this") for n in _walk_shallow(body, False))
 
 
-def _has(node, kind) -> bool:
-    return any(n and n[0] == kind for n in _walk(node))
-
-
-def _assigned_names(node) -> set:
-    return {n[2][1] for n in _walk(node) if n and n[0] in ("assign", "update") and isinstance(n[2], tuple) and n[2][0] == "id"}
-
-
-def _declared_names(node) -> set:
-    out = set()
-    for n in _walk(node):
-        if n and n[0] == "decl":
-            out |= {name for name, _ in n[1]}
-        elif n and n[0] in ("forrange", "forwhile", "forof"):
-            out.add(n[1])
-    return out
-
-
 def _own_continue(node) -> bool:
     """A `continue` that belongs to the loop whose body `node` is (not to a loop nested inside it)."""
     if isinstance(node, tuple):
