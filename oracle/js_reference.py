@@ -14,8 +14,8 @@ Why: no Node/V8 (or any JS engine) exists in the build image or on the GPU box, 
 Node harness (n-body-sim_b200/addon/run_reference.js) cannot run.  This module is the same
 harness with the engine replaced by a transliterator: the statements that execute are the
 reference's, not a restatement written from reading them.  It pins oracle/nbody_oracle.c
-and oracle/collide_oracle.c (tests/test_reference_source.py) and generates the committed
-vectors tests/golden/ref_js_*.npz.
+oracle/collide_oracle.c and oracle/visual_oracle.c's ribbon loop (tests/test_reference_source.py,
+tests/test_shim_source.py) and generates the committed vectors tests/golden/ref_js_*.npz.
 
 Supplied from outside the reference, exactly as run_reference.js does:
   * `THREE.Vector3` (three@0.160.0, CDN import idx:24, not on disk): the methods the
@@ -26,12 +26,18 @@ Supplied from outside the reference, exactly as run_reference.js does:
   * `Body.id` = `Math.random().toString(36).substr(2, 9)` (idx:210): the draw itself stands
     for the string (it is only ever an identity: sorted and joined into a map key, idx:311).
 
-The subset covers what idx:52-75 and idx:208-444 use: classes and methods with default
-parameters, const/let, if/else, `for (let i = a; i < b; i++)` with a loop-invariant bound,
-for-of, continue/break/return, assignment and compound assignment statements, `?:`,
-`|| && !`, comparisons, arithmetic, member/index/call chains, `new`, array and object
-literals, expression-bodied arrow functions.  Anything else raises SyntaxError naming the
-token, so a changed reference fails loudly instead of being half-translated.
+What is executed this way: `CONFIG` (idx:52-75), `Body` and `PhysicsSystem` (idx:208-444), `resetScenario` (idx:744-764),
+`VisualSystem.update` (idx:500-597, class `ReferenceVisuals`), and this repository's own `addon/physics_shim.js` installed
+on the page's `physics` object (`install_shim`).  The planet fragment shader is oracle/glsl_reference.py's.
+
+The subset: classes and methods with default parameters, function declarations and expressions (closures rebind the
+enclosing function's variables through `nonlocal`; a function using `this` must be assigned to an object member and is
+bound to that object), expression- and block-bodied arrow functions, const/let, if/else, `for (let i = a; i < b; i++)`
+(a `range` when the bound is a name or literal the body leaves alone, else re-evaluated every pass), for-of,
+continue/break/return, assignment and compound assignment statements, `++`/`--` statements, `?:`, `|| && !`,
+comparisons, arithmetic (`/` with IEEE division by zero), member/index/call chains, `new`, array literals, object
+literals with methods, getters and shorthand properties (missing members read as undefined), typed arrays.  Anything
+else raises SyntaxError naming the token, so a changed reference fails loudly instead of being half-translated.
 """
 from __future__ import annotations
 
