@@ -128,7 +128,8 @@ def run_reference(args, rank):
                                    f"{sample_n} bodies (bounded sample)", "n": args.n, "sample_n": sample_n},
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": 1, "kind": "port",
                              "sample": f"first {sample_n} bodies, {args.steps} steps, 1 thread (the reference is "
-                                       f"single-threaded JS, idx:873-883; Node/V8 unavailable in this image); host has {os.cpu_count()} cores"},
+                                       f"single-threaded JS, idx:873-883; Node/V8 unavailable in this image: the C restatement, bit-identical to the "
+                                       f"page's own source executed by oracle/js_reference.py); host has {os.cpu_count()} cores"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "all_cores": all_cores}
     print(json.dumps(line), flush=True)
