@@ -185,6 +185,31 @@ def test_live_edge_cases_bit_exact(oracle, name):
 
 
 @live
+def test_live_collision_scenario_bit_exact(oracle):
+    """The page's second built-in scene, resetScenario('collision') (idx:760-763): two mass-100 bodies fall
+    together and merge; 10,000 complete steps, page == oracle at every checkpoint."""
+    r = jr.Reference(seed=8, collisions=True)
+    r.resetScenario("collision")
+    s0 = r.state()
+    w = oracle.World(seed=8, max_bodies=300)
+    for i in range(2):
+        w.add(s0["pos_mass"][i, 3], s0["pos_mass"][i, :3], s0["vel"][i, :3], jr.TYPES[s0["type"][i]], s0["temp"][i])
+    r.Math.state = 99
+    w.seed(99)
+    sizes = []
+    for _ in range(40):
+        r.integrate(0.008, 250)
+        w.integrate(0.008, 0.5, 0.5, True, 250)
+        a, b = r.state(), w.state()
+        sizes.append(len(a["temp"]))
+        assert len(a["temp"]) == len(b["temp"])
+        for k in ("pos_mass", "vel", "acc", "temp", "radius", "type"):
+            assert np.array_equal(a[k], b[k]), k
+    assert sizes[0] == 2 and sizes[-1] == 1 and w.counters()["merge"] == 1
+    assert a["pos_mass"][0, 3] == 200.0                       # mass conserved by mergeBodies (idx:393)
+
+
+@live
 def test_live_reset_scenario_equals_mirror(nb):
     """The page's scene generator (idx:744-759) and the host mirror's, same Math.random stream."""
     ph = nb.physics
