@@ -185,6 +185,34 @@ def test_live_edge_cases_bit_exact(oracle, name):
 
 
 @live
+@pytest.mark.parametrize("seed", range(8))
+def test_live_random_small_worlds_bit_exact(oracle, seed):
+    """Random little worlds (2-14 bodies in a box a few radii wide, speeds from gentle to shattering, random CONFIG
+    thresholds): whatever mixture of bounces, merges, fractures and list overflows they produce, page == oracle."""
+    rng = np.random.default_rng(1000 + seed)
+    n, cap = int(rng.integers(2, 15)), int(rng.choice([6, 12, 300]))
+    speed = float(rng.choice([0.2, 2.0, 12.0, 40.0]))
+    r = jr.Reference(seed=seed, collisions=True)
+    c = r.CONFIG
+    c.maxBodies, c.fractureThreshold, c.minFragmentMass, c.mergeTime = cap, float(rng.choice([5.0, 25.0])), float(rng.choice([0.05, 0.2])), float(rng.choice([0.02, 0.5]))
+    w = oracle.World(seed=seed, max_bodies=cap)
+    w.config(c.fractureThreshold, c.minFragmentMass, c.mergeTime, c.heatDecay)
+    for _ in range(n):
+        m, p, v = float(rng.uniform(0.1, 4.0)), tuple(rng.uniform(-2.0, 2.0, 3)), tuple(rng.normal(0, speed, 3))
+        ty, t = jr.TYPES[int(rng.integers(0, 3))], float(rng.uniform(0, 80))
+        r.add(m, p, v, ty, t)
+        w.add(m, p, v, ty, t)
+    for step in range(60):
+        r.integrate(0.008)
+        w.integrate(0.008, c.G, c.softening, True, 1)
+        a, b = r.state(), w.state()
+        assert len(a["temp"]) == len(b["temp"]), step
+        for k in a:
+            assert np.array_equal(a[k], b[k], equal_nan=True), (step, k)
+    assert r.physics.contactPairs.size == w.n_contacts and (r.visuals.flash, r.visuals.explosion) == (w.counters()["flash"], w.counters()["explosion"])
+
+
+@live
 def test_live_collision_scenario_bit_exact(oracle):
     """The page's second built-in scene, resetScenario('collision') (idx:760-763): two mass-100 bodies fall
     together and merge; 10,000 complete steps, page == oracle at every checkpoint."""
