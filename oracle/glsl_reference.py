@@ -1,4 +1,4 @@
-"""Runs the reference's OWN planet fragment shader text (GLSL ES, idx:99-202) without a graphics stack.
+"""Runs the reference's OWN planet shader text (GLSL ES: fragment idx:99-202, vertex idx:83-97) without a graphics stack.
 
 TEST INFRASTRUCTURE ONLY.  `/root/reference/index.html` is read at run time, the `planetFragmentShader` template
 string is sliced out, parsed by the GLSL-subset parser below (it reuses oracle/js_reference.py's tokenizer and
@@ -18,7 +18,8 @@ Parity against a real WebGL driver stays unpinned (no graphics stack exists here
 
 The subset is what idx:99-202 uses: uniform/varying declarations, function definitions (overloads must have identical
 bodies: mod289), `[const] type name = expr;`, assignment and `*=`, `return`, calls, constructors vec2/3/4, read
-swizzles, `+ - * /`, unary minus.  Anything else raises SyntaxError.
+swizzles, `+ - * /`, unary minus; for the vertex shader mat3/mat4 uniforms whose `*` is the matrix product (class Mat).
+Anything else raises SyntaxError.
 """
 from __future__ import annotations
 
@@ -27,7 +28,7 @@ import numpy as np
 from . import js_reference as jr
 
 F = np.float32
-_TYPES = ("float", "vec2", "vec3", "vec4", "void")
+_TYPES = ("float", "vec2", "vec3", "vec4", "mat3", "mat4", "void")
 
 
 class _Parser(jr.Parser):
@@ -71,14 +72,14 @@ class _Parser(jr.Parser):
             self.eat("=")
             e = self.expr()
             self.eat(";")
-            return ("set", name, e)
+            return ("set", name, e, True)
         name = self.eat(kind="id")
         op = self.eat()
         if op not in ("=", "*=", "+=", "-="):
             raise SyntaxError(f"glsl subset: unsupported statement at {name} {op}")
         e = self.expr()
         self.eat(";")
-        return ("set", name, e if op == "=" else ("bin", op[0], ("id", name), e))
+        return ("set", name, e if op == "=" else ("bin", op[0], ("id", name), e), False)
 
 
 def _emit(e) -> str:
@@ -107,8 +108,10 @@ def transliterate(glsl: str) -> str:
     out, seen = [], {}
     for name, params, body in funcs:
         lines = [f"    {s[1]} = {_emit(s[2])}" if s[0] == "set" else f"    return {_emit(s[1])}" for s in body]
-        if name == "main":
-            lines.insert(0, "    global gl_FragColor")
+        if name == "main":       # varyings and gl_* outputs: the names main() assigns without declaring
+            outs = sorted({st[1] for st in body if st[0] == "set" and not st[3]} - {st[1] for st in body if st[0] == "set" and st[3]})
+            if outs:
+                lines.insert(0, "    global " + ", ".join(outs))
         text = "\n".join(lines)
         if name in seen:
             if seen[name] != text:
@@ -176,6 +179,44 @@ def glsl_pow(x, y):
 
 _BUILTINS = {"F": F, "vec": vec, "swz": swz, "dot": dot, "step": step, "mix": mix, "clamp": clamp, "smoothstep": smoothstep,
              "normalize": normalize, "pow": glsl_pow, "floor": np.floor, "abs": np.abs, "min": np.minimum, "max": np.maximum}
+
+
+class Mat(np.ndarray):
+    """mat3 / mat4: `*` with a matrix or a vector is the linear-algebra product, as in GLSL (row-major storage here)."""
+
+    def __new__(cls, rows):
+        return np.asarray(rows, dtype=F).view(cls)
+
+    def __mul__(self, other):
+        o = np.asarray(other, dtype=F)
+        a = np.asarray(self)
+        if o.ndim == 0:
+            return Mat(a * o)
+        out = np.zeros(a.shape[0] if o.ndim == 1 else (a.shape[0], o.shape[1]), dtype=F)
+        for k in range(a.shape[1]):                      # products added left to right, one rounding each
+            out = (out + (a[:, k] * o[k] if o.ndim == 1 else np.outer(a[:, k], o[k]))).astype(F)
+        return Mat(out) if o.ndim == 2 else out
+
+
+class PlanetVertexShader:
+    """`planetVertexShader` of the page (idx:83-97), executable per vertex: the varyings the fragment shader receives."""
+
+    def __init__(self, html=jr.REFERENCE_HTML):
+        with open(html, encoding="utf-8") as f:
+            page = f.read()
+        a = page.index("const planetVertexShader = `") + len("const planetVertexShader = `")
+        self.glsl = page[a:page.index("`", a)]
+        self.python_source = transliterate(self.glsl)
+        self.ns = dict(_BUILTINS)
+        exec(compile(self.python_source, "<planetVertexShader idx:83-97 transliterated>", "exec"), self.ns)
+
+    def vertex(self, position, normal, modelMatrix, viewMatrix, projectionMatrix, normalMatrix, uv=(0.0, 0.0)):
+        ns = self.ns
+        ns.update(position=vec(3, *position), normal=vec(3, *normal), uv=vec(2, *uv), modelMatrix=Mat(modelMatrix), viewMatrix=Mat(viewMatrix),
+                  projectionMatrix=Mat(projectionMatrix), normalMatrix=Mat(normalMatrix))
+        with np.errstate(all="ignore"):
+            ns["main"]()
+        return {k: np.asarray(ns[k], dtype=F) for k in ("vNormal", "vPosition", "vViewPosition", "gl_Position")}
 
 
 class PlanetShader:

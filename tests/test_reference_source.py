@@ -349,6 +349,51 @@ def test_live_planet_shader_text_equals_restatement(oracle):
     assert all(("uniform %s;" % u) in " ".join(sh.glsl.split()) for u in ("vec3 color1", "vec3 color2", "float temperature", "float seed", "vec3 sunPosition"))
 
 
+@live
+def test_live_page_shader_pipeline_matches_oracle_render(oracle):
+    """planetVertexShader (idx:83-97) + planetFragmentShader executed from their text with three.js's matrices
+    (modelMatrix = T*S, viewMatrix = lookAt inverse, normalMatrix = inverse transpose of modelView) against the
+    pixels of oracle.render, which ray-casts the sphere instead of rasterising it.  The varyings then differ in
+    their last bits and the noise amplifies that, so the gate is statistical; the control shows what a wrong
+    convention costs (the page's vNormal is a VIEW-space normal lit by a WORLD-space light: the oracle keeps that)."""
+    from oracle import glsl_reference as gr
+    vs, fs, cfg = gr.PlanetVertexShader(), gr.PlanetShader(), jr.Reference().CONFIG
+    W, H, fov = 64, 36, 45.0
+    cam = np.array([0.0, 80.0, 150.0])                         # camera.position, idx:705; looking at the origin
+    z = cam / np.linalg.norm(cam)
+    x = np.cross([0.0, 1.0, 0.0], z)
+    x /= np.linalg.norm(x)
+    y = np.cross(z, x)
+    Rv = np.stack([x, y, z])
+    view = np.eye(4)
+    view[:3, :3], view[:3, 3] = Rv, -Rv @ cam
+    th, asp = np.tan(np.radians(fov) / 2), W / H
+    rng = np.random.default_rng(0)
+    good, control = [], []
+    for scene in range(6):
+        c, r = np.float32(rng.uniform(-15, 15, 3)).astype(np.float64), float(np.float32(rng.uniform(4, 12)))
+        ty, temp, seed = int(rng.integers(0, 3)), float(rng.choice([0, 30, 80])), float(np.float32(rng.uniform(0, 100)))
+        rgba, ids = oracle.render(np.array([[*c, 1.0]]), [r], [temp], [ty], [seed], W, H, camera=tuple(cam), target=(0.0, 0.0, 0.0), fov_deg=fov)
+        model = np.eye(4)
+        model[:3, :3] *= r
+        model[:3, 3] = c
+        ys, xs = np.nonzero(ids == 0)
+        m = cfg.materials[jr.TYPES[ty]]
+        for k in rng.choice(len(ys), size=min(25, len(ys)), replace=False):
+            px, py = xs[k], ys[k]
+            d = x * (((2 * (px + 0.5)) / W - 1) * th * asp) + y * ((1 - (2 * (py + 0.5)) / H) * th) - z
+            oc = cam - c
+            a, b, cc = d @ d, oc @ d, oc @ oc - r * r
+            n = (cam + ((-b - np.sqrt(b * b - a * cc)) / a) * d - c) / r            # the unit-sphere vertex under this pixel
+            for nmat, sink in ((Rv / r, good), (np.eye(3) / r, control)):
+                var = vs.vertex(n, n, model, view, np.eye(4), nmat)
+                col = fs.fragment(var["vPosition"], var["vNormal"], var["vViewPosition"], m.color1.rgb, m.color2.rgb, temp, seed)
+                sink.append(float(np.abs(col - rgba[py, px]).max()))
+    good, control = np.array(good), np.array(control)
+    assert len(good) >= 60 and np.median(good) < 2e-4 and np.percentile(good, 90) < 5e-3
+    assert np.median(control) > 100 * np.median(good)
+
+
 def test_glsl_subset_rejects_control_flow():
     from oracle import glsl_reference as gr
     assert "def f(x):" in gr.transliterate("float f(float x) { float y = x * 2.0; y *= x; return y - 1.0; }")
