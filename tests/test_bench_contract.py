@@ -1,0 +1,39 @@
+"""bench.py's reference arm (`--impl reference`) keeps the driver's JSON contract: one line, BASELINE.json's metric and
+unit, `impl`, a `cpu_baseline` describing the run and an `e2e` that repeats the value with zero copies; under torchrun
+only rank 0 works and prints, the other ranks exit 0 silently.  (The GPU arm needs a device: tests/test_gpu_*.py and the
+driver's own run cover it.)"""
+import json
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _run(env_extra, *args):
+    env = dict(os.environ, **env_extra)
+    return subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "2", "--warmup", "1",
+                           "--ref-sample", "1024", *args], capture_output=True, text=True, env=env, cwd=ROOT, timeout=300)
+
+
+def test_reference_arm_line():
+    r = _run({})
+    assert r.returncode == 0, r.stderr
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    base = json.load(open(os.path.join(ROOT, "BASELINE.json")))
+    assert d["impl"] == "reference" and d["higher_is_better"] is True and d["vs_baseline"] is None
+    assert d["unit"] == "G interactions/s" and "N=1M" in d["metric"] and "interactions/s" in base["metric"]
+    assert d["steps"] == 2 and d["warmup"] == 1 and d["n_gpus"] == 1 and d["value"] > 0 and d["ms_per_step"] > 0
+    assert d["config"]["n"] == 1048576 and d["config"]["sample_n"] == 1024 and "uniform_cube" in d["config"]["workload"]
+    cb = d["cpu_baseline"]
+    assert cb["kind"] == "port" and cb["cores"] == 1 and cb["value"] == d["value"] and "1024 bodies" in cb["sample"]
+    assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    # value = N(N-1) one-sided interactions per step / time
+    assert abs(d["value"] - 1024 * 1023 / (d["ms_per_step"] * 1e-3) * 1e-9) < 1e-9 * d["value"] + 1e-12
+
+
+def test_reference_arm_other_ranks_stay_silent():
+    r = _run({"RANK": "1", "WORLD_SIZE": "2", "LOCAL_RANK": "1"}, "--gpus", "2")
+    assert r.returncode == 0 and r.stdout.strip() == ""
