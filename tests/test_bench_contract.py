@@ -7,6 +7,8 @@ import os
 import subprocess
 import sys
 
+import pytest
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
@@ -37,3 +39,27 @@ def test_reference_arm_line():
 def test_reference_arm_other_ranks_stay_silent():
     r = _run({"RANK": "1", "WORLD_SIZE": "2", "LOCAL_RANK": "1"}, "--gpus", "2")
     assert r.returncode == 0 and r.stdout.strip() == ""
+
+
+@pytest.mark.gpu
+def test_gpu_arm_line_reduced_size():
+    """The product arm at a reduced body count (the default run is the driver's job): every key of the contract is there
+    and consistent -- value = n^2 / time, roofline achieved/peak/frac, e2e through host arrays with the bytes counted,
+    launches counted, clocks sampled, the CPU baseline labelled."""
+    n = 131072
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--bodies", str(n), "--steps", "3", "--warmup", "3", "--cpu-sample", "2048",
+                        "--cpu-steps", "1"], capture_output=True, text=True, cwd=ROOT, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip().startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["unit"] == "G interactions/s" and d["n_gpus"] == 1 and d["steps"] == 3 and d["warmup"] == 3 and d["dtype"] == "f32"
+    assert d["higher_is_better"] is True and d["vs_baseline"] is None and d["data"] == "synthetic" and "workload" in d["config"]
+    assert abs(d["value"] - n * n / (d["ms_per_step"] * 1e-3) * 1e-9) < 1e-6 * d["value"]
+    roof = d["roofline"]
+    assert abs(roof["frac"] - roof["achieved"] / roof["peak"]) < 1e-9 and 0.5 < roof["frac"] < 1.05 and roof["kernel_launches"] == 3
+    assert d["gpu_launches"] >= 2 * 3
+    e = d["e2e"]
+    assert e["h2d_bytes_per_step"] == e["d2h_bytes_per_step"] == 3 * n * 16 and 0 < e["value"] <= d["value"] * 1.02
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] == 1 and d["cpu_baseline"]["value"] > 0
+    assert set(d["clocks"]) >= {"sm_mhz", "sm_max_mhz", "reasons"}
