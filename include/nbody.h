@@ -269,6 +269,11 @@ typedef struct {
                             mass multiply.  1+k: all but k (<= 64) bodies share one mass; same kernel, k corrections per body */
     int f64_symmetric;   /* fp64, one GPU: > 0 when the force pass evaluates every pair once and applies it to both bodies,
                             as the reference's i<j loop does (idx:272-288); the value is the j-blocks per CTA.  0: one-sided */
+    int f32_symmetric;   /* fp32: > 0 when force passes (softening > 0, no radii set) evaluate every pair once and apply it to both
+                            bodies through exact fixed-point accumulators (force_f32_sym.cuh); the value is the position tiles
+                            (512 bodies) per work unit.  0: the one-sided sweep */
+    int f32_sym_bodies_per_thread; /* i-bodies per thread of that pass (4 or 8), 0 when it is off */
+    int f32_sym_last_pass;         /* 1 when the last force pass actually was the pairs-once one (softening == 0 and set radii take the sweep) */
 } nbody_info;
 NBODY_API int nbody_get_info(nbody_ctx* ctx, nbody_info* out);
 

@@ -44,6 +44,8 @@ class Info(ctypes.Structure):
         ("rank", ctypes.c_int), ("sm_count", ctypes.c_int), ("j_chunks", ctypes.c_int),
         ("i_tile", ctypes.c_int), ("kernel_launches", ctypes.c_longlong), ("exchange", ctypes.c_int),
         ("uniform_mass", ctypes.c_int), ("f64_symmetric", ctypes.c_int),
+        ("f32_symmetric", ctypes.c_int), ("f32_sym_bodies_per_thread", ctypes.c_int),
+        ("f32_sym_last_pass", ctypes.c_int),
     ]
 
 

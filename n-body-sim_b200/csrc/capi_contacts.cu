@@ -224,7 +224,10 @@ int all_contacts(nbody_ctx* c, double margin, bool use_flags, std::vector<unsign
             c->cstat[0] += n_cand[k] + c->shards[k].n_big;
         }
         // F^2 tests among the candidates against F*N/2 of candidates x everybody (contacts.cuh)
-        compact = flagged > 0 && 2 * flagged < c->n && env_int("NBODY_CONTACTS_COMPACT", 1) != 0;
+        // One process per GPU: this rank knows only its OWN candidates, and a pair whose partner another rank flagged would be
+        // found by nobody; candidates x everybody is complete for the own bodies, so the union over ranks stays the whole set.
+        const bool all_candidates_here = !(c->rank_mode && c->world > 1);
+        compact = all_candidates_here && flagged > 0 && 2 * flagged < c->n && env_int("NBODY_CONTACTS_COMPACT", 1) != 0;
         if (compact) {
             int rc = build_candidate_records(c, n_cand, offsets, &total);
             if (rc != NBODY_OK) return rc;

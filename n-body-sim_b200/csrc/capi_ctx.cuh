@@ -28,6 +28,8 @@ struct Shard {
     int rank = 0;
     cudaStream_t own_stream = nullptr;
     cudaStream_t stream = nullptr;
+    void* arena = nullptr;              // the one allocation peers map: pos[0] | pos[1] | accfix | flags, sym_ctl
+    size_t arena_bytes = 0, off_pos1 = 0, off_acc = 0, off_flags = 0;
     void* pos[2] = {nullptr, nullptr};  // full padded pos_mass, double-buffered
     void* vel = nullptr;                // local range
     void* acc = nullptr;
@@ -67,6 +69,14 @@ struct Shard {
     // headless renderer (render.cu), first shard only
     int* mat_type = nullptr;            // Body.type per body (0 rock, 1 metal, 2 ice)
     float* mat_seed = nullptr;          // the `seed` uniform of each body's material (idx:492)
+    // fp32 pairs-once pass (force_f32_sym.cuh)
+    unsigned long long* accfix = nullptr;  // [3][cap_pad] fixed-point acceleration sums of ALL bodies, slot order
+    unsigned* sym_ctl = nullptr;           // the unit counter of the persistent CTAs; cleared before every launch
+    void* sym_units = nullptr;             // the unit table (SymUnit), the same on every device
+    size_t sym_units_cap = 0;
+    double* mass_sums = nullptr;           // per-block sums of |m| from pack_pos_kernel (the bound behind the fixed-point scale)
+    void* peer_acc[kMaxPeers] = {};        // every rank's accfix / sym_ctl as mapped on this device
+    void* peer_ctl[kMaxPeers] = {};
     MassOutlier* outliers = nullptr;    // fp32: bodies whose mass differs from the common one (force_f32.cuh)
     unsigned* outlier_count = nullptr;  // how many pack_pos_kernel found
     void* temp_full = nullptr;          // all temperatures gathered on this device (multi-GPU contexts)
@@ -110,6 +120,18 @@ struct nbody_ctx {
     int f64_sym_r = 4;              // i-bodies per thread of that pass (fewer for small systems)
     int f64_sym_k = 0;              // j-blocks per CTA of that pass for the current upload; 0: the one-sided kernel
     int f64_R_forced = 0;          // NBODY_F64_R at create: 1 or 2 i-bodies per thread in the fp64 kernel, 0 = by body count
+    // fp32 pairs-once pass (force_f32_sym.cuh)
+    bool sym32_allowed = false;     // NBODY_F32_SYM at create (default on): fp32, softening > 0, no nearest-neighbour tracking
+    int sym32_R = 4;                // i-bodies per thread for the current upload: 8 with equal masses, 4 with general ones
+    int sym32_R_forced = 0;         // NBODY_F32_SYM_R at create: 4 or 8 whatever the masses
+    size_t sym32_min_n = 0;         // smallest system that takes it (NBODY_F32_SYM_MIN)
+    int sym32_run = 0;              // position tiles per unit for the current upload; 0: no table (one-sided sweep)
+    size_t sym32_table_n = 0;       // the body count / R / run the device table was built for
+    int sym32_table_R = 0, sym32_table_run = 0;
+    std::vector<unsigned> sym32_split;  // unit ranges of the ranks: rank r takes [split[r], split[r+1])
+    double sum_abs_mass = 0.0;      // of the current upload (the equal-mass sweep counts every body as 1)
+    int sym32_slots[2] = {0, 0};    // resident CTAs per device of the general / equal-mass kernel (grid size of the persistent launch)
+    bool sym32_used = false;        // the last force pass was the pairs-once one
     size_t medium_max_n = 0;        // largest system that kernel takes (fp32 5,120, fp64 4,096; NBODY_MEDIUM_MAX lowers it)
     int medium_ctas = 0;            // > 0: systems of up to medium_max_n bodies run all steps of a call in one cooperative launch
                                     // of this many CTAs (medium.cuh; NBODY_MEDIUM at create, one GPU, needs cooperative launch)

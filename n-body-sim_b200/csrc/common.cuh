@@ -1,11 +1,16 @@
 // Shared definitions of the device-side state layout and kernel parameters.
 //
 // HBM layout (DESIGN.md "Data layout"):
-//   fp32  pos_mass: PAIR-INTERLEAVED.  Bodies 2p and 2p+1 share 32 bytes:
-//           float4 A_p = (x0, x1, y0, y1), float4 B_p = (z0, z1, m0, m1)
-//         so that a j-tile lands in shared memory by one bulk copy and one
-//         LDS.128 yields two aligned 64-bit register pairs that feed the packed
-//         FADD2/FFMA2/FMUL2 pipe directly (two j-bodies per instruction).
+//   fp32  pos_mass: TILE-SoA.  Tile t = bodies [512 t, 512 t + 512) is 8 KiB: four planes
+//         x[512] y[512] z[512] m[512], so that a j-tile lands in shared memory by ONE
+//         bulk copy (the equal-mass kernels skip the mass plane: 6 KiB).  Inside a plane
+//         every group of 64 bodies is stored as 32 adjacent couples (b, b + 32):
+//           slot(o) = (o & ~63) | ((o & 31) << 1) | ((o >> 5) & 1),   o = body & 511
+//         Any two adjacent floats are two j-bodies of one aligned 64-bit register pair
+//         for the packed FADD2/FFMA2/FMUL2 pipe (one broadcast LDS.128 per plane = two
+//         couples, force_f32.cuh), and in the pairs-once kernel (force_f32_sym.cuh) lane l
+//         of a warp fetches the couple (l + q) & 31 of a group with one conflict-free
+//         LDS.64 per plane while the couple's sums rotate through the warp.
 //   fp64  pos_mass: double4 (x, y, z, m) per body.
 //   vel, acc: Real4 per body (x, y, z, unused), indexed from the shard's i_begin.
 //   partial : Real4 [j_chunks][local bodies]; per-chunk acceleration sums.
@@ -57,9 +62,13 @@ template <> struct Vec4<double> { using type = double4; };
 
 // Scalar element index of component c (0=x,1=y,2=z,3=m) of body i in pos_mass.
 template <typename Real> __host__ __device__ __forceinline__ size_t pm_index(size_t i, int c);
+constexpr int kPosTile = 512;  // bodies per fp32 position tile (4 planes of kPosTile floats)
+// slot of body o (0..511) inside a plane of its tile, and back
+__host__ __device__ __forceinline__ unsigned tile_slot(unsigned o) { return (o & ~63u) | ((o & 31u) << 1) | ((o >> 5) & 1u); }
+__host__ __device__ __forceinline__ unsigned tile_body(unsigned s) { return (s & ~63u) | ((s & 1u) << 5) | ((s >> 1) & 31u); }
 template <> __host__ __device__ __forceinline__ size_t pm_index<float>(size_t i, int c)
 {
-    return 8 * (i >> 1) + 2 * c + (i & 1);
+    return (i >> 9) * size_t(4 * kPosTile) + size_t(c) * kPosTile + tile_slot(unsigned(i) & 511u);
 }
 template <> __host__ __device__ __forceinline__ size_t pm_index<double>(size_t i, int c)
 {

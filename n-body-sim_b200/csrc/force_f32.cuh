@@ -1,13 +1,16 @@
-// fp32 all-pairs force kernel for sm_100a, fused with the kick/drift integrator.
+// fp32 all-pairs force kernel (one-sided sweep) for sm_100a, fused with the kick/drift integrator.
+// Since round 2 the large systems run on the pairs-once kernel (force_f32_sym.cuh); this sweep serves
+// softening == 0, contexts with radii (nearest-neighbour tracking for the contact stage), mid-size
+// systems, multi-GPU contexts without peer access -- and the diagonal blocks of the pairs-once kernel.
 // Replaces PhysicsSystem.computeGravity (/root/reference/index.html:264-291) and
 // the two O(N) loops of integrate (idx:250-253, 258-261).
 //
 // Work unit = one CTA = (i-tile of kF32Threads*R bodies) x (j-chunk).  i-bodies live
 // in registers; the j-chunk streams through a kF32Stages-deep shared-memory ring of
-// FULL 8 KiB tiles (256 j-pairs) filled by 1-D bulk copies (TMA, UBLKCP) issued by a
-// dedicated producer warp and tracked with full/empty mbarriers.  Because pos_mass is
-// pair-interleaved in HBM, one broadcast LDS.128 pair delivers two j-bodies as aligned
-// 64-bit register pairs, and each interaction PAIR costs
+// FULL 8 KiB tiles (512 bodies) filled by 1-D bulk copies (TMA, UBLKCP) issued by a
+// dedicated producer warp and tracked with full/empty mbarriers.  pos_mass is tile-SoA in
+// HBM with couples of bodies adjacent (common.cuh), so one broadcast LDS.128 per plane
+// delivers four j-bodies as aligned 64-bit register pairs, and each interaction PAIR costs
 //     3 FADD2 + 3 FFMA2 + 2 MUFU.RSQ + 3 FMUL2 + 3 FFMA2
 // = 12 packed FP32 instructions + 2 MUFU for two interactions: the 12 FP32-lane-ops
 // per interaction of the roofline in 7 issue slots instead of 13.
@@ -66,6 +69,15 @@ __device__ __forceinline__ float rsqrt_approx(float x)
 #ifndef NB_F32_UNROLL
 #define NB_F32_UNROLL 16
 #endif
+#ifndef NB_F32_LOOP_FORM
+#define NB_F32_LOOP_FORM 0  // how consume_tile states its shared-memory loads (0: LDS.128 per plane and quad, re-stated per i-body; 1: hoisted; 2: LDS.64 per couple)
+#endif
+#ifndef NB_F32_MIN_CTAS
+#define NB_F32_MIN_CTAS 1   // __launch_bounds__ second argument of force_f32_kernel: general masses ...
+#endif
+#ifndef NB_F32_MIN_CTAS_UNIFORM
+#define NB_F32_MIN_CTAS_UNIFORM 1  // ... and the equal-mass instances
+#endif
 constexpr int kF32Unroll = NB_F32_UNROLL;  // j-pairs per inner-loop iteration
 // TP = j-PAIRS per ring stage: kF32TilePairs (512 bodies, 8 KiB) for large systems, kF32SmallTilePairs (128 bodies,
 // 2 KiB) for systems of up to 4,096 bodies, where a CTA's 512 x 512 interactions are a ~20 us dependent chain whatever
@@ -93,49 +105,95 @@ template <int TP = kF32TilePairs> constexpr size_t force_f32_smem_bytes() { retu
 // interactions/s against 2,651 for the general kernel (+6.7 %); unroll 16 (166 registers,
 // 2 CTAs/SM) beats unroll 8 (2,809), 32 (2,741) and 4 (2,724); profiles/r1d_uniform_variants.txt.
 template <int R, bool ZERO_SOFT, int U, bool NEAR, bool DIAG, bool UNIFORM, int TP>
-__device__ __forceinline__ void consume_tile(const float4* __restrict__ tp, const f32x2 (&nx)[R], const f32x2 (&ny)[R],
+__device__ __forceinline__ void consume_tile(const float* __restrict__ tp, const f32x2 (&nx)[R], const f32x2 (&ny)[R],
                                              const f32x2 (&nz)[R], f32x2 (&ax)[R], f32x2 (&ay)[R], f32x2 (&az)[R],
                                              float (&nr)[R], const f32x2 eps2, const int self0)
 {
-#pragma unroll U
-    for (int q = 0; q < TP; ++q) {
+    // the stage holds 2 TP bodies as four planes x | y | z | m of 2 TP floats (common.cuh: tile-SoA); one broadcast
+    // LDS.128 per plane delivers two couples = four j-bodies
+    constexpr int kPlane = 2 * TP;
+    int sslot[R];
+    if (NEAR && DIAG) {
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            // (the loads are re-stated per i-body and merged by the compiler: this form
-            // schedules best, see force_lab)
-            const float4 A = tp[2 * q];      // x0 x1 y0 y1
-            const float4 B = tp[2 * q + 1];  // z0 z1 m0 m1
-            const f32x2 jx = pack2(A.x, A.y), jy = pack2(A.z, A.w);
-            const f32x2 jz = pack2(B.x, B.y), jm = pack2(B.z, B.w);
-            const f32x2 dx = add2(jx, nx[r]);
-            const f32x2 dy = add2(jy, ny[r]);
-            const f32x2 dz = add2(jz, nz[r]);
-            f32x2 r2 = fma2(dx, dx, eps2);
-            r2 = fma2(dy, dy, r2);
-            r2 = fma2(dz, dz, r2);
-            float r2a, r2b;
-            unpack2(r2, r2a, r2b);
-            if (ZERO_SOFT) {
-                r2a = fmaxf(r2a, 1e-20f);
-                r2b = fmaxf(r2b, 1e-20f);
-            }
-            const float ia = rsqrt_approx(r2a), ib = rsqrt_approx(r2b);
-            if (NEAR) {
-                float ma = ia, mb = ib;
-                if (DIAG) {
-                    const int s = self0 + r * kF32Threads;  // this body's index inside the tile (outside [0, 2 TP): not in it)
-                    ma = (2 * q == s) ? 0.f : ia;
-                    mb = (2 * q + 1 == s) ? 0.f : ib;
+            const int sb = self0 + r * kF32Threads;  // this body's index inside the stage (outside [0, 2 TP): not in it)
+            sslot[r] = (sb >= 0 && sb < kPlane) ? int(tile_slot(unsigned(sb))) : -1;
+        }
+    }
+    constexpr int kU4 = U / 2 > 0 ? U / 2 : 1;  // U j-pairs per iteration = U / 2 quads
+#pragma unroll kU4
+    for (int q4 = 0; q4 < TP / 2; ++q4) {
+#if NB_F32_LOOP_FORM == 1
+        const float4 X = reinterpret_cast<const float4*>(tp)[q4];
+        const float4 Y = reinterpret_cast<const float4*>(tp + kPlane)[q4];
+        const float4 Z = reinterpret_cast<const float4*>(tp + 2 * kPlane)[q4];
+        float4 M = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (!UNIFORM) M = reinterpret_cast<const float4*>(tp + 3 * kPlane)[q4];
+#endif
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+#if NB_F32_LOOP_FORM == 2
+            const float2 X2 = reinterpret_cast<const float2*>(tp)[2 * q4 + h];
+            const float2 Y2 = reinterpret_cast<const float2*>(tp + kPlane)[2 * q4 + h];
+            const float2 Z2 = reinterpret_cast<const float2*>(tp + 2 * kPlane)[2 * q4 + h];
+            float2 M2 = make_float2(0.f, 0.f);
+            if (!UNIFORM) M2 = reinterpret_cast<const float2*>(tp + 3 * kPlane)[2 * q4 + h];
+#endif
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+#if NB_F32_LOOP_FORM == 0
+                // (the loads are re-stated per i-body and merged by the compiler)
+                const float4 X = reinterpret_cast<const float4*>(tp)[q4];
+                const float4 Y = reinterpret_cast<const float4*>(tp + kPlane)[q4];
+                const float4 Z = reinterpret_cast<const float4*>(tp + 2 * kPlane)[q4];
+#endif
+#if NB_F32_LOOP_FORM == 2
+                const f32x2 jx = pack2(X2.x, X2.y), jy = pack2(Y2.x, Y2.y), jz = pack2(Z2.x, Z2.y);
+#else
+                const f32x2 jx = h ? pack2(X.z, X.w) : pack2(X.x, X.y);
+                const f32x2 jy = h ? pack2(Y.z, Y.w) : pack2(Y.x, Y.y);
+                const f32x2 jz = h ? pack2(Z.z, Z.w) : pack2(Z.x, Z.y);
+#endif
+                const f32x2 dx = add2(jx, nx[r]);
+                const f32x2 dy = add2(jy, ny[r]);
+                const f32x2 dz = add2(jz, nz[r]);
+                f32x2 r2 = fma2(dx, dx, eps2);
+                r2 = fma2(dy, dy, r2);
+                r2 = fma2(dz, dz, r2);
+                float r2a, r2b;
+                unpack2(r2, r2a, r2b);
+                if (ZERO_SOFT) {
+                    r2a = fmaxf(r2a, 1e-20f);
+                    r2b = fmaxf(r2b, 1e-20f);
                 }
-                nr[r] = fmaxf(nr[r], fmaxf(ma, mb));
+                const float ia = rsqrt_approx(r2a), ib = rsqrt_approx(r2b);
+                if (NEAR) {
+                    float ma = ia, mb = ib;
+                    if (DIAG) {
+                        const int s0 = 4 * q4 + 2 * h;  // slot of this couple's first body
+                        ma = (s0 == sslot[r]) ? 0.f : ia;
+                        mb = (s0 + 1 == sslot[r]) ? 0.f : ib;
+                    }
+                    nr[r] = fmaxf(nr[r], fmaxf(ma, mb));
+                }
+                const f32x2 inv = pack2(ia, ib);
+                const f32x2 inv2 = mul2(inv, inv);
+                f32x2 mi = inv;
+                if (!UNIFORM) {
+#if NB_F32_LOOP_FORM == 0
+                    const float4 M = reinterpret_cast<const float4*>(tp + 3 * kPlane)[q4];
+#endif
+#if NB_F32_LOOP_FORM == 2
+                    mi = mul2(pack2(M2.x, M2.y), inv);
+#else
+                    mi = mul2(h ? pack2(M.z, M.w) : pack2(M.x, M.y), inv);
+#endif
+                }
+                const f32x2 s = mul2(mi, inv2);  // m_j / (r^2+eps^2)^1.5   (UNIFORM: 1 / ...)
+                ax[r] = fma2(s, dx, ax[r]);
+                ay[r] = fma2(s, dy, ay[r]);
+                az[r] = fma2(s, dz, az[r]);
             }
-            const f32x2 inv = pack2(ia, ib);
-            const f32x2 inv2 = mul2(inv, inv);
-            const f32x2 mi = UNIFORM ? inv : mul2(jm, inv);
-            const f32x2 s = mul2(mi, inv2);  // m_j / (r^2+eps^2)^1.5   (UNIFORM: 1 / ...)
-            ax[r] = fma2(s, dx, ax[r]);
-            ay[r] = fma2(s, dy, ay[r]);
-            az[r] = fma2(s, dz, az[r]);
         }
     }
 }
@@ -189,7 +247,8 @@ __device__ __forceinline__ void force_f32_body(const ForceParams<float>& p)
     const size_t j0 = size_t(chunk) * p.chunk_len;
     const size_t j1 = (j0 + p.chunk_len < p.n_j) ? j0 + p.chunk_len : p.n_j;
     const int ntiles = static_cast<int>((j1 - j0) / kTileBodies);
-    const unsigned char* src = reinterpret_cast<const unsigned char*>(p.pos_cur) + j0 * 16;
+    // the equal-mass sweep never reads the mass plane: three planes per stage
+    constexpr int kPlanes = UNIFORM ? 3 : 4;
 
     if (tid == 0) {
         for (int s = 0; s < kF32Stages; ++s) {
@@ -206,8 +265,15 @@ __device__ __forceinline__ void force_f32_body(const ForceParams<float>& p)
                 const int slot = t % kF32Stages;
                 const int k = t / kF32Stages;
                 if (k > 0) mbar_wait(&empty[slot], (k - 1) & 1);
-                mbar_expect_tx(&full[slot], kF32TileBytes);
-                bulk_g2s(smem_raw + size_t(slot) * kF32TileBytes, src + size_t(t) * kF32TileBytes, kF32TileBytes, &full[slot]);
+                const size_t jb = j0 + size_t(t) * kTileBodies;  // first body of the stage
+                const float* src = p.pos_cur + (jb >> 9) * size_t(4 * kPosTile) + (jb & 511);
+                unsigned char* dst = smem_raw + size_t(slot) * kF32TileBytes;
+                mbar_expect_tx(&full[slot], kPlanes * kTileBodies * 4);
+                if (kTileBodies == kPosTile) {  // a whole tile: its planes are contiguous
+                    bulk_g2s(dst, src, kPlanes * kTileBodies * 4, &full[slot]);
+                } else {
+                    for (int c = 0; c < kPlanes; ++c) bulk_g2s(dst + c * kTileBodies * 4, src + c * kPosTile, kTileBodies * 4, &full[slot]);
+                }
             }
         }
         return;
@@ -238,7 +304,7 @@ __device__ __forceinline__ void force_f32_body(const ForceParams<float>& p)
     for (int t = 0; t < ntiles; ++t) {
         const int slot = t % kF32Stages;
         mbar_wait(&full[slot], (t / kF32Stages) & 1);
-        const float4* tp = reinterpret_cast<const float4*>(smem_raw + size_t(slot) * kF32TileBytes);
+        const float* tp = reinterpret_cast<const float*>(smem_raw + size_t(slot) * kF32TileBytes);
         const long long off = i0 - (static_cast<long long>(j0) + static_cast<long long>(t) * kTileBodies);  // first own body, relative to the tile
         if (NEAR && off > -static_cast<long long>(kF32Threads * R) && off < kTileBodies)
             consume_tile<R, ZERO_SOFT, U, NEAR, true, UNIFORM, TP>(tp, nx, ny, nz, ax, ay, az, nr, eps2, static_cast<int>(off) + tid);
@@ -307,7 +373,7 @@ __device__ __forceinline__ void force_f32_body(const ForceParams<float>& p)
 }
 
 template <int R, bool ZERO_SOFT, int U = kF32Unroll, bool UNIFORM = false, int TP = kF32TilePairs>
-__global__ void __launch_bounds__(kF32Threads + 32) force_f32_kernel(const ForceParams<float> p)
+__global__ void __launch_bounds__(kF32Threads + 32, UNIFORM ? NB_F32_MIN_CTAS_UNIFORM : NB_F32_MIN_CTAS) force_f32_kernel(const ForceParams<float> p)
 {
     force_f32_body<R, ZERO_SOFT, U, false, UNIFORM, TP>(p);
 }

@@ -63,22 +63,38 @@ __global__ void kick2_kernel(Real* vel, const Real* acc, Real* temp, size_t n_lo
 // detect != nullptr (fp32): also find the bodies whose mass is not `m0` -- detect[0] counts them
 // (a non-finite mass pushes the count past any limit) and the first kMaxOutliers found are
 // appended to `outliers` in no particular order; the host sorts them (nbody_upload).
+// mass_sums != nullptr: block b also leaves sum |m| of its 256 bodies in mass_sums[b], added in a fixed order (the host
+// adds the blocks in index order): the bound behind the fixed-point scale of the pairs-once pass (force_f32_sym.cuh)
+// must be the same number on every rank and in every run.
 template <typename Real>
 __global__ void pack_pos_kernel(const Real* aos, Real* pos_a, Real* pos_b, size_t n, size_t n_pad, Real pad_x, Real m0,
-                                unsigned* detect, MassOutlier* outliers)
+                                unsigned* detect, MassOutlier* outliers, double* mass_sums = nullptr)
 {
     const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (i >= n_pad) return;
+    double am = 0.0;
+    if (i < n_pad) {
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
-        const Real v = i < n ? aos[4 * i + c] : (c == 0 ? (sizeof(Real) == 8 ? pad_x * Real(1 + (i - n)) : pad_x) : Real(0));
-        pos_a[pm_index<Real>(i, c)] = v;
-        pos_b[pm_index<Real>(i, c)] = v;  // mass is constant: both buffers carry it
-        if (c == 3 && detect != nullptr && i < n && !(v == m0)) {
-            const bool finite = v - v == Real(0);
-            const unsigned k = atomicAdd(detect, finite ? 1u : unsigned(kMaxOutliers) + 1u);
-            if (finite && k < unsigned(kMaxOutliers)) outliers[k] = MassOutlier{unsigned(i), float(v - m0)};
+        for (int c = 0; c < 4; ++c) {
+            const Real v = i < n ? aos[4 * i + c] : (c == 0 ? (sizeof(Real) == 8 ? pad_x * Real(1 + (i - n)) : pad_x) : Real(0));
+            pos_a[pm_index<Real>(i, c)] = v;
+            pos_b[pm_index<Real>(i, c)] = v;  // mass is constant: both buffers carry it
+            if (c == 3) am = fabs(double(v));
+            if (c == 3 && detect != nullptr && i < n && !(v == m0)) {
+                const bool finite = v - v == Real(0);
+                const unsigned k = atomicAdd(detect, finite ? 1u : unsigned(kMaxOutliers) + 1u);
+                if (finite && k < unsigned(kMaxOutliers)) outliers[k] = MassOutlier{unsigned(i), float(v - m0)};
+            }
         }
+    }
+    if (mass_sums == nullptr) return;  // (uniform over the grid)
+    __shared__ double wsum[8];
+    for (int o = 16; o > 0; o >>= 1) am += __shfl_xor_sync(0xffffffffu, am, o);
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = am;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < int(blockDim.x >> 5); ++w) t += wsum[w];
+        mass_sums[blockIdx.x] = t;
     }
 }
 

@@ -8,6 +8,7 @@
 
 #include "exchange.cuh"
 #include "force_f32.cuh"
+#include "force_f32_sym.cuh"
 #include "force_f64.cuh"
 #include "force_f64_sym.cuh"
 #include "integrate.cuh"
@@ -19,6 +20,11 @@
 #define NB_UNIFORM_UNROLL 16
 #endif
 constexpr int kUniUnroll = NB_UNIFORM_UNROLL;  // inner-loop unroll of the equal-mass force kernel
+// i-bodies per thread of the pairs-once fp32 pass.  Measured at N=1M (profiles/r2a_sym_lab.jsonl): equal masses 4,057 G
+// interactions/s with 8 (168 registers, 2 CTAs/SM) against 3,805 with 4; general masses 3,334 with 8 (the eight extra mass
+// registers spill) against 3,370 with 4 (128 registers, 3 CTAs/SM).
+constexpr int kSym32EqualMassR = 8, kSym32GeneralR = 4;
+constexpr int kSym32DefaultMinN = 32768;            // smallest system that takes it (below: too few units for the SMs)
 
 namespace {
 
@@ -96,9 +102,11 @@ int f64_bodies_per_thread(const nbody_ctx* c, size_t n)
 }
 
 // n is padded to whole i-tiles per shard AND to whole j units: lcm(i_tile * world, j_unit)
+// (fp32: the i-tile of the pairs-once pass when that is the larger one)
 size_t pad_unit(const nbody_ctx* c)
 {
-    const size_t a = size_t(c->i_tile) * size_t(c->world);
+    const size_t tile = c->prec == NBODY_F32 && c->sym32_allowed ? std::max(c->i_tile, kF32Threads * 8) : c->i_tile;
+    const size_t a = tile * size_t(c->world);
     return a / gcd_sz(a, size_t(c->j_unit)) * size_t(c->j_unit);
 }
 
@@ -137,23 +145,40 @@ int alloc_shard(nbody_ctx* c, Shard& s)
     s.stream = s.own_stream;
     const size_t local_cap = c->cap_pad / c->world;
     const size_t v4 = 4 * c->esz;
-    CU(c, cudaMalloc(&s.pos[0], c->cap_pad * v4));
-    CU(c, cudaMalloc(&s.pos[1], c->cap_pad * v4));
+    // everything a peer maps lives in ONE allocation (one CUDA IPC handle in rank mode): the two position buffers, the
+    // fixed-point accumulators of the fp32 pairs-once pass (force_f32_sym.cuh), the exchange flags and that pass's control words
+    {
+        const size_t pos_bytes = round_up(c->cap_pad * v4, 256);
+        const size_t acc_bytes = c->prec == NBODY_F32 ? round_up((3 * c->cap_pad + 1) * sizeof(unsigned long long), 256) : 0;
+        const size_t flag_bytes = 256;  // kMaxPeers epoch flags, then 2 control words
+        s.arena_bytes = 2 * pos_bytes + acc_bytes + flag_bytes;
+        CU(c, cudaMalloc(&s.arena, s.arena_bytes));
+        CU(c, cudaMemset(s.arena, 0, s.arena_bytes));
+        s.off_pos1 = pos_bytes;
+        s.off_acc = 2 * pos_bytes;
+        s.off_flags = 2 * pos_bytes + acc_bytes;
+        char* base = static_cast<char*>(s.arena);
+        s.pos[0] = base;
+        s.pos[1] = base + s.off_pos1;
+        s.accfix = acc_bytes ? reinterpret_cast<unsigned long long*>(base + s.off_acc) : nullptr;
+        s.flags = reinterpret_cast<unsigned long long*>(base + s.off_flags);
+        s.sym_ctl = reinterpret_cast<unsigned*>(s.flags + kMaxPeers);
+    }
     CU(c, cudaMalloc(&s.stage, c->cap_pad * v4));
     CU(c, cudaMalloc(&s.vel, local_cap * v4));
     CU(c, cudaMalloc(&s.acc, local_cap * v4));
     CU(c, cudaMalloc(&s.temp, local_cap * c->esz));
-    const size_t ntiles = local_cap / c->i_tile + 1;
+    // (an fp64 upload re-picks its i-tile per body count: size for the smallest one, kThreads)
+    const size_t ntiles = local_cap / size_t(c->prec == NBODY_F64 ? kThreads : c->i_tile) + 1;
     CU(c, cudaMalloc(&s.counters, ntiles * sizeof(unsigned)));
     CU(c, cudaMemset(s.counters, 0, ntiles * sizeof(unsigned)));
-    CU(c, cudaMalloc(&s.flags, kMaxPeers * sizeof(unsigned long long)));
-    CU(c, cudaMemset(s.flags, 0, kMaxPeers * sizeof(unsigned long long)));
     CU(c, cudaMalloc(&s.medium_arrivals, sizeof(unsigned)));
     CU(c, cudaMalloc(&s.xerr, sizeof(unsigned)));
     CU(c, cudaMemset(s.xerr, 0, sizeof(unsigned)));
     s.energy_rows = (local_cap + kEnergyThreads - 1) / kEnergyThreads + 1;
     CU(c, cudaMalloc(&s.energy_out, s.energy_rows * 5 * sizeof(double)));
     CU(c, cudaMalloc(&s.radius, c->cap_pad * c->esz));
+    if (c->prec == NBODY_F32) CU(c, cudaMalloc(&s.mass_sums, (c->cap_pad / 256 + 1) * sizeof(double)));
     CU(c, cudaMalloc(&s.outliers, kMaxOutliers * sizeof(MassOutlier)));
     CU(c, cudaMalloc(&s.outlier_count, sizeof(unsigned)));
     CU(c, cudaMalloc(&s.near, local_cap * sizeof(float)));
@@ -263,6 +288,10 @@ int create_common(nbody_ctx** out, nbody_prec prec, int world, size_t capacity, 
         c->R = env_int("NBODY_R", 4);
         if (c->R != 2 && c->R != 4) c->R = 4;
         c->i_tile = kF32Threads * c->R;
+        // pairs-once pass (force_f32_sym.cuh): the default for systems of sym32_min_n bodies and more
+        c->sym32_allowed = env_int("NBODY_F32_SYM", 1) != 0 && c->R == 4;
+        c->sym32_R_forced = env_int("NBODY_F32_SYM_R", 0);  // 4 or 8; otherwise by kernel variant (build_sym32_table)
+        c->sym32_min_n = size_t(std::max(env_int("NBODY_F32_SYM_MIN", kSym32DefaultMinN), 1));
     } else {
         c->f64_math = env_int("NBODY_F64_MATH", 2);
         c->f64_R_forced = env_int("NBODY_F64_R", 0);
@@ -325,11 +354,9 @@ extern "C" void nbody_destroy(nbody_ctx* c)
         if (s.comm && nccl().ok()) nccl().CommDestroy(s.comm);
         for (cudaEvent_t e : s.ev) cudaEventDestroy(e);
         for (void* m : s.ipc_opened) cudaIpcCloseMemHandle(m);
-        cudaFree(s.flags);
+        cudaFree(s.arena);  // pos[0], pos[1], accfix, flags, sym_ctl
         cudaFree(s.xerr);
         cudaFree(s.medium_arrivals);
-        cudaFree(s.pos[0]);
-        cudaFree(s.pos[1]);
         cudaFree(s.stage);
         cudaFree(s.io_dev);
         if (s.io_host) cudaFreeHost(s.io_host);
@@ -359,6 +386,8 @@ extern "C" void nbody_destroy(nbody_ctx* c)
         cudaFree(s.mat_seed);
         cudaFree(s.outliers);
         cudaFree(s.outlier_count);
+        cudaFree(s.sym_units);
+        cudaFree(s.mass_sums);
         cudaFree(s.temp_full);
         render_scratch_free(s.render_scratch);
         cudaFree(s.image);
@@ -407,13 +436,15 @@ static int setup_peer_exchange(nbody_ctx* c)
                 a.peer_pos[b.rank][0] = b.pos[0];
                 a.peer_pos[b.rank][1] = b.pos[1];
                 a.peer_flags.flags[b.rank] = b.flags;
+                a.peer_acc[b.rank] = b.accfix;
+                a.peer_ctl[b.rank] = b.sym_ctl;
             }
         }
         c->p2p = true;
         return NBODY_OK;
     }
     struct Blob {
-        cudaIpcMemHandle_t pos0, pos1, flags;
+        cudaIpcMemHandle_t arena;
         int ok;
     };
     Shard& s = c->shards[0];
@@ -421,8 +452,7 @@ static int setup_peer_exchange(nbody_ctx* c)
     std::vector<Blob> all(c->world);
     Blob mine;
     memset(&mine, 0, sizeof mine);
-    mine.ok = cudaIpcGetMemHandle(&mine.pos0, s.pos[0]) == cudaSuccess && cudaIpcGetMemHandle(&mine.pos1, s.pos[1]) == cudaSuccess &&
-              cudaIpcGetMemHandle(&mine.flags, s.flags) == cudaSuccess;
+    mine.ok = cudaIpcGetMemHandle(&mine.arena, s.arena) == cudaSuccess;
     cudaGetLastError();
     Blob* dev = nullptr;
     CU(c, cudaMalloc(&dev, sizeof(Blob) * c->world));
@@ -439,25 +469,23 @@ static int setup_peer_exchange(nbody_ctx* c)
     for (int r = 0; r < c->world; ++r) ok = ok && all[r].ok;
     if (ok) {
         for (int r = 0; r < c->world && ok; ++r) {
-            if (r == c->my_rank) {
-                s.peer_pos[r][0] = s.pos[0];
-                s.peer_pos[r][1] = s.pos[1];
-                s.peer_flags.flags[r] = s.flags;
-                continue;
-            }
-            void* ptr[3] = {nullptr, nullptr, nullptr};
-            const cudaIpcMemHandle_t* h[3] = {&all[r].pos0, &all[r].pos1, &all[r].flags};
-            for (int k = 0; k < 3 && ok; ++k) {
-                if (cudaIpcOpenMemHandle(&ptr[k], *h[k], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+            char* base = static_cast<char*>(s.arena);
+            if (r != c->my_rank) {
+                void* ptr = nullptr;
+                if (cudaIpcOpenMemHandle(&ptr, all[r].arena, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
                     cudaGetLastError();
                     ok = false;
-                } else {
-                    s.ipc_opened.push_back(ptr[k]);
+                    break;
                 }
+                s.ipc_opened.push_back(ptr);
+                base = static_cast<char*>(ptr);
             }
-            s.peer_pos[r][0] = ptr[0];
-            s.peer_pos[r][1] = ptr[1];
-            s.peer_flags.flags[r] = static_cast<unsigned long long*>(ptr[2]);
+            // (every rank's arena has the same layout: same precision and capacity)
+            s.peer_pos[r][0] = base;
+            s.peer_pos[r][1] = base + s.off_pos1;
+            s.peer_acc[r] = s.accfix ? base + s.off_acc : nullptr;
+            s.peer_flags.flags[r] = reinterpret_cast<unsigned long long*>(base + s.off_flags);
+            s.peer_ctl[r] = s.peer_flags.flags[r] + kMaxPeers;
         }
     }
     mine.ok = ok;  // second round: did EVERY rank map every peer?
@@ -606,6 +634,9 @@ extern "C" int nbody_get_info(nbody_ctx* c, nbody_info* o)
     o->exchange = c->world == 1 ? 0 : (c->p2p ? 2 : 1);
     o->uniform_mass = c->uniform ? 1 + int(c->outliers.size()) : 0;
     o->f64_symmetric = c->f64_sym_k;
+    o->f32_symmetric = c->sym32_run;
+    o->f32_sym_bodies_per_thread = c->sym32_run > 0 ? c->sym32_R : 0;
+    o->f32_sym_last_pass = c->sym32_used ? 1 : 0;
     return NBODY_OK;
 }
 
@@ -615,10 +646,22 @@ extern "C" int nbody_get_info(nbody_ctx* c, nbody_info* o)
 
 namespace {
 
+int queue_exchange_barrier(nbody_ctx* c);  // defined with the exchange code below
+
 template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, const Real* vel, const Real* acc, const Real* temp)
 {
     const size_t v4 = 4 * sizeof(Real);
     bool small_io = false;
+    // One process per GPU with peer stores: a peer that is a step ahead (or behind) reads and writes THIS rank's position
+    // buffers and accumulators.  The upload is a collective there: an epoch barrier before the buffers are rewritten (every
+    // rank has finished the work it had queued) and one after (every rank's buffers are packed before any peer store).
+    const bool handshake = c->rank_mode && c->world > 1 && c->p2p;
+    if (handshake) {
+        const int rcb = queue_exchange_barrier(c);
+        if (rcb != NBODY_OK) return rcb;
+    }
+    const bool want_mass = sizeof(Real) == 4 && c->sym32_allowed && n >= c->sym32_min_n;
+    double small_mass = 0.0;
     for (Shard& s : c->shards) {
         CU(c, cudaSetDevice(s.device));
         s.n_local = c->n_pad / c->world;
@@ -646,6 +689,11 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
             CU(c, cudaGetLastError());
             CU(c, cudaEventRecord(s.io_done, s.stream));
             small_io = true;
+            if (want_mass) {  // (a few thousand bodies: the host adds them, in index order)
+                double t = 0.0;
+                for (size_t i = 0; i < n; ++i) t += std::fabs(double(pm[4 * i + 3]));
+                small_mass = t;
+            }
         } else {
         // positions + masses: host AoS -> staging -> device layout (both buffers)
         CU(c, cudaMemcpyAsync(s.stage, pm, n * v4, cudaMemcpyHostToDevice, s.stream));
@@ -654,7 +702,9 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
         if (detect) CU(c, cudaMemsetAsync(s.outlier_count, 0, sizeof(unsigned), s.stream));
         pack_pos_kernel<Real><<<blocks, 256, 0, s.stream>>>(static_cast<const Real*>(s.stage), static_cast<Real*>(s.pos[0]),
                                                            static_cast<Real*>(s.pos[1]), n, c->n_pad, Real(sizeof(Real) == 8 ? 1e150 : 1e18), Real(c->uniform_mass),
-                                                           detect ? s.outlier_count : nullptr, s.outliers);
+                                                           detect ? s.outlier_count : nullptr, s.outliers,
+                                                           want_mass && &s == &c->shards[0] ? s.mass_sums : nullptr);
+        if (s.accfix) CU(c, cudaMemsetAsync(s.accfix, 0, (3 * c->n_pad + 1) * sizeof(unsigned long long), s.stream));  // (zero unless a pass was abandoned)
         c->launches++;
         CU(c, cudaGetLastError());
         CU(c, cudaMemsetAsync(s.vel, 0, s.n_local * v4, s.stream));
@@ -679,7 +729,21 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
     }
     // host buffers are borrowed for the duration of the call only (the small-system path has copied them already)
     c->upload_deferred = small_io;
+    c->sum_abs_mass = small_mass;
     if (small_io) return NBODY_OK;
+    if (handshake) {
+        const int rcb = queue_exchange_barrier(c);
+        if (rcb != NBODY_OK) return rcb;
+    }
+    c->sum_abs_mass = 0.0;
+    if (want_mass) {  // sum |m|, block sums added in index order: the same number on every rank and in every run
+        Shard& s0 = c->shards[0];
+        CU(c, cudaSetDevice(s0.device));
+        std::vector<double> sums((c->n_pad + 255) / 256);
+        CU(c, cudaMemcpyAsync(sums.data(), s0.mass_sums, sums.size() * sizeof(double), cudaMemcpyDeviceToHost, s0.stream));
+        CU(c, cudaStreamSynchronize(s0.stream));
+        for (double v : sums) c->sum_abs_mass += v;
+    }
     for (Shard& s : c->shards) {
         CU(c, cudaSetDevice(s.device));
         CU(c, cudaStreamSynchronize(s.stream));
@@ -756,6 +820,70 @@ int ensure_sym_buffers(nbody_ctx* c)
         CU(c, cudaMalloc(&s.sym_part_j, bj));
         s.sym_bytes_j = bj;
     }
+    return NBODY_OK;
+}
+
+// The unit table of the fp32 pairs-once pass (force_f32_sym.cuh) for the current body count: row I = i-tile I against its own
+// position tiles (one diagonal unit), then against the tiles above it in runs of `run`.  A pure function of n (and of the
+// kernel shape), never of the GPU count: every partial sum a unit produces is the same number wherever the unit runs, and
+// the GPUs share the table by cost (position-tile visits), in order.
+int build_sym32_table(nbody_ctx* c)
+{
+    c->sym32_run = 0;
+    if (c->prec != NBODY_F32 || !c->sym32_allowed || c->n < c->sym32_min_n) return NBODY_OK;
+    if (c->detect_pending) {  // (a small upload returned before its mass detection was read)
+        const int rcd = resolve_mass_detection(c);
+        if (rcd != NBODY_OK) return rcd;
+    }
+    const int R = (c->sym32_R_forced == 4 || c->sym32_R_forced == 8) ? c->sym32_R_forced : (c->uniform ? kSym32EqualMassR : kSym32GeneralR);
+    c->sym32_R = R;
+    const size_t itile = size_t(kF32Threads) * R, spt = itile / kPosTile;
+    const size_t NS = (c->n + kPosTile - 1) / kPosTile;  // position tiles that hold bodies
+    const size_t T = (c->n + itile - 1) / itile;
+    if (NS >= (1u << 24)) return NBODY_OK;
+    int run = env_int("NBODY_F32_SYM_RUN", 0);
+    if (run <= 0) run = int(std::min<size_t>(8, std::max<size_t>(1, NS / 512)));  // N=1M: 4 tiles (2,048 bodies) per unit
+    run = std::min(run, kSymUnitMaxRun);
+    if (c->sym32_table_n != c->n || c->sym32_table_R != R || c->sym32_table_run != run) {
+        std::vector<SymUnit> units;
+        std::vector<unsigned long long> cost;  // position-tile visits up to and including unit u
+        unsigned long long total = 0;
+        for (size_t I = 0; I < T; ++I) {
+            const size_t s0 = I * spt, s1 = std::min((I + 1) * spt, NS);
+            units.push_back(SymUnit{unsigned(I), unsigned(s0) | unsigned(s1 - s0) << 24 | kSymUnitDiag});
+            cost.push_back(total += s1 - s0);
+            for (size_t st = s1; st < NS; st += size_t(run)) {
+                const size_t cnt = std::min(size_t(run), NS - st);
+                units.push_back(SymUnit{unsigned(I), unsigned(st) | unsigned(cnt) << 24});
+                cost.push_back(total += cnt);
+            }
+        }
+        c->sym32_split.assign(size_t(c->world) + 1, 0);
+        size_t u = 0;
+        for (int r = 1; r < c->world; ++r) {
+            const unsigned long long target = total / c->world * r;
+            while (u < units.size() && cost[u] < target) ++u;
+            c->sym32_split[r] = unsigned(u);
+        }
+        c->sym32_split[c->world] = unsigned(units.size());
+        for (Shard& s : c->shards) {
+            CU(c, cudaSetDevice(s.device));
+            if (units.size() > s.sym_units_cap) {
+                CU(c, cudaStreamSynchronize(s.stream));
+                cudaFree(s.sym_units);
+                s.sym_units = nullptr;
+                s.sym_units_cap = 0;
+                CU(c, cudaMalloc(&s.sym_units, units.size() * sizeof(SymUnit)));
+                s.sym_units_cap = units.size();
+            }
+            CU(c, cudaMemcpyAsync(s.sym_units, units.data(), units.size() * sizeof(SymUnit), cudaMemcpyHostToDevice, s.stream));
+            CU(c, cudaStreamSynchronize(s.stream));  // (`units` is pageable and goes out of scope)
+        }
+        c->sym32_table_n = c->n;
+        c->sym32_table_R = R;
+        c->sym32_table_run = run;
+    }
+    c->sym32_run = run;
     return NBODY_OK;
 }
 
@@ -853,6 +981,7 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     if (rc == NBODY_OK && c->detect_masses && !c->detect_pending) rc = finish_mass_detection(c);
     c->detect_masses = false;
     if (rc == NBODY_OK && c->f64_sym_k > 0) rc = ensure_sym_buffers(c);
+    if (rc == NBODY_OK) rc = build_sym32_table(c);
     return rc;
 }
 
@@ -890,20 +1019,25 @@ int fold_timing(nbody_ctx* c, Shard& s)
 // Complete the exchange of the slices just written to pos[which].
 // Peer-store mode: the update kernel already stored every slice on every rank; queue
 // the epoch barrier.  Otherwise: ncclAllGather of the own slices, in place.
+// One cross-GPU epoch barrier (exchange.cuh) queued on every shard's stream: when it retires on a device, every rank has
+// finished the work queued before ITS barrier -- peer stores into this device's buffers have landed, peer reads of them are over.
+int queue_exchange_barrier(nbody_ctx* c)
+{
+    c->epoch++;
+    const unsigned long long timeout_ns = (unsigned long long)env_int("NBODY_EXCHANGE_TIMEOUT_S", 60) * 1000000000ull;
+    for (Shard& s : c->shards) {
+        CU(c, cudaSetDevice(s.device));
+        exchange_barrier_kernel<<<1, 32, 0, s.stream>>>(s.peer_flags, s.rank, c->world, c->epoch, timeout_ns, s.xerr);
+        c->launches++;
+        CU(c, cudaGetLastError());
+    }
+    return NBODY_OK;
+}
+
 int exchange_positions(nbody_ctx* c, int which)
 {
     if (c->world == 1) return NBODY_OK;
-    if (c->p2p) {
-        c->epoch++;
-        const unsigned long long timeout_ns = (unsigned long long)env_int("NBODY_EXCHANGE_TIMEOUT_S", 60) * 1000000000ull;
-        for (Shard& s : c->shards) {
-            CU(c, cudaSetDevice(s.device));
-            exchange_barrier_kernel<<<1, 32, 0, s.stream>>>(s.peer_flags, s.rank, c->world, c->epoch, timeout_ns, s.xerr);
-            c->launches++;
-            CU(c, cudaGetLastError());
-        }
-        return NBODY_OK;
-    }
+    if (c->p2p) return queue_exchange_barrier(c);
     const size_t v4 = 4 * c->esz;
     if (!c->rank_mode) NC(c, nccl().GroupStart());
     for (Shard& s : c->shards) {
@@ -969,11 +1103,144 @@ template <typename Real> ForceParams<Real> make_params(nbody_ctx* c, Shard& s, i
     return p;
 }
 
+int start_force_timing(nbody_ctx* c, Shard& s)
+{
+    if (s.ev_used + 2 > s.ev.size()) {
+        if (s.ev.size() < 2 * kEventPool) {
+            for (int k = 0; k < 2; ++k) {
+                cudaEvent_t e;
+                CU(c, cudaEventCreate(&e));
+                s.ev.push_back(e);
+            }
+        } else {
+            int rc = fold_timing(c, s);
+            if (rc != NBODY_OK) return rc;
+        }
+    }
+    CU(c, cudaEventRecord(s.ev[s.ev_used], s.stream));
+    return NBODY_OK;
+}
+
+template <typename F> void pick_f32_sym_kernel(int R, bool uniform, F&& f)
+{
+    if (R == 8) return uniform ? f(force_f32_sym_kernel<8, true>) : f(force_f32_sym_kernel<8, false>);
+    return uniform ? f(force_f32_sym_kernel<4, true>) : f(force_f32_sym_kernel<4, false>);
+}
+
+// The fp32 pairs-once pass (force_f32_sym.cuh): persistent CTAs work through this device's share of the unit table and add
+// fixed-point partial sums to the accumulators of ALL bodies; after a cross-GPU barrier one O(N) kernel per device adds the
+// peers' accumulators for the bodies it owns and runs the integrator epilogue.  Returns 1 when the pass does not apply
+// (the caller takes the one-sided sweep), 0 when it was queued.
+int launch_force_sym32(nbody_ctx* c, int mode, double dt, double G, double eps)
+{
+    if (c->sym32_run <= 0 || !(eps > 0.0) || !std::isfinite(eps)) return 1;
+    const bool uniform = c->uniform;
+    // |sum| <= sum_j |m_j| * max_r r / (r^2 + eps^2)^1.5 = sum|m| * 2 / (3 sqrt(3) eps^2); the equal-mass sweep counts every body as 1
+    const double eps2 = double(float(eps) * float(eps));
+    const double wmax = 2.0 / (3.0 * std::sqrt(3.0) * eps2);
+    const double bound = 1.001 * wmax * (uniform ? double(c->n) : c->sum_abs_mass);
+    if (!(bound > 0.0) || !std::isfinite(bound) || bound > 1e37) return 1;
+    int e = 0;
+    std::frexp(bound, &e);         // bound < 2^e
+    const int k = std::max(-100, std::min(100, 61 - e));  // bound * 2^k < 2^61
+    if (61 - e < -100) return 1;
+    int& slots = c->sym32_slots[uniform ? 1 : 0];
+    if (slots == 0) {
+        int per_sm = 0;
+        cudaError_t err = cudaSuccess;
+        CU(c, cudaSetDevice(c->shards[0].device));
+        pick_f32_sym_kernel(c->sym32_R, uniform, [&](auto kernel) {
+            err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kF32Threads + 32, force_f32_sym_smem_bytes());
+        });
+        if (err != cudaSuccess || per_sm < 1) return fail(c, NBODY_ECUDA, "pairs-once kernel does not fit an SM: %s", cudaGetErrorString(err));
+        slots = per_sm * c->sm_count;
+    }
+    for (Shard& s : c->shards) {
+        CU(c, cudaSetDevice(s.device));
+        if (c->timing && &s == &c->shards[0]) {
+            const int rc = start_force_timing(c, s);
+            if (rc != NBODY_OK) return rc;
+        }
+        Sym32Params sp;
+        sp.pos = static_cast<const float*>(s.pos[c->cur]);
+        sp.units = static_cast<const SymUnit*>(s.sym_units);
+        sp.u_begin = c->sym32_split[s.rank];
+        sp.u_end = c->sym32_split[s.rank + 1];
+        sp.sched = s.sym_ctl;
+        sp.accfix = s.accfix;
+        sp.n_pad = c->n_pad;
+        sp.eps2 = float(eps) * float(eps);
+        sp.scale = std::ldexp(1.0f, k);
+        sp.bound = std::nextafter(float(bound), INFINITY);
+        CU(c, cudaMemsetAsync(s.sym_ctl, 0, sizeof(unsigned), s.stream));
+        if (c->world > 1 && !c->p2p)  // (after the all-reduce below every device holds ALL bodies' totals and clears only its own)
+            CU(c, cudaMemsetAsync(s.accfix, 0, (3 * c->n_pad + 1) * sizeof(unsigned long long), s.stream));
+        else
+            CU(c, cudaMemsetAsync(s.accfix + 3 * c->n_pad, 0, sizeof(unsigned long long), s.stream));
+        const unsigned units = sp.u_end - sp.u_begin;
+        const unsigned grid = std::max(1u, std::min(units, unsigned(slots)));
+        pick_f32_sym_kernel(c->sym32_R, uniform, [&](auto kernel) { kernel<<<grid, kF32Threads + 32, force_f32_sym_smem_bytes(), s.stream>>>(sp); });
+        c->launches++;
+        CU(c, cudaGetLastError());
+    }
+    if (c->world > 1 && c->p2p) {  // every rank's accumulators are complete
+        const int rc = queue_exchange_barrier(c);
+        if (rc != NBODY_OK) return rc;
+    } else if (c->world > 1) {  // no peer mappings: an exact all-reduce of the accumulators (and the poison word)
+        if (!c->rank_mode) NC(c, nccl().GroupStart());
+        for (Shard& s : c->shards) {
+            if (!c->rank_mode) CU(c, cudaSetDevice(s.device));
+            NC(c, nccl().AllReduce(s.accfix, s.accfix, 3 * c->n_pad + 1, ncclInt64_, ncclSum_, s.comm, s.stream));
+        }
+        if (!c->rank_mode) NC(c, nccl().GroupEnd());
+    }
+    for (Shard& s : c->shards) {
+        CU(c, cudaSetDevice(s.device));
+        ForceParams<float> p = make_params<float>(c, s, mode, dt, G, eps);
+        if (uniform && c->outliers.empty()) {
+            p.G = float(G) * float(c->uniform_mass);
+        } else if (uniform) {
+            p.n_outliers = int(c->outliers.size());
+            p.bulk_mass = float(c->uniform_mass);
+        }
+        Sym32Sources src;
+        src.n = 0;
+        src.inv_scale = std::ldexp(1.0, -k);
+        if (c->world == 1 || !c->p2p) {
+            src.acc[src.n++] = s.accfix;
+        } else {
+            for (int r = 0; r < c->world; ++r) src.acc[src.n++] = static_cast<unsigned long long*>(s.peer_acc[r]);
+        }
+        const unsigned blocks = unsigned((s.n_local + kSym32FinishThreads - 1) / kSym32FinishThreads);
+        if (uniform) f32_sym_finish_kernel<true><<<blocks, kSym32FinishThreads, 0, s.stream>>>(p, src, c->n_pad);
+        else f32_sym_finish_kernel<false><<<blocks, kSym32FinishThreads, 0, s.stream>>>(p, src, c->n_pad);
+        c->launches++;
+        CU(c, cudaGetLastError());
+        if (c->timing && &s == &c->shards[0]) {
+            CU(c, cudaEventRecord(s.ev[s.ev_used + 1], s.stream));
+            s.ev_used += 2;
+        }
+    }
+    // the accumulators a peer has just read and cleared belong to the next pass: nobody may add to them before every finish
+    // kernel has retired.  A fused step gets that barrier from its position exchange (nbody_step).
+    if (c->world > 1 && c->p2p && mode != kForceKick2Kick1) return queue_exchange_barrier(c);
+    return NBODY_OK;
+}
+
 int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
 {
     if (c->detect_pending) {
         const int rcd = resolve_mass_detection(c);
         if (rcd != NBODY_OK) return rcd;
+    }
+    c->sym32_used = false;
+    if (c->prec == NBODY_F32 && !(c->has_radius && env_int("NBODY_NEAR", 1) != 0)) {
+        const int rcs = launch_force_sym32(c, mode, dt, G, eps);
+        if (rcs <= 0) {
+            c->near_valid = false;
+            c->sym32_used = rcs == 0;
+            return rcs;
+        }
     }
     // With radii set, the fp32 sweep also tracks each body's nearest neighbour for the
     // collision broad phase (contacts.cuh).  The result describes the positions the
@@ -986,19 +1253,8 @@ int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
         const unsigned grid = unsigned(s.n_local / c->i_tile) * unsigned(c->j_chunks);
         const bool time_it = c->timing && &s == &c->shards[0];
         if (time_it) {
-            if (s.ev_used + 2 > s.ev.size()) {
-                if (s.ev.size() < 2 * kEventPool) {
-                    for (int k = 0; k < 2; ++k) {
-                        cudaEvent_t e;
-                        CU(c, cudaEventCreate(&e));
-                        s.ev.push_back(e);
-                    }
-                } else {
-                    int rc = fold_timing(c, s);
-                    if (rc != NBODY_OK) return rc;
-                }
-            }
-            CU(c, cudaEventRecord(s.ev[s.ev_used], s.stream));
+            const int rct = start_force_timing(c, s);
+            if (rct != NBODY_OK) return rct;
         }
         if (c->prec == NBODY_F32) {
             ForceParams<float> p = make_params<float>(c, s, mode, dt, G, eps);

@@ -15,7 +15,7 @@ namespace nb {
 typedef struct ncclComm* ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
 typedef int ncclResult_t;  // 0 == ncclSuccess
-enum { ncclUint8_ = 1, ncclFloat64_ = 8 };
+enum { ncclUint8_ = 1, ncclInt64_ = 4, ncclFloat64_ = 8 };
 enum { ncclSum_ = 0 };
 
 struct NcclApi {

@@ -12,7 +12,7 @@ from typing import Tuple
 
 import math
 
-I_TILE_F32 = 512   # kF32Threads * R (128 x 4), csrc/common.cuh
+I_TILE_F32 = 1024  # the larger i-tile of the fp32 kernels: 128 threads x 8 bodies (pairs-once pass, equal masses), csrc/force_f32_sym.cuh
 I_TILE_F64 = 256   # kThreads; 512 from 32,768 bodies up (two i-bodies per thread, nbody_capi.cu f64_bodies_per_thread)
 J_UNIT_F32 = 512   # kJUnit: one ring stage of the fp32 kernel
 J_UNIT_F64 = 64    # kJUnitF64

@@ -1,0 +1,73 @@
+#!/usr/bin/env python
+"""Kernel-variant timings of the fp32 force pass on one GPU (builder's lab, not the bench):
+one JSON line per (scene, n, variant) with the device time of the force pass per step."""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import nbody_b200 as nb  # noqa: E402
+
+
+def run(scene, n, general, env, steps=3, label=""):
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update({k: str(v) for k, v in env.items()})
+    try:
+        s = nb.scenes.SCENES[scene](n)
+        pm, vel, _ = s.astype(np.float32)
+        if general:
+            pm[:, 3] = (pm[:, 3].mean() * np.random.default_rng(1).uniform(0.5, 1.5, s.n)).astype(np.float32)
+        with nb.Engine(s.n, precision="f32") as e:
+            e.upload(pm, vel)
+            e.step(s.dt, s.G, s.softening, 1)
+            e.sync()
+            e.enable_timing(True)
+            e.read_timing()
+            t0 = time.perf_counter()
+            e.step(s.dt, s.G, s.softening, steps)
+            e.sync()
+            wall = (time.perf_counter() - t0) / steps
+            k, ms = e.read_timing()
+            info = e.info()
+        ms_step = ms / max(k, 1)
+        print(json.dumps({"scene": scene, "n": n, "general_masses": general, "variant": label, "env": env, "force_ms": ms_step,
+                          "wall_ms": wall * 1e3, "G_int_per_s": float(n) ** 2 / (ms_step * 1e-3) * 1e-9,
+                          "sym": info["f32_symmetric"], "sym_R": info["f32_sym_bodies_per_thread"], "sym_used": info["f32_sym_last_pass"],
+                          "uniform": info["uniform_mass"], "j_chunks": info["j_chunks"]}), flush=True)
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+if __name__ == "__main__":
+    which = sys.argv[1] if len(sys.argv) > 1 else "all"
+    N = int(os.environ.get("LAB_N", 1 << 20))
+    tag = os.environ.get("LAB_TAG", "")
+    variants = [("sym R4", {"NBODY_F32_SYM_R": 4}), ("sym R8", {"NBODY_F32_SYM_R": 8}), ("one-sided", {"NBODY_F32_SYM": 0})]
+    if which in ("all", "1m"):
+        for general in (False, True):
+            for label, env in variants:
+                run("uniform_cube", N, general, env, label=label)
+        for run_len in (1, 2, 8, 16):
+            run("uniform_cube", N, False, {"NBODY_F32_SYM_R": 4, "NBODY_F32_SYM_RUN": run_len}, label=f"sym R4 run={run_len}")
+    if which in ("all", "mid"):
+        for n in (32768, 65536, 131072, 262144):
+            for label, env in variants:
+                run("two_galaxies", n, False, env, steps=5, label=label)
+        for n in (16384, 32768):
+            for label, env in variants:
+                e2 = dict(env)
+                e2["NBODY_F32_SYM_MIN"] = 1
+                run("plummer", n, True, e2, steps=5, label=label + " (forced)")
+    if which == "onesided":      # a kernel-variant build (NBODY_LIB) of the one-sided sweep
+        for general in (False, True):
+            run("uniform_cube", N, general, {"NBODY_F32_SYM": 0}, label="one-sided " + tag)
+    if which == "sym":           # ... and of the pairs-once pass, default bodies per thread
+        for general in (False, True):
+            run("uniform_cube", N, general, {}, label="sym " + tag)

@@ -48,7 +48,7 @@ def test_gpu_arm_line_reduced_size():
     launches counted, clocks sampled, the CPU baseline labelled."""
     n = 131072
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--bodies", str(n), "--steps", "3", "--warmup", "3", "--cpu-sample", "2048",
-                        "--cpu-steps", "1"], capture_output=True, text=True, cwd=ROOT, timeout=600)
+                        "--cpu-reps", "2"], capture_output=True, text=True, cwd=ROOT, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
     lines = [ln for ln in r.stdout.splitlines() if ln.strip().startswith("{")]
     assert len(lines) == 1
@@ -58,7 +58,15 @@ def test_gpu_arm_line_reduced_size():
     assert abs(d["value"] - n * n / (d["ms_per_step"] * 1e-3) * 1e-9) < 1e-6 * d["value"]
     roof = d["roofline"]
     assert abs(roof["frac"] - roof["achieved"] / roof["peak"]) < 1e-9 and 0.5 < roof["frac"] < 1.05 and roof["kernel_launches"] == 3
+    assert roof["kernel_model"].startswith("pairs_once") and abs(roof["frac_vs_survey_R"] - roof["achieved"] / roof["peak_survey_R"]) < 1e-9
     assert d["gpu_launches"] >= 2 * 3
+    # the line checks what it timed: sampled accelerations against the oracle, a state hash, and the fused call
+    ck = d["check"]
+    assert ck["ok"] is True and ck["sampled_acc_err"] < ck["gate"] == 2e-5 and len(ck["state_hash"]) == 16 and ck["state_hash_same_on_all_ranks"]
+    assert d["fused"]["value"] > 0.8 * d["value"] and d["fused"]["gpu_launches"] >= 3
+    assert d["ms_per_step_with_l2_flush"] >= d["ms_per_step"]
+    cb = d["cpu_baseline"]
+    assert cb["repetitions"] == 2 and cb["min"] <= cb["median"] <= cb["max"] == cb["value"]
     e = d["e2e"]
     assert e["h2d_bytes_per_step"] == e["d2h_bytes_per_step"] == 3 * n * 16 and 0 < e["value"] <= d["value"] * 1.02
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] == 1 and d["cpu_baseline"]["value"] > 0

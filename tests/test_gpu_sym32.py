@@ -1,0 +1,177 @@
+"""The fp32 pairs-once pass (csrc/force_f32_sym.cuh): every pair evaluated once and applied to
+both bodies, as the reference's i<j loop does (/root/reference/index.html:272-288), through exact
+fixed-point accumulators.  Parity against the oracle at the fp32 tolerance, agreement with the
+one-sided sweep, and the properties the fixed-point accumulation buys: the same bits run after
+run, fused or split, for every unit size's schedule and on every GPU count."""
+import os
+
+import numpy as np
+import pytest
+
+from .conftest import norm_rel_err
+
+pytestmark = pytest.mark.gpu
+
+F32_ACC_TOL = 2e-5   # same gate as the one-sided sweep (tests/test_gpu_parity.py)
+
+
+class env:
+    def __init__(self, **kv):
+        self.kv = {k: str(v) for k, v in kv.items()}
+
+    def __enter__(self):
+        self.old = {k: os.environ.get(k) for k in self.kv}
+        os.environ.update(self.kv)
+
+    def __exit__(self, *exc):
+        for k, v in self.old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+def scene_arrays(nb, name, n, general):
+    s = nb.scenes.SCENES[name](n)
+    pm = s.pos_mass.astype(np.float32)
+    if general:
+        pm[:, 3] = (pm[:, 3].mean() * np.random.default_rng(n).uniform(0.2, 2.5, s.n)).astype(np.float32)
+    return s, pm, s.vel.astype(np.float32)
+
+
+def force(nb, pm, vel, G, eps, **kv):
+    with env(**kv):
+        with nb.Engine(len(pm), precision="f32") as e:
+            e.upload(pm, vel)
+            e.force(G, eps)
+            return e.download()["acc"], e.info()
+
+
+@pytest.mark.parametrize("R", [4, 8])
+@pytest.mark.parametrize("general", [False, True])
+@pytest.mark.parametrize("scene,n", [("plummer", 1), ("plummer", 2), ("plummer", 513), ("two_galaxies", 1026), ("plummer", 3001),
+                                     ("uniform_cube", 5000), ("cold_collapse", 40000)])
+def test_sym32_force_vs_oracle(nb, oracle, scene, n, general, R):
+    s, pm, vel = scene_arrays(nb, scene, n, general)
+    ref = oracle.compute_gravity(pm.astype(np.float64), s.G, s.softening, mt=True)
+    acc, info = force(nb, pm, vel, s.G, s.softening, NBODY_F32_SYM_MIN=1, NBODY_F32_SYM_R=R)
+    assert info["f32_symmetric"] > 0 and info["f32_sym_bodies_per_thread"] == R and info["f32_sym_last_pass"] == 1
+    err = norm_rel_err(acc, ref) if n > 1 else float(np.abs(acc[:, :3]).max())
+    print(f"pairs-once R={R} {scene} n={s.n} {'general' if general else 'scene'} masses: acc norm-rel err {err:.3e}")
+    assert err < F32_ACC_TOL
+    one, info1 = force(nb, pm, vel, s.G, s.softening, NBODY_F32_SYM=0, NBODY_SMALL=0, NBODY_MEDIUM=0)
+    assert info1["f32_symmetric"] == 0 and info1["f32_sym_last_pass"] == 0
+    if n > 1:
+        assert norm_rel_err(acc, one) < F32_ACC_TOL
+
+
+@pytest.mark.parametrize("R", [4, 8])
+def test_sym32_newtons_third_law(nb, R):
+    """sum m_i a_i = 0 (idx:282-288): each pair's two contributions are the same fp32 products with opposite signs."""
+    s, pm, vel = scene_arrays(nb, "two_galaxies", 50000, True)
+    acc, _ = force(nb, pm, vel, s.G, s.softening, NBODY_F32_SYM_R=R)
+    ma = pm[:, 3:4].astype(np.float64) * acc[:, :3].astype(np.float64)
+    assert np.abs(ma.sum(axis=0)).max() < 1e-6 * np.abs(ma).sum()
+
+
+@pytest.mark.parametrize("general", [False, True])
+def test_sym32_bits_do_not_depend_on_the_schedule(nb, general):
+    """Dynamic unit scheduling + integer accumulation: two runs agree bit for bit; so do nsteps fused into one
+    call, single steps, and the split entry points."""
+    s, pm, vel = scene_arrays(nb, "plummer", 40000, general)
+    s.softening = 0.02
+    outs = []
+    for how in ("fused", "fused", "single", "split"):
+        with nb.Engine(s.n, precision="f32") as e:
+            e.upload(pm, vel)
+            assert e.info()["f32_symmetric"] > 0
+            if how == "fused":
+                e.step(s.dt, s.G, s.softening, 4)
+            elif how == "single":
+                for _ in range(4):
+                    e.step(s.dt, s.G, s.softening, 1)
+            else:
+                for _ in range(4):
+                    e.kick1_drift(s.dt)
+                    e.force(s.G, s.softening)
+                    e.kick2(s.dt, 0.998)
+            outs.append(e.download())
+    for o in outs[1:]:
+        for k in ("pos_mass", "vel", "acc"):
+            assert np.array_equal(o[k], outs[0][k]), k
+
+
+def test_sym32_unit_size_only_reorders_fp32_sums(nb):
+    s, pm, vel = scene_arrays(nb, "plummer", 65536, False)
+    base, info = force(nb, pm, vel, s.G, s.softening)
+    assert info["f32_symmetric"] == 1          # 128 position tiles: one tile per unit
+    for run in (2, 7, 64):
+        acc, info = force(nb, pm, vel, s.G, s.softening, NBODY_F32_SYM_RUN=run)
+        assert info["f32_symmetric"] == run
+        assert norm_rel_err(acc, base) < F32_ACC_TOL
+
+
+def test_sym32_uniform_mass_with_outliers(nb, oracle):
+    """Config 3's shape: two mass-500 centres among equal disc bodies (the equal-mass sweep + per-body corrections)."""
+    s = nb.scenes.two_galaxies(40000)
+    pm, vel, _ = s.astype(np.float32)
+    ref = oracle.compute_gravity(pm.astype(np.float64), s.G, s.softening, mt=True)
+    acc, info = force(nb, pm, vel, s.G, s.softening)
+    assert info["f32_symmetric"] > 0 and info["uniform_mass"] == 3
+    assert norm_rel_err(acc, ref) < F32_ACC_TOL
+    gen, info = force(nb, pm, vel, s.G, s.softening, NBODY_UNIFORM=0)
+    assert info["uniform_mass"] == 0
+    assert norm_rel_err(gen, ref) < F32_ACC_TOL
+
+
+def test_sym32_non_finite_input_poisons_the_step(nb):
+    """The reference turns every acceleration into NaN when one body's position is NaN (every pair with it is NaN,
+    idx:277-288); a fixed-point accumulator cannot hold a NaN, so the pass carries a poison mark instead."""
+    s, pm, vel = scene_arrays(nb, "plummer", 33000, False)
+    pm[12345, 1] = np.nan
+    acc, info = force(nb, pm, vel, s.G, s.softening)
+    assert info["f32_symmetric"] > 0
+    assert np.isnan(acc[:, :3]).all()
+    pm[12345, 1] = 0.25
+    acc, _ = force(nb, pm, vel, s.G, s.softening)      # ... and the next pass is clean again
+    assert np.isfinite(acc).all()
+
+
+def test_sym32_falls_back_when_it_cannot_apply(nb, oracle):
+    s, pm, vel = scene_arrays(nb, "plummer", 33000, False)
+    acc0, info = force(nb, pm, vel, s.G, 0.0)                        # no bound without softening: the one-sided sweep runs
+    assert info["f32_sym_last_pass"] == 0
+    ref = oracle.acc_subset(pm.astype(np.float64), np.arange(0, s.n, 1111), s.G, 0.0)
+    assert norm_rel_err(acc0[::1111], ref) < 5e-5
+    with nb.Engine(s.n, precision="f32") as e:                        # radii set: the sweep that tracks nearest neighbours
+        e.upload(pm, vel)
+        e.set_radius(np.full(s.n, 1e-4, np.float32))
+        e.force(s.G, s.softening)
+        a = e.download()["acc"]
+        assert e.info()["f32_sym_last_pass"] == 0
+    acc1, _ = force(nb, pm, vel, s.G, s.softening)
+    assert norm_rel_err(a, acc1) < F32_ACC_TOL
+
+
+def test_sym32_multi_gpu_same_bits(nb):
+    """Each GPU works through its share of the unit table for ALL bodies and the owners add the peers' accumulators:
+    integer sums, so 1, 2, 4 and 8 GPUs give the same bits -- with peer mappings and with the NCCL all-reduce."""
+    ng = nb.device_count()
+    if ng < 2:
+        pytest.skip("needs >= 2 GPUs")
+    s, pm, vel = scene_arrays(nb, "two_galaxies", 70001, True)
+    outs = []
+    for exchange in ("peer", "nccl"):
+        for g in sorted({1, 2, min(ng, 4), min(ng, 8)}):
+            with env(NBODY_EXCHANGE=exchange):
+                with nb.Engine(s.n, precision="f32", n_gpus=g) as e:
+                    e.upload(pm, vel)
+                    assert e.info()["f32_symmetric"] > 0
+                    e.step(s.dt, s.G, s.softening, 3)
+                    e.force(s.G, s.softening)
+                    e.force(s.G, s.softening)
+                    e.step(s.dt, s.G, s.softening, 1)
+                    outs.append((exchange, g, e.download()))
+    for exchange, g, o in outs[1:]:
+        for k in ("pos_mass", "vel", "acc"):
+            assert np.array_equal(o[k], outs[0][2][k]), (exchange, g, k)
