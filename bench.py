@@ -425,12 +425,11 @@ def main():
                 t0 = time.perf_counter()
             eng.upload(host["pos_mass"], host["vel"], host["acc"])
             eng.step(scene.dt, scene.G, scene.softening, 1)
-            eng.download(pos_mass=True, vel=True, acc=True, out=host)
+            eng.download(pos_mass=True, vel=True, acc=True, out=host, own_only=True)   # every rank reads back the bodies it owns
         barrier()
         e2e_s = allmax((time.perf_counter() - t0) / e2e_steps)
-        up = eng.info().get("upload_bytes", 0) or (args.n * 16 + 2 * (hi - lo) * 16)
-        h2d = allsum(up)
-        d2h = allsum(args.n * 16 + 2 * (hi - lo) * 16)
+        h2d = allsum(eng.info()["upload_h2d_bytes"])      # counted by the library from the copies it issues
+        d2h = allsum(3 * (hi - lo) * 16)
 
     ms_total = allmax(ms_total)
     ms_outer = allmax(ms_outer)
@@ -502,7 +501,8 @@ def main():
         if not args.no_e2e:
             line["e2e"] = {"value": inter_step / e2e_s * 1e-9, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                            "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_s * 1e3,
-                           "api": "Engine.upload(host) -> Engine.step(dt,G,eps,1) -> Engine.download(host) (pinned host arrays)"}
+                           "api": "Engine.upload(host) -> Engine.step(dt,G,eps,1) -> Engine.download(host, own_only) (pinned host arrays; every rank uploads "
+                                  "and reads back the slice it owns, positions reach the peers over NVLink)"}
         if not args.no_cpu and n_dev == 1:
             times, core = cpu_step_times(scene, min(args.n, args.cpu_sample), reps=args.cpu_reps)
             line["cpu_baseline"] = cpu_record(times, min(args.n, args.cpu_sample), core)

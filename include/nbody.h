@@ -85,7 +85,9 @@ NBODY_API void nbody_destroy(nbody_ctx* ctx);
 /* Replace the whole body list, as resetScenario / addBody do (idx:745,
  * 239-245).  acc == NULL => acc = 0, like a new Body (idx:217).  temp == NULL
  * => temperatures 0 and never updated.  In rank mode every rank passes the
- * SAME full arrays and keeps the slice it owns. */
+ * SAME full arrays and the call is a COLLECTIVE (every rank must make it): with peer mappings each rank copies only
+ * the slice it owns to its device and packs it into every peer's position buffers, between two cross-rank barriers
+ * (a peer a step ahead or behind reads and writes this rank's buffers). */
 NBODY_API int nbody_upload(nbody_ctx* ctx, size_t n, const void* pos_mass, const void* vel,
                            const void* acc, const void* temp);
 
@@ -93,6 +95,11 @@ NBODY_API int nbody_upload(nbody_ctx* ctx, size_t n, const void* pos_mass, const
  * Any pointer may be NULL.  In rank mode pos_mass is complete and vel/acc/temp
  * are written only for the rank's own range [nbody_range()]. */
 NBODY_API int nbody_download(nbody_ctx* ctx, void* pos_mass, void* vel, void* acc, void* temp);
+
+/* As nbody_download, but pos_mass too is written for the own range only ([i_begin, i_end) of nbody_get_info; every other
+ * row of the caller's array is left alone): in rank mode the ranks together read each body back once instead of once per
+ * rank.  With one process driving all devices it equals nbody_download. */
+NBODY_API int nbody_download_own(nbody_ctx* ctx, void* pos_mass, void* vel, void* acc, void* temp);
 
 /* ---- the hot path ------------------------------------------------------ */
 
@@ -274,6 +281,8 @@ typedef struct {
                             (512 bodies) per work unit.  0: the one-sided sweep */
     int f32_sym_bodies_per_thread; /* i-bodies per thread of that pass (4 or 8), 0 when it is off */
     int f32_sym_last_pass;         /* 1 when the last force pass actually was the pairs-once one (softening == 0 and set radii take the sweep) */
+    long long upload_h2d_bytes;    /* host->device bytes THIS process copied in the last nbody_upload (with peer mappings every device
+                                      copies only its own slice of pos_mass and packs it into every peer's buffers) */
 } nbody_info;
 NBODY_API int nbody_get_info(nbody_ctx* ctx, nbody_info* out);
 

@@ -21,7 +21,7 @@ NCCL_ID_BYTES = 128
 # every symbol include/nbody.h declares (tests check the library exports them all)
 SYMBOLS = (
     "nbody_create", "nbody_create_rank", "nbody_nccl_unique_id", "nbody_destroy",
-    "nbody_upload", "nbody_download", "nbody_step", "nbody_step_host", "nbody_kick1_drift", "nbody_force",
+    "nbody_upload", "nbody_download", "nbody_download_own", "nbody_step", "nbody_step_host", "nbody_kick1_drift", "nbody_force",
     "nbody_kick2", "nbody_set_heat_decay", "nbody_energy", "nbody_sync", "nbody_last_error",
     "nbody_strerror", "nbody_version", "nbody_device_count", "nbody_set_stream",
     "nbody_enable_timing", "nbody_read_timing", "nbody_get_info",
@@ -45,7 +45,7 @@ class Info(ctypes.Structure):
         ("i_tile", ctypes.c_int), ("kernel_launches", ctypes.c_longlong), ("exchange", ctypes.c_int),
         ("uniform_mass", ctypes.c_int), ("f64_symmetric", ctypes.c_int),
         ("f32_symmetric", ctypes.c_int), ("f32_sym_bodies_per_thread", ctypes.c_int),
-        ("f32_sym_last_pass", ctypes.c_int),
+        ("f32_sym_last_pass", ctypes.c_int), ("upload_h2d_bytes", ctypes.c_longlong),
     ]
 
 
@@ -80,6 +80,7 @@ def lib() -> ctypes.CDLL:
     L.nbody_destroy.restype = None
     L.nbody_upload.argtypes = [vp, sz, vp, vp, vp, vp]
     L.nbody_download.argtypes = [vp, vp, vp, vp, vp]
+    L.nbody_download_own.argtypes = [vp, vp, vp, vp, vp]
     L.nbody_step.argtypes = [vp, d, d, d, i]
     L.nbody_step_host.argtypes = [vp, sz, vp, vp, vp, vp, d, d, d, i]
     L.nbody_kick1_drift.argtypes = [vp, d]

@@ -40,25 +40,31 @@ function installGpuIntegrate(physics, CONFIG, addon, opts = {}) {
   const S = { pm: new Arr(4 * capacity), vel: new Arr(4 * capacity), acc: new Arr(4 * capacity), temp: new Arr(capacity),
               radius: new Arr(capacity), list: null, n: 0, first: null, last: null, bound: [], binds: 0 };
   const pairScratch = new Uint32Array(2);                // only the count is needed here
-  const AXES = ['x', 'y', 'z'];
-
-  function viewVector(v, name, row) {                    // v.x, v.y, v.z <-> S[name][4 row + 0..2]
-    for (let k = 0; k < 3; k++) {
-      const o = 4 * row + k;
-      Object.defineProperty(v, AXES[k], { get: () => S[name][o], set: (val) => { S[name][o] = val; }, configurable: true, enumerable: true });
-    }
+  function viewNumber(obj, key, name, o) {               // obj[key] <-> S[name][o]
+    Object.defineProperty(obj, key, { get: () => S[name][o], set: (val) => { S[name][o] = val; }, configurable: true, enumerable: true });
   }
 
-  function plainVector(v) {                              // back to ordinary numbers (the current values)
-    for (let k = 0; k < 3; k++) {
-      Object.defineProperty(v, AXES[k], { value: v[AXES[k]], writable: true, configurable: true, enumerable: true });
-    }
+  function plainNumber(obj, key, value) {                // back to an ordinary data property
+    Object.defineProperty(obj, key, { value: value, writable: true, configurable: true, enumerable: true });
+  }
+
+  function viewVector(v, name, row) {                    // v.x, v.y, v.z <-> S[name][4 row + 0..2]
+    viewNumber(v, 'x', name, 4 * row);
+    viewNumber(v, 'y', name, 4 * row + 1);
+    viewNumber(v, 'z', name, 4 * row + 2);
+  }
+
+  function plainVector(v) {
+    const x = v.x, y = v.y, z = v.z;
+    plainNumber(v, 'x', x);
+    plainNumber(v, 'y', y);
+    plainNumber(v, 'z', z);
   }
 
   function release(b) {
     plainVector(b.pos); plainVector(b.vel); plainVector(b.acc);
-    Object.defineProperty(b, 'mass', { value: b.mass, writable: true, configurable: true, enumerable: true });
-    Object.defineProperty(b, 'temperature', { value: b.temperature, writable: true, configurable: true, enumerable: true });
+    plainNumber(b, 'mass', b.mass);
+    plainNumber(b, 'temperature', b.temperature);
   }
 
   // Bind `bodies` to rows 0..n-1.  Values are read through whatever the bodies carry now (views of their OLD rows, or plain
@@ -85,8 +91,8 @@ function installGpuIntegrate(physics, CONFIG, addon, opts = {}) {
     for (let i = 0; i < n; i++) {
       const b = bodies[i];
       viewVector(b.pos, 'pm', i); viewVector(b.vel, 'vel', i); viewVector(b.acc, 'acc', i);
-      Object.defineProperty(b, 'mass', { get: () => S.pm[4 * i + 3], set: (val) => { S.pm[4 * i + 3] = val; }, configurable: true, enumerable: true });
-      Object.defineProperty(b, 'temperature', { get: () => S.temp[i], set: (val) => { S.temp[i] = val; }, configurable: true, enumerable: true });
+      viewNumber(b, 'mass', 'pm', 4 * i + 3);
+      viewNumber(b, 'temperature', 'temp', i);
       S.bound.push(b);
     }
     S.list = bodies; S.n = n; S.first = n > 0 ? bodies[0] : null; S.last = n > 0 ? bodies[n - 1] : null;

@@ -139,6 +139,8 @@ struct nbody_ctx {
     bool small_path = true;         // NBODY_SMALL at create: one-cluster multi-step kernel for n <= kSmallMaxN (small.cuh)
     bool detect_masses = false;     // upload in flight: pack_pos_kernel compares every mass with uniform_mass
     void* step_rec_out = nullptr;   // nbody_step_host -> launch_small_steps: where the cluster kernel also writes the final state
+    bool upload_sharded = false;    // the last upload packed every shard's own slice into every rank's buffers (several devices, peer mappings)
+    long long upload_h2d_bytes = 0; // host->device bytes this process copied in the last upload
     bool upload_deferred = false;   // the last upload took the small-system path and returned without a synchronise
     bool detect_pending = false;    // ... so nobody has read the detection count yet: resolve_mass_detection() does
                                     // before the first consumer of `uniform` (a force launch of the large kernels, nbody_get_info)

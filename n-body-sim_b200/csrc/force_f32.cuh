@@ -66,17 +66,20 @@ __device__ __forceinline__ float rsqrt_approx(float x)
     return r;
 }
 
+// Shapes re-measured after the layout change of round 2 (profiles/r2b_variants.jsonl, N=1M, G interactions/s): general masses
+// unroll 12 at 3 CTAs/SM 2,619 (unroll 8: 2,552, unroll 16 at 2 CTAs: 2,356, unbounded registers: 2,471); equal masses unroll 8
+// at 2 CTAs/SM 2,866 (unroll 16: 2,745, unbounded: 2,633).
 #ifndef NB_F32_UNROLL
-#define NB_F32_UNROLL 16
+#define NB_F32_UNROLL 12
 #endif
 #ifndef NB_F32_LOOP_FORM
 #define NB_F32_LOOP_FORM 0  // how consume_tile states its shared-memory loads (0: LDS.128 per plane and quad, re-stated per i-body; 1: hoisted; 2: LDS.64 per couple)
 #endif
 #ifndef NB_F32_MIN_CTAS
-#define NB_F32_MIN_CTAS 1   // __launch_bounds__ second argument of force_f32_kernel: general masses ...
+#define NB_F32_MIN_CTAS 3   // __launch_bounds__ second argument of force_f32_kernel: general masses ...
 #endif
 #ifndef NB_F32_MIN_CTAS_UNIFORM
-#define NB_F32_MIN_CTAS_UNIFORM 1  // ... and the equal-mass instances
+#define NB_F32_MIN_CTAS_UNIFORM 2  // ... and the equal-mass instances
 #endif
 constexpr int kF32Unroll = NB_F32_UNROLL;  // j-pairs per inner-loop iteration
 // TP = j-PAIRS per ring stage: kF32TilePairs (512 bodies, 8 KiB) for large systems, kF32SmallTilePairs (128 bodies,

@@ -46,11 +46,17 @@ namespace nb {
 #ifndef NB_SYM_STAGES
 #define NB_SYM_STAGES 4
 #endif
-#ifndef NB_SYM32_UNROLL
-#define NB_SYM32_UNROLL 2
+// rotation steps per inner-loop iteration, by kernel variant.  Measured at N=1M (profiles/r2b_variants.jsonl, r2c_variants.jsonl;
+// G interactions/s): equal masses, 8 bodies per thread: 4,240 / 4,061 / 4,109 / 4,183 / 4,187 / 3,403 with 1 / 2 / 4 / 8 / 16 / 32;
+// general masses, 8 per thread: 3,541 / 3,608 with 1 / 16; 4 per thread (3 CTAs per SM): 3,169 / 3,374 / 3,469 / 3,489 / 3,526 with
+// 1 / 2 / 4 / 8 / 16 (general) and 3,859 / 3,920 with 8 / 32 (equal masses).
+#ifndef NB_SYM32_UNROLL_EQUAL
+#define NB_SYM32_UNROLL_EQUAL 1
+#endif
+#ifndef NB_SYM32_UNROLL_GENERAL
+#define NB_SYM32_UNROLL_GENERAL 16
 #endif
 constexpr int kSym32Stages = NB_SYM_STAGES;    // ring depth, 8 KiB (one position tile) per stage
-constexpr int kSym32Unroll = NB_SYM32_UNROLL;  // rotation steps per inner-loop iteration
 constexpr int kSym32StageBytes = 4 * kPosTile * 4;
 constexpr size_t force_f32_sym_smem_bytes() { return size_t(kSym32Stages) * kSym32StageBytes + kSym32Stages * (2 * 8 + 8); }
 
@@ -97,7 +103,8 @@ __device__ __forceinline__ void sym_stage(const float* __restrict__ tp, const in
         const int grp = (gi + 2 * warp) & 7;  // the four warps start on different groups
         const float* px = tp + grp * 64;
         f32x2 gx = 0ull, gy = 0ull, gz = 0ull;  // sum over this warp's i-bodies of w * m_i * d for the couple this lane holds
-#pragma unroll kSym32Unroll
+        constexpr int kUnroll = UNIFORM ? (R == 8 ? NB_SYM32_UNROLL_EQUAL : 32) : NB_SYM32_UNROLL_GENERAL;
+#pragma unroll kUnroll
         for (int q = 0; q < 32; ++q) {
             const int o = 2 * ((lane + q) & 31);
             const float2 X = *reinterpret_cast<const float2*>(px + o);

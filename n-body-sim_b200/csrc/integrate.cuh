@@ -98,6 +98,56 @@ __global__ void pack_pos_kernel(const Real* aos, Real* pos_a, Real* pos_b, size_
     }
 }
 
+// Several devices with peer mappings: every shard packs ITS OWN slice [i_begin, i_begin + n_local) of the host array -- `aos`
+// holds that slice only -- into BOTH position buffers of EVERY rank (peer stores), so the host->device traffic of an upload
+// is one copy of the array in total instead of one per device.  Same pads, same mass detection, same block sums as above.
+template <typename Real> struct PackDst {
+    Real* p[2 * kMaxPeers];
+    int n;
+};
+template <typename Real>
+__global__ void pack_pos_shard_kernel(const Real* aos, PackDst<Real> dst, size_t i_begin, size_t n_local, size_t n, Real pad_x, Real m0,
+                                      unsigned* detect, MassOutlier* outliers, double* mass_sums)
+{
+    const size_t il = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    const size_t i = i_begin + il;
+    double am = 0.0;
+    if (il < n_local) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const Real v = i < n ? aos[4 * il + c] : (c == 0 ? (sizeof(Real) == 8 ? pad_x * Real(1 + (i - n)) : pad_x) : Real(0));
+            const size_t at = pm_index<Real>(i, c);
+            for (int k = 0; k < dst.n; ++k) dst.p[k][at] = v;
+            if (c == 3) am = fabs(double(v));
+            if (c == 3 && detect != nullptr && i < n && !(v == m0)) {
+                const bool finite = v - v == Real(0);
+                const unsigned k = atomicAdd(detect, finite ? 1u : unsigned(kMaxOutliers) + 1u);
+                if (finite && k < unsigned(kMaxOutliers)) outliers[k] = MassOutlier{unsigned(i), float(v - m0)};
+            }
+        }
+    }
+    if (mass_sums == nullptr) return;
+    __shared__ double wsum[8];
+    for (int o = 16; o > 0; o >>= 1) am += __shfl_xor_sync(0xffffffffu, am, o);
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = am;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < int(blockDim.x >> 5); ++w) t += wsum[w];
+        mass_sums[blockIdx.x] = t;
+    }
+}
+
+// one shard's own range of the device positions -> the same range of the host AoS (nbody_download_own)
+template <typename Real>
+__global__ void unpack_pos_range_kernel(const Real* pos, Real* aos, size_t i_begin, size_t count)
+{
+    const size_t k = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (k >= count) return;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) aos[4 * k + c] = pos[pm_index<Real>(i_begin + k, c)];
+}
+
 // Small systems (nbody_upload / nbody_download with at most kSmallIoMaxN bodies on one device): the host arrays travel as
 // ONE record [pos_mass 4n | vel 4n | acc 4n | temp n] through pinned memory, so a call is one copy + one kernel instead of
 // four copies, three memsets and a kernel -- the per-frame flow of the JS shim (upload, step, download every frame at the

@@ -17,13 +17,12 @@
 
 
 #ifndef NB_UNIFORM_UNROLL
-#define NB_UNIFORM_UNROLL 16
+#define NB_UNIFORM_UNROLL 8
 #endif
 constexpr int kUniUnroll = NB_UNIFORM_UNROLL;  // inner-loop unroll of the equal-mass force kernel
-// i-bodies per thread of the pairs-once fp32 pass.  Measured at N=1M (profiles/r2a_sym_lab.jsonl): equal masses 4,057 G
-// interactions/s with 8 (168 registers, 2 CTAs/SM) against 3,805 with 4; general masses 3,334 with 8 (the eight extra mass
-// registers spill) against 3,370 with 4 (128 registers, 3 CTAs/SM).
-constexpr int kSym32EqualMassR = 8, kSym32GeneralR = 4;
+// i-bodies per thread of the pairs-once fp32 pass: 8 (168 registers, 2 CTAs/SM) beats 4 (128 registers, 3 CTAs/SM) for both
+// mass variants once each runs at its best unroll (force_f32_sym.cuh; N=1M: 4,240 against 3,920 and 3,608 against 3,526).
+constexpr int kSym32EqualMassR = 8, kSym32GeneralR = 8;
 constexpr int kSym32DefaultMinN = 32768;            // smallest system that takes it (below: too few units for the SMs)
 
 namespace {
@@ -253,6 +252,12 @@ template <typename F> int for_each_f64_kernel(F&& f, nbody_ctx* c)
     return NBODY_OK;
 }
 
+template <typename F> void pick_f32_sym_kernel(int R, bool uniform, F&& f)
+{
+    if (R == 8) return uniform ? f(force_f32_sym_kernel<8, true>) : f(force_f32_sym_kernel<8, false>);
+    return uniform ? f(force_f32_sym_kernel<4, true>) : f(force_f32_sym_kernel<4, false>);
+}
+
 int set_kernel_attrs(nbody_ctx* c)
 {
     const int sm32 = int(force_f32_smem_bytes());
@@ -266,6 +271,14 @@ int set_kernel_attrs(nbody_ctx* c)
                                     [&](auto kernel) { e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm32); });
                     if (e != cudaSuccess) return fail(c, NBODY_ECUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
                 }
+    for (int R : {4, 8})
+        for (int uni = 0; uni < 2; ++uni) {
+            cudaError_t e = cudaSuccess;
+            pick_f32_sym_kernel(R, uni != 0, [&](auto kernel) {
+                e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(force_f32_sym_smem_bytes()));
+            });
+            if (e != cudaSuccess) return fail(c, NBODY_ECUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        }
     CU(c, cudaFuncSetAttribute(small_step_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(small_smem_bytes<float>())));
     CU(c, cudaFuncSetAttribute(small_step_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(small_smem_bytes<double>())));
     CU(c, cudaFuncSetAttribute(medium_step_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(medium_smem_bytes<float>())));
@@ -637,6 +650,7 @@ extern "C" int nbody_get_info(nbody_ctx* c, nbody_info* o)
     o->f32_symmetric = c->sym32_run;
     o->f32_sym_bodies_per_thread = c->sym32_run > 0 ? c->sym32_R : 0;
     o->f32_sym_last_pass = c->sym32_used ? 1 : 0;
+    o->upload_h2d_bytes = c->upload_h2d_bytes;
     return NBODY_OK;
 }
 
@@ -662,6 +676,15 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
     }
     const bool want_mass = sizeof(Real) == 4 && c->sym32_allowed && n >= c->sym32_min_n;
     double small_mass = 0.0;
+    // several devices with peer mappings: each shard uploads and packs its own slice only (pack_pos_shard_kernel)
+    const bool sharded = c->world > 1 && c->p2p && env_int("NBODY_SHARDED_UPLOAD", 1) != 0;
+    c->upload_sharded = sharded;
+    c->upload_h2d_bytes = 0;
+    if (sharded && !c->rank_mode)  // (one process: a shard's pack stores into the other shards' buffers -- let them go idle first)
+        for (Shard& s : c->shards) {
+            CU(c, cudaSetDevice(s.device));
+            CU(c, cudaStreamSynchronize(s.stream));
+        }
     for (Shard& s : c->shards) {
         CU(c, cudaSetDevice(s.device));
         s.n_local = c->n_pad / c->world;
@@ -694,9 +717,24 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
                 for (size_t i = 0; i < n; ++i) t += std::fabs(double(pm[4 * i + 3]));
                 small_mass = t;
             }
+        } else if (sharded) {
+        // positions + masses: the OWN slice of the host AoS -> staging -> every rank's device layout (both buffers, peer stores)
+        if (s.n_local_real) CU(c, cudaMemcpyAsync(s.stage, pm + 4 * lo, s.n_local_real * v4, cudaMemcpyHostToDevice, s.stream));
+        c->upload_h2d_bytes += (long long)(s.n_local_real * v4);
+        if (c->detect_masses) CU(c, cudaMemsetAsync(s.outlier_count, 0, sizeof(unsigned), s.stream));
+        PackDst<Real> dst;
+        dst.n = 0;
+        for (int r = 0; r < c->world; ++r) {
+            dst.p[dst.n++] = static_cast<Real*>(s.peer_pos[r][0]);
+            dst.p[dst.n++] = static_cast<Real*>(s.peer_pos[r][1]);
+        }
+        pack_pos_shard_kernel<Real><<<unsigned((s.n_local + 255) / 256), 256, 0, s.stream>>>(
+            static_cast<const Real*>(s.stage), dst, s.i_begin, s.n_local, n, Real(sizeof(Real) == 8 ? 1e150 : 1e18), Real(c->uniform_mass),
+            c->detect_masses ? s.outlier_count : nullptr, s.outliers, want_mass ? s.mass_sums + s.i_begin / 256 : nullptr);
         } else {
         // positions + masses: host AoS -> staging -> device layout (both buffers)
         CU(c, cudaMemcpyAsync(s.stage, pm, n * v4, cudaMemcpyHostToDevice, s.stream));
+        c->upload_h2d_bytes += (long long)(n * v4);
         const unsigned blocks = unsigned((c->n_pad + 255) / 256);
         const bool detect = c->detect_masses && &s == &c->shards[0];  // every shard packs the same array: one looks
         if (detect) CU(c, cudaMemsetAsync(s.outlier_count, 0, sizeof(unsigned), s.stream));
@@ -704,6 +742,8 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
                                                            static_cast<Real*>(s.pos[1]), n, c->n_pad, Real(sizeof(Real) == 8 ? 1e150 : 1e18), Real(c->uniform_mass),
                                                            detect ? s.outlier_count : nullptr, s.outliers,
                                                            want_mass && &s == &c->shards[0] ? s.mass_sums : nullptr);
+        }
+        if (!small_io) {
         if (s.accfix) CU(c, cudaMemsetAsync(s.accfix, 0, (3 * c->n_pad + 1) * sizeof(unsigned long long), s.stream));  // (zero unless a pass was abandoned)
         c->launches++;
         CU(c, cudaGetLastError());
@@ -714,6 +754,7 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
             CU(c, cudaMemcpyAsync(s.vel, vel + 4 * lo, s.n_local_real * v4, cudaMemcpyHostToDevice, s.stream));
             if (acc) CU(c, cudaMemcpyAsync(s.acc, acc + 4 * lo, s.n_local_real * v4, cudaMemcpyHostToDevice, s.stream));
             if (temp) CU(c, cudaMemcpyAsync(s.temp, temp + lo, s.n_local_real * sizeof(Real), cudaMemcpyHostToDevice, s.stream));
+            c->upload_h2d_bytes += (long long)(s.n_local_real * (v4 * (acc ? 2 : 1) + (temp ? sizeof(Real) : 0)));
         }
         }
         // per-chunk partial sums
@@ -737,11 +778,27 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
     }
     c->sum_abs_mass = 0.0;
     if (want_mass) {  // sum |m|, block sums added in index order: the same number on every rank and in every run
-        Shard& s0 = c->shards[0];
-        CU(c, cudaSetDevice(s0.device));
         std::vector<double> sums((c->n_pad + 255) / 256);
-        CU(c, cudaMemcpyAsync(sums.data(), s0.mass_sums, sums.size() * sizeof(double), cudaMemcpyDeviceToHost, s0.stream));
-        CU(c, cudaStreamSynchronize(s0.stream));
+        if (!sharded) {
+            Shard& s0 = c->shards[0];
+            CU(c, cudaSetDevice(s0.device));
+            CU(c, cudaMemcpyAsync(sums.data(), s0.mass_sums, sums.size() * sizeof(double), cudaMemcpyDeviceToHost, s0.stream));
+            CU(c, cudaStreamSynchronize(s0.stream));
+        } else if (!c->rank_mode) {  // every shard holds the sums of its own blocks
+            for (Shard& s : c->shards) {
+                CU(c, cudaSetDevice(s.device));
+                const size_t b0 = s.i_begin / 256, nb = s.n_local / 256;
+                CU(c, cudaMemcpyAsync(sums.data() + b0, s.mass_sums + b0, nb * sizeof(double), cudaMemcpyDeviceToHost, s.stream));
+                CU(c, cudaStreamSynchronize(s.stream));
+            }
+        } else {                     // ... of which the other ranks' arrive by all-gather
+            Shard& s = c->shards[0];
+            CU(c, cudaSetDevice(s.device));
+            const size_t nb = s.n_local / 256;
+            NC(c, nccl().AllGather(s.mass_sums + size_t(s.rank) * nb, s.mass_sums, nb * sizeof(double), ncclUint8_, s.comm, s.stream));
+            CU(c, cudaMemcpyAsync(sums.data(), s.mass_sums, sums.size() * sizeof(double), cudaMemcpyDeviceToHost, s.stream));
+            CU(c, cudaStreamSynchronize(s.stream));
+        }
         for (double v : sums) c->sum_abs_mass += v;
     }
     for (Shard& s : c->shards) {
@@ -751,9 +808,22 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
     return NBODY_OK;
 }
 
-template <typename Real> int download_t(nbody_ctx* c, Real* pm, Real* vel, Real* acc, Real* temp)
+template <typename Real> int download_t(nbody_ctx* c, Real* pm, Real* vel, Real* acc, Real* temp, bool own_only = false)
 {
     const size_t v4 = 4 * sizeof(Real);
+    if (own_only && pm && c->n) {  // positions of the own range(s) only, like vel / acc / temp below
+        for (Shard& s : c->shards) {
+            if (s.n_local_real == 0) continue;
+            CU(c, cudaSetDevice(s.device));
+            const size_t lo = std::min(s.i_begin, c->n);
+            unpack_pos_range_kernel<Real><<<unsigned((s.n_local_real + 255) / 256), 256, 0, s.stream>>>(static_cast<const Real*>(s.pos[c->cur]),
+                                                                                                   static_cast<Real*>(s.stage), lo, s.n_local_real);
+            c->launches++;
+            CU(c, cudaGetLastError());
+            CU(c, cudaMemcpyAsync(pm + 4 * lo, s.stage, s.n_local_real * v4, cudaMemcpyDeviceToHost, s.stream));
+        }
+        pm = nullptr;
+    }
     if (c->shards[0].io_host && c->n <= kSmallIoMaxN) {
         // small system on one device: one kernel gathers the state into a record, one copy, one synchronise (integrate.cuh)
         Shard& s = c->shards[0];
@@ -892,17 +962,56 @@ int build_sym32_table(nbody_ctx* c)
 // corrections, and with it every bit of the result, does not depend on the order the atomics landed in.
 int finish_mass_detection(nbody_ctx* c)
 {
-    Shard& s0 = c->shards[0];
-    CU(c, cudaSetDevice(s0.device));
-    unsigned count = 0;
-    CU(c, cudaMemcpy(&count, s0.outlier_count, sizeof(unsigned), cudaMemcpyDeviceToHost));
     // (exceptions are corrected in the fp32 epilogue only: an fp64 context takes the sweep for exactly equal masses)
     const size_t max_out = c->prec == NBODY_F64 ? 0 : std::min<size_t>(size_t(std::max(0, env_int("NBODY_OUTLIERS", kMaxOutliers))), kMaxOutliers);
+    struct Found {
+        unsigned count;
+        MassOutlier list[kMaxOutliers];
+    };
+    std::vector<Found> found;
+    auto read_shard = [&](Shard& s, Found& f) -> int {
+        CU(c, cudaSetDevice(s.device));
+        CU(c, cudaMemcpy(&f.count, s.outlier_count, sizeof(unsigned), cudaMemcpyDeviceToHost));
+        const unsigned k = std::min<unsigned>(f.count, kMaxOutliers);
+        if (k) CU(c, cudaMemcpy(f.list, s.outliers, k * sizeof(MassOutlier), cudaMemcpyDeviceToHost));
+        return NBODY_OK;
+    };
+    if (!c->upload_sharded) {           // one shard looked at the whole array
+        found.resize(1);
+        const int rc = read_shard(c->shards[0], found[0]);
+        if (rc != NBODY_OK) return rc;
+    } else if (!c->rank_mode) {         // every shard looked at its own slice
+        found.resize(c->shards.size());
+        for (size_t k = 0; k < c->shards.size(); ++k) {
+            const int rc = read_shard(c->shards[k], found[k]);
+            if (rc != NBODY_OK) return rc;
+        }
+    } else {                            // ... and the other ranks' findings arrive by all-gather
+        found.resize(c->world);
+        Shard& s = c->shards[0];
+        Found mine;
+        memset(&mine, 0, sizeof mine);
+        int rc = read_shard(s, mine);
+        if (rc != NBODY_OK) return rc;
+        Found* dev = nullptr;
+        CU(c, cudaMalloc(&dev, sizeof(Found) * c->world));
+        auto gather = [&]() -> int {
+            CU(c, cudaMemcpyAsync(dev + c->my_rank, &mine, sizeof(Found), cudaMemcpyHostToDevice, s.stream));
+            NC(c, nccl().AllGather(dev + c->my_rank, dev, sizeof(Found), ncclUint8_, s.comm, s.stream));
+            CU(c, cudaMemcpyAsync(found.data(), dev, sizeof(Found) * c->world, cudaMemcpyDeviceToHost, s.stream));
+            CU(c, cudaStreamSynchronize(s.stream));
+            return NBODY_OK;
+        };
+        rc = gather();
+        cudaFree(dev);
+        if (rc != NBODY_OK) return rc;
+    }
+    size_t count = 0;
+    for (const Found& f : found) count += f.count;
     if (count > max_out) return NBODY_OK;  // too many different masses: the general kernel
     c->uniform = true;
     if (count == 0) return NBODY_OK;
-    c->outliers.resize(count);
-    CU(c, cudaMemcpy(c->outliers.data(), s0.outliers, count * sizeof(MassOutlier), cudaMemcpyDeviceToHost));
+    for (const Found& f : found) c->outliers.insert(c->outliers.end(), f.list, f.list + f.count);
     std::sort(c->outliers.begin(), c->outliers.end(), [](const MassOutlier& a, const MassOutlier& b) { return a.index < b.index; });
     for (Shard& s : c->shards) {
         CU(c, cudaSetDevice(s.device));
@@ -983,6 +1092,14 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     if (rc == NBODY_OK && c->f64_sym_k > 0) rc = ensure_sym_buffers(c);
     if (rc == NBODY_OK) rc = build_sym32_table(c);
     return rc;
+}
+
+extern "C" int nbody_download_own(nbody_ctx* c, void* pos_mass, void* vel, void* acc, void* temp)
+{
+    if (!c) return NBODY_EINVAL;
+    if (c->n == 0) return fail(c, NBODY_EINVAL, "download before upload");
+    return c->prec == NBODY_F32 ? download_t<float>(c, (float*)pos_mass, (float*)vel, (float*)acc, (float*)temp, true)
+                                : download_t<double>(c, (double*)pos_mass, (double*)vel, (double*)acc, (double*)temp, true);
 }
 
 extern "C" int nbody_download(nbody_ctx* c, void* pos_mass, void* vel, void* acc, void* temp)
@@ -1119,12 +1236,6 @@ int start_force_timing(nbody_ctx* c, Shard& s)
     }
     CU(c, cudaEventRecord(s.ev[s.ev_used], s.stream));
     return NBODY_OK;
-}
-
-template <typename F> void pick_f32_sym_kernel(int R, bool uniform, F&& f)
-{
-    if (R == 8) return uniform ? f(force_f32_sym_kernel<8, true>) : f(force_f32_sym_kernel<8, false>);
-    return uniform ? f(force_f32_sym_kernel<4, true>) : f(force_f32_sym_kernel<4, false>);
 }
 
 // The fp32 pairs-once pass (force_f32_sym.cuh): persistent CTAs work through this device's share of the unit table and add

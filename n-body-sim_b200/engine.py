@@ -94,8 +94,9 @@ class Engine:
         check(self._L.nbody_upload(self._ctx, n, _ptr(pm), _ptr(v), _ptr(a), _ptr(t)), self._ctx)
         self.n = n
 
-    def download(self, pos_mass=True, vel=True, acc=True, temp=False, out=None):
-        """Returns dict of arrays.  `out` may hold preallocated arrays to fill."""
+    def download(self, pos_mass=True, vel=True, acc=True, temp=False, out=None, own_only=False):
+        """Returns dict of arrays.  `out` may hold preallocated arrays to fill.  own_only: pos_mass too is read back for
+        the own range only (nbody_download_own; in rank mode the ranks together read every body once)."""
         n = self.n
         out = dict(out or {})
         want = {"pos_mass": pos_mass, "vel": vel, "acc": acc, "temp": temp}
@@ -105,8 +106,8 @@ class Engine:
         for k, a in out.items():
             if a.dtype != self.dtype or not a.flags.c_contiguous:
                 raise ValueError(f"out[{k}] must be contiguous {self.dtype}")
-        check(self._L.nbody_download(self._ctx, _ptr(out.get("pos_mass")), _ptr(out.get("vel")),
-                                     _ptr(out.get("acc")), _ptr(out.get("temp"))), self._ctx)
+        fn = self._L.nbody_download_own if own_only else self._L.nbody_download
+        check(fn(self._ctx, _ptr(out.get("pos_mass")), _ptr(out.get("vel")), _ptr(out.get("acc")), _ptr(out.get("temp"))), self._ctx)
         return out
 
     # -- hot path ------------------------------------------------------------------

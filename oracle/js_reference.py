@@ -695,6 +695,38 @@ class JSObject:
         self.__dict__[key] = value
 
 
+class _ObjectNS:
+    """`Object.defineProperty(obj, key, descriptor)` for the shim's typed-array-backed Body views (addon/physics_shim.js):
+    an accessor descriptor ({get, set}) or a data descriptor ({value}) on ONE object.  Python keeps accessors on classes, so
+    the object moves to a private subclass of its class that carries the properties (slots classes included)."""
+
+    @staticmethod
+    def defineProperty(obj, key, desc):
+        cls = type(obj)
+        if not cls.__dict__.get("_js_own_class", False):
+            body = {"_js_own_class": True}
+            if not hasattr(obj, "__dict__"):
+                body["__slots__"] = ()
+            sub = type(cls.__name__, (cls,), body)
+            obj.__class__ = sub
+            cls = sub
+        get, set_ = desc.get, desc.set
+        if get is not None or set_ is not None:
+            def fget(self, _g=get):
+                return _g()
+
+            def fset(self, value, _s=set_):
+                if _s is None:
+                    raise TypeError(f"js: property {key!r} has no setter")
+                _s(value)
+            setattr(cls, key, property(fget, fset))
+        else:
+            if key in cls.__dict__:
+                delattr(cls, key)                # the accessor goes; the base class's slot / the instance dict takes over
+            object.__setattr__(obj, key, desc.value)
+        return obj
+
+
 def _bind(fn, obj):
     """`obj.name = function () { ... this ... }`: calls through obj see it as `this`."""
     import types
@@ -1074,7 +1106,7 @@ def install_shim(reference: "Reference", addon, **opts):
     module = JSObject({})
     ns = {"JSArray": JSArray, "JSObject": JSObject, "JSGetter": JSGetter, "_bind": _bind, "_div": _div, "Math": reference.Math,
           "Float64Array": typed_array("float64"), "Float32Array": typed_array("float32"), "Uint32Array": typed_array("uint32"),
-          "module": module}
+          "Object": _ObjectNS, "module": module}
     exec(compile(transliterate(src), "<physics_shim.js transliterated>", "exec"), ns)
     return module.exports.installGpuIntegrate(reference.physics, reference.CONFIG, addon, JSObject(opts))
 

@@ -68,6 +68,11 @@ if __name__ == "__main__":
     if which == "onesided":      # a kernel-variant build (NBODY_LIB) of the one-sided sweep
         for general in (False, True):
             run("uniform_cube", N, general, {"NBODY_F32_SYM": 0}, label="one-sided " + tag)
+    if which == "symx":          # the other bodies-per-thread choice of each mass variant
+        run("uniform_cube", N, False, {"NBODY_F32_SYM_R": 4}, label="sym R4 " + tag)
+        run("uniform_cube", N, True, {"NBODY_F32_SYM_R": 8}, label="sym R8 " + tag)
+    if which == "ncu":           # one short run for the profiler: one warm step, one profiled
+        run("uniform_cube", N, os.environ.get("LAB_GENERAL", "0") == "1", {}, steps=1, label="ncu " + tag)
     if which == "sym":           # ... and of the pairs-once pass, default bodies per thread
         for general in (False, True):
             run("uniform_cube", N, general, {}, label="sym " + tag)

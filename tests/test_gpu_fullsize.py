@@ -32,6 +32,30 @@ def test_f32_1m_uniform_cube_sampled_vs_oracle(nb, oracle):
     assert np.abs(net).max() < 1e-5 * scale          # sum m_i a_i = 0 (idx:282-288)
 
 
+def test_f32_4m_cold_collapse_sampled_vs_oracle(nb, oracle):
+    """Config 5's scene at full size on ONE GPU: N=4,194,304 cold collapse, G=1, eps=0.005 -- one force pass
+    (1.76e13 interactions), sampled rows against the oracle's fp64 sums over all N bodies, and sum m_i a_i = 0."""
+    s = nb.scenes.cold_collapse(4194304)
+    pm32 = s.pos_mass.astype(np.float32)
+    with nb.Engine(s.n, precision="f32") as e:
+        e.upload(pm32, np.zeros((s.n, 4), np.float32))
+        e.force(s.G, s.softening)
+        acc = e.download()["acc"].astype(np.float64)
+        info = e.info()
+    assert info["f32_sym_last_pass"] == 1 and info["uniform_mass"] == 1
+    idx = np.unique(np.concatenate([[0, 1, 511, 512, 1023, 1024, s.n - 1], np.random.default_rng(5).integers(0, s.n, 25)]))
+    ref = oracle.acc_subset(pm32.astype(np.float64), idx, s.G, s.softening)
+    err = norm_rel_err(acc[idx], ref)
+    per_body = np.linalg.norm(acc[idx, :3] - ref[:, :3], axis=1) / np.linalg.norm(ref[:, :3], axis=1)
+    print(f"4M cold collapse f32: sampled norm-rel err {err:.3e}, worst per-body {per_body.max():.3e}, "
+          f"pairs-once units of {info['f32_symmetric']} tiles, {info['f32_sym_bodies_per_thread']} bodies/thread")
+    assert err < 2e-5 and per_body.max() < 1e-4
+    assert np.isfinite(acc).all()
+    net = (pm32[:, 3:4].astype(np.float64) * acc[:, :3]).sum(axis=0)
+    scale = np.abs(pm32[:, 3:4] * acc[:, :3]).sum()
+    assert np.abs(net).max() < 1e-6 * scale          # sum m_i a_i = 0 (idx:282-288)
+
+
 def test_f32_two_galaxies_131072_conservation(nb):
     """Config 3 at full size, shortened to 200 steps here (bench/energy script runs 10k):
     momentum stays put and energy drift stays small."""

@@ -167,6 +167,90 @@ def test_shim_gravity_only_is_one_addon_call_per_integrate(oracle):
 
 
 @live
+def test_shim_binds_bodies_to_the_arrays_only_when_the_list_changes(oracle):
+    """Body.pos/vel/acc (and mass, temperature) are views of the addon's typed arrays, re-bound only on
+    spawn (idx:835), the 300-body shift of addBody (idx:240-242), a collision that edits the list (idx:383-389) and reset
+    (idx:745); a gravity-only integrate() is one addon call with no per-body work in between."""
+    page, dropin = _pages(7, _crowd(40, 11, 40.0, 0.2), collisions=False)
+    addon = Addon(lambda prec, cap: OracleEngine(oracle, cap))
+    handle = jr.install_shim(dropin, addon, collisions=False)
+    for _ in range(6):
+        page.integrate(0.008, 2)
+        dropin.integrate(0.008, 2)
+        _assert_same(dropin, page, exact=True)
+    assert handle.binds == 1 and addon.calls == {"stepHost": 12}
+    # the Vector3 objects are still the page's own; their fields read and write the arrays the addon works on
+    b = dropin.physics.bodies[3]
+    pos_object = b.pos
+    b.pos.x = 123.5
+    b.vel.addScaledVector(b.acc, 2.0)
+    b.temperature = 7.25
+    pb = page.physics.bodies[3]
+    pb.pos.x = 123.5
+    pb.vel.addScaledVector(pb.acc, 2.0)
+    pb.temperature = 7.25
+    page.integrate(0.008)
+    dropin.integrate(0.008)
+    _assert_same(dropin, page, exact=True)
+    assert handle.binds == 1 and dropin.physics.bodies[3].pos is pos_object
+    # spawn (idx:835): addBody -> one re-bind at the next call, none after
+    for r in (page, dropin):
+        r.add(2.0, (5.0, 1.0, -3.0), (0.1, 0.0, 0.2), "ice", 4.0)
+    for _ in range(3):
+        page.integrate(0.008)
+        dropin.integrate(0.008)
+        _assert_same(dropin, page, exact=True)
+    assert handle.binds == 2
+    # the 300-body shift (idx:240-242): same array, same length, other bodies
+    for r in (page, dropin):
+        r.CONFIG.maxBodies = len(r.physics.bodies)
+        r.add(1.5, (-8.0, 2.0, 9.0), (0.0, 0.3, 0.0), "metal", 0.0)
+    gone = dropin.physics.bodies        # (the list object is the same one)
+    assert len(page.physics.bodies) == 41 == len(dropin.physics.bodies)
+    page.integrate(0.008, 2)
+    dropin.integrate(0.008, 2)
+    _assert_same(dropin, page, exact=True)
+    assert handle.binds == 3 and dropin.physics.bodies is gone
+    # reset (idx:745): a new array
+    for r in (page, dropin):
+        r.CONFIG.maxBodies = 300
+        r.resetScenario("galaxy")
+    page.integrate(0.008, 2)
+    dropin.integrate(0.008, 2)
+    _assert_same(dropin, page, exact=True)
+    assert handle.binds == 4 and len(dropin.physics.bodies) == 151
+    # dispose: the bodies get plain numbers back
+    keep = dropin.physics.bodies[5]
+    x = keep.pos.x
+    handle.dispose()
+    keep.pos.x = x + 1.0
+    assert keep.pos.x == x + 1.0 and dropin.state()["pos_mass"][5, 0] == x + 1.0
+
+
+@live
+def test_shim_releases_bodies_that_left_the_list(oracle):
+    """A Body removed by a merge keeps its last values as plain numbers: a stale reference cannot alias another body's row."""
+    page, dropin = _pages(42, _crowd(70, 3, 5.0, 0.3), collisions=True)
+    addon = Addon(lambda prec, cap: OracleEngine(oracle, cap))
+    handle = jr.install_shim(dropin, addon)
+    before = list(dropin.physics.bodies)
+    for _ in range(80):
+        page.integrate(0.008)
+        dropin.integrate(0.008)
+    _assert_same(dropin, page, exact=True)
+    now = set(map(id, dropin.physics.bodies))
+    left = [b for b in before if id(b) not in now]
+    assert left and handle.binds > 1
+    snapshot = dropin.state()
+    for b in left:
+        b.pos.x += 1000.0                               # writes to a released body touch nothing else
+        b.temperature = 1e9
+    after = dropin.state()
+    for k in KEYS:
+        assert np.array_equal(snapshot[k], after[k]), k
+
+
+@live
 @pytest.mark.parametrize("mode", [None, "gpu-broad-phase"])
 @pytest.mark.parametrize("speed,nsteps", [(0.3, 80), (8.0, 25)])
 def test_shim_with_the_pages_own_collision_stage(oracle, mode, speed, nsteps):
