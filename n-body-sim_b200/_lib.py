@@ -50,7 +50,7 @@ class Info(ctypes.Structure):
 
 
 def build(force: bool = False) -> str:
-    """Compile libnbody.so (and the pipe microbenchmark) for sm_100a with nvcc."""
+    """Compile libnbody.so for sm_100a with nvcc."""
     args = ["make", "-C", CSRC, "-s"]
     if force:
         args.append("-B")

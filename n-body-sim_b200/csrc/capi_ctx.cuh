@@ -197,6 +197,13 @@ int fail(nbody_ctx* c, int code, const char* fmt, ...)
                         "%s: %s", #call, cudaGetErrorString(e_));                             \
     } while (0)
 
+// after a kernel launch: name the kernel and the device in the message
+#define CUK(ctx, what, dev)                                                                   \
+    do {                                                                                      \
+        cudaError_t e_ = cudaGetLastError();                                                  \
+        if (e_ != cudaSuccess) return fail(ctx, NBODY_ECUDA, "%s on device %d: %s", what, int(dev), cudaGetErrorString(e_)); \
+    } while (0)
+
 #define NC(ctx, call)                                                                         \
     do {                                                                                      \
         ncclResult_t r_ = (call);                                                             \
@@ -218,6 +225,7 @@ size_t gcd_sz(size_t a, size_t b) { return b ? gcd_sz(b, a % b) : a; }
 inline int check_ready(nbody_ctx* c, const char* what)
 {
     if (!c) return NBODY_EINVAL;
+    cudaGetLastError();  // a non-sticky error another library of the process left behind is not this call's (a fault of ours is sticky and stays)
     if (c->n == 0) return fail(c, NBODY_EINVAL, "%s before upload", what);
     return NBODY_OK;
 }

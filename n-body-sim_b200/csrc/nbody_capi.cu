@@ -731,6 +731,7 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
         pack_pos_shard_kernel<Real><<<unsigned((s.n_local + 255) / 256), 256, 0, s.stream>>>(
             static_cast<const Real*>(s.stage), dst, s.i_begin, s.n_local, n, Real(sizeof(Real) == 8 ? 1e150 : 1e18), Real(c->uniform_mass),
             c->detect_masses ? s.outlier_count : nullptr, s.outliers, want_mass ? s.mass_sums + s.i_begin / 256 : nullptr);
+        CUK(c, "pack_pos_shard_kernel", s.device);
         } else {
         // positions + masses: host AoS -> staging -> device layout (both buffers)
         CU(c, cudaMemcpyAsync(s.stage, pm, n * v4, cudaMemcpyHostToDevice, s.stream));
@@ -742,6 +743,7 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
                                                            static_cast<Real*>(s.pos[1]), n, c->n_pad, Real(sizeof(Real) == 8 ? 1e150 : 1e18), Real(c->uniform_mass),
                                                            detect ? s.outlier_count : nullptr, s.outliers,
                                                            want_mass && &s == &c->shards[0] ? s.mass_sums : nullptr);
+        CUK(c, "pack_pos_kernel", s.device);
         }
         if (!small_io) {
         if (s.accfix) CU(c, cudaMemsetAsync(s.accfix, 0, (3 * c->n_pad + 1) * sizeof(unsigned long long), s.stream));  // (zero unless a pass was abandoned)
@@ -1038,6 +1040,7 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     if (!c) return NBODY_EINVAL;
     if (n == 0 || n > c->capacity) return fail(c, NBODY_EINVAL, "upload: n=%zu outside 1..capacity=%zu", n, c->capacity);
     if (!pos_mass || !vel) return fail(c, NBODY_EINVAL, "upload: pos_mass and vel are required");
+    cudaGetLastError();  // (see check_ready)
     c->n = n;
     c->f64_sym_k = 0;
     if (c->prec == NBODY_F32) {

@@ -26,7 +26,8 @@ def main():
         dist.all_gather_object(out, obj)
         return out
 
-    for precision, n in (("f32", 70002), ("f64", 6001)):
+    os.environ["NBODY_F64_SYM"] = "0"     # (fp64 on ONE GPU would take the pairs-once pass: the same terms in another order)
+    for precision, n in (("f32", 70002), ("f64", 6000)):
         dt = np.float32 if precision == "f32" else np.float64
         s = nb.scenes.two_galaxies(n - n % 2)
         pm, vel, temp = s.astype(dt)
@@ -95,7 +96,7 @@ def main():
         eng.close()
     allf = [f for fs in gather(failures) for f in fs]
     if rank == 0:
-        print("RANK-MODE " + ("OK" if not allf else "FAIL: " + "; ".join(allf)), flush=True)
+        print("RANK-MODE " + ("OK" if not allf else "FAIL:\n  " + "\n  ".join(allf)), flush=True)
     dist.barrier()
     dist.destroy_process_group()
     sys.exit(1 if allf else 0)

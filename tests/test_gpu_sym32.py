@@ -159,7 +159,7 @@ def test_sym32_multi_gpu_same_bits(nb):
     ng = nb.device_count()
     if ng < 2:
         pytest.skip("needs >= 2 GPUs")
-    s, pm, vel = scene_arrays(nb, "two_galaxies", 70001, True)
+    s, pm, vel = scene_arrays(nb, "two_galaxies", 70002, True)
     outs = []
     for exchange in ("peer", "nccl"):
         for g in sorted({1, 2, min(ng, 4), min(ng, 8)}):
