@@ -157,6 +157,38 @@ NBODY_API int nbody_contacts(nbody_ctx* ctx, double margin, unsigned* pairs /* 2
  * every other, 2 the flagged bodies against each other (under half the bodies flagged)}. */
 NBODY_API int nbody_contact_stats(nbody_ctx* ctx, long long out[4]);
 
+/* ---- the page's COMPLETE step on the device (response included) ---- */
+
+#define NBODY_WORLD_MAX_BODIES 1024
+
+/* Turns an fp64 context on one GPU into the page's `physics` object (idx:233-237): besides positions, velocities,
+ * accelerations, temperatures and radii the device then keeps Body.id and Body.type of every body, PhysicsSystem.contactPairs
+ * and a seeded Math.random stream, and nbody_world_step runs PhysicsSystem.integrate(dt) WITH resolveCollisions, mergeBodies
+ * and fractureBodies (idx:247-262, 293-443) without returning to the host: one CTA, the state in shared memory, the
+ * collision stage bit-identical to the reference's statements in IEEE binary64 (csrc/page_world.cu).
+ * seed: the Math.random stand-in is a sequential splitmix64 stream (the oracles' stream); max_bodies = CONFIG.maxBodies
+ * (idx:57), at most NBODY_WORLD_MAX_BODIES and the context's capacity. */
+NBODY_API int nbody_world_enable(nbody_ctx* ctx, unsigned long long seed, size_t max_bodies);
+/* CONFIG.fractureThreshold, .minFragmentMass, .mergeTime (idx:62-64; defaults 25, 0.2, 0.5). */
+NBODY_API int nbody_world_config(nbody_ctx* ctx, double fracture_threshold, double min_fragment_mass, double merge_time);
+/* After nbody_upload: Body.id (here the Math.random draw the constructor spent, idx:210: a double in [0,1)), Body.type
+ * (0 rock, 1 metal, 2 ice) and Body.radius (idx:221) of the n bodies; empties the contact map like resetScenario (idx:745). */
+NBODY_API int nbody_world_set_bodies(nbody_ctx* ctx, const double* id, const int* type, const double* radius);
+/* nsteps x PhysicsSystem.integrate(dt), complete (collisions != 0) or with idx:256 removed (collisions == 0).
+ * Asynchronous; merges and fractures change the body count ON THE DEVICE: call nbody_world_sync before any other entry point. */
+NBODY_API int nbody_world_step(nbody_ctx* ctx, double dt, double G, double softening, int nsteps, int collisions);
+/* Synchronises; the context adopts the device's body count (nbody_download etc. then work on the new list).  Any output may
+ * be NULL: *n, id[n], type[n], radius[n], counters = {merges, fractures, overlapping pairs acted on, visuals.triggerFlash
+ * calls, visuals.spawnExplosion calls} since nbody_world_enable, the size of the contact map, the random stream's state. */
+NBODY_API int nbody_world_sync(nbody_ctx* ctx, size_t* n, double* id, int* type, double* radius, long long counters[5],
+                               size_t* n_contacts, unsigned long long* rng_state);
+/* PhysicsSystem.contactPairs as (lower id, higher id, accumulated contact time) triples, in no particular order. */
+NBODY_API int nbody_world_contacts(nbody_ctx* ctx, double* lo_hi_time /* 3*cap */, size_t cap, size_t* count);
+
+/* Test hook: y[k] = Math.pow(x[k], 1/3) as nbody_world_step evaluates Body.radius of merged bodies and fragments (idx:221):
+ * a double-double evaluation, correctly rounded (the device's pow() is a 2-ulp routine).  Host arrays. */
+NBODY_API int nbody_selftest_pow_third(nbody_ctx* ctx, const double* x, double* y, size_t n);
+
 /* ---- renderer feed: position history and ribbon trails ---- */
 
 /* Keep Body.history on the device: the last `depth` positions of every body,

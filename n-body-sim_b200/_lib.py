@@ -28,6 +28,8 @@ SYMBOLS = (
     "nbody_set_radius", "nbody_contacts", "nbody_contact_stats",
     "nbody_history_enable", "nbody_history_push", "nbody_history_remap", "nbody_history_download", "nbody_trail_ribbons",
     "nbody_snapshot_save", "nbody_snapshot_load", "nbody_set_materials", "nbody_render",
+    "nbody_world_enable", "nbody_world_config", "nbody_world_set_bodies", "nbody_world_step", "nbody_world_sync", "nbody_world_contacts",
+    "nbody_selftest_pow_third",
 )
 
 
@@ -112,6 +114,14 @@ def lib() -> ctypes.CDLL:
     ull = ctypes.c_ulonglong
     L.nbody_snapshot_save.argtypes = [vp, ctypes.c_char_p, ull, d, d, d]
     L.nbody_snapshot_load.argtypes = [vp, ctypes.c_char_p, ctypes.POINTER(ull), pd, pd, pd]
+    pi, pll = ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_longlong)
+    L.nbody_world_enable.argtypes = [vp, ull, sz]
+    L.nbody_world_config.argtypes = [vp, d, d, d]
+    L.nbody_world_set_bodies.argtypes = [vp, vp, vp, vp]
+    L.nbody_world_step.argtypes = [vp, d, d, d, i, i]
+    L.nbody_world_sync.argtypes = [vp, ctypes.POINTER(sz), vp, vp, vp, pll, ctypes.POINTER(sz), ctypes.POINTER(ull)]
+    L.nbody_world_contacts.argtypes = [vp, vp, sz, ctypes.POINTER(sz)]
+    L.nbody_selftest_pow_third.argtypes = [vp, vp, vp, sz]
     _lib = L
     return L
 

@@ -10,6 +10,7 @@
 
 extern "C" int nbody_set_radius(nbody_ctx* c, const void* radius)
 {
+    DeviceGuard device_guard_;
     int rc = check_ready(c, "set_radius");
     if (rc != NBODY_OK) return rc;
     if (!radius) {
@@ -261,6 +262,7 @@ int all_contacts(nbody_ctx* c, double margin, bool use_flags, std::vector<unsign
 
 extern "C" int nbody_contacts(nbody_ctx* c, double margin, unsigned* pairs, size_t cap, size_t* count)
 {
+    DeviceGuard device_guard_;
     int rc = check_ready(c, "contacts");
     if (rc != NBODY_OK) return rc;
     if (!count) return fail(c, NBODY_EINVAL, "contacts: count is required");
@@ -293,6 +295,7 @@ extern "C" int nbody_contacts(nbody_ctx* c, double margin, unsigned* pairs, size
 
 extern "C" int nbody_contact_stats(nbody_ctx* c, long long out[4])
 {
+    DeviceGuard device_guard_;
     if (!c || !out) return NBODY_EINVAL;
     for (int k = 0; k < 4; ++k) out[k] = c->cstat[k];
     return NBODY_OK;

@@ -172,11 +172,20 @@ struct nbody_ctx {
     bool timing = false;
     long long t_launches = 0;
     double t_ms = 0.0;
+    void* world_state = nullptr;    // the page's complete step on the device (page_world.cu): ids, types, contact map, random stream
+    bool world_dirty = false;       // a world step ran: the body count on the device may differ from n until nbody_world_sync
     std::string err;
 };
 
 namespace {
 
+// Every entry point leaves the calling thread's current device as it found it (a context drives several devices; a host
+// such as PyTorch creates its streams on whatever cudaGetDevice answers).
+struct DeviceGuard {
+    int dev = -1;
+    DeviceGuard() { if (cudaGetDevice(&dev) != cudaSuccess) { dev = -1; cudaGetLastError(); } }
+    ~DeviceGuard() { if (dev >= 0) cudaSetDevice(dev); }
+};
 
 int fail(nbody_ctx* c, int code, const char* fmt, ...)
 {
@@ -221,6 +230,15 @@ int env_int(const char* name, int dflt)
 }
 
 size_t gcd_sz(size_t a, size_t b) { return b ? gcd_sz(b, a % b) : a; }
+
+// n is padded to whole i-tiles per shard AND to whole j units: lcm(i_tile * world, j_unit)
+// (fp32: the i-tile of the pairs-once pass when that is the larger one)
+inline size_t pad_unit_of(const nbody_ctx* c)
+{
+    const size_t tile = c->prec == NBODY_F32 && c->sym32_allowed ? size_t(std::max(c->i_tile, kF32Threads * 8)) : size_t(c->i_tile);
+    const size_t a = tile * size_t(c->world);
+    return a / gcd_sz(a, size_t(c->j_unit)) * size_t(c->j_unit);
+}
 
 inline int check_ready(nbody_ctx* c, const char* what)
 {

@@ -12,6 +12,7 @@
 
 extern "C" int nbody_history_enable(nbody_ctx* c, int depth)
 {
+    DeviceGuard device_guard_;
     if (!c) return NBODY_EINVAL;
     if (depth != 0 && (depth < 2 || depth > 256)) return fail(c, NBODY_EINVAL, "history_enable: depth=%d outside 2..256", depth);
     Shard& s = c->shards[0];
@@ -36,6 +37,7 @@ extern "C" int nbody_history_enable(nbody_ctx* c, int depth)
 
 extern "C" int nbody_history_push(nbody_ctx* c)
 {
+    DeviceGuard device_guard_;
     int rc = check_ready(c, "history_push");
     if (rc != NBODY_OK) return rc;
     if (c->hist_depth == 0) return fail(c, NBODY_EINVAL, "history_push before history_enable");
@@ -62,6 +64,7 @@ extern "C" int nbody_history_push(nbody_ctx* c)
 
 extern "C" int nbody_history_remap(nbody_ctx* c, const int* source)
 {
+    DeviceGuard device_guard_;
     int rc = check_ready(c, "history_remap");
     if (rc != NBODY_OK) return rc;
     if (!source) return fail(c, NBODY_EINVAL, "history_remap: source is NULL");
@@ -104,6 +107,7 @@ int history_ready(nbody_ctx* c, const char* what)
 
 extern "C" int nbody_history_download(nbody_ctx* c, void* out)
 {
+    DeviceGuard device_guard_;
     int rc = history_ready(c, "history_download");
     if (rc != NBODY_OK) return rc;
     if (!out) return fail(c, NBODY_EINVAL, "history_download: out is NULL");
@@ -165,6 +169,7 @@ int build_ribbons(nbody_ctx* c, const double camera[3])
 
 extern "C" int nbody_trail_ribbons(nbody_ctx* c, const double camera[3], float* out)
 {
+    DeviceGuard device_guard_;
     int rc = history_ready(c, "trail_ribbons");
     if (rc != NBODY_OK) return rc;
     if (!camera) return fail(c, NBODY_EINVAL, "trail_ribbons: camera is NULL");
@@ -197,6 +202,7 @@ const char kSnapMagic[8] = {'N', 'B', 'O', 'D', 'Y', 'S', 'N', '1'};
 
 extern "C" int nbody_snapshot_save(nbody_ctx* c, const char* path, unsigned long long step, double dt, double G, double softening)
 {
+    DeviceGuard device_guard_;
     int rc = check_ready(c, "snapshot_save");
     if (rc != NBODY_OK) return rc;
     if (!path) return fail(c, NBODY_EINVAL, "snapshot_save: path is NULL");
@@ -240,6 +246,7 @@ extern "C" int nbody_snapshot_save(nbody_ctx* c, const char* path, unsigned long
 
 extern "C" int nbody_snapshot_load(nbody_ctx* c, const char* path, unsigned long long* step, double* dt, double* G, double* softening)
 {
+    DeviceGuard device_guard_;
     if (!c) return NBODY_EINVAL;
     if (!path) return fail(c, NBODY_EINVAL, "snapshot_load: path is NULL");
     FILE* f = fopen(path, "rb");
@@ -292,6 +299,7 @@ extern "C" int nbody_snapshot_load(nbody_ctx* c, const char* path, unsigned long
 
 extern "C" int nbody_set_materials(nbody_ctx* c, const int* type, const float* seed)
 {
+    DeviceGuard device_guard_;
     int rc = check_ready(c, "set_materials");
     if (rc != NBODY_OK) return rc;
     Shard& s = c->shards[0];
@@ -315,6 +323,7 @@ extern "C" int nbody_set_materials(nbody_ctx* c, const int* type, const float* s
 extern "C" int nbody_render(nbody_ctx* c, int width, int height, const double cam_position[3], const double cam_target[3],
                             double fov_deg, float* rgba, int* ids)
 {
+    DeviceGuard device_guard_;
     int rc = check_ready(c, "render");
     if (rc != NBODY_OK) return rc;
     if (width < 1 || height < 1 || size_t(width) * size_t(height) > (size_t(1) << 28))

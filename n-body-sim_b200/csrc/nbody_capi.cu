@@ -100,14 +100,7 @@ int f64_bodies_per_thread(const nbody_ctx* c, size_t n)
     return n >= kF64TwoBodyMinN ? 2 : 1;
 }
 
-// n is padded to whole i-tiles per shard AND to whole j units: lcm(i_tile * world, j_unit)
-// (fp32: the i-tile of the pairs-once pass when that is the larger one)
-size_t pad_unit(const nbody_ctx* c)
-{
-    const size_t tile = c->prec == NBODY_F32 && c->sym32_allowed ? std::max(c->i_tile, kF32Threads * 8) : c->i_tile;
-    const size_t a = tile * size_t(c->world);
-    return a / gcd_sz(a, size_t(c->j_unit)) * size_t(c->j_unit);
-}
+size_t pad_unit(const nbody_ctx* c) { return pad_unit_of(c); }
 
 // j-range decomposition: a pure function of n (through n_j) and the i-tile, never of
 // the number of GPUs, so partial sums are added in the same order on 1/2/4/8 GPUs.
@@ -332,6 +325,7 @@ int create_common(nbody_ctx** out, nbody_prec prec, int world, size_t capacity, 
 
 extern "C" int nbody_device_count(void)
 {
+    DeviceGuard device_guard_;
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
     if (e != cudaSuccess) {
@@ -345,6 +339,7 @@ extern "C" const char* nbody_version(void) { return "nbody-b200 0.1 (sm_100a)"; 
 
 extern "C" const char* nbody_strerror(int status)
 {
+    DeviceGuard device_guard_;
     switch (status) {
     case NBODY_OK: return "ok";
     case NBODY_EINVAL: return "invalid argument";
@@ -358,9 +353,16 @@ extern "C" const char* nbody_strerror(int status)
 
 extern "C" const char* nbody_last_error(const nbody_ctx* ctx) { return ctx ? ctx->err.c_str() : ""; }
 
+void world_free(nbody_ctx* c);  // page_world.cu
+
 extern "C" void nbody_destroy(nbody_ctx* c)
 {
+    DeviceGuard device_guard_;
     if (!c) return;
+    if (!c->shards.empty()) {
+        cudaSetDevice(c->shards[0].device);
+        world_free(c);
+    }
     for (Shard& s : c->shards) {
         cudaSetDevice(s.device);
         if (s.own_stream) cudaStreamSynchronize(s.own_stream);
@@ -564,6 +566,7 @@ static int create_body(nbody_ctx* c, const int* devs, int n_local_shards, const 
 
 extern "C" int nbody_create(nbody_ctx** out, nbody_prec prec, int n_gpus, const int* device_ids, size_t capacity)
 {
+    DeviceGuard device_guard_;
     nbody_ctx* c = nullptr;
     int rc = create_common(out, prec, n_gpus, capacity, &c);
     if (rc != NBODY_OK) return rc;
@@ -575,6 +578,7 @@ extern "C" int nbody_create(nbody_ctx** out, nbody_prec prec, int n_gpus, const 
 extern "C" int nbody_create_rank(nbody_ctx** out, nbody_prec prec, int rank, int world, int device,
                                  const void* nccl_id, size_t capacity)
 {
+    DeviceGuard device_guard_;
     if (rank < 0 || rank >= world) return NBODY_EINVAL;
     nbody_ctx* c = nullptr;
     int rc = create_common(out, prec, world, capacity, &c);
@@ -586,6 +590,7 @@ extern "C" int nbody_create_rank(nbody_ctx** out, nbody_prec prec, int rank, int
 
 extern "C" int nbody_nccl_unique_id(void* id_out)
 {
+    DeviceGuard device_guard_;
     if (!id_out) return NBODY_EINVAL;
     if (!nccl().ok()) {
         fprintf(stderr, "libnbody: %s\n", nccl().error.c_str());
@@ -599,6 +604,7 @@ extern "C" int nbody_nccl_unique_id(void* id_out)
 
 extern "C" int nbody_set_heat_decay(nbody_ctx* c, double heat_decay)
 {
+    DeviceGuard device_guard_;
     if (!c) return NBODY_EINVAL;
     c->heat_decay = heat_decay;
     return NBODY_OK;
@@ -606,6 +612,7 @@ extern "C" int nbody_set_heat_decay(nbody_ctx* c, double heat_decay)
 
 extern "C" int nbody_set_stream(nbody_ctx* c, void* cuda_stream)
 {
+    DeviceGuard device_guard_;
     if (!c) return NBODY_EINVAL;
     Shard& s = c->shards[0];
     CU(c, cudaSetDevice(s.device));
@@ -616,6 +623,7 @@ extern "C" int nbody_set_stream(nbody_ctx* c, void* cuda_stream)
 
 extern "C" int nbody_sync(nbody_ctx* c)
 {
+    DeviceGuard device_guard_;
     if (!c) return NBODY_EINVAL;
     for (Shard& s : c->shards) {
         CU(c, cudaSetDevice(s.device));
@@ -626,6 +634,7 @@ extern "C" int nbody_sync(nbody_ctx* c)
 
 extern "C" int nbody_get_info(nbody_ctx* c, nbody_info* o)
 {
+    DeviceGuard device_guard_;
     if (!c || !o) return NBODY_EINVAL;
     memset(o, 0, sizeof *o);
     if (c->detect_pending) {
@@ -1037,6 +1046,7 @@ int resolve_mass_detection(nbody_ctx* c)
 
 extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const void* vel, const void* acc, const void* temp)
 {
+    DeviceGuard device_guard_;
     if (!c) return NBODY_EINVAL;
     if (n == 0 || n > c->capacity) return fail(c, NBODY_EINVAL, "upload: n=%zu outside 1..capacity=%zu", n, c->capacity);
     if (!pos_mass || !vel) return fail(c, NBODY_EINVAL, "upload: pos_mass and vel are required");
@@ -1097,8 +1107,48 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     return rc;
 }
 
+// page_world.cu: a world step changed the body count on the device.  Re-derive what nbody_upload derives from n (fp64, one GPU);
+// the kernel has already rewritten the rows beyond n as pads, and the radii stay valid (it maintains them).
+int world_adopt_count(nbody_ctx* c, size_t n)
+{
+    if (n == 0 || n > c->capacity) return fail(c, NBODY_EINVAL, "world: the device holds %zu bodies, capacity %zu", n, c->capacity);
+    Shard& s = c->shards[0];
+    CU(c, cudaSetDevice(s.device));
+    const bool changed = n != c->n;
+    c->n = n;
+    c->R = f64_bodies_per_thread(c, n);
+    c->i_tile = kThreads * c->R;
+    c->f64_sym_k = sym_pick_k(c, n, &c->f64_sym_r);
+    c->n_pad = round_up(n, pad_unit(c));
+    c->n_j = round_up(n, size_t(c->j_unit));
+    c->has_temp = true;
+    c->uniform = false;  // (merged masses: the general kernels)
+    c->outliers.clear();
+    c->detect_pending = false;
+    c->near_valid = false;
+    if (changed) {
+        if (c->hist_n) c->hist_prev_n = c->hist_n;
+        c->hist_n = 0;
+        c->has_materials = false;
+    }
+    choose_chunks(c);
+    s.n_local = c->n_pad;
+    s.i_begin = 0;
+    s.n_local_real = n;
+    const size_t need = c->j_chunks > 1 ? size_t(c->j_chunks) * s.n_local * 4 * c->esz : 0;
+    if (need > s.partial_bytes) {
+        cudaFree(s.partial);
+        s.partial = nullptr;
+        s.partial_bytes = 0;
+        CU(c, cudaMalloc(&s.partial, need));
+        s.partial_bytes = need;
+    }
+    return c->f64_sym_k > 0 ? ensure_sym_buffers(c) : NBODY_OK;
+}
+
 extern "C" int nbody_download_own(nbody_ctx* c, void* pos_mass, void* vel, void* acc, void* temp)
 {
+    DeviceGuard device_guard_;
     if (!c) return NBODY_EINVAL;
     if (c->n == 0) return fail(c, NBODY_EINVAL, "download before upload");
     return c->prec == NBODY_F32 ? download_t<float>(c, (float*)pos_mass, (float*)vel, (float*)acc, (float*)temp, true)
@@ -1107,6 +1157,7 @@ extern "C" int nbody_download_own(nbody_ctx* c, void* pos_mass, void* vel, void*
 
 extern "C" int nbody_download(nbody_ctx* c, void* pos_mass, void* vel, void* acc, void* temp)
 {
+    DeviceGuard device_guard_;
     if (!c) return NBODY_EINVAL;
     if (c->n == 0) return fail(c, NBODY_EINVAL, "download before upload");
     return c->prec == NBODY_F32 ? download_t<float>(c, (float*)pos_mass, (float*)vel, (float*)acc, (float*)temp)
@@ -1517,6 +1568,7 @@ int launch_kick1_drift(nbody_ctx* c, double dt)
 
 extern "C" int nbody_step(nbody_ctx* c, double dt, double G, double softening, int nsteps)
 {
+    DeviceGuard device_guard_;
     int rc = check_ready(c, "step");
     if (rc != NBODY_OK) return rc;
     if (nsteps < 0 || softening < 0.0) return fail(c, NBODY_EINVAL, "step: nsteps=%d softening=%g", nsteps, softening);
@@ -1544,6 +1596,7 @@ extern "C" int nbody_step(nbody_ctx* c, double dt, double G, double softening, i
 extern "C" int nbody_step_host(nbody_ctx* c, size_t n, void* pos_mass, void* vel, void* acc, void* temp, double dt, double G, double softening,
                                int nsteps)
 {
+    DeviceGuard device_guard_;
     // The JS shim's frame: typed arrays in, nsteps x integrate(dt), typed arrays out.  For a small
     // system on one device this is one copy in, pack, the step kernel(s), unpack, one copy out and ONE synchronise.
     if (!c) return NBODY_EINVAL;
@@ -1577,6 +1630,7 @@ extern "C" int nbody_step_host(nbody_ctx* c, size_t n, void* pos_mass, void* vel
 
 extern "C" int nbody_kick1_drift(nbody_ctx* c, double dt)
 {
+    DeviceGuard device_guard_;
     int rc = check_ready(c, "kick1_drift");
     if (rc != NBODY_OK) return rc;
     return launch_kick1_drift(c, dt);
@@ -1584,6 +1638,7 @@ extern "C" int nbody_kick1_drift(nbody_ctx* c, double dt)
 
 extern "C" int nbody_force(nbody_ctx* c, double G, double softening)
 {
+    DeviceGuard device_guard_;
     int rc = check_ready(c, "force");
     if (rc != NBODY_OK) return rc;
     if (softening < 0.0) return fail(c, NBODY_EINVAL, "force: softening=%g", softening);
@@ -1592,6 +1647,7 @@ extern "C" int nbody_force(nbody_ctx* c, double G, double softening)
 
 extern "C" int nbody_kick2(nbody_ctx* c, double dt, double heat_decay)
 {
+    DeviceGuard device_guard_;
     int rc = check_ready(c, "kick2");
     if (rc != NBODY_OK) return rc;
     for (Shard& s : c->shards) {
@@ -1611,6 +1667,7 @@ extern "C" int nbody_kick2(nbody_ctx* c, double dt, double heat_decay)
 
 extern "C" int nbody_enable_timing(nbody_ctx* c, int enable)
 {
+    DeviceGuard device_guard_;
     if (!c) return NBODY_EINVAL;
     int rc = fold_timing(c, c->shards[0]);
     c->timing = enable != 0;
@@ -1619,6 +1676,7 @@ extern "C" int nbody_enable_timing(nbody_ctx* c, int enable)
 
 extern "C" int nbody_read_timing(nbody_ctx* c, long long* launches, double* force_ms)
 {
+    DeviceGuard device_guard_;
     if (!c) return NBODY_EINVAL;
     int rc = fold_timing(c, c->shards[0]);
     if (rc != NBODY_OK) return rc;
@@ -1635,6 +1693,7 @@ extern "C" int nbody_read_timing(nbody_ctx* c, long long* launches, double* forc
 
 extern "C" int nbody_energy(nbody_ctx* c, double G, double softening, double* kinetic, double* potential, double momentum[3])
 {
+    DeviceGuard device_guard_;
     int rc = check_ready(c, "energy");
     if (rc != NBODY_OK) return rc;
     double tot[5] = {0, 0, 0, 0, 0};

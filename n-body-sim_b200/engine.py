@@ -167,6 +167,48 @@ class Engine:
         check(self._L.nbody_contact_stats(self._ctx, st), self._ctx)
         return {"flagged": st[0], "scanned": st[1], "pairs": st[2], "used_flags": bool(st[3]), "candidates_only": st[3] == 2}
 
+    # -- the page's complete step on the device (response included) ---------
+    def world_enable(self, seed: int = 0x5EED0001, max_bodies: int = 300) -> None:
+        """The context becomes the page's `physics` object: ids, types, radii, contactPairs and a seeded Math.random
+        stream live on the device (fp64, one GPU; csrc/page_world.cu)."""
+        check(self._L.nbody_world_enable(self._ctx, int(seed), int(max_bodies)), self._ctx)
+
+    def world_config(self, fracture_threshold: float = 25.0, min_fragment_mass: float = 0.2, merge_time: float = 0.5) -> None:
+        check(self._L.nbody_world_config(self._ctx, fracture_threshold, min_fragment_mass, merge_time), self._ctx)
+
+    def world_set_bodies(self, id, type, radius) -> None:
+        """Body.id / .type / .radius of the uploaded bodies; empties the contact map."""
+        i = np.ascontiguousarray(id, dtype=np.float64)
+        t = np.ascontiguousarray(type, dtype=np.int32)
+        r = np.ascontiguousarray(radius, dtype=np.float64)
+        if i.shape != (self.n,) or t.shape != (self.n,) or r.shape != (self.n,):
+            raise ValueError("id, type and radius must have one entry per body")
+        check(self._L.nbody_world_set_bodies(self._ctx, _ptr(i), _ptr(t), _ptr(r)), self._ctx)
+
+    def world_step(self, dt: float, G: float, softening: float, nsteps: int = 1, collisions: bool = True) -> None:
+        """nsteps x the reference's complete integrate(dt) (idx:247-262, resolveCollisions included), on the device."""
+        check(self._L.nbody_world_step(self._ctx, dt, G, softening, int(nsteps), int(bool(collisions))), self._ctx)
+
+    def world_sync(self) -> dict:
+        """Synchronise and adopt the device's body count; returns id, type, radius, counters, contact count, rng state."""
+        n, nc, rng = ctypes.c_size_t(), ctypes.c_size_t(), ctypes.c_ulonglong()
+        check(self._L.nbody_world_sync(self._ctx, ctypes.byref(n), None, None, None, None, ctypes.byref(nc), ctypes.byref(rng)), self._ctx)
+        self.n = n.value
+        ids, ty, rad = np.zeros(self.n), np.zeros(self.n, np.int32), np.zeros(self.n)
+        cnt = (ctypes.c_longlong * 5)()
+        check(self._L.nbody_world_sync(self._ctx, None, _ptr(ids), _ptr(ty), _ptr(rad), cnt, None, None), self._ctx)
+        return {"n": self.n, "id": ids, "type": ty, "radius": rad, "n_contacts": nc.value, "rng": rng.value,
+                "counters": dict(zip(("merges", "fractures", "overlaps", "flashes", "explosions"), list(cnt)))}
+
+    def world_contacts(self) -> np.ndarray:
+        """contactPairs as rows (lower id, higher id, accumulated time), sorted."""
+        cap = 2048
+        out = np.zeros((cap, 3))
+        cnt = ctypes.c_size_t()
+        check(self._L.nbody_world_contacts(self._ctx, _ptr(out), cap, ctypes.byref(cnt)), self._ctx)
+        rows = out[:cnt.value]
+        return rows[np.lexsort((rows[:, 1], rows[:, 0]))] if len(rows) else rows
+
     # -- renderer feed: Body.history and ribbon trails (SURVEY.md 8f row 3) -----------------
     def history_enable(self, depth: int = 80) -> None:
         """Keep the last `depth` positions of every body on the device (CONFIG.trailLength, idx:58)."""

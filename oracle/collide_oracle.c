@@ -158,6 +158,17 @@ ORACLE_API void oracle_world_clear(oracle_world *w) /* resetScenario, idx:745-74
 ORACLE_API size_t oracle_world_size(const oracle_world *w) { return w->n; }
 ORACLE_API size_t oracle_world_contacts(const oracle_world *w) { return w->nc; }
 
+/* contactPairs as (lower id, higher id, accumulated time) triples, in storage order; the Math.random state */
+ORACLE_API void oracle_world_get_contacts(const oracle_world *w, double *lo_hi_time)
+{
+    for (size_t k = 0; k < w->nc; k++) {
+        lo_hi_time[3 * k] = w->c[k].lo;
+        lo_hi_time[3 * k + 1] = w->c[k].hi;
+        lo_hi_time[3 * k + 2] = w->c[k].time;
+    }
+}
+ORACLE_API uint64_t oracle_world_rng(const oracle_world *w) { return w->rng; }
+
 ORACLE_API void oracle_world_counters(const oracle_world *w, long *out /* [5] */)
 {
     out[0] = w->n_merge;

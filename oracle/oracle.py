@@ -73,6 +73,10 @@ def lib() -> ctypes.CDLL:
         L.oracle_world_contacts.restype = sz
         L.oracle_world_counters.argtypes = [wp, ctypes.POINTER(ctypes.c_long)]
         L.oracle_world_counters.restype = None
+        L.oracle_world_get_contacts.argtypes = [wp, _dp]
+        L.oracle_world_get_contacts.restype = None
+        L.oracle_world_rng.argtypes = [wp]
+        L.oracle_world_rng.restype = ctypes.c_uint64
         L.oracle_world_get.argtypes = [wp, _dp, _dp, _dp, _dp, _dp, _i32p, _dp]
         L.oracle_world_get.restype = None
         L.oracle_world_resolve_collisions.argtypes = [wp, d]
@@ -217,6 +221,18 @@ class World:
     @property
     def n_contacts(self):
         return int(self._L.oracle_world_contacts(self._w))
+
+    def contacts(self):
+        """contactPairs as rows (lower id, higher id, accumulated time), sorted."""
+        rows = np.zeros((self.n_contacts, 3))
+        if len(rows):
+            self._L.oracle_world_get_contacts(self._w, _p(rows))
+            rows = rows[np.lexsort((rows[:, 1], rows[:, 0]))]
+        return rows
+
+    @property
+    def rng(self):
+        return int(self._L.oracle_world_rng(self._w))
 
     def counters(self):
         c = (ctypes.c_long * 5)()

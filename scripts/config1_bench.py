@@ -64,7 +64,43 @@ for prec in ("f64", "f32"):
                      "step_host_equals_resident": bool(np.array_equal(hp, res_state["pos_mass"])),
                      "pos_err_resident_vs_cpu": err(res_state["pos_mass"], p), "pos_err_per_frame_vs_cpu": err(pm, p),
                      "per_frame_equals_resident": bool(np.array_equal(pm, res_state["pos_mass"]))}
+# the COMPLETE reference step (resolveCollisions, merges, fractures included) on the device: csrc/page_world.cu, fp64
+TYPES = ("rock", "metal", "ice")
+w = oracle.World(seed=0x5EED0001, max_bodies=300)
+rng = np.random.default_rng(1)
+for i in range(s.n):
+    w.add(s.pos_mass[i, 3], s.pos_mass[i, :3], s.vel[i, :3], "metal" if i == 0 else TYPES[int(rng.integers(0, 3))], s.temp[i])
+st0 = w.state()
+t0 = time.perf_counter()
+w.integrate(s.dt, s.G, s.softening, collisions=True, nsteps=FRAMES * SUB)
+cpu_full_s = time.perf_counter() - t0
+world = {}
+with nb.Engine(1024, precision="f64") as e:
+    best = 1e9
+    for _ in range(3):
+        e.upload(st0["pos_mass"], st0["vel"], st0["acc"], st0["temp"])
+        e.world_enable(seed=0x5EED0001 + 151, max_bodies=300)
+        e.world_set_bodies(st0["id"], st0["type"], st0["radius"])
+        e.world_step(s.dt, s.G, s.softening, SUB, collisions=True)
+        e.world_sync()
+        t0 = time.perf_counter()
+        for _ in range(FRAMES):
+            e.world_step(s.dt, s.G, s.softening, SUB, collisions=True)
+        info = e.world_sync()
+        best = min(best, time.perf_counter() - t0)
+    best_dl = 1e9
+    for _ in range(3):
+        t0 = time.perf_counter()
+        for _ in range(FRAMES):
+            e.world_step(s.dt, s.G, s.softening, SUB, collisions=True)
+            e.world_sync()
+            e.download(temp=True)
+        best_dl = min(best_dl, time.perf_counter() - t0)
+    world = {"resident_frame_us": best / FRAMES * 1e6, "frame_with_sync_and_download_us": best_dl / FRAMES * 1e6,
+             "bodies_left": info["n"], "counters": info["counters"]}
 print(json.dumps({"config": "BASELINE configs[0]: default scene N=151, 1000 x integrate(0.008), gravity only",
+                  "complete_step_with_collisions": {"cpu_us_per_frame": cpu_full_s / FRAMES * 1e6, "cpu_bodies_left": len(w),
+                                                    "cpu_counters": w.counters(), "gpu": world},
                   "cpu": {"kind": "port", "cores": 1, "us_per_step": cpu_s / (FRAMES * SUB) * 1e6,
                           "g_interactions_per_s": s.n * (s.n - 1) * FRAMES * SUB / cpu_s * 1e-9},
                   "gpu": out}))
