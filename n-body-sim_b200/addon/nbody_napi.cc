@@ -545,6 +545,96 @@ napi_value SetMaterials(napi_env env, napi_callback_info info)  // Body.type + m
     return rc == NBODY_OK ? undefined(env) : fail(env, "setMaterials", rc, h->ctx);
 }
 
+// ---- the page's complete step on the device (include/nbody.h, nbody_world_*) ----------------
+
+// worldEnable(ctx, seed, maxBodies [, fractureThreshold, minFragmentMass, mergeTime]): CONFIG idx:57, 62-64
+napi_value WorldEnable(napi_env env, napi_callback_info info)
+{
+    Args a;
+    if (!get_args(env, info, a, 3, "worldEnable")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "worldEnable");
+    if (!h) return undefined(env);
+    double seed = 0, max_bodies = 0, cfg[3] = {25.0, 0.2, 0.5};
+    if (!get_double(env, a.v[1], &seed) || !get_double(env, a.v[2], &max_bodies) || seed < 0 || max_bodies < 1) {
+        napi_throw_error(env, "NBODY", "nbody.worldEnable(ctx, seed, maxBodies[, fractureThreshold, minFragmentMass, mergeTime])");
+        return undefined(env);
+    }
+    for (int k = 0; k < 3 && size_t(k + 3) < a.argc; ++k) get_double(env, a.v[k + 3], &cfg[k]);
+    int rc = nbody_world_enable(h->ctx, static_cast<unsigned long long>(seed), size_t(max_bodies));
+    if (rc == NBODY_OK) rc = nbody_world_config(h->ctx, cfg[0], cfg[1], cfg[2]);
+    return rc == NBODY_OK ? undefined(env) : fail(env, "worldEnable", rc, h->ctx);
+}
+
+// worldSetBodies(ctx, id: Float64Array[n], type: Int32Array[n], radius: Float64Array[n]): Body.id / .type / .radius, idx:210-221
+napi_value WorldSetBodies(napi_env env, napi_callback_info info)
+{
+    Args a;
+    if (!get_args(env, info, a, 4, "worldSetBodies")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "worldSetBodies");
+    if (!h) return undefined(env);
+    nbody_info inf;
+    nbody_get_info(h->ctx, &inf);
+    void* p[3] = {};
+    const napi_typedarray_type want[3] = {napi_float64_array, napi_int32_array, napi_float64_array};
+    for (int k = 0; k < 3; ++k) {
+        size_t len = 0;
+        if (!get_typed(env, a.v[k + 1], want[k], &p[k], &len) || len < inf.n) {
+            napi_throw_error(env, "NBODY", "nbody.worldSetBodies(ctx, id: Float64Array[n], type: Int32Array[n], radius: Float64Array[n])");
+            return undefined(env);
+        }
+    }
+    const int rc = nbody_world_set_bodies(h->ctx, static_cast<const double*>(p[0]), static_cast<const int*>(p[1]), static_cast<const double*>(p[2]));
+    return rc == NBODY_OK ? undefined(env) : fail(env, "worldSetBodies", rc, h->ctx);
+}
+
+// worldStep(ctx, dt, G, softening, nsteps, collisions): nsteps x the COMPLETE integrate(dt), idx:247-262 with idx:256
+napi_value WorldStep(napi_env env, napi_callback_info info)
+{
+    Args a;
+    if (!get_args(env, info, a, 6, "worldStep")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "worldStep");
+    if (!h) return undefined(env);
+    double dt, G, eps;
+    int32_t nsteps = 1, collisions = 1;
+    if (!get_double(env, a.v[1], &dt) || !get_double(env, a.v[2], &G) || !get_double(env, a.v[3], &eps) ||
+        napi_get_value_int32(env, a.v[4], &nsteps) != napi_ok || napi_get_value_int32(env, a.v[5], &collisions) != napi_ok) {
+        napi_throw_error(env, "NBODY", "nbody.worldStep(ctx, dt, G, softening, nsteps, collisions: 0|1)");
+        return undefined(env);
+    }
+    const int rc = nbody_world_step(h->ctx, dt, G, eps, nsteps, collisions ? 1 : 0);
+    return rc == NBODY_OK ? undefined(env) : fail(env, "worldStep", rc, h->ctx);
+}
+
+// worldSync(ctx, id: Float64Array|null, type: Int32Array|null, radius: Float64Array|null) -> the body count the device holds now;
+// the arrays (capacity entries) receive Body.id / .type / .radius of the current list.  nbody.download then reads the new list.
+napi_value WorldSync(napi_env env, napi_callback_info info)
+{
+    Args a;
+    if (!get_args(env, info, a, 1, "worldSync")) return undefined(env);
+    Handle* h = get_handle(env, a.v[0], "worldSync");
+    if (!h) return undefined(env);
+    size_t n = 0;
+    int rc = nbody_world_sync(h->ctx, &n, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+    if (rc != NBODY_OK) return fail(env, "worldSync", rc, h->ctx);
+    void* p[3] = {};
+    const napi_typedarray_type want[3] = {napi_float64_array, napi_int32_array, napi_float64_array};
+    for (int k = 0; k < 3 && size_t(k + 1) < a.argc; ++k) {
+        napi_valuetype t = napi_undefined;
+        napi_typeof(env, a.v[k + 1], &t);
+        if (t == napi_undefined || t == napi_null) continue;
+        size_t len = 0;
+        if (!get_typed(env, a.v[k + 1], want[k], &p[k], &len) || len < n) {
+            napi_throw_error(env, "NBODY", "nbody.worldSync(ctx, id: Float64Array|null, type: Int32Array|null, radius: Float64Array|null): arrays too short");
+            return undefined(env);
+        }
+    }
+    rc = nbody_world_sync(h->ctx, nullptr, static_cast<double*>(p[0]), static_cast<int*>(p[1]), static_cast<double*>(p[2]), nullptr, nullptr, nullptr);
+    if (rc != NBODY_OK) return fail(env, "worldSync", rc, h->ctx);
+    napi_value out = nullptr;
+    napi_create_double(env, double(n), &out);
+    return out;
+}
+
 napi_value Render(napi_env env, napi_callback_info info)  // planet shaders, idx:83-202
 {
     Args a;
@@ -586,7 +676,8 @@ extern "C" __attribute__((visibility("default"))) napi_value napi_register_modul
         {"setRadius", SetRadius}, {"contacts", Contacts}, {"historyEnable", HistoryEnable}, {"historyPush", HistoryPush},
         {"historyRemap", HistoryRemap},
         {"historyDownload", HistoryDownload}, {"trailRibbons", TrailRibbons}, {"snapshotSave", SnapshotSave},
-        {"snapshotLoad", SnapshotLoad}, {"setMaterials", SetMaterials}, {"render", Render}};
+        {"snapshotLoad", SnapshotLoad}, {"setMaterials", SetMaterials}, {"render", Render},
+        {"worldEnable", WorldEnable}, {"worldSetBodies", WorldSetBodies}, {"worldStep", WorldStep}, {"worldSync", WorldSync}};
     for (const auto& f : fns) {
         napi_value fn = nullptr;
         if (napi_create_function(env, f.name, NAPI_AUTO_LENGTH, f.cb, nullptr, &fn) != napi_ok) return exports;

@@ -18,6 +18,16 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 
+// NB_DEBUG_CHECKS (make variant NAME=checked EXTRA=-DNB_DEBUG_CHECKS): device-side assert()s on the indices the hand-rolled
+// machinery computes.  compute-sanitizer is closed on the build pool (profiles/r2_sanitizer_closed.txt); an out-of-range index
+// then traps in the checked build instead of corrupting memory.  The release build compiles them away.
+#ifdef NB_DEBUG_CHECKS
+#include <cassert>
+#define NB_CHECK(cond) assert(cond)
+#else
+#define NB_CHECK(cond) ((void)0)
+#endif
+
 namespace nb {
 
 // fp64 kernel: 8 compute warps + 1 producer warp, one i-body per thread

@@ -29,6 +29,7 @@ __device__ __forceinline__ void finish_body(const ForceParams<Real>& p, size_t i
                                             Real sz, Real scale)
 {
     using V4 = typename Vec4<Real>::type;
+    NB_CHECK(il < p.n_local);
     V4 a;
     a.x = mul_rn(sx, scale);
     a.y = mul_rn(sy, scale);
@@ -75,6 +76,7 @@ __device__ __forceinline__ bool tile_arrive_last(unsigned* counter, int j_chunks
     asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
     if (threadIdx.x == 0) {
         const unsigned prev = atomicAdd(counter, 1u);
+        NB_CHECK(prev < unsigned(j_chunks));
         *s_flag = (prev == static_cast<unsigned>(j_chunks - 1));
     }
     asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");

@@ -269,6 +269,7 @@ __device__ __forceinline__ void force_f32_body(const ForceParams<float>& p)
                 const int k = t / kF32Stages;
                 if (k > 0) mbar_wait(&empty[slot], (k - 1) & 1);
                 const size_t jb = j0 + size_t(t) * kTileBodies;  // first body of the stage
+                NB_CHECK(jb + kTileBodies <= p.n_j && slot >= 0 && slot < kF32Stages);
                 const float* src = p.pos_cur + (jb >> 9) * size_t(4 * kPosTile) + (jb & 511);
                 unsigned char* dst = smem_raw + size_t(slot) * kF32TileBytes;
                 mbar_expect_tx(&full[slot], kPlanes * kTileBodies * 4);
@@ -346,6 +347,7 @@ __device__ __forceinline__ void force_f32_body(const ForceParams<float>& p)
     }
 
     float4* part = reinterpret_cast<float4*>(p.partial);
+    NB_CHECK(chunk < p.j_chunks && il0 + size_t(R - 1) * kF32Threads < p.n_local && tile_i < p.n_local / (kF32Threads * R));
 #pragma unroll
     for (int r = 0; r < R; ++r)
         part[size_t(chunk) * p.n_local + il0 + size_t(r) * kF32Threads] = make_float4(sx[r], sy[r], sz[r], NEAR ? nr[r] : 0.f);

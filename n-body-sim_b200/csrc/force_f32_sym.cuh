@@ -144,6 +144,7 @@ __device__ __forceinline__ void sym_stage(const float* __restrict__ tp, const in
         }
         // 32 rotations: lane l holds the sums of couple l = bodies (l, l + 32) of the group again.
         // acc_j -= (f * m_i) * vec, idx:286-288
+        NB_CHECK(size_t(stage) * kPosTile + grp * 64 + 2 * lane + 1 < p.n_pad);
         unsigned long long* dst = p.accfix + size_t(stage) * kPosTile + grp * 64 + 2 * lane;
         float lo, hi;
         unpack2(gx, lo, hi);
@@ -191,6 +192,7 @@ __device__ __forceinline__ void force_f32_sym_body(const Sym32Params& p)
             const uint2 raw = __ldg(reinterpret_cast<const uint2*>(p.units) + u);
             const SymUnit un{raw.x, raw.y};
             const unsigned stage0 = un.run & 0xffffffu, count = (un.run >> 24) & 0x7fu;
+            NB_CHECK(count >= 1 && size_t(stage0 + count) * kPosTile <= p.n_pad && size_t(un.tile + 1) * kITile <= p.n_pad);
             const unsigned diag = (un.run & kSymUnitDiag) ? kSymDiag : 0u;
             for (unsigned k = 0; k < count; ++k, ++t) {
                 const unsigned slot = t % kSym32Stages;
@@ -218,6 +220,7 @@ __device__ __forceinline__ void force_f32_sym_body(const Sym32Params& p)
         mbar_wait(&full[slot], (t / kSym32Stages) & 1);
         const uint2 inf = info[slot];
         if (inf.y & kSymStop) break;
+        NB_CHECK(size_t(inf.y >> 4) * kPosTile < p.n_pad);
         const float* tp = reinterpret_cast<const float*>(smem_raw + size_t(slot) * kSym32StageBytes);
         if (inf.y & kSymFirst) {
             g0 = size_t(inf.x) * kITile + tid;
@@ -248,6 +251,7 @@ __device__ __forceinline__ void force_f32_sym_body(const Sym32Params& p)
         if (inf.y & kSymLast) {
 #pragma unroll
             for (int r = 0; r < R; ++r) {
+                NB_CHECK(fix_slot(g0 + size_t(r) * kF32Threads) < p.n_pad);
                 unsigned long long* dst = p.accfix + fix_slot(g0 + size_t(r) * kF32Threads);
                 float lo, hi;
                 unpack2(ax[r], lo, hi);
@@ -291,6 +295,7 @@ __global__ void __launch_bounds__(kSym32FinishThreads) f32_sym_finish_kernel(con
     if (sl >= p.n_local) return;
     const size_t il = (sl & ~size_t(511)) + tile_body(unsigned(sl) & 511u);  // (i_begin is a multiple of the tile)
     const size_t gs = p.i_begin + sl;
+    NB_CHECK(gs < n_pad && il < p.n_local);
     long long s[3] = {0, 0, 0};
     unsigned bad = 0;
     for (int k = 0; k < src.n; ++k) {

@@ -187,6 +187,7 @@ __global__ void __launch_bounds__(kThreads + 32) force_f64_kernel(const ForcePar
         return;
     }
     double4* part = reinterpret_cast<double4*>(p.partial);
+    NB_CHECK(chunk < p.j_chunks && il0 + size_t(R - 1) * kThreads < p.n_local);
 #pragma unroll
     for (int r = 0; r < R; ++r) part[size_t(chunk) * p.n_local + il0 + size_t(r) * kThreads] = make_double4(ax[r], ay[r], az[r], 0.0);
     if (!tile_arrive_last(&p.tile_counter[tile_i], p.j_chunks, &s_last, kThreads)) return;

@@ -109,6 +109,7 @@ __device__ double pow_third(double x)
 
 __device__ __forceinline__ bool overlap(const Smem& S, int i, int j)
 {
+    NB_CHECK(i >= 0 && j >= 0 && i < S.n && j < S.n && S.n <= kWorldMax);
     const double vx = S.px[j] - S.px[i], vy = S.py[j] - S.py[i], vz = S.pz[j] - S.pz[i];  // vec.subVectors(B.pos, A.pos), idx:309
     const double distSq = vx * vx + vy * vy + vz * vz;                                    // idx:310
     const double minDist = S.rad[i] + S.rad[j];                                           // idx:311
@@ -200,6 +201,7 @@ __device__ void fracture_bodies(Smem& S, const WorldParams& p, int a, int b, dou
 
 __device__ void contact_delete(Smem& S, int k)
 {
+    NB_CHECK(k >= 0 && k < S.nc && S.nc <= kWorldMaxContacts);
     --S.nc;  // Map order has no effect on results
     S.c_lo[k] = S.c_lo[S.nc];
     S.c_hi[k] = S.c_hi[S.nc];
@@ -363,6 +365,7 @@ __device__ void resolve_collisions(Smem& S, const WorldParams& p)
         for (int j0 = i + 1; j0 < N; j0 += 32) {
             const int j = j0 + lane;
             const unsigned hit = __ballot_sync(0xffffffffu, j < N && overlap(S, i, j));
+            NB_CHECK(at + __popc(hit) <= kWorldMaxCand);
             if (hit & (1u << lane)) S.cand[at + __popc(hit & ((1u << lane) - 1u))] = make_uint2(unsigned(i), unsigned(j));
             at += __popc(hit);
         }
@@ -476,6 +479,7 @@ __device__ void resolve_collisions(Smem& S, const WorldParams& p)
     for (int k = tid; k < S.n_new; k += kWorldThreads) {
         const int at = kept_total + k - drop;
         if (at < 0) continue;
+        NB_CHECK(at < kWorldMax);
         const NewBody o = p.fresh[k];
         S.px[at] = o.pos[0]; S.py[at] = o.pos[1]; S.pz[at] = o.pos[2];
         S.vx[at] = o.vel[0]; S.vy[at] = o.vel[1]; S.vz[at] = o.vel[2];

@@ -4,10 +4,13 @@
 partial-sum pass), the fp64 and fp32 pairs-once passes (lane rotation, persistent scheduler, 64-bit reductions), contacts, the
 history ring + ribbons and the renderer.  Every case is checked against the oracle, so a clean sanitizer log describes runs that
 also computed the right thing."""
+import hashlib
 import os
 import sys
 
 import numpy as np
+
+REPEAT = int(os.environ.get("CASES_REPEAT", "3"))   # every case this many times: the results must hash the same (no data race)
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import nbody_b200 as nb  # noqa: E402
@@ -30,14 +33,18 @@ def step_case(name, n, precision, env, nsteps=2, general=False, scene="plummer")
             pm[:, 3] *= np.random.default_rng(n).uniform(0.5, 2.0, s.n).astype(dt)
         p, v, a, t = oracle.integrate(pm.astype(np.float64), vel.astype(np.float64), np.zeros((s.n, 4)), temp.astype(np.float64), s.dt, s.G,
                                       s.softening, nsteps=nsteps)
-        with nb.Engine(s.n, precision=precision) as e:
-            e.upload(pm, vel, None, temp)
-            e.step(s.dt, s.G, s.softening, nsteps)
-            o = e.download(temp=True)
-            info = e.info()
+        hashes = set()
+        for _ in range(REPEAT):
+            with nb.Engine(s.n, precision=precision) as e:
+                e.upload(pm, vel, None, temp)
+                e.step(s.dt, s.G, s.softening, nsteps)
+                o = e.download(temp=True)
+                info = e.info()
+            hashes.add(hashlib.blake2b(b"".join(np.ascontiguousarray(o[k]).tobytes() for k in ("pos_mass", "vel", "acc", "temp")), digest_size=8).hexdigest())
+        assert len(hashes) == 1, (name, "results differ between repetitions", hashes)
         tol = 1e-11 if precision == "f64" else 5e-5
         worst = max(err(o["pos_mass"], p), err(o["vel"], v), err(o["acc"], a))
-        print(f"{name:44s} n={s.n:6d} {precision} err {worst:.2e}  sym32={info['f32_sym_last_pass']} sym64={info['f64_symmetric']} uniform={info['uniform_mass']}", flush=True)
+        print(f"{name:44s} n={s.n:6d} {precision} err {worst:.2e} x{REPEAT} {next(iter(hashes))}  sym32={info['f32_sym_last_pass']} sym64={info['f64_symmetric']} uniform={info['uniform_mass']}", flush=True)
         assert worst < tol, (name, worst)
     finally:
         for k, v in old.items():
@@ -82,6 +89,24 @@ def main():
             e.trail_ribbons((0, 80, 150))
             e.render(64, 36, ids=True)
         print(f"contacts / history / ribbons / render                 n={s.n:6d} {precision} {len(pairs)} pairs", flush=True)
+    # the page's complete step on the device (page_world.cu): collisions, merges and fractures, bit-identical to the oracle at G = 0
+    rng = np.random.default_rng(3)
+    w = oracle.World(seed=0xC0FFEE, max_bodies=300)
+    for _ in range(70):
+        w.add(float(rng.uniform(0.3, 3.0)), rng.uniform(-5, 5, 3), rng.normal(0, 8.0, 3), ("rock", "metal", "ice")[int(rng.integers(0, 3))], float(rng.uniform(0, 5)))
+    st = w.state()
+    with nb.Engine(1024, precision="f64") as e:
+        e.upload(st["pos_mass"], st["vel"], st["acc"], st["temp"])
+        e.world_enable(seed=w.rng, max_bodies=300)
+        e.world_set_bodies(st["id"], st["type"], st["radius"])
+        for _ in range(10):
+            w.integrate(0.008, 0.0, 0.5, collisions=True, nsteps=3)
+            e.world_step(0.008, 0.0, 0.5, 3, collisions=True)
+        info = e.world_sync()
+        o = e.download(temp=True)
+    want = w.state()
+    assert info["n"] == len(w) and np.array_equal(o["pos_mass"], want["pos_mass"]) and np.array_equal(o["vel"], want["vel"]) and np.array_equal(info["id"], want["id"])
+    print(f"complete step with collisions on the device          n={info['n']:6d} f64 {info['counters']}", flush=True)
     print("sanitize cases ok")
 
 

@@ -221,6 +221,7 @@ static napi_value call(const char* name, std::vector<napi_value> args, bool expe
 
 static std::string g_out_path;  // collide mode writes <out>.pairs, <out>.ribbons and <out>.nbs next to the state
 static bool g_collide = false;
+static bool g_world = false;    // "world" mode: the page's complete step on the device (worldEnable / worldSetBodies / worldStep / worldSync)
 static bool g_host = false;     // "host" mode: the frame as ONE addon call (stepHost), arrays in and out in place
 
 template <typename T> static void run(bool f64, const char* prec, const std::vector<double>& in, size_t n, double dt, double G,
@@ -316,6 +317,26 @@ template <typename T> static void run(bool f64, const char* prec, const std::vec
             fwrite(&d, 8, 1, fp);
         }
         fclose(fp);
+    } else if (g_world) {
+        // fp64 only.  Radii so small that nothing touches: the complete step then equals the gravity-only contract
+        std::vector<double> id(n), radius(n, 1e-6);
+        std::vector<int> type(n);
+        for (size_t k = 0; k < n; ++k) {
+            id[k] = double(k + 1) / 1024.0;
+            type[k] = int(k % 3);
+        }
+        call("worldStep", {ctx, num(dt), num(G), num(eps), num(1), num(1)}, true);  // before worldEnable: throws
+        call("worldEnable", {ctx, num(12345), num(double(n)), num(25.0), num(0.2), num(0.5)});
+        call("worldSetBodies", {ctx, typed_as(napi_float64_array, id.data(), n), typed_as(napi_int32_array, type.data(), n - 1),
+                                typed_as(napi_float64_array, radius.data(), n)}, true);  // a short array throws
+        call("worldSetBodies", {ctx, typed_as(napi_float64_array, id.data(), n), typed_as(napi_int32_array, type.data(), n),
+                                typed_as(napi_float64_array, radius.data(), n)});
+        call("worldStep", {ctx, num(dt), num(G), num(eps), num(nsteps), num(1)});
+        std::vector<double> id2(n), radius2(n);
+        std::vector<int> type2(n);
+        const double n_now = call("worldSync", {ctx, typed_as(napi_float64_array, id2.data(), n), typed_as(napi_int32_array, type2.data(), n),
+                                                 typed_as(napi_float64_array, radius2.data(), n)})->num;
+        if (n_now != double(n) || id2 != id || type2 != type || radius2 != radius) exit(8);
     } else if (g_host) {
         // the arrays uploaded above are handed over again and come back advanced; a bad array must throw, not crash
         call("stepHost", {ctx, typed(f64, pm.data(), 4 * n), typed(f64, vel.data(), 4 * n - 4), typed(f64, acc.data(), 4 * n),
@@ -391,6 +412,7 @@ int main(int argc, char** argv)
     const bool split = strcmp(argv[5], "split") == 0;
     g_collide = strcmp(argv[5], "collide") == 0;
     g_host = strcmp(argv[5], "host") == 0;
+    g_world = strcmp(argv[5], "world") == 0;
     g_out_path = argv[3];
     const bool f64 = strcmp(argv[6], "f64") == 0;
     std::vector<double> out;

@@ -60,6 +60,22 @@ def test_addon_matches_oracle(nb, oracle, tmp_path, mode, prec, tol):
 
 
 @pytest.mark.gpu
+def test_addon_world_entry_points(nb, oracle, tmp_path):
+    """worldEnable / worldSetBodies / worldStep / worldSync through the addon glue: the complete step on the device with
+    radii so small that nothing touches equals the gravity-only contract; wrong calls throw."""
+    s = nb.scenes.galaxy_default()
+    acc0 = np.zeros_like(s.vel)
+    fin, fout = tmp_path / "in.bin", tmp_path / "out.bin"
+    _fixture_bytes(s, acc0, s.temp).tofile(fin)
+    r = subprocess.run([HOST, ADDON, str(fin), str(fout), "4", "world", "f64"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    pm, vel, acc, temp = _split(np.fromfile(fout, dtype=np.float64), s.n)
+    p, v, a, t = oracle.integrate(s.pos_mass, s.vel, acc0, s.temp, s.dt, s.G, s.softening, nsteps=4)
+    assert norm_rel_err(pm, p) < 1e-12 and norm_rel_err(vel, v) < 1e-12 and norm_rel_err(acc, a) < 1e-12
+    assert np.array_equal(temp, t)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("prec", ["f64", "f32"])
 def test_addon_collision_and_renderer_feed(nb, oracle, tmp_path, prec):
     """setRadius / contacts / history / trailRibbons / snapshot through the addon glue."""
