@@ -60,7 +60,8 @@ typedef enum {
 /* ---- lifetime ---------------------------------------------------------- */
 
 /* One host process driving n_gpus devices (the N-API host is one process):
- * i-bodies are sharded evenly by contiguous range, positions are exchanged
+ * i-bodies are sharded evenly by contiguous range (the pairs-once force passes share their work-unit table by cost
+ * instead and add the devices' exact accumulators), positions are exchanged
  * every step: by default the kernels that move bodies store each
  * new position straight into every peer's buffer over NVLink (peer access / CUDA
  * IPC) and a one-warp epoch barrier follows; NBODY_EXCHANGE=nccl in the
@@ -107,7 +108,13 @@ NBODY_API int nbody_download_own(nbody_ctx* ctx, void* pos_mass, void* vel, void
  * (idx:247-262 minus idx:256), G and softening as read from CONFIG at
  * idx:268-269.  nsteps = CONFIG.subSteps reproduces animate()'s inner loop
  * (idx:877-879).  Temperatures decay by CONFIG.heatDecay = 0.998 per step when
- * a temp array was uploaded (idx:227-230, 260); see nbody_set_heat_decay. */
+ * a temp array was uploaded (idx:227-230, 260); see nbody_set_heat_decay.
+ * Deviations and notes.  (1) fp32, softening == 0, two DISTINCT bodies at one point: the page yields NaN there
+ * (idx:280: G / Math.pow(0, 1.5) = Infinity, times 0) and one step later every body is NaN; the fp32 kernels clamp r^2
+ * and the pair contributes 0, the run stays finite.  The fp64 mode follows the page.  (2) fp32 systems of 32,768 bodies
+ * and more with softening > 0 are stepped by the pairs-once kernel (every pair evaluated once for both bodies, as the
+ * page's i<j loop does, exact fixed-point accumulation): a NaN or infinite coordinate turns EVERY acceleration of that
+ * step into NaN (the page reaches the same state one step later).  Results do not depend on the number of GPUs. */
 NBODY_API int nbody_step(nbody_ctx* ctx, double dt, double G, double softening, int nsteps);
 
 /* One frame of the JS shim in one call (animate(), idx:877-881): upload the caller's arrays

@@ -52,7 +52,25 @@ struct SymParams {
     int n_iblocks;       // n_pad / (kSymThreads * r)
     int k;               // j-blocks per CTA
     double eps2;
+    // FIXED: the sums leave as exact fixed-point contributions instead (round 2; several GPUs, any n).  Every partial sum v is
+    // split into hi = rint(v 2^k1) and lo = rint((v - hi 2^-k1) 2^(k1+50)) -- both exact -- and added to the body's two 64-bit
+    // accumulators with RED.ADD.64: integer sums do not depend on the order or the GPU the contributions come from.
+    int i_block_begin;           // first i-block (row) of this device's share; gridDim.y rows are launched
+    unsigned long long* acc_hi;  // [3][n_pad] + the poison word at [3 n_pad]
+    unsigned long long* acc_lo;  // [3][n_pad]
+    double scale_hi, inv_scale_hi, scale_lo;  // 2^k1, 2^-k1, 2^(k1+50); |sum| <= bound maps to 2^61
+    double bound;
 };
+
+__device__ __forceinline__ void sym64_red(const SymParams& p, size_t idx, double v)
+{
+    if (!(fabs(v) <= p.bound)) atomicOr(p.acc_hi + 3 * p.n_pad, 1ull);  // NaN, infinity or a broken bound poisons the step
+    const long long h = __double2ll_rn(v * p.scale_hi);
+    const double r = v - double(h) * p.inv_scale_hi;  // exact: |r| <= 2^-k1-1
+    const long long l = __double2ll_rn(r * p.scale_lo);
+    atomicAdd(p.acc_hi + idx, static_cast<unsigned long long>(h));
+    atomicAdd(p.acc_lo + idx, static_cast<unsigned long long>(l));
+}
 
 __host__ __device__ inline int sym_chunks_of_row(int n_iblocks, int r, int k, int I)
 {
@@ -65,7 +83,7 @@ __device__ __forceinline__ double sym_pair_weight(double dx, double dy, double d
     return inv_cube_f64(__fma_rn(dz, dz, __fma_rn(dy, dy, __fma_rn(dx, dx, eps2))));
 }
 
-template <bool ZERO_SOFT, bool UNIFORM, int kSymR>
+template <bool ZERO_SOFT, bool UNIFORM, int kSymR, bool FIXED = false>
 __global__ void __launch_bounds__(kSymThreads) force_f64_sym_kernel(const SymParams p)
 {
     constexpr int kSymJPerI = kSymR;
@@ -73,7 +91,7 @@ __global__ void __launch_bounds__(kSymThreads) force_f64_sym_kernel(const SymPar
     __shared__ double sx[kSymJBlock], sy[kSymJBlock], sz[kSymJBlock], sm[kSymJBlock];
     __shared__ double fx[kSymJBlock], fy[kSymJBlock], fz[kSymJBlock];
 
-    const int I = blockIdx.y, c = blockIdx.x;
+    const int I = int(blockIdx.y) + (FIXED ? p.i_block_begin : 0), c = blockIdx.x;
     if (c >= sym_chunks_of_row(p.n_iblocks, kSymR, p.k, I)) return;
     const int jb0 = I * kSymJPerI + c * p.k;
     const int jb_end = p.n_iblocks * kSymJPerI;
@@ -160,12 +178,29 @@ __global__ void __launch_bounds__(kSymThreads) force_f64_sym_kernel(const SymPar
             __syncthreads();
         }
         // acc_j -= (f*m_i)*vec, idx:286-288
-        double* row = p.part_j + size_t(I) * 3 * p.n_pad + size_t(jb) * kSymJBlock + tid;
-        row[0] = -fx[tid];
-        row[p.n_pad] = -fy[tid];
-        row[2 * p.n_pad] = -fz[tid];
+        if (FIXED) {
+            const size_t at = size_t(jb) * kSymJBlock + tid;
+            sym64_red(p, at, -fx[tid]);
+            sym64_red(p, p.n_pad + at, -fy[tid]);
+            sym64_red(p, 2 * p.n_pad + at, -fz[tid]);
+        } else {
+            double* row = p.part_j + size_t(I) * 3 * p.n_pad + size_t(jb) * kSymJBlock + tid;
+            row[0] = -fx[tid];
+            row[p.n_pad] = -fy[tid];
+            row[2 * p.n_pad] = -fz[tid];
+        }
     }
 
+    if (FIXED) {
+#pragma unroll
+        for (int r = 0; r < kSymR; ++r) {
+            const size_t at = i0 + size_t(r) * kSymThreads;
+            sym64_red(p, at, ax[r]);
+            sym64_red(p, p.n_pad + at, ay[r]);
+            sym64_red(p, 2 * p.n_pad + at, az[r]);
+        }
+        return;
+    }
     double* row = p.part_i + size_t(c) * 3 * p.n_pad + i0;
 #pragma unroll
     for (int r = 0; r < kSymR; ++r) {
@@ -173,6 +208,38 @@ __global__ void __launch_bounds__(kSymThreads) force_f64_sym_kernel(const SymPar
         row[p.n_pad + size_t(r) * kSymThreads] = ay[r];
         row[2 * p.n_pad + size_t(r) * kSymThreads] = az[r];
     }
+}
+
+// FIXED: one thread per owned body adds the accumulators of every rank (exact), clears them, converts
+// (hi 2^-k1 + lo 2^-(k1+50): one rounding each, a fixed formula of integers) and runs the integrator epilogue.
+struct Sym64Sources {
+    unsigned long long* hi[kMaxPeers];
+    unsigned long long* lo[kMaxPeers];
+    int n;
+    double inv_scale_hi, inv_scale_lo;
+};
+__global__ void __launch_bounds__(256) f64_sym_fixed_finish_kernel(const ForceParams<double> p, const Sym64Sources src, const size_t n_pad, double scale)
+{
+    const size_t il = size_t(blockIdx.x) * 256 + threadIdx.x;
+    if (il >= p.n_local) return;
+    const size_t g = p.i_begin + il;
+    long long h[3] = {0, 0, 0}, l[3] = {0, 0, 0};
+    bool bad = false;
+    for (int k = 0; k < src.n; ++k) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            h[c] += static_cast<long long>(src.hi[k][c * n_pad + g]);
+            l[c] += static_cast<long long>(src.lo[k][c * n_pad + g]);
+            src.hi[k][c * n_pad + g] = 0ull;
+            src.lo[k][c * n_pad + g] = 0ull;
+        }
+        bad = bad || src.hi[k][3 * n_pad] != 0ull;
+    }
+    double v[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) v[c] = __fma_rn(double(l[c]), src.inv_scale_lo, __dmul_rn(double(h[c]), src.inv_scale_hi));
+    if (bad) v[0] = v[1] = v[2] = __longlong_as_double(0x7ff8000000000000LL);
+    finish_body<double>(p, il, v[0], v[1], v[2], scale);
 }
 
 // One CTA finishes 32 bodies: warp w adds the slots w, w + 8, ... of each body (rows of lower

@@ -87,9 +87,7 @@ int sym_pick_k(const nbody_ctx* c, size_t n, int* r_out)
             k = t;
         }
     }
-    const size_t budget = size_t(std::max(1, env_int("NBODY_F64_SYM_MAX_MB", 4096))) << 20;
-    while (k < 64 && sym_partial_bytes(n_pad, r, k, nullptr, nullptr) > budget) ++k;
-    return sym_partial_bytes(n_pad, r, k, nullptr, nullptr) > budget ? 0 : k;
+    return k;  // (the array form of the pass, softening == 0 on one GPU, checks its memory budget at launch)
 }
 
 int f64_bodies_per_thread(const nbody_ctx* c, size_t n)
@@ -141,7 +139,8 @@ int alloc_shard(nbody_ctx* c, Shard& s)
     // fixed-point accumulators of the fp32 pairs-once pass (force_f32_sym.cuh), the exchange flags and that pass's control words
     {
         const size_t pos_bytes = round_up(c->cap_pad * v4, 256);
-        const size_t acc_bytes = c->prec == NBODY_F32 ? round_up((3 * c->cap_pad + 1) * sizeof(unsigned long long), 256) : 0;
+        // fp32: [3][cap] sums + poison; fp64: hi [3][cap] + poison, then lo [3][cap] (force_f64_sym.cuh, FIXED)
+        const size_t acc_bytes = round_up(((c->prec == NBODY_F32 ? 3 : 6) * c->cap_pad + 2) * sizeof(unsigned long long), 256);
         const size_t flag_bytes = 256;  // kMaxPeers epoch flags, then 2 control words
         s.arena_bytes = 2 * pos_bytes + acc_bytes + flag_bytes;
         CU(c, cudaMalloc(&s.arena, s.arena_bytes));
@@ -170,7 +169,7 @@ int alloc_shard(nbody_ctx* c, Shard& s)
     s.energy_rows = (local_cap + kEnergyThreads - 1) / kEnergyThreads + 1;
     CU(c, cudaMalloc(&s.energy_out, s.energy_rows * 5 * sizeof(double)));
     CU(c, cudaMalloc(&s.radius, c->cap_pad * c->esz));
-    if (c->prec == NBODY_F32) CU(c, cudaMalloc(&s.mass_sums, (c->cap_pad / 256 + 1) * sizeof(double)));
+    CU(c, cudaMalloc(&s.mass_sums, (c->cap_pad / 256 + 1) * sizeof(double)));
     CU(c, cudaMalloc(&s.outliers, kMaxOutliers * sizeof(MassOutlier)));
     CU(c, cudaMalloc(&s.outlier_count, sizeof(unsigned)));
     CU(c, cudaMalloc(&s.near, local_cap * sizeof(float)));
@@ -302,7 +301,7 @@ int create_common(nbody_ctx** out, nbody_prec prec, int world, size_t capacity, 
         c->f64_math = env_int("NBODY_F64_MATH", 2);
         c->f64_R_forced = env_int("NBODY_F64_R", 0);
         // (forcing the one-sided kernel's shape, or another arithmetic, selects the one-sided kernel)
-        c->f64_sym_allowed = env_int("NBODY_F64_SYM", 1) != 0 && world == 1 && c->f64_math == 2 && c->f64_R_forced == 0;
+        c->f64_sym_allowed = env_int("NBODY_F64_SYM", 1) != 0 && c->f64_math == 2 && c->f64_R_forced == 0;
         c->R = f64_bodies_per_thread(c, capacity);  // for cap_pad: the largest i-tile an upload may pick
         c->i_tile = kThreads * c->R;
         c->j_unit = kJUnitF64;
@@ -683,7 +682,7 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
         const int rcb = queue_exchange_barrier(c);
         if (rcb != NBODY_OK) return rcb;
     }
-    const bool want_mass = sizeof(Real) == 4 && c->sym32_allowed && n >= c->sym32_min_n;
+    const bool want_mass = sizeof(Real) == 4 ? (c->sym32_allowed && n >= c->sym32_min_n) : c->f64_sym_k > 0;
     double small_mass = 0.0;
     // several devices with peer mappings: each shard uploads and packs its own slice only (pack_pos_shard_kernel)
     const bool sharded = c->world > 1 && c->p2p && env_int("NBODY_SHARDED_UPLOAD", 1) != 0;
@@ -755,7 +754,8 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
         CUK(c, "pack_pos_kernel", s.device);
         }
         if (!small_io) {
-        if (s.accfix) CU(c, cudaMemsetAsync(s.accfix, 0, (3 * c->n_pad + 1) * sizeof(unsigned long long), s.stream));  // (zero unless a pass was abandoned)
+        if (s.accfix)  // (zero unless a pass was abandoned)
+            CU(c, cudaMemsetAsync(s.accfix, 0, ((sizeof(Real) == 4 ? 3 : 6) * c->cap_pad + 2) * sizeof(unsigned long long), s.stream));
         c->launches++;
         CU(c, cudaGetLastError());
         CU(c, cudaMemsetAsync(s.vel, 0, s.n_local * v4, s.stream));
@@ -886,7 +886,8 @@ int ensure_sym_buffers(nbody_ctx* c)
     Shard& s = c->shards[0];
     CU(c, cudaSetDevice(s.device));
     size_t bi = 0, bj = 0;
-    sym_partial_bytes(c->n_pad, c->f64_sym_r, c->f64_sym_k, &bi, &bj);
+    const size_t budget = size_t(std::max(1, env_int("NBODY_F64_SYM_MAX_MB", 4096))) << 20;
+    if (sym_partial_bytes(c->n_pad, c->f64_sym_r, c->f64_sym_k, &bi, &bj) > budget) return 1;  // the one-sided kernel then
     if (bi > s.sym_bytes_i) {
         cudaFree(s.sym_part_i);
         s.sym_part_i = nullptr;
@@ -923,7 +924,9 @@ int build_sym32_table(nbody_ctx* c)
     const size_t T = (c->n + itile - 1) / itile;
     if (NS >= (1u << 24)) return NBODY_OK;
     int run = env_int("NBODY_F32_SYM_RUN", 0);
-    if (run <= 0) run = int(std::min<size_t>(8, std::max<size_t>(1, NS / 512)));  // N=1M: 4 tiles (2,048 bodies) per unit
+    // N=1M: 2 tiles (1,024 bodies) per unit = 0.13 ms of one CTA: the tail of a device's share stays ~0.2 % even when 8 GPUs
+    // split the step (units of 1..16 tiles run within 0.5 % of each other on one GPU, profiles/r2a_sym_lab.jsonl)
+    if (run <= 0) run = int(std::min<size_t>(8, std::max<size_t>(1, NS / 1024)));
     run = std::min(run, kSymUnitMaxRun);
     if (c->sym32_table_n != c->n || c->sym32_table_R != R || c->sym32_table_run != run) {
         std::vector<SymUnit> units;
@@ -1102,7 +1105,6 @@ extern "C" int nbody_upload(nbody_ctx* c, size_t n, const void* pos_mass, const 
     c->detect_pending = rc == NBODY_OK && c->detect_masses && c->upload_deferred;
     if (rc == NBODY_OK && c->detect_masses && !c->detect_pending) rc = finish_mass_detection(c);
     c->detect_masses = false;
-    if (rc == NBODY_OK && c->f64_sym_k > 0) rc = ensure_sym_buffers(c);
     if (rc == NBODY_OK) rc = build_sym32_table(c);
     return rc;
 }
@@ -1143,7 +1145,7 @@ int world_adopt_count(nbody_ctx* c, size_t n)
         CU(c, cudaMalloc(&s.partial, need));
         s.partial_bytes = need;
     }
-    return c->f64_sym_k > 0 ? ensure_sym_buffers(c) : NBODY_OK;
+    return NBODY_OK;
 }
 
 extern "C" int nbody_download_own(nbody_ctx* c, void* pos_mass, void* vel, void* acc, void* temp)
@@ -1392,6 +1394,122 @@ int launch_force_sym32(nbody_ctx* c, int mode, double dt, double G, double eps)
     return NBODY_OK;
 }
 
+template <typename F> void pick_f64_sym_fixed_kernel(bool uniform, int r, F&& f)
+{
+    if (uniform) {
+        if (r == 1) return f(force_f64_sym_kernel<false, true, 1, true>);
+        if (r == 2) return f(force_f64_sym_kernel<false, true, 2, true>);
+        return f(force_f64_sym_kernel<false, true, 4, true>);
+    }
+    if (r == 1) return f(force_f64_sym_kernel<false, false, 1, true>);
+    if (r == 2) return f(force_f64_sym_kernel<false, false, 2, true>);
+    return f(force_f64_sym_kernel<false, false, 4, true>);
+}
+
+// The fp64 pairs-once pass with exact fixed-point accumulators (force_f64_sym.cuh, FIXED): softening > 0, any number of GPUs.
+// The ranks share the rows (i-blocks) of the pair triangle by cost; each accumulates hi/lo contributions for ALL bodies; after a
+// barrier every device adds the ranks' accumulators for the bodies it owns and runs the integrator.  Returns 1 when it does not apply.
+int launch_force_sym64(nbody_ctx* c, int mode, double dt, double G, double eps)
+{
+    if (c->f64_sym_k <= 0 || !(eps > 0.0) || !std::isfinite(eps)) return 1;
+    const bool uni = c->uniform && c->f64_math == 2;
+    const double wmax = 2.0 / (3.0 * std::sqrt(3.0) * eps * eps);
+    const double bound = 1.001 * wmax * (uni ? double(c->n) : c->sum_abs_mass);
+    if (!(bound > 0.0) || !std::isfinite(bound) || bound > 1e250) return 1;
+    int e = 0;
+    std::frexp(bound, &e);
+    const int k1 = 61 - e;  // bound * 2^k1 < 2^61
+    if (k1 < -900 || k1 > 900) return 1;
+    const int r = c->f64_sym_r, k = c->f64_sym_k;
+    const int n_iblocks = int(c->n_pad / (size_t(kSymThreads) * r));
+    // rows by cost: row I walks (n_iblocks - I) * r j-blocks
+    std::vector<int> split(size_t(c->world) + 1, 0);
+    {
+        double total = 0.0;
+        for (int I = 0; I < n_iblocks; ++I) total += double(n_iblocks - I);
+        double run = 0.0;
+        int I = 0;
+        for (int g = 1; g < c->world; ++g) {
+            while (I < n_iblocks && run + 0.5 * double(n_iblocks - I) < total * g / c->world) run += double(n_iblocks - I++);
+            split[g] = I;
+        }
+        split[c->world] = n_iblocks;
+    }
+    const size_t lo_off = 3 * c->cap_pad + 1;
+    const size_t words = lo_off + 3 * c->n_pad;
+    for (Shard& s : c->shards) {
+        CU(c, cudaSetDevice(s.device));
+        if (c->timing && &s == &c->shards[0]) {
+            const int rc = start_force_timing(c, s);
+            if (rc != NBODY_OK) return rc;
+        }
+        if (c->world > 1 && !c->p2p) CU(c, cudaMemsetAsync(s.accfix, 0, words * sizeof(unsigned long long), s.stream));
+        else CU(c, cudaMemsetAsync(s.accfix + 3 * c->n_pad, 0, sizeof(unsigned long long), s.stream));
+        const int I0 = split[s.rank], I1 = split[s.rank + 1];
+        if (I1 > I0) {
+            SymParams sp;
+            memset(&sp, 0, sizeof sp);
+            sp.pos = static_cast<const double*>(s.pos[c->cur]);
+            sp.n_pad = c->n_pad;
+            sp.r = r;
+            sp.n_iblocks = n_iblocks;
+            sp.k = k;
+            sp.eps2 = eps * eps;
+            sp.i_block_begin = I0;
+            sp.acc_hi = s.accfix;
+            sp.acc_lo = s.accfix + lo_off;
+            sp.scale_hi = std::ldexp(1.0, k1);
+            sp.inv_scale_hi = std::ldexp(1.0, -k1);
+            sp.scale_lo = std::ldexp(1.0, k1 + 50);
+            sp.bound = bound;
+            const dim3 sgrid(unsigned(sym_chunks_of_row(n_iblocks, r, k, I0)), unsigned(I1 - I0));
+            pick_f64_sym_fixed_kernel(uni, r, [&](auto kernel) { kernel<<<sgrid, kSymThreads, 0, s.stream>>>(sp); });
+            c->launches++;
+            CUK(c, "force_f64_sym_kernel", s.device);
+        }
+    }
+    if (c->world > 1 && c->p2p) {
+        const int rc = queue_exchange_barrier(c);
+        if (rc != NBODY_OK) return rc;
+    } else if (c->world > 1) {
+        if (!c->rank_mode) NC(c, nccl().GroupStart());
+        for (Shard& s : c->shards) {
+            if (!c->rank_mode) CU(c, cudaSetDevice(s.device));
+            NC(c, nccl().AllReduce(s.accfix, s.accfix, words, ncclInt64_, ncclSum_, s.comm, s.stream));
+        }
+        if (!c->rank_mode) NC(c, nccl().GroupEnd());
+    }
+    for (Shard& s : c->shards) {
+        CU(c, cudaSetDevice(s.device));
+        ForceParams<double> p = make_params<double>(c, s, mode, dt, G, eps);
+        if (uni) p.G = G * c->uniform_mass;
+        Sym64Sources src;
+        src.n = 0;
+        src.inv_scale_hi = std::ldexp(1.0, -k1);
+        src.inv_scale_lo = std::ldexp(1.0, -(k1 + 50));
+        if (c->world == 1 || !c->p2p) {
+            src.hi[0] = s.accfix;
+            src.lo[0] = s.accfix + lo_off;
+            src.n = 1;
+        } else {
+            for (int g = 0; g < c->world; ++g) {
+                src.hi[src.n] = static_cast<unsigned long long*>(s.peer_acc[g]);
+                src.lo[src.n] = src.hi[src.n] + lo_off;
+                src.n++;
+            }
+        }
+        f64_sym_fixed_finish_kernel<<<unsigned((s.n_local + 255) / 256), 256, 0, s.stream>>>(p, src, c->n_pad, p.G);
+        c->launches++;
+        CUK(c, "f64_sym_fixed_finish_kernel", s.device);
+        if (c->timing && &s == &c->shards[0]) {
+            CU(c, cudaEventRecord(s.ev[s.ev_used + 1], s.stream));
+            s.ev_used += 2;
+        }
+    }
+    if (c->world > 1 && c->p2p && mode != kForceKick2Kick1) return queue_exchange_barrier(c);
+    return NBODY_OK;
+}
+
 int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
 {
     if (c->detect_pending) {
@@ -1399,6 +1517,13 @@ int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
         if (rcd != NBODY_OK) return rcd;
     }
     c->sym32_used = false;
+    if (c->prec == NBODY_F64) {
+        const int rcs = launch_force_sym64(c, mode, dt, G, eps);
+        if (rcs <= 0) {
+            c->near_valid = false;
+            return rcs;
+        }
+    }
     if (c->prec == NBODY_F32 && !(c->has_radius && env_int("NBODY_NEAR", 1) != 0)) {
         const int rcs = launch_force_sym32(c, mode, dt, G, eps);
         if (rcs <= 0) {
@@ -1441,9 +1566,13 @@ int launch_force(nbody_ctx* c, int mode, double dt, double G, double eps)
             ForceParams<double> q = p;
             const bool uni = c->uniform && c->f64_math == 2;
             if (uni) q.G = G * c->uniform_mass;  // equal masses: the common m joins G (force_f64.cuh, UNIFORM)
-            if (c->f64_sym_k > 0) {
+            int sym_rc = 1;
+            if (c->f64_sym_k > 0 && c->world == 1 && eps == 0.0) sym_rc = ensure_sym_buffers(c);  // (array form; 1 = over its budget)
+            if (sym_rc < 0) return sym_rc;
+            if (sym_rc == 0) {
                 // every pair once, then one pass that adds the partial sums and runs the epilogue (force_f64_sym.cuh)
                 SymParams sp;
+                memset(&sp, 0, sizeof sp);
                 sp.pos = q.pos_cur;
                 sp.part_i = s.sym_part_i;
                 sp.part_j = s.sym_part_j;

@@ -26,7 +26,6 @@ def main():
         dist.all_gather_object(out, obj)
         return out
 
-    os.environ["NBODY_F64_SYM"] = "0"     # (fp64 on ONE GPU would take the pairs-once pass: the same terms in another order)
     for precision, n in (("f32", 70002), ("f64", 6000)):
         dt = np.float32 if precision == "f32" else np.float64
         s = nb.scenes.two_galaxies(n - n % 2)

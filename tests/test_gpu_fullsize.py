@@ -111,9 +111,8 @@ def test_multi_gpu_bit_identical(nb, precision, exchange):
     pm, vel, t = s.astype(dt)
     outs = []
     os.environ["NBODY_EXCHANGE"] = exchange
-    # (fp64 on ONE GPU would take the pairs-once pass, force_f64_sym.cuh: the same terms added in another order,
-    # 1e-15 away; the property tested here is the sharded one-sided kernels')
-    os.environ["NBODY_F64_SYM"] = "0"
+    # (fp32 and fp64 both take their pairs-once passes here -- n = 32,768, softening > 0 -- whose integer accumulators make the
+    # result independent of the GPU count; the one-sided sweeps' fixed j-chunk order is covered by the softening = 0 run below)
     try:
         for g in sorted({1, 2, min(ng, 4), min(ng, 8)}):
             with nb.Engine(s.n, precision=precision, n_gpus=g) as e:
@@ -124,11 +123,59 @@ def test_multi_gpu_bit_identical(nb, precision, exchange):
                 outs.append((g, e.download(temp=True), e.energy(s.G, s.softening)))
     finally:
         os.environ.pop("NBODY_EXCHANGE", None)
-        os.environ.pop("NBODY_F64_SYM", None)
     for g, o, en in outs[1:]:
         for k in ("pos_mass", "vel", "acc", "temp"):
             assert np.array_equal(o[k], outs[0][1][k]), (g, k)
         assert abs(en[0] - outs[0][2][0]) < 1e-12 * abs(en[0])
+
+
+@pytest.mark.parametrize("precision", ["f32", "f64"])
+def test_multi_gpu_bit_identical_one_sided_sweeps(nb, precision):
+    """softening = 0 selects the one-sided sweeps (no bound for the fixed-point scale): i-range shards with a j-chunk
+    decomposition that is a function of N only -- the same bits on 1 and P GPUs as well."""
+    ng = _multi_gpu(nb)
+    s = nb.scenes.plummer(20000)
+    dt = np.float32 if precision == "f32" else np.float64
+    pm, vel, t = s.astype(dt)
+    outs = []
+    os.environ["NBODY_F64_SYM"] = "0"   # (fp64 on ONE GPU would take the array form of the pairs-once pass at softening 0: another order)
+    try:
+        for g in sorted({1, 2, min(ng, 4)}):
+            with nb.Engine(s.n, precision=precision, n_gpus=g) as e:
+                e.upload(pm, vel, None, t)
+                e.step(s.dt, s.G, 0.0, 3)
+                assert e.info()["f32_sym_last_pass"] == 0
+                outs.append(e.download(temp=True))
+    finally:
+        os.environ.pop("NBODY_F64_SYM", None)
+    for o in outs[1:]:
+        for k in ("pos_mass", "vel", "acc", "temp"):
+            assert np.array_equal(o[k], outs[0][k]), k
+
+
+def test_f64_pairs_once_on_several_gpus(nb, oracle):
+    """The fp64 pairs-once pass with exact hi/lo fixed-point accumulators (force_f64_sym.cuh, FIXED) on 1, 2 and 4 GPUs:
+    the same bits, within the 1e-12 gate of the oracle, and the rows of the pair triangle shared by cost."""
+    ng = _multi_gpu(nb)
+    s = nb.scenes.plummer(24000)
+    pm = s.pos_mass.copy()
+    pm[:, 3] *= np.random.default_rng(5).uniform(0.5, 2.0, s.n)
+    idx = np.arange(0, s.n, 997)
+    ref = oracle.acc_subset(pm, idx, s.G, s.softening)
+    outs = []
+    for g in sorted({1, 2, min(ng, 4)}):
+        with nb.Engine(s.n, precision="f64", n_gpus=g) as e:
+            e.upload(pm, s.vel)
+            assert e.info()["f64_symmetric"] > 0
+            e.force(s.G, s.softening)
+            acc = e.download()["acc"]
+            e.step(s.dt, s.G, s.softening, 3)
+            outs.append((acc, e.download()))
+        assert norm_rel_err(acc[idx], ref) < 1e-12
+    for acc, o in outs[1:]:
+        assert np.array_equal(acc, outs[0][0])
+        for k in ("pos_mass", "vel", "acc"):
+            assert np.array_equal(o[k], outs[0][1][k]), k
 
 
 def test_multi_gpu_ragged_and_split_api(nb, oracle):
