@@ -196,6 +196,12 @@ NBODY_API int nbody_world_contacts(nbody_ctx* ctx, double* lo_hi_time /* 3*cap *
  * a double-double evaluation, correctly rounded (the device's pow() is a 2-ulp routine).  Host arrays. */
 NBODY_API int nbody_selftest_pow_third(nbody_ctx* ctx, const double* x, double* y, size_t n);
 
+/* Test hook, host logic only (works without a device): the work-unit table of the fp32 pairs-once pass for n bodies
+ * (bodies_per_thread 4 or 8, `run` position tiles of 512 bodies per unit) and the contiguous shares of `world` ranks,
+ * balanced by tile visits.  units_out receives (i-tile, first tile, tile count, diagonal flag) per unit. */
+NBODY_API int nbody_selftest_sym32_units(size_t n, int bodies_per_thread, int run, int world, unsigned* units_out /* 4*cap */,
+                                         size_t cap, size_t* count, unsigned* split_out /* world + 1 */);
+
 /* ---- renderer feed: position history and ribbon trails ---- */
 
 /* Keep Body.history on the device: the last `depth` positions of every body,

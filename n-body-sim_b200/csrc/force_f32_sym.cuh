@@ -50,6 +50,9 @@ namespace nb {
 // G interactions/s): equal masses, 8 bodies per thread: 4,240 / 4,061 / 4,109 / 4,183 / 4,187 / 3,403 with 1 / 2 / 4 / 8 / 16 / 32;
 // general masses, 8 per thread: 3,541 / 3,608 with 1 / 16; 4 per thread (3 CTAs per SM): 3,169 / 3,374 / 3,469 / 3,489 / 3,526 with
 // 1 / 2 / 4 / 8 / 16 (general) and 3,859 / 3,920 with 8 / 32 (equal masses).
+#ifndef NB_SYM32_SPLIT_G
+#define NB_SYM32_SPLIT_G 0  // lab switch: two half-length j-side accumulation chains per step (measured: see DESIGN.md 4.1)
+#endif
 #ifndef NB_SYM32_UNROLL_EQUAL
 #define NB_SYM32_UNROLL_EQUAL 1
 #endif
@@ -103,6 +106,9 @@ __device__ __forceinline__ void sym_stage(const float* __restrict__ tp, const in
         const int grp = (gi + 2 * warp) & 7;  // the four warps start on different groups
         const float* px = tp + grp * 64;
         f32x2 gx = 0ull, gy = 0ull, gz = 0ull;  // sum over this warp's i-bodies of w * m_i * d for the couple this lane holds
+#if NB_SYM32_SPLIT_G
+        f32x2 hx = 0ull, hy = 0ull, hz = 0ull;  // (lab: the odd i-bodies' half of the chain)
+#endif
         constexpr int kUnroll = UNIFORM ? (R == 8 ? NB_SYM32_UNROLL_EQUAL : 32) : NB_SYM32_UNROLL_GENERAL;
 #pragma unroll kUnroll
         for (int q = 0; q < 32; ++q) {
@@ -133,10 +139,25 @@ __device__ __forceinline__ void sym_stage(const float* __restrict__ tp, const in
                 ax[r] = fma2(wi, dx, ax[r]);
                 ay[r] = fma2(wi, dy, ay[r]);
                 az[r] = fma2(wi, dz, az[r]);
-                gx = fma2(wj, dx, gx);
-                gy = fma2(wj, dy, gy);
-                gz = fma2(wj, dz, gz);
+#if NB_SYM32_SPLIT_G
+                if (r & 1) {
+                    hx = fma2(wj, dx, hx);
+                    hy = fma2(wj, dy, hy);
+                    hz = fma2(wj, dz, hz);
+                } else
+#endif
+                {
+                    gx = fma2(wj, dx, gx);
+                    gy = fma2(wj, dy, gy);
+                    gz = fma2(wj, dz, gz);
+                }
             }
+#if NB_SYM32_SPLIT_G
+            gx = add2(gx, hx);
+            gy = add2(gy, hy);
+            gz = add2(gz, hz);
+            hx = hy = hz = 0ull;
+#endif
             // at step q + 1 this lane meets the couple that lane + 1 met at step q: its sums come along
             gx = __shfl_sync(0xffffffffu, gx, (lane + 1) & 31);
             gy = __shfl_sync(0xffffffffu, gy, (lane + 1) & 31);

@@ -23,6 +23,7 @@ constexpr int kUniUnroll = NB_UNIFORM_UNROLL;  // inner-loop unroll of the equal
 // i-bodies per thread of the pairs-once fp32 pass: 8 (168 registers, 2 CTAs/SM) beats 4 (128 registers, 3 CTAs/SM) for both
 // mass variants once each runs at its best unroll (force_f32_sym.cuh; N=1M: 4,240 against 3,920 and 3,608 against 3,526).
 constexpr int kSym32EqualMassR = 8, kSym32GeneralR = 8;
+constexpr size_t kSym32SmallN = 49152;              // below: 4 bodies per thread
 constexpr int kSym32DefaultMinN = 32768;            // smallest system that takes it (below: too few units for the SMs)
 
 namespace {
@@ -909,6 +910,34 @@ int ensure_sym_buffers(nbody_ctx* c)
 // position tiles (one diagonal unit), then against the tiles above it in runs of `run`.  A pure function of n (and of the
 // kernel shape), never of the GPU count: every partial sum a unit produces is the same number wherever the unit runs, and
 // the GPUs share the table by cost (position-tile visits), in order.
+void make_sym32_units(size_t n, int R, int run, int world, std::vector<SymUnit>& units, std::vector<unsigned>& split)
+{
+    const size_t itile = size_t(kF32Threads) * R, spt = itile / kPosTile;
+    const size_t NS = (n + kPosTile - 1) / kPosTile;  // position tiles that hold bodies
+    const size_t T = (n + itile - 1) / itile;
+    std::vector<unsigned long long> cost;  // position-tile visits up to and including unit u
+    unsigned long long total = 0;
+    units.clear();
+    for (size_t I = 0; I < T; ++I) {
+        const size_t s0 = I * spt, s1 = std::min((I + 1) * spt, NS);
+        units.push_back(SymUnit{unsigned(I), unsigned(s0) | unsigned(s1 - s0) << 24 | kSymUnitDiag});
+        cost.push_back(total += s1 - s0);
+        for (size_t st = s1; st < NS; st += size_t(run)) {
+            const size_t cnt = std::min(size_t(run), NS - st);
+            units.push_back(SymUnit{unsigned(I), unsigned(st) | unsigned(cnt) << 24});
+            cost.push_back(total += cnt);
+        }
+    }
+    split.assign(size_t(world) + 1, 0);
+    size_t u = 0;
+    for (int r = 1; r < world; ++r) {
+        const unsigned long long target = total / world * r;
+        while (u < units.size() && cost[u] < target) ++u;
+        split[r] = unsigned(u);
+    }
+    split[world] = unsigned(units.size());
+}
+
 int build_sym32_table(nbody_ctx* c)
 {
     c->sym32_run = 0;
@@ -917,11 +946,12 @@ int build_sym32_table(nbody_ctx* c)
         const int rcd = resolve_mass_detection(c);
         if (rcd != NBODY_OK) return rcd;
     }
-    const int R = (c->sym32_R_forced == 4 || c->sym32_R_forced == 8) ? c->sym32_R_forced : (c->uniform ? kSym32EqualMassR : kSym32GeneralR);
+    // (below ~49k bodies the 512-body i-tiles of R = 4 give the 444 resident CTAs twice as many units: N=32,768 2,961 against
+    // 2,778 G interactions/s; from 65,536 up R = 8 wins, 3,767 against 3,534: profiles/r2a_sym_lab.jsonl)
+    const int R = (c->sym32_R_forced == 4 || c->sym32_R_forced == 8) ? c->sym32_R_forced
+                  : (c->n < kSym32SmallN ? 4 : (c->uniform ? kSym32EqualMassR : kSym32GeneralR));
     c->sym32_R = R;
-    const size_t itile = size_t(kF32Threads) * R, spt = itile / kPosTile;
     const size_t NS = (c->n + kPosTile - 1) / kPosTile;  // position tiles that hold bodies
-    const size_t T = (c->n + itile - 1) / itile;
     if (NS >= (1u << 24)) return NBODY_OK;
     int run = env_int("NBODY_F32_SYM_RUN", 0);
     // N=1M: 2 tiles (1,024 bodies) per unit = 0.13 ms of one CTA: the tail of a device's share stays ~0.2 % even when 8 GPUs
@@ -930,26 +960,7 @@ int build_sym32_table(nbody_ctx* c)
     run = std::min(run, kSymUnitMaxRun);
     if (c->sym32_table_n != c->n || c->sym32_table_R != R || c->sym32_table_run != run) {
         std::vector<SymUnit> units;
-        std::vector<unsigned long long> cost;  // position-tile visits up to and including unit u
-        unsigned long long total = 0;
-        for (size_t I = 0; I < T; ++I) {
-            const size_t s0 = I * spt, s1 = std::min((I + 1) * spt, NS);
-            units.push_back(SymUnit{unsigned(I), unsigned(s0) | unsigned(s1 - s0) << 24 | kSymUnitDiag});
-            cost.push_back(total += s1 - s0);
-            for (size_t st = s1; st < NS; st += size_t(run)) {
-                const size_t cnt = std::min(size_t(run), NS - st);
-                units.push_back(SymUnit{unsigned(I), unsigned(st) | unsigned(cnt) << 24});
-                cost.push_back(total += cnt);
-            }
-        }
-        c->sym32_split.assign(size_t(c->world) + 1, 0);
-        size_t u = 0;
-        for (int r = 1; r < c->world; ++r) {
-            const unsigned long long target = total / c->world * r;
-            while (u < units.size() && cost[u] < target) ++u;
-            c->sym32_split[r] = unsigned(u);
-        }
-        c->sym32_split[c->world] = unsigned(units.size());
+        make_sym32_units(c->n, R, run, c->world, units, c->sym32_split);
         for (Shard& s : c->shards) {
             CU(c, cudaSetDevice(s.device));
             if (units.size() > s.sym_units_cap) {
@@ -1864,5 +1875,26 @@ extern "C" int nbody_energy(nbody_ctx* c, double G, double softening, double* ki
         momentum[1] = tot[3];
         momentum[2] = tot[4];
     }
+    return NBODY_OK;
+}
+
+// Host logic only (no device needed): the pairs-once unit table for n bodies and the ranks' shares of it, for the CPU tests.
+// units_out: (i-tile, first position tile, tile count, diagonal flag) per unit.
+extern "C" int nbody_selftest_sym32_units(size_t n, int bodies_per_thread, int run, int world, unsigned* units_out /* 4*cap */, size_t cap,
+                                          size_t* count, unsigned* split_out /* world + 1 */)
+{
+    if (n == 0 || (bodies_per_thread != 4 && bodies_per_thread != 8) || run < 1 || run > kSymUnitMaxRun || world < 1 || !count) return NBODY_EINVAL;
+    std::vector<SymUnit> units;
+    std::vector<unsigned> split;
+    make_sym32_units(n, bodies_per_thread, run, world, units, split);
+    *count = units.size();
+    if (units.size() > cap) return NBODY_ENOMEM;
+    for (size_t k = 0; units_out && k < units.size(); ++k) {
+        units_out[4 * k] = units[k].tile;
+        units_out[4 * k + 1] = units[k].run & 0xffffffu;
+        units_out[4 * k + 2] = (units[k].run >> 24) & 0x7fu;
+        units_out[4 * k + 3] = units[k].run >> 31;
+    }
+    for (int r = 0; split_out && r <= world; ++r) split_out[r] = split[r];
     return NBODY_OK;
 }

@@ -53,3 +53,22 @@ def create_rank_engine(capacity: int, precision: str = "f32"):
     box = [nccl_unique_id() if rank == 0 else None]
     dist.broadcast_object_list(box, src=0)
     return Engine(capacity, precision=precision, rank=rank, world=world, device=device, nccl_id=box[0])
+
+
+def sym32_units(n: int, bodies_per_thread: int = 8, run: int = 1, world: int = 1):
+    """The work-unit table of the fp32 pairs-once pass (csrc/force_f32_sym.cuh) and the ranks' shares of it, from the
+    library's own host code (no device needed).  Returns (units[k, 4] = i-tile, first position tile, tile count, diagonal
+    flag; split[world + 1])."""
+    import ctypes
+
+    import numpy as np
+
+    from . import _lib
+    L = _lib.lib()
+    cnt = ctypes.c_size_t()
+    split = np.zeros(world + 1, dtype=np.uint32)
+    L.nbody_selftest_sym32_units(n, bodies_per_thread, run, world, None, 0, ctypes.byref(cnt), None)
+    units = np.zeros((cnt.value, 4), dtype=np.uint32)
+    _lib.check(L.nbody_selftest_sym32_units(n, bodies_per_thread, run, world, ctypes.c_void_p(units.ctypes.data), cnt.value,
+                                            ctypes.byref(cnt), ctypes.c_void_p(split.ctypes.data)))
+    return units, split
