@@ -189,6 +189,14 @@ NBODY_API int nbody_world_step(nbody_ctx* ctx, double dt, double G, double softe
  * calls, visuals.spawnExplosion calls} since nbody_world_enable, the size of the contact map, the random stream's state. */
 NBODY_API int nbody_world_sync(nbody_ctx* ctx, size_t* n, double* id, int* type, double* radius, long long counters[5],
                                size_t* n_contacts, unsigned long long* rng_state);
+/* The page's frame in one call (idx:873-883: subSteps x integrate(dt), then visuals.update reads every body): nbody_world_step
+ * (nsteps >= 0) followed by everything nbody_world_sync and nbody_download would return, through ONE kernel launch and ONE
+ * synchronise -- the step kernel stores the frame's record straight into pinned host memory.  `cap` = the rows the caller's
+ * arrays hold (pos_mass, vel, acc: 4 doubles per row); any output may be NULL; NBODY_ENOMEM when the device's body list has
+ * outgrown cap (the context has adopted the new count all the same: call again with larger arrays and nsteps = 0). */
+NBODY_API int nbody_world_frame(nbody_ctx* ctx, double dt, double G, double softening, int nsteps, int collisions, size_t cap,
+                                size_t* n, double* pos_mass, double* vel, double* acc, double* temp, double* id, int* type,
+                                double* radius, long long counters[5], size_t* n_contacts, unsigned long long* rng_state);
 /* PhysicsSystem.contactPairs as (lower id, higher id, accumulated contact time) triples, in no particular order. */
 NBODY_API int nbody_world_contacts(nbody_ctx* ctx, double* lo_hi_time /* 3*cap */, size_t cap, size_t* count);
 

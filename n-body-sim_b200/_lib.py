@@ -28,7 +28,7 @@ SYMBOLS = (
     "nbody_set_radius", "nbody_contacts", "nbody_contact_stats",
     "nbody_history_enable", "nbody_history_push", "nbody_history_remap", "nbody_history_download", "nbody_trail_ribbons",
     "nbody_snapshot_save", "nbody_snapshot_load", "nbody_set_materials", "nbody_render",
-    "nbody_world_enable", "nbody_world_config", "nbody_world_set_bodies", "nbody_world_step", "nbody_world_sync", "nbody_world_contacts",
+    "nbody_world_enable", "nbody_world_config", "nbody_world_set_bodies", "nbody_world_step", "nbody_world_sync", "nbody_world_frame", "nbody_world_contacts",
     "nbody_selftest_pow_third", "nbody_selftest_sym32_units",
 )
 
@@ -120,6 +120,8 @@ def lib() -> ctypes.CDLL:
     L.nbody_world_set_bodies.argtypes = [vp, vp, vp, vp]
     L.nbody_world_step.argtypes = [vp, d, d, d, i, i]
     L.nbody_world_sync.argtypes = [vp, ctypes.POINTER(sz), vp, vp, vp, pll, ctypes.POINTER(sz), ctypes.POINTER(ull)]
+    L.nbody_world_frame.argtypes = [vp, d, d, d, i, i, sz, ctypes.POINTER(sz), vp, vp, vp, vp, vp, vp, vp, pll, ctypes.POINTER(sz),
+                                    ctypes.POINTER(ull)]
     L.nbody_world_contacts.argtypes = [vp, vp, sz, ctypes.POINTER(sz)]
     L.nbody_selftest_pow_third.argtypes = [vp, vp, vp, sz]
     L.nbody_selftest_sym32_units.argtypes = [sz, i, i, i, vp, sz, ctypes.POINTER(sz), vp]

@@ -27,6 +27,7 @@
 //                                                          planet shaders idx:83-202, headless
 #include "napi_min.h"
 
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 
@@ -635,6 +636,61 @@ napi_value WorldSync(napi_env env, napi_callback_info info)
     return out;
 }
 
+// worldFrame(ctx, dt, G, softening, nsteps, collisions, posMass, vel, acc, temp, id, type, radius [, stats: Float64Array[6]])
+// -> the body count now.  The page's frame (idx:873-883) in one launch and one synchronise: the Float64Arrays (Int32Array for
+// type) receive the state visuals.update reads; stats = merges, fractures, overlaps, flashes, explosions, contacts.
+napi_value WorldFrame(napi_env env, napi_callback_info info)
+{
+    napi_value argv[14] = {};
+    size_t argc = 14;
+    const char* usage = "nbody.worldFrame(ctx, dt, G, softening, nsteps, collisions: 0|1, posMass, vel, acc: Float64Array[4*cap], temp, id: "
+                        "Float64Array[cap], type: Int32Array[cap], radius: Float64Array[cap][, stats: Float64Array[6]])";
+    if (napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr) != napi_ok || argc < 13) {
+        napi_throw_error(env, "NBODY", usage);
+        return undefined(env);
+    }
+    Handle* h = get_handle(env, argv[0], "worldFrame");
+    if (!h) return undefined(env);
+    double dt, G, eps;
+    int32_t nsteps = 1, collisions = 1;
+    if (!get_double(env, argv[1], &dt) || !get_double(env, argv[2], &G) || !get_double(env, argv[3], &eps) ||
+        napi_get_value_int32(env, argv[4], &nsteps) != napi_ok || napi_get_value_int32(env, argv[5], &collisions) != napi_ok) {
+        napi_throw_error(env, "NBODY", usage);
+        return undefined(env);
+    }
+    void* p[8] = {};
+    size_t len[8] = {};
+    const napi_typedarray_type want[8] = {napi_float64_array, napi_float64_array, napi_float64_array, napi_float64_array,
+                                          napi_float64_array, napi_int32_array,   napi_float64_array, napi_float64_array};
+    for (int k = 0; k < 8 && size_t(k + 6) < argc; ++k) {
+        if (k == 7) {
+            napi_valuetype t = napi_undefined;
+            napi_typeof(env, argv[13], &t);
+            if (t == napi_undefined || t == napi_null) continue;
+        }
+        if (!get_typed(env, argv[k + 6], want[k], &p[k], &len[k]) || (k == 7 && len[k] < 6)) {
+            napi_throw_error(env, "NBODY", usage);
+            return undefined(env);
+        }
+    }
+    size_t cap = len[3];  // rows every array has room for
+    for (int k = 0; k < 7; ++k) cap = std::min(cap, k < 3 ? len[k] / 4 : len[k]);
+    size_t n = 0, contacts = 0;
+    long long counters[5] = {};
+    const int rc = nbody_world_frame(h->ctx, dt, G, eps, nsteps, collisions ? 1 : 0, cap, &n, static_cast<double*>(p[0]), static_cast<double*>(p[1]),
+                                     static_cast<double*>(p[2]), static_cast<double*>(p[3]), static_cast<double*>(p[4]), static_cast<int*>(p[5]),
+                                     static_cast<double*>(p[6]), counters, &contacts, nullptr);
+    if (rc != NBODY_OK) return fail(env, "worldFrame", rc, h->ctx);
+    if (p[7]) {
+        double* st = static_cast<double*>(p[7]);
+        for (int k = 0; k < 5; ++k) st[k] = double(counters[k]);
+        st[5] = double(contacts);
+    }
+    napi_value out = nullptr;
+    napi_create_double(env, double(n), &out);
+    return out;
+}
+
 napi_value Render(napi_env env, napi_callback_info info)  // planet shaders, idx:83-202
 {
     Args a;
@@ -677,7 +733,7 @@ extern "C" __attribute__((visibility("default"))) napi_value napi_register_modul
         {"historyRemap", HistoryRemap},
         {"historyDownload", HistoryDownload}, {"trailRibbons", TrailRibbons}, {"snapshotSave", SnapshotSave},
         {"snapshotLoad", SnapshotLoad}, {"setMaterials", SetMaterials}, {"render", Render},
-        {"worldEnable", WorldEnable}, {"worldSetBodies", WorldSetBodies}, {"worldStep", WorldStep}, {"worldSync", WorldSync}};
+        {"worldEnable", WorldEnable}, {"worldSetBodies", WorldSetBodies}, {"worldStep", WorldStep}, {"worldSync", WorldSync}, {"worldFrame", WorldFrame}};
     for (const auto& f : fns) {
         napi_value fn = nullptr;
         if (napi_create_function(env, f.name, NAPI_AUTO_LENGTH, f.cb, nullptr, &fn) != napi_ok) return exports;

@@ -58,7 +58,13 @@ struct WorldParams {
     double dt, half_dt, G, eps2, heat_decay;
     double fracture_threshold, min_fragment_mass, merge_time;  // idx:62-64
     double pad_x;
+    double* rec;      // nbody_world_frame: the frame's record in pinned, device-mapped host memory (or null)
 };
+
+// The record nbody_world_frame reads after ONE synchronise: sixteen 64-bit words (n, contacts, error, the random stream's
+// state, the five counters), then pos_mass[4n] | vel[4n] | acc[4n] | temp[n] | id[n] | radius[n] | type[n] (as doubles).
+constexpr int kWorldRecHeader = 16;
+constexpr size_t world_rec_bytes(size_t rows) { return (kWorldRecHeader + 16 * rows) * sizeof(double); }
 
 struct Smem {
     double px[kWorldMax], py[kWorldMax], pz[kWorldMax];
@@ -628,6 +634,26 @@ __global__ void __launch_bounds__(kWorldThreads, 1) world_step_kernel(const Worl
         *p.rng = S.rng;
         for (int k = 0; k < 5; ++k) p.counters[k] = S.counters[k];
     }
+    if (p.rec) {  // what the caller reads each frame goes straight to its side of the bus: no copy to queue, one synchronise
+        if (tid == 0) {
+            long long* h = reinterpret_cast<long long*>(p.rec);
+            h[0] = S.n;
+            h[1] = S.nc;
+            h[2] = S.err;
+            h[3] = static_cast<long long>(S.rng);
+            for (int k = 0; k < 5; ++k) h[4 + k] = S.counters[k];
+        }
+        double* b = p.rec + kWorldRecHeader;
+        for (int r = tid; r < n; r += kWorldThreads) {
+            reinterpret_cast<double4*>(b)[r] = make_double4(S.px[r], S.py[r], S.pz[r], S.m[r]);
+            reinterpret_cast<double4*>(b + 4 * size_t(n))[r] = make_double4(S.vx[r], S.vy[r], S.vz[r], 0.0);
+            reinterpret_cast<double4*>(b + 8 * size_t(n))[r] = make_double4(S.ax[r], S.ay[r], S.az[r], 0.0);
+            b[12 * size_t(n) + r] = S.temp[r];
+            b[13 * size_t(n) + r] = S.id[r];
+            b[14 * size_t(n) + r] = S.rad[r];
+            b[15 * size_t(n) + r] = double(S.type[r]);
+        }
+    }
 }
 
 __global__ void pow_third_kernel(const double* x, double* y, int n)
@@ -644,6 +670,7 @@ struct World {
     int* state = nullptr;
     unsigned long long* rng = nullptr;
     long long* counters = nullptr;
+    double* rec_host = nullptr;  // nbody_world_frame's record: pinned and device-mapped
     int max_bodies = 300;
     double fracture_threshold = 25.0, min_fragment_mass = 0.2, merge_time = 0.5;  // CONFIG, idx:62-64
     bool bodies_set = false;
@@ -666,6 +693,7 @@ void world_free(nbody_ctx* c)
     cudaFree(w->state);
     cudaFree(w->rng);
     cudaFree(w->counters);
+    if (w->rec_host) cudaFreeHost(w->rec_host);
     delete w;
     c->world_state = nullptr;
 }
@@ -693,6 +721,7 @@ extern "C" int nbody_world_enable(nbody_ctx* c, unsigned long long seed, size_t 
         CU(c, cudaMalloc(&w->state, 4 * sizeof(int)));
         CU(c, cudaMalloc(&w->rng, sizeof(unsigned long long)));
         CU(c, cudaMalloc(&w->counters, 5 * sizeof(long long)));
+        CU(c, cudaHostAlloc(&w->rec_host, world_rec_bytes(kWorldMax), cudaHostAllocMapped | cudaHostAllocPortable));
         CU(c, cudaFuncSetAttribute(world_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(Smem))));
     }
     w->max_bodies = int(max_bodies);
@@ -738,15 +767,16 @@ extern "C" int nbody_world_set_bodies(nbody_ctx* c, const double* id, const int*
     return NBODY_OK;
 }
 
-extern "C" int nbody_world_step(nbody_ctx* c, double dt, double G, double softening, int nsteps, int collisions)
+namespace {
+
+int launch_world(nbody_ctx* c, const char* who, double dt, double G, double softening, int nsteps, int collisions, double* rec)
 {
-    DeviceGuard device_guard_;
-    int rc = check_ready(c, "world_step");
+    int rc = check_ready(c, who);
     if (rc != NBODY_OK) return rc;
     World* w = world_of(c);
-    if (!w || !w->bodies_set) return fail(c, NBODY_EINVAL, "world_step before world_enable / world_set_bodies");
-    if (nsteps < 0 || softening < 0.0) return fail(c, NBODY_EINVAL, "world_step: nsteps=%d softening=%g", nsteps, softening);
-    if (nsteps == 0) return NBODY_OK;
+    if (!w || !w->bodies_set) return fail(c, NBODY_EINVAL, "%s before world_enable / world_set_bodies", who);
+    if (nsteps < 0 || softening < 0.0) return fail(c, NBODY_EINVAL, "%s: nsteps=%d softening=%g", who, nsteps, softening);
+    if (nsteps == 0 && !rec) return NBODY_OK;
     Shard& s = c->shards[0];
     CU(c, cudaSetDevice(s.device));
     WorldParams p;
@@ -778,6 +808,7 @@ extern "C" int nbody_world_step(nbody_ctx* c, double dt, double G, double soften
     p.min_fragment_mass = w->min_fragment_mass;
     p.merge_time = w->merge_time;
     p.pad_x = 1e150;
+    p.rec = rec;
     world_step_kernel<<<1, kWorldThreads, sizeof(Smem), s.stream>>>(p);
     c->launches++;
     CUK(c, "world_step_kernel", s.device);
@@ -786,8 +817,63 @@ extern "C" int nbody_world_step(nbody_ctx* c, double dt, double G, double soften
     return NBODY_OK;
 }
 
-// The body count follows the device (merges, fractures): everything nbody_upload derives from n is re-derived.
+const char* world_error_text(long long e)
+{
+    static const char* what[] = {"", "contact map full", "overlap list full", "too many new bodies in one call", "body list outgrew the device arrays"};
+    return what[e > 0 && e < 5 ? e : 0];
+}
+
+}  // namespace
+
+extern "C" int nbody_world_step(nbody_ctx* c, double dt, double G, double softening, int nsteps, int collisions)
+{
+    DeviceGuard device_guard_;
+    return launch_world(c, "world_step", dt, G, softening, nsteps, collisions, nullptr);
+}
+
 int world_adopt_count(nbody_ctx* c, size_t n);  // nbody_capi.cu
+
+// The page's frame in one call (idx:873-883: subSteps x integrate, then visuals.update reads every body): the step kernel
+// itself stores what the caller reads into a pinned, device-mapped record, so the frame costs one launch and ONE
+// synchronise -- nbody_world_step + nbody_world_sync + nbody_download is one launch, three synchronises and nine copies.
+extern "C" int nbody_world_frame(nbody_ctx* c, double dt, double G, double softening, int nsteps, int collisions, size_t cap, size_t* n_out,
+                                 double* pos_mass, double* vel, double* acc, double* temp, double* id, int* type, double* radius,
+                                 long long counters[5], size_t* n_contacts, unsigned long long* rng_state)
+{
+    DeviceGuard device_guard_;
+    if (!c) return NBODY_EINVAL;
+    World* w = world_of(c);
+    if (!w) return fail(c, NBODY_EINVAL, "world_frame: world not enabled");
+    int rc = launch_world(c, "world_frame", dt, G, softening, nsteps, collisions, w->rec_host);
+    if (rc != NBODY_OK) return rc;
+    Shard& s = c->shards[0];
+    CU(c, cudaStreamSynchronize(s.stream));
+    const long long* h = reinterpret_cast<const long long*>(w->rec_host);
+    if (h[2]) return fail(c, NBODY_ENOMEM, "world_frame: %s", world_error_text(h[2]));
+    rc = world_adopt_count(c, size_t(h[0]));
+    if (rc != NBODY_OK) return rc;
+    c->world_dirty = false;
+    const size_t n = c->n;
+    if (n_out) *n_out = n;
+    if (n_contacts) *n_contacts = size_t(h[1]);
+    if (rng_state) *rng_state = static_cast<unsigned long long>(h[3]);
+    if (counters) memcpy(counters, h + 4, 5 * sizeof(long long));
+    if ((pos_mass || vel || acc || temp || id || type || radius) && n > cap)
+        return fail(c, NBODY_ENOMEM, "world_frame: the device holds %zu bodies, the caller's arrays %zu", n, cap);
+    const double* b = w->rec_host + kWorldRecHeader;
+    if (pos_mass) memcpy(pos_mass, b, 4 * n * sizeof(double));
+    if (vel) memcpy(vel, b + 4 * n, 4 * n * sizeof(double));
+    if (acc) memcpy(acc, b + 8 * n, 4 * n * sizeof(double));
+    if (temp) memcpy(temp, b + 12 * n, n * sizeof(double));
+    if (id) memcpy(id, b + 13 * n, n * sizeof(double));
+    if (radius) memcpy(radius, b + 14 * n, n * sizeof(double));
+    if (type)
+        for (size_t k = 0; k < n; ++k) type[k] = int(b[15 * n + k]);
+    return NBODY_OK;
+}
+
+// The body count follows the device (merges, fractures): everything nbody_upload derives from n is re-derived
+// (world_adopt_count, nbody_capi.cu).
 
 extern "C" int nbody_world_sync(nbody_ctx* c, size_t* n_out, double* id, int* type, double* radius, long long counters[5], size_t* n_contacts,
                                 unsigned long long* rng_state)
@@ -802,10 +888,7 @@ extern "C" int nbody_world_sync(nbody_ctx* c, size_t* n_out, double* id, int* ty
     int st[4] = {0, 0, 0, 0};
     CU(c, cudaMemcpyAsync(st, w->state, sizeof st, cudaMemcpyDeviceToHost, s.stream));
     CU(c, cudaStreamSynchronize(s.stream));
-    if (st[2]) {
-        static const char* what[] = {"", "contact map full", "overlap list full", "too many new bodies in one call", "body list outgrew the device arrays"};
-        return fail(c, NBODY_ENOMEM, "world_step: %s", what[st[2] < 5 ? st[2] : 0]);
-    }
+    if (st[2]) return fail(c, NBODY_ENOMEM, "world_step: %s", world_error_text(st[2]));
     if (c->world_dirty) {
         rc = world_adopt_count(c, size_t(st[0]));
         if (rc != NBODY_OK) return rc;

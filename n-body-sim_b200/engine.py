@@ -55,6 +55,7 @@ class Engine:
             self._ctx = ctypes.c_void_p()
             check(st)
         self.n = 0
+        self.capacity = int(capacity)
 
     # -- lifetime ----------------------------------------------------------------
     def close(self) -> None:
@@ -199,6 +200,26 @@ class Engine:
         check(self._L.nbody_world_sync(self._ctx, None, _ptr(ids), _ptr(ty), _ptr(rad), cnt, None, None), self._ctx)
         return {"n": self.n, "id": ids, "type": ty, "radius": rad, "n_contacts": nc.value, "rng": rng.value,
                 "counters": dict(zip(("merges", "fractures", "overlaps", "flashes", "explosions"), list(cnt)))}
+
+    def world_frame(self, dt: float, G: float, softening: float, nsteps: int = 2, collisions: bool = True, out: dict | None = None) -> dict:
+        """The page's frame (idx:873-883): nsteps x the complete integrate(dt), then everything visuals.update reads,
+        through one launch and one synchronise.  `out` (a previous call's result) is refilled in place when it is large enough."""
+        cap = self.capacity
+        if out is None or len(out["_buf"]["temp"]) < cap:
+            buf = {"pos_mass": np.zeros((cap, 4)), "vel": np.zeros((cap, 4)), "acc": np.zeros((cap, 4)), "temp": np.zeros(cap),
+                   "id": np.zeros(cap), "type": np.zeros(cap, np.int32), "radius": np.zeros(cap)}
+        else:
+            buf = out["_buf"]
+        n, nc, rng = ctypes.c_size_t(), ctypes.c_size_t(), ctypes.c_ulonglong()
+        cnt = (ctypes.c_longlong * 5)()
+        check(self._L.nbody_world_frame(self._ctx, dt, G, softening, int(nsteps), int(bool(collisions)), cap, ctypes.byref(n),
+                                        _ptr(buf["pos_mass"]), _ptr(buf["vel"]), _ptr(buf["acc"]), _ptr(buf["temp"]), _ptr(buf["id"]),
+                                        _ptr(buf["type"]), _ptr(buf["radius"]), cnt, ctypes.byref(nc), ctypes.byref(rng)), self._ctx)
+        self.n = n.value
+        res = {k: v[:self.n] for k, v in buf.items()}
+        res.update(n=self.n, n_contacts=nc.value, rng=rng.value, _buf=buf,
+                   counters=dict(zip(("merges", "fractures", "overlaps", "flashes", "explosions"), list(cnt))))
+        return res
 
     def world_contacts(self) -> np.ndarray:
         """contactPairs as rows (lower id, higher id, accumulated time), sorted."""

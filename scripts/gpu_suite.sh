@@ -6,6 +6,7 @@
 #   multitests the multi-GPU tests only (bit-identity across GPU counts, rank mode under torchrun)
 #   bench      bench.py on one GPU: the default line, the general-mass line, the reference arm
 #   scale      bench.py under torchrun on every GPU count the lease allows (2, 4, 8), plus the single-process model
+#   config1    configs[0]: the page's default scene four ways + the complete step with collisions (scripts/config1_bench.py)
 #   energy     configs[2]: 10k steps of the two-galaxy scene with the energy-drift record
 #   launches   ncu launch list of a short bench run (after the same command ran plain)
 #   ncu        ncu --set full of the pairs-once force kernel, equal and general masses, N=262,144
@@ -54,6 +55,9 @@ print(sys.argv[1], "gpus", d["n_gpus"], "value", round(d["value"], 1), "e2e", ro
       "check", d["check"]["ok"], d["check"]["state_hash"], "err", d["check"]["sampled_acc_err"], "h2d", d["e2e"]["h2d_bytes_per_step"])
 PY
   done ;;
+config1)
+  timeout 600 python scripts/config1_bench.py > gpurun_out/${tag}_config1.json 2> gpurun_out/${tag}_config1.err; echo "config1 rc=$?"
+  python -m json.tool gpurun_out/${tag}_config1.json | head -40; tail -3 gpurun_out/${tag}_config1.err ;;
 energy)
   timeout 900 python bench.py --energy --scene two_galaxies --bodies 131072 --steps 10000 > gpurun_out/${tag}_energy_drift_n131072_10k.json 2> gpurun_out/${tag}_energy.err; echo "energy rc=$?"
   cut -c1-700 gpurun_out/${tag}_energy_drift_n131072_10k.json ;;

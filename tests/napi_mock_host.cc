@@ -337,6 +337,24 @@ template <typename T> static void run(bool f64, const char* prec, const std::vec
         const double n_now = call("worldSync", {ctx, typed_as(napi_float64_array, id2.data(), n), typed_as(napi_int32_array, type2.data(), n),
                                                  typed_as(napi_float64_array, radius2.data(), n)})->num;
         if (n_now != double(n) || id2 != id || type2 != type || radius2 != radius) exit(8);
+        // worldFrame with nsteps = 0 returns what worldSync + download return, through one call
+        std::vector<double> fpm(4 * n), fvel(4 * n), facc(4 * n), ftemp(n), fid(n), frad(n), stats(6, -1.0);
+        std::vector<int> ftype(n);
+        std::vector<double> dpm(4 * n), dvel(4 * n), dacc(4 * n), dtemp(n);
+        call("download", {ctx, typed_as(napi_float64_array, dpm.data(), 4 * n), typed_as(napi_float64_array, dvel.data(), 4 * n),
+                          typed_as(napi_float64_array, dacc.data(), 4 * n), typed_as(napi_float64_array, dtemp.data(), n)});
+        call("worldFrame", {ctx, num(dt), num(G), num(eps), num(0), num(1), typed_as(napi_float64_array, fpm.data(), 4 * n),
+                            typed_as(napi_float64_array, fvel.data(), 4 * n - 4), typed_as(napi_float64_array, facc.data(), 4 * n),
+                            typed_as(napi_float64_array, ftemp.data(), n), typed_as(napi_float64_array, fid.data(), n),
+                            typed_as(napi_int32_array, ftype.data(), n), typed_as(napi_float64_array, frad.data(), n)}, true);  // one row short: throws
+        const double n_frame = call("worldFrame", {ctx, num(dt), num(G), num(eps), num(0), num(1), typed_as(napi_float64_array, fpm.data(), 4 * n),
+                                                   typed_as(napi_float64_array, fvel.data(), 4 * n), typed_as(napi_float64_array, facc.data(), 4 * n),
+                                                   typed_as(napi_float64_array, ftemp.data(), n), typed_as(napi_float64_array, fid.data(), n),
+                                                   typed_as(napi_int32_array, ftype.data(), n), typed_as(napi_float64_array, frad.data(), n),
+                                                   typed_as(napi_float64_array, stats.data(), 6)})->num;
+        if (n_frame != double(n) || fpm != dpm || fvel != dvel || facc != dacc || ftemp != dtemp || fid != id || ftype != type || frad != radius) exit(9);
+        for (double v : stats)
+            if (v != 0.0) exit(10);  // nothing touched: no merges, fractures, overlaps, flashes, explosions, contacts
     } else if (g_host) {
         // the arrays uploaded above are handed over again and come back advanced; a bad array must throw, not crash
         call("stepHost", {ctx, typed(f64, pm.data(), 4 * n), typed(f64, vel.data(), 4 * n - 4), typed(f64, acc.data(), 4 * n),

@@ -120,6 +120,60 @@ def test_world_with_gravity_default_scene(nb, oracle):
     e.close()
 
 
+def test_world_frame_is_step_plus_sync_plus_download(nb, oracle):
+    """nbody_world_frame = nbody_world_step + nbody_world_sync + nbody_download through one launch and one synchronise: the
+    same bits as the three calls, through merges and fractures (the body count changes under the caller's arrays)."""
+    w = crowd(oracle, 80, 5, 4.0, 9.0, max_bodies=90)
+    a, b = mirror(nb, w, max_bodies=90), mirror(nb, w, max_bodies=90)
+    out, sizes = None, set()
+    for block in range(6):
+        w.integrate(0.008, 0.0, 0.5, collisions=True, nsteps=2)
+        a.world_step(0.008, 0.0, 0.5, 2, collisions=True)
+        got, info = device_state(a)
+        out = b.world_frame(0.008, 0.0, 0.5, 2, collisions=True, out=out)
+        want = w.state()
+        assert out["n"] == info["n"] == len(w) == b.n
+        for k in KEYS:
+            assert np.array_equal(out[k], got[k]) and np.array_equal(out[k], want[k]), (block, k)
+        assert np.array_equal(out["acc"], a.download()["acc"])
+        assert out["rng"] == info["rng"] == w.rng and out["counters"] == info["counters"] and out["n_contacts"] == info["n_contacts"]
+        sizes.add(out["n"])
+    assert len(sizes) > 1 and out["counters"]["fractures"] > 0
+    same = b.world_frame(0.008, 0.0, 0.5, 0)                          # nsteps = 0: just the record
+    for k in KEYS + ("acc",):
+        assert np.array_equal(same[k], out[k])
+    d = b.download(temp=True)                                         # ... and the context's own arrays hold the same state
+    assert np.array_equal(d["pos_mass"], out["pos_mass"]) and np.array_equal(d["temp"], out["temp"])
+    # arrays too short for the device's list: an error, never a partial frame
+    import ctypes
+    n = ctypes.c_size_t()
+    pm = np.zeros((4, 4))
+    rc = b._L.nbody_world_frame(b._ctx, 0.008, 0.0, 0.5, 0, 1, 4, ctypes.byref(n), pm.ctypes.data, None, None, None, None, None, None, None, None, None)
+    assert rc == nb._lib.NBODY_ENOMEM and n.value == out["n"] and not pm.any()
+    a.close()
+    b.close()
+
+
+def test_world_frame_timing_default_scene(nb, oracle):
+    s = nb.scenes.galaxy_default()
+    w = oracle.World(seed=0x5EED0001, max_bodies=300)
+    rng = np.random.default_rng(1)
+    for i in range(s.n):
+        w.add(s.pos_mass[i, 3], s.pos_mass[i, :3], s.vel[i, :3], "metal" if i == 0 else TYPES[int(rng.integers(0, 3))], s.temp[i])
+    e = mirror(nb, w)
+    out = None
+    for _ in range(20):
+        out = e.world_frame(s.dt, s.G, s.softening, 2, out=out)
+    t0 = time.perf_counter()
+    frames = 300
+    for _ in range(frames):
+        out = e.world_frame(s.dt, s.G, s.softening, 2, out=out)
+    us = (time.perf_counter() - t0) / frames * 1e6
+    print(f"complete frame with host arrays out (2 x integrate with collisions, {out['n']} bodies): {us:.1f} us")
+    assert np.isfinite(out["pos_mass"]).all()
+    e.close()
+
+
 def test_world_without_collisions_equals_the_step_contract(nb, oracle):
     s = nb.scenes.galaxy_default()
     p, v, a, t = oracle.integrate(s.pos_mass, s.vel, np.zeros_like(s.vel), s.temp, s.dt, s.G, s.softening, nsteps=4)
