@@ -213,7 +213,8 @@ def state_hash(a: np.ndarray) -> str:
 
 def kernel_model(info):
     if info.get("f32_sym_last_pass"):
-        return ("pairs_once_equal_mass" if info.get("uniform_mass") else "pairs_once_general"), "force_f32_sym_kernel (+ f32_sym_finish_kernel)"
+        kernel = "force_f32_symw_kernel" if info.get("f32_sym_warp_units") else "force_f32_sym_kernel"   # same arithmetic per pair, warp-sized units
+        return ("pairs_once_equal_mass" if info.get("uniform_mass") else "pairs_once_general"), kernel + " (+ f32_sym_finish_kernel)"
     return ("sweep_equal_mass" if info.get("uniform_mass") else "sweep_general"), "force_f32_kernel"
 
 
@@ -489,6 +490,7 @@ def main():
                            "l2": "flushed between steps (256 MiB write), outside the per-step event pairs",
                            "timed_call": "nbody_step(dt,G,eps,1) per step: kick1_drift + force pass (+ finish) in mode kick-2",
                            "pairs_once_tiles_per_unit": info.get("f32_symmetric", 0), "bodies_per_thread": info.get("f32_sym_bodies_per_thread", 0),
+                           "pairs_once_warp_units": bool(info.get("f32_sym_warp_units", 0)),
                            "flop_convention": "20 flop/interaction", "tflops_20": value * 20e-3,
                            "equal_mass_kernel": bool(info.get("uniform_mass"))},
                 "roofline": roof, "gpu_launches": int(launches_all), "clocks": clocks,

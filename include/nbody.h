@@ -209,6 +209,10 @@ NBODY_API int nbody_selftest_pow_third(nbody_ctx* ctx, const double* x, double* 
  * balanced by tile visits.  units_out receives (i-tile, first tile, tile count, diagonal flag) per unit. */
 NBODY_API int nbody_selftest_sym32_units(size_t n, int bodies_per_thread, int run, int world, unsigned* units_out /* 4*cap */,
                                          size_t cap, size_t* count, unsigned* split_out /* world + 1 */);
+/* ... and of its warp-unit form (csrc/force_f32_symw.cuh; bodies_per_thread 2, 4 or 8): i-blocks of 32 x bodies_per_thread
+ * bodies against runs of `run` groups of 64 bodies; (i-block, first group, group count, diagonal flag). */
+NBODY_API int nbody_selftest_symw_units(size_t n, int bodies_per_thread, int run, int world, unsigned* units_out /* 4*cap */,
+                                        size_t cap, size_t* count, unsigned* split_out /* world + 1 */);
 
 /* ---- renderer feed: position history and ribbon trails ---- */
 
@@ -336,6 +340,8 @@ typedef struct {
     int f32_sym_last_pass;         /* 1 when the last force pass actually was the pairs-once one (softening == 0 and set radii take the sweep) */
     long long upload_h2d_bytes;    /* host->device bytes THIS process copied in the last nbody_upload (with peer mappings every device
                                       copies only its own slice of pos_mass and packs it into every peer's buffers) */
+    int f32_sym_warp_units;        /* 1 when that pass is the warp-unit form (force_f32_symw.cuh): every warp its own worker, units of
+                                      (32 x bodies_per_thread i-bodies) x (f32_symmetric groups of 64 bodies) */
 } nbody_info;
 NBODY_API int nbody_get_info(nbody_ctx* ctx, nbody_info* out);
 

@@ -130,8 +130,15 @@ struct nbody_ctx {
     int sym32_table_R = 0, sym32_table_run = 0;
     std::vector<unsigned> sym32_split;  // unit ranges of the ranks: rank r takes [split[r], split[r+1])
     double sum_abs_mass = 0.0;      // of the current upload (the equal-mass sweep counts every body as 1)
-    int sym32_slots[2] = {0, 0};    // resident CTAs per device of the general / equal-mass kernel (grid size of the persistent launch)
+    int sym32_slots[2][2] = {};    // resident CTAs per device of the general / equal-mass kernel (grid size of the persistent launch)
     bool sym32_used = false;        // the last force pass was the pairs-once one
+    unsigned sym32_pass = 0;        // fp32 pairs-once passes since the last upload (one GPU: which poison word is in use)
+    bool sym32_fine = false;        // the current table is the warp-unit one (force_f32_symw.cuh): units of 64-body groups
+    bool sym32_table_fine = false;
+    size_t symw_min_n = 0, symw_max_n = 0;  // body counts that always take the warp-unit form (NBODY_F32_SYMW_MIN / _MAX)
+    int symw_R_forced = 0;          // NBODY_F32_SYMW_R at create: 2, 4 or 8
+    bool symw_general_large = true; // NBODY_F32_SYMW_GENERAL at create: general masses keep the warp units above symw_max_n
+    int symw_slots[2][3] = {};      // resident CTAs per device of the warp-unit kernels [equal masses][R = 2, 4, 8]
     size_t medium_max_n = 0;        // largest system that kernel takes (fp32 5,120, fp64 4,096; NBODY_MEDIUM_MAX lowers it)
     int medium_ctas = 0;            // > 0: systems of up to medium_max_n bodies run all steps of a call in one cooperative launch
                                     // of this many CTAs (medium.cuh; NBODY_MEDIUM at create, one GPU, needs cooperative launch)

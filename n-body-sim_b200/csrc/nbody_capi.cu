@@ -9,6 +9,7 @@
 #include "exchange.cuh"
 #include "force_f32.cuh"
 #include "force_f32_sym.cuh"
+#include "force_f32_symw.cuh"
 #include "force_f64.cuh"
 #include "force_f64_sym.cuh"
 #include "integrate.cuh"
@@ -24,7 +25,11 @@ constexpr int kUniUnroll = NB_UNIFORM_UNROLL;  // inner-loop unroll of the equal
 // mass variants once each runs at its best unroll (force_f32_sym.cuh; N=1M: 4,240 against 3,920 and 3,608 against 3,526).
 constexpr int kSym32EqualMassR = 8, kSym32GeneralR = 8;
 constexpr size_t kSym32SmallN = 49152;              // below: 4 bodies per thread
-constexpr int kSym32DefaultMinN = 32768;            // smallest system that takes it (below: too few units for the SMs)
+constexpr int kSym32DefaultMinN = 32768;            // smallest system that takes the CTA-wide form (below: too few units for the SMs)
+constexpr int kSymwDefaultMinN = 6144;              // the warp-unit form (force_f32_symw.cuh) takes [min, max) bodies whatever the masses,
+constexpr int kSymwDefaultMaxN = 57344;             // and general masses at every size from min up
+constexpr size_t kSymwTinyN = 7168;                 // below: 2 bodies per thread (N=6,144: 24.3 us/step against 28.0 with 4; 8,192: 35.4 against 32.6)
+constexpr size_t kSymwSmallN = 28672;               // below: 4 bodies per thread, from here 8
 
 namespace {
 
@@ -251,6 +256,13 @@ template <typename F> void pick_f32_sym_kernel(int R, bool uniform, F&& f)
     return uniform ? f(force_f32_sym_kernel<4, true>) : f(force_f32_sym_kernel<4, false>);
 }
 
+template <typename F> void pick_f32_symw_kernel(int R, bool uniform, F&& f)
+{
+    if (R == 8) return uniform ? f(force_f32_symw_kernel<8, true>) : f(force_f32_symw_kernel<8, false>);
+    if (R == 2) return uniform ? f(force_f32_symw_kernel<2, true>) : f(force_f32_symw_kernel<2, false>);
+    return uniform ? f(force_f32_symw_kernel<4, true>) : f(force_f32_symw_kernel<4, false>);
+}
+
 int set_kernel_attrs(nbody_ctx* c)
 {
     const int sm32 = int(force_f32_smem_bytes());
@@ -298,6 +310,11 @@ int create_common(nbody_ctx** out, nbody_prec prec, int world, size_t capacity, 
         c->sym32_allowed = env_int("NBODY_F32_SYM", 1) != 0 && c->R == 4;
         c->sym32_R_forced = env_int("NBODY_F32_SYM_R", 0);  // 4 or 8; otherwise by kernel variant (build_sym32_table)
         c->sym32_min_n = size_t(std::max(env_int("NBODY_F32_SYM_MIN", kSym32DefaultMinN), 1));
+        // ... and its warp-unit form (force_f32_symw.cuh)
+        c->symw_min_n = size_t(std::max(env_int("NBODY_F32_SYMW_MIN", kSymwDefaultMinN), 1));
+        c->symw_max_n = env_int("NBODY_F32_SYMW", 1) != 0 ? size_t(std::max(env_int("NBODY_F32_SYMW_MAX", kSymwDefaultMaxN), 0)) : 0;
+        c->symw_R_forced = env_int("NBODY_F32_SYMW_R", 0);
+        c->symw_general_large = env_int("NBODY_F32_SYMW_GENERAL", 1) != 0;
     } else {
         c->f64_math = env_int("NBODY_F64_MATH", 2);
         c->f64_R_forced = env_int("NBODY_F64_R", 0);
@@ -660,6 +677,7 @@ extern "C" int nbody_get_info(nbody_ctx* c, nbody_info* o)
     o->f32_sym_bodies_per_thread = c->sym32_run > 0 ? c->sym32_R : 0;
     o->f32_sym_last_pass = c->sym32_used ? 1 : 0;
     o->upload_h2d_bytes = c->upload_h2d_bytes;
+    o->f32_sym_warp_units = c->sym32_run > 0 && c->sym32_fine ? 1 : 0;
     return NBODY_OK;
 }
 
@@ -683,7 +701,7 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
         const int rcb = queue_exchange_barrier(c);
         if (rcb != NBODY_OK) return rcb;
     }
-    const bool want_mass = sizeof(Real) == 4 ? (c->sym32_allowed && n >= c->sym32_min_n) : c->f64_sym_k > 0;
+    const bool want_mass = sizeof(Real) == 4 ? (c->sym32_allowed && (n >= c->sym32_min_n || (n >= c->symw_min_n && n < c->symw_max_n))) : c->f64_sym_k > 0;
     double small_mass = 0.0;
     // several devices with peer mappings: each shard uploads and packs its own slice only (pack_pos_shard_kernel)
     const bool sharded = c->world > 1 && c->p2p && env_int("NBODY_SHARDED_UPLOAD", 1) != 0;
@@ -722,6 +740,10 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
             CU(c, cudaEventRecord(s.io_done, s.stream));
             small_io = true;
             if (want_mass) {  // (a few thousand bodies: the host adds them, in index order)
+                if (s.accfix) {  // the pairs-once pass may take this upload: its accumulators, poison words and counter start at zero
+                    CU(c, cudaMemsetAsync(s.accfix, 0, ((sizeof(Real) == 4 ? 3 : 6) * c->cap_pad + 2) * sizeof(unsigned long long), s.stream));
+                    CU(c, cudaMemsetAsync(s.sym_ctl, 0, sizeof(unsigned), s.stream));
+                }
                 double t = 0.0;
                 for (size_t i = 0; i < n; ++i) t += std::fabs(double(pm[4 * i + 3]));
                 small_mass = t;
@@ -755,8 +777,10 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
         CUK(c, "pack_pos_kernel", s.device);
         }
         if (!small_io) {
-        if (s.accfix)  // (zero unless a pass was abandoned)
+        if (s.accfix) {  // (zero unless a pass was abandoned)
             CU(c, cudaMemsetAsync(s.accfix, 0, ((sizeof(Real) == 4 ? 3 : 6) * c->cap_pad + 2) * sizeof(unsigned long long), s.stream));
+            CU(c, cudaMemsetAsync(s.sym_ctl, 0, sizeof(unsigned), s.stream));
+        }
         c->launches++;
         CU(c, cudaGetLastError());
         CU(c, cudaMemsetAsync(s.vel, 0, s.n_local * v4, s.stream));
@@ -782,6 +806,7 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
     }
     // host buffers are borrowed for the duration of the call only (the small-system path has copied them already)
     c->upload_deferred = small_io;
+    c->sym32_pass = 0;
     c->sum_abs_mass = small_mass;
     if (small_io) return NBODY_OK;
     if (handshake) {
@@ -938,29 +963,87 @@ void make_sym32_units(size_t n, int R, int run, int world, std::vector<SymUnit>&
     split[world] = unsigned(units.size());
 }
 
+// The warp-unit form's table (force_f32_symw.cuh): i-blocks of R/2 groups of 64 bodies, each against its own groups (the
+// diagonal unit, one-sided) and against the groups above it in runs of `run`.  The same rules: a function of n and of the
+// kernel shape only; the GPUs share it by cost (group visits), in order.
+void make_symw_units(size_t n, int R, int run, int world, std::vector<SymUnit>& units, std::vector<unsigned>& split)
+{
+    const size_t h = size_t(R) / 2;
+    const size_t NG = (n + kSymwGroup - 1) / kSymwGroup;  // groups that hold bodies
+    const size_t NB = (NG + h - 1) / h;
+    std::vector<unsigned long long> cost;
+    unsigned long long total = 0;
+    units.clear();
+    for (size_t b = 0; b < NB; ++b) {
+        const size_t s0 = b * h, s1 = std::min((b + 1) * h, NG);
+        units.push_back(SymUnit{unsigned(b), unsigned(s0) | unsigned(s1 - s0) << 24 | kSymUnitDiag});
+        cost.push_back(total += s1 - s0);
+        for (size_t st = s1; st < NG; st += size_t(run)) {
+            const size_t cnt = std::min(size_t(run), NG - st);
+            units.push_back(SymUnit{unsigned(b), unsigned(st) | unsigned(cnt) << 24});
+            cost.push_back(total += cnt);
+        }
+    }
+    split.assign(size_t(world) + 1, 0);
+    size_t u = 0;
+    for (int r = 1; r < world; ++r) {
+        const unsigned long long target = total / world * r;
+        while (u < units.size() && cost[u] < target) ++u;
+        split[r] = unsigned(u);
+    }
+    split[world] = unsigned(units.size());
+}
+
 int build_sym32_table(nbody_ctx* c)
 {
     c->sym32_run = 0;
-    if (c->prec != NBODY_F32 || !c->sym32_allowed || c->n < c->sym32_min_n) return NBODY_OK;
+    const bool mid = c->n >= c->symw_min_n && c->n < c->symw_max_n;
+    if (c->prec != NBODY_F32 || !c->sym32_allowed || (!mid && c->n < c->sym32_min_n)) return NBODY_OK;
     if (c->detect_pending) {  // (a small upload returned before its mass detection was read)
         const int rcd = resolve_mass_detection(c);
         if (rcd != NBODY_OK) return rcd;
     }
-    // (below ~49k bodies the 512-body i-tiles of R = 4 give the 444 resident CTAs twice as many units: N=32,768 2,961 against
-    // 2,778 G interactions/s; from 65,536 up R = 8 wins, 3,767 against 3,534: profiles/r2a_sym_lab.jsonl)
-    const int R = (c->sym32_R_forced == 4 || c->sym32_R_forced == 8) ? c->sym32_R_forced
-                  : (c->n < kSym32SmallN ? 4 : (c->uniform ? kSym32EqualMassR : kSym32GeneralR));
+    // Which form (profiles/r2o_fine_lab.jsonl, r2o_big.jsonl; G interactions/s, before -> warp units): below symw_max_n the warp
+    // units always (N=8,192: 1,722 -> 2,053; 16,384: 2,424 -> 2,936; 32,768: 3,200 -> 3,620; 49,152: 3,616 -> 3,847; at 65,536 the
+    // CTA-wide kernel is back in front with equal masses, 3,816 against 3,710).  Above it, general masses keep them -- N=262,144:
+    // 3,544 -> 3,737, N=1M: 3,560 -> 3,761 -- and equal masses take the CTA-wide kernel (N=1M: 4,180 against 4,150).
+    const bool fine = mid || (c->symw_max_n > 0 && c->n >= c->symw_min_n && !c->uniform && c->symw_general_large);
+    int R, run;
+    if (fine) {
+        // 4 bodies per thread (12 warps per SM) up to ~28k bodies, 8 (8 warps) above: N=24,576 3,313 against 3,055, N=49,152 3,590 against 3,720
+        R = (c->symw_R_forced == 2 || c->symw_R_forced == 4 || c->symw_R_forced == 8) ? c->symw_R_forced : (c->n < kSymwTinyN ? 2 : c->n < kSymwSmallN ? 4 : 8);
+        // groups per unit: about eight units per resident warp of ONE device (a function of n only: the table, and with it every
+        // bit of the result, must not depend on the GPU count), at least one group (~2 us of a warp at R = 4), and few enough
+        // units that the table stays a few tens of MB at several million bodies
+        const size_t NG = (c->n + kSymwGroup - 1) / kSymwGroup;
+        const size_t rounds = NG * NG / size_t(R);
+        const size_t warps = size_t(c->sm_count) * (R == 8 ? 8 : R == 4 ? 12 : 16);
+        run = env_int("NBODY_F32_SYMW_RUN", 0);
+        if (run <= 0) {
+            run = int(std::min<size_t>(16, std::max<size_t>(1, rounds / (warps * 8))));
+            const size_t cells = NG * ((NG + size_t(R) / 2 - 1) / (size_t(R) / 2)) / 2;  // (i-block, group) cells above the diagonal
+            while (run < kSymUnitMaxRun && cells / size_t(run) > (size_t(4) << 20)) ++run;
+        }
+        if (NG >= (1u << 24)) return NBODY_OK;
+    } else {
+        // (below ~49k bodies the 512-body i-tiles of R = 4 give the 444 resident CTAs twice as many units: N=32,768 2,961 against
+        // 2,778 G interactions/s; from 65,536 up R = 8 wins, 3,767 against 3,534: profiles/r2a_sym_lab.jsonl)
+        R = (c->sym32_R_forced == 4 || c->sym32_R_forced == 8) ? c->sym32_R_forced
+            : (c->n < kSym32SmallN ? 4 : (c->uniform ? kSym32EqualMassR : kSym32GeneralR));
+        const size_t NS = (c->n + kPosTile - 1) / kPosTile;  // position tiles that hold bodies
+        if (NS >= (1u << 24)) return NBODY_OK;
+        run = env_int("NBODY_F32_SYM_RUN", 0);
+        // N=1M: 2 tiles (1,024 bodies) per unit = 0.13 ms of one CTA: the tail of a device's share stays ~0.2 % even when 8 GPUs
+        // split the step (units of 1..16 tiles run within 0.5 % of each other on one GPU, profiles/r2a_sym_lab.jsonl)
+        if (run <= 0) run = int(std::min<size_t>(8, std::max<size_t>(1, NS / 1024)));
+    }
     c->sym32_R = R;
-    const size_t NS = (c->n + kPosTile - 1) / kPosTile;  // position tiles that hold bodies
-    if (NS >= (1u << 24)) return NBODY_OK;
-    int run = env_int("NBODY_F32_SYM_RUN", 0);
-    // N=1M: 2 tiles (1,024 bodies) per unit = 0.13 ms of one CTA: the tail of a device's share stays ~0.2 % even when 8 GPUs
-    // split the step (units of 1..16 tiles run within 0.5 % of each other on one GPU, profiles/r2a_sym_lab.jsonl)
-    if (run <= 0) run = int(std::min<size_t>(8, std::max<size_t>(1, NS / 1024)));
+    c->sym32_fine = fine;
     run = std::min(run, kSymUnitMaxRun);
-    if (c->sym32_table_n != c->n || c->sym32_table_R != R || c->sym32_table_run != run) {
+    if (c->sym32_table_n != c->n || c->sym32_table_R != R || c->sym32_table_run != run || c->sym32_table_fine != fine) {
         std::vector<SymUnit> units;
-        make_sym32_units(c->n, R, run, c->world, units, c->sym32_split);
+        if (fine) make_symw_units(c->n, R, run, c->world, units, c->sym32_split);
+        else make_sym32_units(c->n, R, run, c->world, units, c->sym32_split);
         for (Shard& s : c->shards) {
             CU(c, cudaSetDevice(s.device));
             if (units.size() > s.sym_units_cap) {
@@ -977,6 +1060,7 @@ int build_sym32_table(nbody_ctx* c)
         c->sym32_table_n = c->n;
         c->sym32_table_R = R;
         c->sym32_table_run = run;
+        c->sym32_table_fine = fine;
     }
     c->sym32_run = run;
     return NBODY_OK;
@@ -1322,17 +1406,25 @@ int launch_force_sym32(nbody_ctx* c, int mode, double dt, double G, double eps)
     std::frexp(bound, &e);         // bound < 2^e
     const int k = std::max(-100, std::min(100, 61 - e));  // bound * 2^k < 2^61
     if (61 - e < -100) return 1;
-    int& slots = c->sym32_slots[uniform ? 1 : 0];
+    const bool fine = c->sym32_fine;
+    int& slots = fine ? c->symw_slots[uniform ? 1 : 0][c->sym32_R == 2 ? 0 : c->sym32_R == 4 ? 1 : 2] : c->sym32_slots[uniform ? 1 : 0][c->sym32_R == 8 ? 1 : 0];
     if (slots == 0) {
         int per_sm = 0;
         cudaError_t err = cudaSuccess;
         CU(c, cudaSetDevice(c->shards[0].device));
-        pick_f32_sym_kernel(c->sym32_R, uniform, [&](auto kernel) {
-            err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kF32Threads + 32, force_f32_sym_smem_bytes());
-        });
+        if (fine)
+            pick_f32_symw_kernel(c->sym32_R, uniform, [&](auto kernel) { err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kSymwThreads, 0); });
+        else
+            pick_f32_sym_kernel(c->sym32_R, uniform, [&](auto kernel) {
+                err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kF32Threads + 32, force_f32_sym_smem_bytes());
+            });
         if (err != cudaSuccess || per_sm < 1) return fail(c, NBODY_ECUDA, "pairs-once kernel does not fit an SM: %s", cudaGetErrorString(err));
         slots = per_sm * c->sm_count;
     }
+    // one GPU: two poison words used in turn (see Sym32Sources); upload_t zeroes both and the unit counter
+    const size_t poison_at = 3 * c->n_pad + (c->world == 1 ? size_t(c->sym32_pass & 1u) : 0);
+    const size_t poison_next = 3 * c->n_pad + size_t((c->sym32_pass & 1u) ^ 1u);
+    c->sym32_pass++;
     for (Shard& s : c->shards) {
         CU(c, cudaSetDevice(s.device));
         if (c->timing && &s == &c->shards[0]) {
@@ -1346,18 +1438,28 @@ int launch_force_sym32(nbody_ctx* c, int mode, double dt, double G, double eps)
         sp.u_end = c->sym32_split[s.rank + 1];
         sp.sched = s.sym_ctl;
         sp.accfix = s.accfix;
+        sp.poison = s.accfix + poison_at;
         sp.n_pad = c->n_pad;
         sp.eps2 = float(eps) * float(eps);
         sp.scale = std::ldexp(1.0f, k);
         sp.bound = std::nextafter(float(bound), INFINITY);
-        CU(c, cudaMemsetAsync(s.sym_ctl, 0, sizeof(unsigned), s.stream));
-        if (c->world > 1 && !c->p2p)  // (after the all-reduce below every device holds ALL bodies' totals and clears only its own)
-            CU(c, cudaMemsetAsync(s.accfix, 0, (3 * c->n_pad + 1) * sizeof(unsigned long long), s.stream));
-        else
-            CU(c, cudaMemsetAsync(s.accfix + 3 * c->n_pad, 0, sizeof(unsigned long long), s.stream));
+        if (c->world == 1) {
+            // nothing to clear: the previous finish kernel rewound the counter and cleared this pass's poison word (Sym32Sources)
+        } else {
+            CU(c, cudaMemsetAsync(s.sym_ctl, 0, sizeof(unsigned), s.stream));
+            if (!c->p2p)  // (after the all-reduce below every device holds ALL bodies' totals and clears only its own)
+                CU(c, cudaMemsetAsync(s.accfix, 0, (3 * c->n_pad + 1) * sizeof(unsigned long long), s.stream));
+            else
+                CU(c, cudaMemsetAsync(s.accfix + 3 * c->n_pad, 0, sizeof(unsigned long long), s.stream));
+        }
         const unsigned units = sp.u_end - sp.u_begin;
-        const unsigned grid = std::max(1u, std::min(units, unsigned(slots)));
-        pick_f32_sym_kernel(c->sym32_R, uniform, [&](auto kernel) { kernel<<<grid, kF32Threads + 32, force_f32_sym_smem_bytes(), s.stream>>>(sp); });
+        if (fine) {  // every warp a worker
+            const unsigned grid = std::max(1u, std::min((units + kSymwWarps - 1) / kSymwWarps, unsigned(slots)));
+            pick_f32_symw_kernel(c->sym32_R, uniform, [&](auto kernel) { kernel<<<grid, kSymwThreads, 0, s.stream>>>(sp); });
+        } else {
+            const unsigned grid = std::max(1u, std::min(units, unsigned(slots)));
+            pick_f32_sym_kernel(c->sym32_R, uniform, [&](auto kernel) { kernel<<<grid, kF32Threads + 32, force_f32_sym_smem_bytes(), s.stream>>>(sp); });
+        }
         c->launches++;
         CU(c, cudaGetLastError());
     }
@@ -1384,6 +1486,9 @@ int launch_force_sym32(nbody_ctx* c, int mode, double dt, double G, double eps)
         Sym32Sources src;
         src.n = 0;
         src.inv_scale = std::ldexp(1.0, -k);
+        src.poison_at = poison_at;
+        src.sched_rewind = c->world == 1 ? s.sym_ctl : nullptr;
+        src.poison_next = c->world == 1 ? s.accfix + poison_next : nullptr;
         if (c->world == 1 || !c->p2p) {
             src.acc[src.n++] = s.accfix;
         } else {
@@ -1880,13 +1985,30 @@ extern "C" int nbody_energy(nbody_ctx* c, double G, double softening, double* ki
 
 // Host logic only (no device needed): the pairs-once unit table for n bodies and the ranks' shares of it, for the CPU tests.
 // units_out: (i-tile, first position tile, tile count, diagonal flag) per unit.
+static int selftest_units(bool fine, size_t n, int bodies_per_thread, int run, int world, unsigned* units_out, size_t cap, size_t* count,
+                          unsigned* split_out);
+
 extern "C" int nbody_selftest_sym32_units(size_t n, int bodies_per_thread, int run, int world, unsigned* units_out /* 4*cap */, size_t cap,
                                           size_t* count, unsigned* split_out /* world + 1 */)
 {
-    if (n == 0 || (bodies_per_thread != 4 && bodies_per_thread != 8) || run < 1 || run > kSymUnitMaxRun || world < 1 || !count) return NBODY_EINVAL;
+    return selftest_units(false, n, bodies_per_thread, run, world, units_out, cap, count, split_out);
+}
+
+extern "C" int nbody_selftest_symw_units(size_t n, int bodies_per_thread, int run, int world, unsigned* units_out /* 4*cap */, size_t cap,
+                                         size_t* count, unsigned* split_out /* world + 1 */)
+{
+    return selftest_units(true, n, bodies_per_thread, run, world, units_out, cap, count, split_out);
+}
+
+static int selftest_units(bool fine, size_t n, int bodies_per_thread, int run, int world, unsigned* units_out, size_t cap, size_t* count,
+                          unsigned* split_out)
+{
+    const bool r_ok = fine ? (bodies_per_thread == 2 || bodies_per_thread == 4 || bodies_per_thread == 8) : (bodies_per_thread == 4 || bodies_per_thread == 8);
+    if (n == 0 || !r_ok || run < 1 || run > kSymUnitMaxRun || world < 1 || !count) return NBODY_EINVAL;
     std::vector<SymUnit> units;
     std::vector<unsigned> split;
-    make_sym32_units(n, bodies_per_thread, run, world, units, split);
+    if (fine) make_symw_units(n, bodies_per_thread, run, world, units, split);
+    else make_sym32_units(n, bodies_per_thread, run, world, units, split);
     *count = units.size();
     if (units.size() > cap) return NBODY_ENOMEM;
     for (size_t k = 0; units_out && k < units.size(); ++k) {

@@ -55,20 +55,22 @@ def create_rank_engine(capacity: int, precision: str = "f32"):
     return Engine(capacity, precision=precision, rank=rank, world=world, device=device, nccl_id=box[0])
 
 
-def sym32_units(n: int, bodies_per_thread: int = 8, run: int = 1, world: int = 1):
-    """The work-unit table of the fp32 pairs-once pass (csrc/force_f32_sym.cuh) and the ranks' shares of it, from the
-    library's own host code (no device needed).  Returns (units[k, 4] = i-tile, first position tile, tile count, diagonal
-    flag; split[world + 1])."""
+def sym32_units(n: int, bodies_per_thread: int = 8, run: int = 1, world: int = 1, warp_units: bool = False):
+    """The work-unit table of the fp32 pairs-once pass (csrc/force_f32_sym.cuh; warp_units: its warp-unit form,
+    csrc/force_f32_symw.cuh) and the ranks' shares of it, from the library's own host code (no device needed).
+    Returns (units[k, 4] = i-tile, first position tile, tile count, diagonal flag; split[world + 1]); with warp_units
+    the i-tile is a block of 32 x bodies_per_thread bodies and the tiles are groups of 64."""
     import ctypes
 
     import numpy as np
 
     from . import _lib
     L = _lib.lib()
+    fn = L.nbody_selftest_symw_units if warp_units else L.nbody_selftest_sym32_units
     cnt = ctypes.c_size_t()
     split = np.zeros(world + 1, dtype=np.uint32)
-    L.nbody_selftest_sym32_units(n, bodies_per_thread, run, world, None, 0, ctypes.byref(cnt), None)
+    fn(n, bodies_per_thread, run, world, None, 0, ctypes.byref(cnt), None)
     units = np.zeros((cnt.value, 4), dtype=np.uint32)
-    _lib.check(L.nbody_selftest_sym32_units(n, bodies_per_thread, run, world, ctypes.c_void_p(units.ctypes.data), cnt.value,
-                                            ctypes.byref(cnt), ctypes.c_void_p(split.ctypes.data)))
+    _lib.check(fn(n, bodies_per_thread, run, world, ctypes.c_void_p(units.ctypes.data), cnt.value, ctypes.byref(cnt),
+                  ctypes.c_void_p(split.ctypes.data)))
     return units, split

@@ -54,8 +54,9 @@ def force(nb, pm, vel, G, eps, **kv):
 def test_sym32_force_vs_oracle(nb, oracle, scene, n, general, R):
     s, pm, vel = scene_arrays(nb, scene, n, general)
     ref = oracle.compute_gravity(pm.astype(np.float64), s.G, s.softening, mt=True)
-    acc, info = force(nb, pm, vel, s.G, s.softening, NBODY_F32_SYM_MIN=1, NBODY_F32_SYM_R=R)
+    acc, info = force(nb, pm, vel, s.G, s.softening, NBODY_F32_SYM_MIN=1, NBODY_F32_SYM_R=R, NBODY_F32_SYMW=0)
     assert info["f32_symmetric"] > 0 and info["f32_sym_bodies_per_thread"] == R and info["f32_sym_last_pass"] == 1
+    assert info["f32_sym_warp_units"] == 0
     err = norm_rel_err(acc, ref) if n > 1 else float(np.abs(acc[:, :3]).max())
     print(f"pairs-once R={R} {scene} n={s.n} {'general' if general else 'scene'} masses: acc norm-rel err {err:.3e}")
     assert err < F32_ACC_TOL
@@ -69,7 +70,7 @@ def test_sym32_force_vs_oracle(nb, oracle, scene, n, general, R):
 def test_sym32_newtons_third_law(nb, R):
     """sum m_i a_i = 0 (idx:282-288): each pair's two contributions are the same fp32 products with opposite signs."""
     s, pm, vel = scene_arrays(nb, "two_galaxies", 50000, True)
-    acc, _ = force(nb, pm, vel, s.G, s.softening, NBODY_F32_SYM_R=R)
+    acc, _ = force(nb, pm, vel, s.G, s.softening, NBODY_F32_SYM_R=R, NBODY_F32_SYMW=0)
     ma = pm[:, 3:4].astype(np.float64) * acc[:, :3].astype(np.float64)
     assert np.abs(ma.sum(axis=0)).max() < 1e-6 * np.abs(ma).sum()
 
@@ -153,6 +154,110 @@ def test_sym32_falls_back_when_it_cannot_apply(nb, oracle):
     assert norm_rel_err(a, acc1) < F32_ACC_TOL
 
 
+# ---- the warp-unit form (csrc/force_f32_symw.cuh): mid-size systems, and general masses at every size -------------------------
+
+WIDE = dict(NBODY_F32_SYMW_MIN=1, NBODY_F32_SYMW_MAX=1 << 30)
+
+
+@pytest.mark.parametrize("R", [2, 4, 8])
+@pytest.mark.parametrize("general", [False, True])
+@pytest.mark.parametrize("scene,n", [("plummer", 1), ("plummer", 2), ("plummer", 65), ("plummer", 513), ("two_galaxies", 1026), ("plummer", 3001),
+                                     ("uniform_cube", 8192), ("cold_collapse", 20000)])
+def test_warp_units_force_vs_oracle(nb, oracle, scene, n, general, R):
+    s, pm, vel = scene_arrays(nb, scene, n, general)
+    ref = oracle.compute_gravity(pm.astype(np.float64), s.G, s.softening, mt=True)
+    acc, info = force(nb, pm, vel, s.G, s.softening, NBODY_F32_SYMW_R=R, **WIDE)
+    assert info["f32_sym_warp_units"] == 1 and info["f32_sym_bodies_per_thread"] == R and info["f32_sym_last_pass"] == 1
+    err = norm_rel_err(acc, ref) if n > 1 else float(np.abs(acc[:, :3]).max())
+    print(f"warp units R={R} {scene} n={s.n} {'general' if general else 'scene'} masses: acc norm-rel err {err:.3e}")
+    assert err < F32_ACC_TOL
+    for run in (1, 5):     # the unit size only regroups fp32 partial sums
+        other, info = force(nb, pm, vel, s.G, s.softening, NBODY_F32_SYMW_R=R, NBODY_F32_SYMW_RUN=run, **WIDE)
+        assert info["f32_symmetric"] == run
+        if n > 1:
+            assert norm_rel_err(other, acc) < F32_ACC_TOL
+
+
+def test_warp_units_where_they_are_the_default(nb, oracle):
+    """[6,144, 49,152) bodies whatever the masses; general masses from 6,144 bodies up; equal masses above keep the CTA-wide kernel."""
+    for n, general, fine, R in ((4096, True, None, 0), (8192, False, True, 4), (20000, True, True, 4), (40000, False, True, 8),
+                                (65536, False, False, 8), (65536, True, True, 8), (300000, True, True, 8)):
+        s, pm, vel = scene_arrays(nb, "plummer", n, general)
+        acc, info = force(nb, pm, vel, s.G, s.softening)
+        if fine is not None:
+            assert info["f32_sym_last_pass"] == 1 and info["f32_sym_warp_units"] == int(fine), (n, info)
+            assert info["f32_sym_bodies_per_thread"] == R, (n, info)
+        pick = np.arange(0, s.n, max(1, s.n // 300))
+        ref = oracle.acc_subset(pm.astype(np.float64), pick, s.G, s.softening)
+        assert norm_rel_err(acc[pick], ref) < F32_ACC_TOL
+
+
+@pytest.mark.parametrize("general", [False, True])
+def test_warp_units_bits_do_not_depend_on_the_schedule(nb, general):
+    s, pm, vel = scene_arrays(nb, "plummer", 12000, general)
+    s.softening = 0.02
+    outs = []
+    for how in ("fused", "fused", "single", "split"):
+        with nb.Engine(s.n, precision="f32") as e:
+            e.upload(pm, vel)
+            assert e.info()["f32_sym_warp_units"] == 1
+            if how == "fused":
+                e.step(s.dt, s.G, s.softening, 4)
+            elif how == "single":
+                for _ in range(4):
+                    e.step(s.dt, s.G, s.softening, 1)
+            else:
+                for _ in range(4):
+                    e.kick1_drift(s.dt)
+                    e.force(s.G, s.softening)
+                    e.kick2(s.dt, 0.998)
+            outs.append(e.download())
+    for o in outs[1:]:
+        for k in ("pos_mass", "vel", "acc"):
+            assert np.array_equal(o[k], outs[0][k]), k
+
+
+def test_warp_units_non_finite_input_and_third_law(nb):
+    s, pm, vel = scene_arrays(nb, "two_galaxies", 16002, True)
+    acc, info = force(nb, pm, vel, s.G, s.softening)
+    assert info["f32_sym_warp_units"] == 1
+    ma = pm[:, 3:4].astype(np.float64) * acc[:, :3].astype(np.float64)
+    assert np.abs(ma.sum(axis=0)).max() < 1e-6 * np.abs(ma).sum()
+    with nb.Engine(s.n, precision="f32") as e:        # poisoned pass, clean pass, poisoned pass on ONE context: the two poison
+        e.upload(pm, vel)                              # words of the memset-free single-GPU path take turns
+        for k, bad in enumerate((True, False, False, True, False)):
+            pm2 = pm.copy()
+            if bad:
+                pm2[777, 2] = np.inf
+            e.upload(pm2, vel)
+            for _ in range(k % 2 + 1):
+                e.force(s.G, s.softening)
+            a = e.download()["acc"]
+            assert np.isnan(a[:, :3]).all() if bad else np.isfinite(a).all(), (k, bad)
+
+
+def test_warp_units_multi_gpu_same_bits(nb):
+    ng = nb.device_count()
+    if ng < 2:
+        pytest.skip("needs >= 2 GPUs")
+    for n in (20002, 70002):
+        s, pm, vel = scene_arrays(nb, "two_galaxies", n, True)
+        outs = []
+        for exchange in ("peer", "nccl"):
+            for g in sorted({1, 2, min(ng, 4), min(ng, 8)}):
+                with env(NBODY_EXCHANGE=exchange):
+                    with nb.Engine(s.n, precision="f32", n_gpus=g) as e:
+                        e.upload(pm, vel)
+                        assert e.info()["f32_sym_warp_units"] == 1
+                        e.step(s.dt, s.G, s.softening, 3)
+                        e.force(s.G, s.softening)
+                        e.step(s.dt, s.G, s.softening, 1)
+                        outs.append((exchange, g, e.download()))
+        for exchange, g, o in outs[1:]:
+            for k in ("pos_mass", "vel", "acc"):
+                assert np.array_equal(o[k], outs[0][2][k]), (n, exchange, g, k)
+
+
 def test_sym32_multi_gpu_same_bits(nb):
     """Each GPU works through its share of the unit table for ALL bodies and the owners add the peers' accumulators:
     integer sums, so 1, 2, 4 and 8 GPUs give the same bits -- with peer mappings and with the NCCL all-reduce."""
@@ -163,10 +268,10 @@ def test_sym32_multi_gpu_same_bits(nb):
     outs = []
     for exchange in ("peer", "nccl"):
         for g in sorted({1, 2, min(ng, 4), min(ng, 8)}):
-            with env(NBODY_EXCHANGE=exchange):
+            with env(NBODY_EXCHANGE=exchange, NBODY_F32_SYMW=0):     # (the CTA-wide form; the warp units have their own test above)
                 with nb.Engine(s.n, precision="f32", n_gpus=g) as e:
                     e.upload(pm, vel)
-                    assert e.info()["f32_symmetric"] > 0
+                    assert e.info()["f32_symmetric"] > 0 and e.info()["f32_sym_warp_units"] == 0
                     e.step(s.dt, s.G, s.softening, 3)
                     e.force(s.G, s.softening)
                     e.force(s.G, s.softening)

@@ -53,6 +53,40 @@ def test_unit_table_covers_the_pair_triangle_once(nb, n, R, run):
     assert (np.diff(key) > 0).all()
 
 
+GROUP = 64              # csrc/force_f32_symw.cuh kSymwGroup
+
+
+@pytest.mark.parametrize("n", [1, 63, 64, 65, 129, 1000, 5000, 8192, 40000])
+@pytest.mark.parametrize("R", [2, 4, 8])
+@pytest.mark.parametrize("run", [1, 3, 16])
+def test_warp_unit_table_covers_the_pair_triangle_once(nb, n, R, run):
+    """The warp-unit form (csrc/force_f32_symw.cuh): i-blocks of R/2 groups of 64 bodies against runs of groups."""
+    units, split = nb.dist.sym32_units(n, R, run, 1, warp_units=True)
+    NG, h = (n + GROUP - 1) // GROUP, R // 2
+    NB = (NG + h - 1) // h
+    seen = np.zeros((NB, NG), dtype=np.int32)
+    diag = np.zeros(NB, dtype=np.int32)
+    for b, first, count, d in units.tolist():
+        assert 1 <= count and first + count <= NG
+        if d:
+            assert first == b * h and count == min((b + 1) * h, NG) - first
+            diag[b] += 1
+        else:
+            assert count <= run and first >= (b + 1) * h
+        seen[b, first:first + count] += 1
+    assert (diag == 1).all()
+    for b in range(NB):
+        assert (seen[b, : b * h] == 0).all() and (seen[b, b * h:] == 1).all()
+    assert split.tolist() == [0, len(units)]
+    for world in (2, 3, 8):
+        again, shares = nb.dist.sym32_units(n, R, run, world, warp_units=True)
+        assert np.array_equal(again, units) and shares[0] == 0 and shares[-1] == len(units)
+        assert (np.diff(shares.astype(np.int64)) >= 0).all()
+        visits = units[:, 2].astype(np.int64)
+        share = np.array([visits[shares[r]:shares[r + 1]].sum() for r in range(world)])
+        assert np.abs(share - visits.sum() / world).max() <= 2 * int(visits.max()) + world
+
+
 @pytest.mark.parametrize("n,R,run", [(5000, 8, 1), (65536, 8, 1), (70002, 4, 1), (1048576, 8, 2), (4194304, 8, 8)])
 @pytest.mark.parametrize("world", [2, 3, 4, 8])
 def test_ranks_share_the_table_by_cost(nb, n, R, run, world):
