@@ -214,6 +214,25 @@ NBODY_API int nbody_selftest_sym32_units(size_t n, int bodies_per_thread, int ru
 NBODY_API int nbody_selftest_symw_units(size_t n, int bodies_per_thread, int run, int world, unsigned* units_out /* 4*cap */,
                                         size_t cap, size_t* count, unsigned* split_out /* world + 1 */);
 
+/* ---- an entry point that allocates nothing ---- */
+
+#define NBODY_STATIC_MAX_BODIES 16384
+
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Needs no context.
+ * acc[i] = G * sum_{j != i} m_j (p_j - p_i) / (|p_j - p_i|^2 + softening^2)^1.5 for n <= NBODY_STATIC_MAX_BODIES bodies in fp32, by the
+ * pairs-once force pass with exact fixed-point accumulators (csrc/force_f32_symw.cuh): what nbody_force + nbody_download(acc)
+ * return, within the fp32 tolerance of the tests (2e-5 of the largest acceleration).  softening > 0.
+ * pos_mass_dev: 4n floats (x, y, z, m) and acc_dev: 4n floats (ax, ay, az, 0), both DEVICE pointers on the CURRENT device;
+ * the four kernels are queued on `stream` (a cudaStream_t, NULL = the default stream) and the call returns without
+ * synchronising.  It calls no cudaMalloc / cudaFree and no allocating library routine: all scratch memory (0.76 MiB: packed
+ * positions, accumulators, unit table) is ONE static device array that every GPU which loads the library holds until the
+ * process exits.  Every call on a device shares that array: calls that overlap on the GPU (two streams, two threads) race;
+ * keep them ordered.  n > NBODY_STATIC_MAX_BODIES, NULL pointers or softening <= 0: NBODY_EINVAL; the reason is written to
+ * err (err_cap bytes, may be NULL).  A non-finite coordinate turns every acceleration into NaN, as in nbody_step. */
+NBODY_API int nbody_accel_f32_static(const float* pos_mass_dev, float* acc_dev, size_t n, double G, double softening, void* stream,
+                                     char* err, size_t err_cap);
+
 /* ---- renderer feed: position history and ribbon trails ---- */
 
 /* Keep Body.history on the device: the last `depth` positions of every body,

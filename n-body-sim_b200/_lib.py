@@ -29,7 +29,7 @@ SYMBOLS = (
     "nbody_history_enable", "nbody_history_push", "nbody_history_remap", "nbody_history_download", "nbody_trail_ribbons",
     "nbody_snapshot_save", "nbody_snapshot_load", "nbody_set_materials", "nbody_render",
     "nbody_world_enable", "nbody_world_config", "nbody_world_set_bodies", "nbody_world_step", "nbody_world_sync", "nbody_world_frame", "nbody_world_contacts",
-    "nbody_selftest_pow_third", "nbody_selftest_sym32_units", "nbody_selftest_symw_units",
+    "nbody_selftest_pow_third", "nbody_selftest_sym32_units", "nbody_selftest_symw_units", "nbody_accel_f32_static",
 )
 
 
@@ -127,6 +127,7 @@ def lib() -> ctypes.CDLL:
     L.nbody_selftest_pow_third.argtypes = [vp, vp, vp, sz]
     L.nbody_selftest_sym32_units.argtypes = [sz, i, i, i, vp, sz, ctypes.POINTER(sz), vp]
     L.nbody_selftest_symw_units.argtypes = [sz, i, i, i, vp, sz, ctypes.POINTER(sz), vp]
+    L.nbody_accel_f32_static.argtypes = [vp, vp, sz, d, d, vp, ctypes.c_char_p, sz]
     _lib = L
     return L
 

@@ -330,6 +330,19 @@ class Engine:
         return {k: getattr(inf, k) for k, _ in _lib.Info._fields_}
 
 
+STATIC_MAX_BODIES = 16384   # include/nbody.h NBODY_STATIC_MAX_BODIES
+
+
+def accel_f32_static(pos_mass_dev: int, acc_dev: int, n: int, G: float, softening: float, stream: int = 0) -> None:
+    """nbody_accel_f32_static (include/nbody.h): fp32 accelerations of n <= STATIC_MAX_BODIES bodies between two DEVICE buffers
+    (addresses on the current device), queued on `stream`, with no allocation anywhere: the scratch is a static device array."""
+    err = ctypes.create_string_buffer(256)
+    st = _lib.lib().nbody_accel_f32_static(ctypes.c_void_p(pos_mass_dev), ctypes.c_void_p(acc_dev), int(n), float(G), float(softening),
+                                           ctypes.c_void_p(stream), err, len(err))
+    if st != _lib.NBODY_OK:
+        raise NBodyError(st, err.value.decode() or "nbody_accel_f32_static")
+
+
 def device_count() -> int:
     n = _lib.lib().nbody_device_count()
     if n < 0:
