@@ -132,7 +132,6 @@ struct nbody_ctx {
     double sum_abs_mass = 0.0;      // of the current upload (the equal-mass sweep counts every body as 1)
     int sym32_slots[2][2] = {};    // resident CTAs per device of the general / equal-mass kernel (grid size of the persistent launch)
     bool sym32_used = false;        // the last force pass was the pairs-once one
-    unsigned sym32_pass = 0;        // fp32 pairs-once passes since the last upload (one GPU: which poison word is in use)
     bool sym32_fine = false;        // the current table is the warp-unit one (force_f32_symw.cuh): units of 64-body groups
     bool sym32_table_fine = false;
     size_t symw_min_n = 0, symw_max_n = 0;  // body counts that always take the warp-unit form (NBODY_F32_SYMW_MIN / _MAX)

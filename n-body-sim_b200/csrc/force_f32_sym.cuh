@@ -78,9 +78,8 @@ struct Sym32Params {
     const SymUnit* units;        // the unit table (the same on every GPU)
     unsigned u_begin, u_end;     // this GPU's share of it
     unsigned* sched;             // next unit of the share, relative to u_begin; zero at launch
-    unsigned long long* accfix;  // [3][n_pad] fixed-point sums, bodies in position-slot order (fix_slot)
-    unsigned long long* poison;  // the poison mark, set when a partial sum is not finite (or beyond the bound); zero at launch.
-                                 // accfix[3 n_pad], or on one GPU accfix[3 n_pad + (pass & 1)]: see Sym32Sources
+    unsigned long long* accfix;  // [3][n_pad] fixed-point sums, bodies in position-slot order (fix_slot), then ONE more word:
+                                 // the poison mark, set when a partial sum is not finite (or beyond the bound); zero at launch
     size_t n_pad;
     float eps2;
     float scale;                 // 2^k
@@ -92,7 +91,7 @@ __host__ __device__ __forceinline__ size_t fix_slot(size_t g) { return (g & ~siz
 
 __device__ __forceinline__ void sym_red(unsigned long long* dst, float v, const Sym32Params& p)
 {
-    if (!(fabsf(v) <= p.bound)) atomicOr(p.poison, 1ull);  // NaN, infinity, or a broken bound: never silently wrong
+    if (!(fabsf(v) <= p.bound)) atomicOr(p.accfix + 3 * p.n_pad, 1ull);  // NaN, infinity, or a broken bound: never silently wrong
     atomicAdd(dst, static_cast<unsigned long long>(__float2ll_rn(v * p.scale)));  // RED.E.ADD.64
 }
 
@@ -302,14 +301,13 @@ __global__ void __launch_bounds__(kF32Threads + 32, R == 8 ? NB_SYM32_CTAS_R8 : 
 // Where the sums of the bodies this GPU owns have been accumulated: its own array and, on several GPUs,
 // every peer's (peer-mapped or IPC-opened pointers).
 struct Sym32Sources {
-    unsigned long long* acc[kMaxPeers];  // (each followed by its poison words)
+    unsigned long long* acc[kMaxPeers];  // (each followed by its poison word at [3 n_pad])
     int n;
     double inv_scale;  // 2^-k
-    size_t poison_at;  // this pass's poison word: acc[k][poison_at]
-    // One GPU: no memsets between the kernels.  The finish kernel rewinds the unit counter (the force kernel has retired) and
-    // clears the poison word of the NEXT pass -- the other one of two, last read by the previous finish kernel.
+    // One GPU: no memsets between the kernels.  The LAST block of the finish kernel to retire (counted in `done`, which it
+    // leaves at zero) rewinds the unit counter and clears the poison word: every thread of the pass has read it by then.
     unsigned* sched_rewind;
-    unsigned long long* poison_next;
+    unsigned* done;
 };
 
 // One thread per owned body: add the accumulators (exact), clear them for the next pass, convert, and run the
@@ -319,16 +317,24 @@ template <bool UNIFORM>
 __global__ void __launch_bounds__(kSym32FinishThreads) f32_sym_finish_kernel(const ForceParams<float> p, const Sym32Sources src, const size_t n_pad)
 {
     const size_t sl = size_t(blockIdx.x) * kSym32FinishThreads + threadIdx.x;  // local slot index
-    if (sl == 0) {
-        if (src.sched_rewind) *src.sched_rewind = 0u;
-        if (src.poison_next) *src.poison_next = 0ull;
+    const unsigned bad0 = src.sched_rewind ? unsigned(src.acc[0][3 * n_pad] != 0ull) : 0u;
+    if (src.sched_rewind) {  // (one GPU) every thread of the block has the poison word; the last block to say so clears it
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            if (atomicAdd(src.done, 1u) == gridDim.x - 1) {
+                *src.done = 0u;
+                *src.sched_rewind = 0u;
+                src.acc[0][3 * n_pad] = 0ull;
+            }
+        }
     }
     if (sl >= p.n_local) return;
     const size_t il = (sl & ~size_t(511)) + tile_body(unsigned(sl) & 511u);  // (i_begin is a multiple of the tile)
     const size_t gs = p.i_begin + sl;
     NB_CHECK(gs < n_pad && il < p.n_local);
     long long s[3] = {0, 0, 0};
-    unsigned bad = 0;
+    unsigned bad = bad0;
     for (int k = 0; k < src.n; ++k) {
         unsigned long long* a = src.acc[k] + gs;
 #pragma unroll
@@ -336,7 +342,7 @@ __global__ void __launch_bounds__(kSym32FinishThreads) f32_sym_finish_kernel(con
             s[c] += static_cast<long long>(a[c * n_pad]);
             a[c * n_pad] = 0ull;
         }
-        bad |= unsigned(src.acc[k][src.poison_at] != 0ull);
+        if (!src.sched_rewind) bad |= unsigned(src.acc[k][3 * n_pad] != 0ull);
     }
     float sx = float(double(s[0]) * src.inv_scale);
     float sy = float(double(s[1]) * src.inv_scale);

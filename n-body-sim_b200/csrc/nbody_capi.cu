@@ -743,6 +743,7 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
                 if (s.accfix) {  // the pairs-once pass may take this upload: its accumulators, poison words and counter start at zero
                     CU(c, cudaMemsetAsync(s.accfix, 0, ((sizeof(Real) == 4 ? 3 : 6) * c->cap_pad + 2) * sizeof(unsigned long long), s.stream));
                     CU(c, cudaMemsetAsync(s.sym_ctl, 0, sizeof(unsigned), s.stream));
+                    CU(c, cudaMemsetAsync(s.sym_ctl + 2, 0, sizeof(unsigned), s.stream));
                 }
                 double t = 0.0;
                 for (size_t i = 0; i < n; ++i) t += std::fabs(double(pm[4 * i + 3]));
@@ -780,6 +781,7 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
         if (s.accfix) {  // (zero unless a pass was abandoned)
             CU(c, cudaMemsetAsync(s.accfix, 0, ((sizeof(Real) == 4 ? 3 : 6) * c->cap_pad + 2) * sizeof(unsigned long long), s.stream));
             CU(c, cudaMemsetAsync(s.sym_ctl, 0, sizeof(unsigned), s.stream));
+            CU(c, cudaMemsetAsync(s.sym_ctl + 2, 0, sizeof(unsigned), s.stream));
         }
         c->launches++;
         CU(c, cudaGetLastError());
@@ -806,7 +808,6 @@ template <typename Real> int upload_t(nbody_ctx* c, size_t n, const Real* pm, co
     }
     // host buffers are borrowed for the duration of the call only (the small-system path has copied them already)
     c->upload_deferred = small_io;
-    c->sym32_pass = 0;
     c->sum_abs_mass = small_mass;
     if (small_io) return NBODY_OK;
     if (handshake) {
@@ -1421,10 +1422,6 @@ int launch_force_sym32(nbody_ctx* c, int mode, double dt, double G, double eps)
         if (err != cudaSuccess || per_sm < 1) return fail(c, NBODY_ECUDA, "pairs-once kernel does not fit an SM: %s", cudaGetErrorString(err));
         slots = per_sm * c->sm_count;
     }
-    // one GPU: two poison words used in turn (see Sym32Sources); upload_t zeroes both and the unit counter
-    const size_t poison_at = 3 * c->n_pad + (c->world == 1 ? size_t(c->sym32_pass & 1u) : 0);
-    const size_t poison_next = 3 * c->n_pad + size_t((c->sym32_pass & 1u) ^ 1u);
-    c->sym32_pass++;
     for (Shard& s : c->shards) {
         CU(c, cudaSetDevice(s.device));
         if (c->timing && &s == &c->shards[0]) {
@@ -1438,13 +1435,12 @@ int launch_force_sym32(nbody_ctx* c, int mode, double dt, double G, double eps)
         sp.u_end = c->sym32_split[s.rank + 1];
         sp.sched = s.sym_ctl;
         sp.accfix = s.accfix;
-        sp.poison = s.accfix + poison_at;
         sp.n_pad = c->n_pad;
         sp.eps2 = float(eps) * float(eps);
         sp.scale = std::ldexp(1.0f, k);
         sp.bound = std::nextafter(float(bound), INFINITY);
         if (c->world == 1) {
-            // nothing to clear: the previous finish kernel rewound the counter and cleared this pass's poison word (Sym32Sources)
+            // nothing to clear: the previous finish kernel rewound the counter and cleared the poison word (Sym32Sources)
         } else {
             CU(c, cudaMemsetAsync(s.sym_ctl, 0, sizeof(unsigned), s.stream));
             if (!c->p2p)  // (after the all-reduce below every device holds ALL bodies' totals and clears only its own)
@@ -1486,9 +1482,8 @@ int launch_force_sym32(nbody_ctx* c, int mode, double dt, double G, double eps)
         Sym32Sources src;
         src.n = 0;
         src.inv_scale = std::ldexp(1.0, -k);
-        src.poison_at = poison_at;
         src.sched_rewind = c->world == 1 ? s.sym_ctl : nullptr;
-        src.poison_next = c->world == 1 ? s.accfix + poison_next : nullptr;
+        src.done = s.sym_ctl + 2;
         if (c->world == 1 || !c->p2p) {
             src.acc[src.n++] = s.accfix;
         } else {

@@ -119,7 +119,6 @@ __global__ void __launch_bounds__(kSymwThreads, 3) force_f32_symw_static_kernel(
     p.u_end = n_units;
     p.sched = &reinterpret_cast<StaticHead*>(scratch + kOffHead)->sched;
     p.accfix = reinterpret_cast<unsigned long long*>(scratch + kOffAcc);
-    p.poison = p.accfix + 3 * size_t(n_pad);
     p.n_pad = n_pad;
     p.eps2 = eps2;
     p.scale = h->scale;

@@ -76,7 +76,7 @@ ncu)
 checked)
   NBODY_LIB=$PWD/n-body-sim_b200/variants/libnbody_checked.so CASES_REPEAT=5 timeout 900 python scripts/sanitize_cases.py > gpurun_out/${tag}_checked_build_cases.txt 2>&1; echo "checked build rc=$?"
   tail -32 gpurun_out/${tag}_checked_build_cases.txt | cut -c1-200
-  NBODY_LIB=$PWD/n-body-sim_b200/variants/libnbody_checked.so timeout 900 python -m pytest tests/test_gpu_sym32.py tests/test_gpu_world.py tests/test_gpu_edges.py -q -x 2>&1 | tail -3 ;;
+  NBODY_LIB=$PWD/n-body-sim_b200/variants/libnbody_checked.so timeout 900 python -m pytest tests/test_gpu_sym32.py tests/test_gpu_world.py tests/test_gpu_edges.py tests/test_zz_no_alloc.py -q -x 2>&1 | tail -3 ;;
 sanitize)
   tool=${2:-memcheck}; tag=${3:-r2}
   python scripts/sanitize_cases.py > gpurun_out/${tag}_sanitize_plain.log 2>&1 &&

@@ -44,7 +44,7 @@ def step_case(name, n, precision, env, nsteps=2, general=False, scene="plummer")
         assert len(hashes) == 1, (name, "results differ between repetitions", hashes)
         tol = 1e-11 if precision == "f64" else 5e-5
         worst = max(err(o["pos_mass"], p), err(o["vel"], v), err(o["acc"], a))
-        print(f"{name:44s} n={s.n:6d} {precision} err {worst:.2e} x{REPEAT} {next(iter(hashes))}  sym32={info['f32_sym_last_pass']} sym64={info['f64_symmetric']} uniform={info['uniform_mass']}", flush=True)
+        print(f"{name:44s} n={s.n:6d} {precision} err {worst:.2e} x{REPEAT} {next(iter(hashes))}  sym32={info['f32_sym_last_pass']} warp={info['f32_sym_warp_units']} sym64={info['f64_symmetric']} uniform={info['uniform_mass']}", flush=True)
         assert worst < tol, (name, worst)
     finally:
         for k, v in old.items():
@@ -66,8 +66,13 @@ def main():
     step_case("fp64 pairs-once (force_f64_sym.cuh)", 5000, "f64", per_step, general=True)
     for R in (4, 8):
         for general in (False, True):
-            step_case(f"fp32 pairs-once R={R} (force_f32_sym.cuh)", 5000, "f32", dict(per_step, NBODY_F32_SYM_MIN=1, NBODY_F32_SYM_R=R), nsteps=3, general=general)
-    step_case("fp32 pairs-once, outliers", 3002, "f32", dict(per_step, NBODY_F32_SYM_MIN=1), scene="two_galaxies")
+            step_case(f"fp32 pairs-once R={R} (force_f32_sym.cuh)", 5000, "f32", dict(per_step, NBODY_F32_SYM_MIN=1, NBODY_F32_SYM_R=R, NBODY_F32_SYMW=0), nsteps=3, general=general)
+    step_case("fp32 pairs-once, outliers", 3002, "f32", dict(per_step, NBODY_F32_SYM_MIN=1, NBODY_F32_SYMW=0), scene="two_galaxies")
+    wide = dict(per_step, NBODY_F32_SYMW_MIN=1, NBODY_F32_SYMW_MAX=1 << 30)
+    for R in (2, 4, 8):
+        for general in (False, True):
+            step_case(f"fp32 pairs-once, warp units R={R} (force_f32_symw.cuh)", 5000, "f32", dict(wide, NBODY_F32_SYMW_R=R), nsteps=3, general=general)
+    step_case("fp32 pairs-once, warp units, default shape", 9001, "f32", per_step, nsteps=3, general=True)
 
     # the rows next to the hot path: contacts (flagged and full scan), history ring + ribbons, renderer
     s = nb.scenes.galaxy_default()
