@@ -453,10 +453,12 @@ def main():
         traffic = traffic_source = None
         tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")
         if os.path.exists(tp):                      # dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture
-            t = json.load(open(tp))
-            if t.get("n") == args.n and t.get("world") == n_dev and t.get("kernel_model", model) == model:
-                traffic = t["dram_bytes_read"] + t["dram_bytes_write"]   # bytes per launch
-                traffic_source = t["source"]
+            first = json.load(open(tp))
+            for t in [first] + list(first.get("also", [])):   # one capture per kernel variant
+                if t.get("n") == args.n and t.get("world") == n_dev and t.get("kernel_model", model) == model:
+                    traffic = t["dram_bytes_read"] + t["dram_bytes_write"]   # bytes per launch
+                    traffic_source = t["source"]
+                    break
         alg_bytes = 64.0 * args.n / n_dev + 16.0 * args.n + (48.0 * args.n if model.startswith("pairs_once") else 0.0)
         roof = {"bound": "fp32_issue", "achieved": achieved, "peak": peak_own, "unit": UNIT + " per GPU",
                 "frac": achieved / peak_own, "traffic": traffic, "traffic_source": traffic_source,
