@@ -53,6 +53,12 @@ namespace nb {
 #ifndef NB_SYM32_SPLIT_G
 #define NB_SYM32_SPLIT_G 0  // lab switch: two half-length j-side accumulation chains per step (measured: see DESIGN.md 4.1)
 #endif
+#ifndef NB_SYM32_REPARK
+#define NB_SYM32_REPARK 0  // lab switch: each warp copies the 64-body group it is about to rotate into a private slot where every couple
+                           // is stored twice (force_f32_symw.cuh's layout: no index arithmetic in the loop, two LDS.128 per step).
+                           // 143 instead of 148 instructions per step and still slower HERE: N=1M equal masses 4,009 / 4,083 / 4,138 /
+                           // 4,148 G int/s with unroll 1 / 2 / 4 / 8 against 4,228 (general masses 3,597 -> 3,666): profiles/r2t_repark.jsonl
+#endif
 #ifndef NB_SYM32_UNROLL_EQUAL
 #define NB_SYM32_UNROLL_EQUAL 1
 #endif
@@ -99,7 +105,7 @@ __device__ __forceinline__ void sym_red(unsigned long long* dst, float v, const 
 template <int R, bool UNIFORM>
 __device__ __forceinline__ void sym_stage(const float* __restrict__ tp, const int lane, const int warp, const f32x2 (&nx)[R],
                                           const f32x2 (&ny)[R], const f32x2 (&nz)[R], const f32x2 (&mi)[R], f32x2 (&ax)[R], f32x2 (&ay)[R],
-                                          f32x2 (&az)[R], const f32x2 eps2, const unsigned stage, const Sym32Params& p)
+                                          f32x2 (&az)[R], const f32x2 eps2, const unsigned stage, const Sym32Params& p, float4* __restrict__ slot)
 {
 #pragma unroll 1
     for (int gi = 0; gi < kPosTile / 64; ++gi) {
@@ -110,8 +116,31 @@ __device__ __forceinline__ void sym_stage(const float* __restrict__ tp, const in
         f32x2 hx = 0ull, hy = 0ull, hz = 0ull;  // (lab: the odd i-bodies' half of the chain)
 #endif
         constexpr int kUnroll = UNIFORM ? (R == 8 ? NB_SYM32_UNROLL_EQUAL : 32) : NB_SYM32_UNROLL_GENERAL;
+#if NB_SYM32_REPARK
+        {
+            const float2 X = *reinterpret_cast<const float2*>(px + 2 * lane);
+            const float2 Y = *reinterpret_cast<const float2*>(px + kPosTile + 2 * lane);
+            const float2 Z = *reinterpret_cast<const float2*>(px + 2 * kPosTile + 2 * lane);
+            float2 M = make_float2(0.f, 0.f);
+            if (!UNIFORM) M = *reinterpret_cast<const float2*>(px + 3 * kPosTile + 2 * lane);
+            const float4 a = make_float4(X.x, X.y, Y.x, Y.y), b = make_float4(Z.x, Z.y, M.x, M.y);
+            __syncwarp();  // (every lane is done with the previous group)
+            slot[lane] = a;
+            slot[lane + 32] = a;
+            slot[lane + 64] = b;
+            slot[lane + 96] = b;
+            __syncwarp();
+        }
+        const float4* xy = slot + lane;
+#endif
 #pragma unroll kUnroll
         for (int q = 0; q < 32; ++q) {
+#if NB_SYM32_REPARK
+            const float4 XY = xy[q];
+            const float4 ZM = xy[q + 64];
+            const f32x2 jx = pack2(XY.x, XY.y), jy = pack2(XY.z, XY.w), jz = pack2(ZM.x, ZM.y);
+            const f32x2 jm = UNIFORM ? 0ull : pack2(ZM.z, ZM.w);
+#else
             const int o = 2 * ((lane + q) & 31);
             const float2 X = *reinterpret_cast<const float2*>(px + o);
             const float2 Y = *reinterpret_cast<const float2*>(px + kPosTile + o);
@@ -122,6 +151,7 @@ __device__ __forceinline__ void sym_stage(const float* __restrict__ tp, const in
                 const float2 M = *reinterpret_cast<const float2*>(px + 3 * kPosTile + o);
                 jm = pack2(M.x, M.y);
             }
+#endif
 #pragma unroll
             for (int r = 0; r < R; ++r) {
                 const f32x2 dx = add2(jx, nx[r]);
@@ -187,6 +217,7 @@ __device__ __forceinline__ void force_f32_sym_body(const Sym32Params& p)
     constexpr int kITile = kF32Threads * R;
     constexpr unsigned kBytes = (UNIFORM ? 3 : 4) * kPosTile * 4;  // the equal-mass kernel never reads the mass plane
     extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ __align__(16) float4 repark[kF32Threads / 32][NB_SYM32_REPARK ? 128 : 1];  // 2 KiB per compute warp
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + size_t(kSym32Stages) * kSym32StageBytes);
     uint64_t* empty = full + kSym32Stages;
     uint2* info = reinterpret_cast<uint2*>(empty + kSym32Stages);  // per stage: (i-tile, flags | position tile << 4)
@@ -266,7 +297,7 @@ __device__ __forceinline__ void force_f32_sym_body(const Sym32Params& p)
         if (inf.y & kSymDiag)  // the i-tile's own bodies: every ordered pair, i side only (the self pair is 0 * w: softening > 0)
             consume_tile<R, false, 4, false, false, UNIFORM, kPosTile / 2>(tp, nx, ny, nz, ax, ay, az, nr, eps2, 0);
         else
-            sym_stage<R, UNIFORM>(tp, lane, warp, nx, ny, nz, mi, ax, ay, az, eps2, inf.y >> 4, p);
+            sym_stage<R, UNIFORM>(tp, lane, warp, nx, ny, nz, mi, ax, ay, az, eps2, inf.y >> 4, p, repark[warp]);
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[slot]);
         if (inf.y & kSymLast) {

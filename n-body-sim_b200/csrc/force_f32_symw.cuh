@@ -21,7 +21,10 @@ namespace nb {
 constexpr int kSymwWarps = 4;
 constexpr int kSymwThreads = 32 * kSymwWarps;
 constexpr int kSymwGroup = 64;                       // bodies per group: 32 couples (b, b + 32), adjacent in every plane
-constexpr int kSymwSlotFloats = 4 * kSymwGroup;      // one parked group: x | y | z | m
+// One parked group: two arrays of 64 entries of 16 bytes, (x0, x1, y0, y1) and (z0, z1, m0, m1) of couple c at entries c AND
+// c + 32 -- every couple is stored twice, so that lane l finds the couple of rotation step q, (l + q) & 31, at entry l + q
+// without the wrap: the address is one register plus an immediate (no integer work in the loop) and a step is two LDS.128.
+constexpr int kSymwSlotFloats = 2 * 64 * 4;
 #ifndef NB_SYMW_UNROLL
 #define NB_SYMW_UNROLL 4   // rotation steps per loop iteration (1 / 2 / 4 / 8 / 32 at N=8,192, R=4: 1,906 / 1,934 / 2,167 / 2,164 / 1,963 G int/s)
 #endif
@@ -46,10 +49,13 @@ template <bool UNIFORM> __device__ __forceinline__ SymwCouple symw_fetch(const f
 
 template <bool UNIFORM> __device__ __forceinline__ void symw_park(float* slot, const SymwCouple& c, int lane)
 {
-    *reinterpret_cast<float2*>(slot + 2 * lane) = c.x;
-    *reinterpret_cast<float2*>(slot + kSymwGroup + 2 * lane) = c.y;
-    *reinterpret_cast<float2*>(slot + 2 * kSymwGroup + 2 * lane) = c.z;
-    if (!UNIFORM) *reinterpret_cast<float2*>(slot + 3 * kSymwGroup + 2 * lane) = c.m;
+    float4* xy = reinterpret_cast<float4*>(slot);
+    float4* zm = xy + 64;
+    const float4 a = make_float4(c.x.x, c.x.y, c.y.x, c.y.y), b = make_float4(c.z.x, c.z.y, c.m.x, c.m.y);
+    xy[lane] = a;
+    xy[lane + 32] = a;
+    zm[lane] = b;
+    zm[lane + 32] = b;
 }
 
 // One parked group against this warp's 32 R i-bodies.  DIAG: the group belongs to the i-block itself -- i side only.
@@ -60,18 +66,13 @@ __device__ __forceinline__ void symw_round(const float* __restrict__ slot, const
 {
     gx = gy = gz = 0ull;
     constexpr int kUnroll = NB_SYMW_UNROLL;
+    const float4* xy = reinterpret_cast<const float4*>(slot) + lane;
 #pragma unroll kUnroll
     for (int q = 0; q < 32; ++q) {
-        const int o = 2 * ((lane + q) & 31);
-        const float2 X = *reinterpret_cast<const float2*>(slot + o);
-        const float2 Y = *reinterpret_cast<const float2*>(slot + kSymwGroup + o);
-        const float2 Z = *reinterpret_cast<const float2*>(slot + 2 * kSymwGroup + o);
-        const f32x2 jx = pack2(X.x, X.y), jy = pack2(Y.x, Y.y), jz = pack2(Z.x, Z.y);
-        f32x2 jm = 0ull;
-        if (!UNIFORM) {
-            const float2 M = *reinterpret_cast<const float2*>(slot + 3 * kSymwGroup + o);
-            jm = pack2(M.x, M.y);
-        }
+        const float4 XY = xy[q];
+        const float4 ZM = xy[q + 64];
+        const f32x2 jx = pack2(XY.x, XY.y), jy = pack2(XY.z, XY.w), jz = pack2(ZM.x, ZM.y);
+        const f32x2 jm = UNIFORM ? 0ull : pack2(ZM.z, ZM.w);
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const f32x2 dx = add2(jx, nx[r]);
@@ -105,9 +106,9 @@ __device__ __forceinline__ void symw_round(const float* __restrict__ slot, const
 
 template <int R, bool UNIFORM> __device__ __forceinline__ void force_f32_symw_body(const Sym32Params& p)
 {
-    static_assert(R == 2 || R == 4 || R == 8, "an i-block is R/2 whole groups");
+    static_assert(R == 2 || R == 4 || R == 8, "an i-block is R/2 whole groups (and the padded body count a whole number of i-blocks: powers of two)");
     constexpr int kH = R / 2;  // groups per i-block
-    __shared__ __align__(16) float park[kSymwWarps][2][kSymwSlotFloats];
+    __shared__ __align__(16) float park[kSymwWarps][2][kSymwSlotFloats];  // 16 KiB
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     float* slot0 = park[warp][0];

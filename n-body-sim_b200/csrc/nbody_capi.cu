@@ -27,7 +27,7 @@ constexpr int kSym32EqualMassR = 8, kSym32GeneralR = 8;
 constexpr size_t kSym32SmallN = 49152;              // below: 4 bodies per thread
 constexpr int kSym32DefaultMinN = 32768;            // smallest system that takes the CTA-wide form (below: too few units for the SMs)
 constexpr int kSymwDefaultMinN = 6144;              // the warp-unit form (force_f32_symw.cuh) takes [min, max) bodies whatever the masses,
-constexpr int kSymwDefaultMaxN = 57344;             // and general masses at every size from min up
+constexpr int kSymwDefaultMaxN = 393216;            // and general masses at every size from min up
 constexpr size_t kSymwTinyN = 7168;                 // below: 2 bodies per thread (N=6,144: 24.3 us/step against 28.0 with 4; 8,192: 35.4 against 32.6)
 constexpr size_t kSymwSmallN = 28672;               // below: 4 bodies per thread, from here 8
 
@@ -1004,10 +1004,10 @@ int build_sym32_table(nbody_ctx* c)
         const int rcd = resolve_mass_detection(c);
         if (rcd != NBODY_OK) return rcd;
     }
-    // Which form (profiles/r2o_fine_lab.jsonl, r2o_big.jsonl; G interactions/s, before -> warp units): below symw_max_n the warp
-    // units always (N=8,192: 1,722 -> 2,053; 16,384: 2,424 -> 2,936; 32,768: 3,200 -> 3,620; 49,152: 3,616 -> 3,847; at 65,536 the
-    // CTA-wide kernel is back in front with equal masses, 3,816 against 3,710).  Above it, general masses keep them -- N=262,144:
-    // 3,544 -> 3,737, N=1M: 3,560 -> 3,761 -- and equal masses take the CTA-wide kernel (N=1M: 4,180 against 4,150).
+    // Which form (profiles/r2r_fine_lab.jsonl, r2r_big.jsonl, r2o_*; G interactions/s, before -> warp units): below symw_max_n the warp
+    // units always (N=8,192: 1,722 -> 2,016; 16,384: 2,428 -> 2,948; 32,768: 3,163 -> 3,637; 49,152: 3,663 -> 3,894; 65,536 and
+    // 262,144 bodies with equal masses: 3,869 -> 3,881 and 4,167 -> 4,178, a tie).  Above it, general masses keep them -- N=1M:
+    // 3,588 -> 3,834 -- and equal masses take the CTA-wide kernel, whose TMA ring is worth 0.5 % there (4,229 against 4,209).
     const bool fine = mid || (c->symw_max_n > 0 && c->n >= c->symw_min_n && !c->uniform && c->symw_general_large);
     int R, run;
     if (fine) {
@@ -1018,7 +1018,7 @@ int build_sym32_table(nbody_ctx* c)
         // units that the table stays a few tens of MB at several million bodies
         const size_t NG = (c->n + kSymwGroup - 1) / kSymwGroup;
         const size_t rounds = NG * NG / size_t(R);
-        const size_t warps = size_t(c->sm_count) * (R == 8 ? 8 : R == 4 ? 12 : 16);
+        const size_t warps = size_t(c->sm_count) * (R == 8 ? 8 : R >= 4 ? 12 : 16);
         run = env_int("NBODY_F32_SYMW_RUN", 0);
         if (run <= 0) {
             run = int(std::min<size_t>(16, std::max<size_t>(1, rounds / (warps * 8))));
@@ -1408,7 +1408,7 @@ int launch_force_sym32(nbody_ctx* c, int mode, double dt, double G, double eps)
     const int k = std::max(-100, std::min(100, 61 - e));  // bound * 2^k < 2^61
     if (61 - e < -100) return 1;
     const bool fine = c->sym32_fine;
-    int& slots = fine ? c->symw_slots[uniform ? 1 : 0][c->sym32_R == 2 ? 0 : c->sym32_R == 4 ? 1 : 2] : c->sym32_slots[uniform ? 1 : 0][c->sym32_R == 8 ? 1 : 0];
+    int& slots = fine ? c->symw_slots[uniform ? 1 : 0][c->sym32_R / 2 - 1] : c->sym32_slots[uniform ? 1 : 0][c->sym32_R == 8 ? 1 : 0];
     if (slots == 0) {
         int per_sm = 0;
         cudaError_t err = cudaSuccess;

@@ -115,7 +115,7 @@ if __name__ == "__main__":
                 steps = 200 if n <= 32768 else 20
                 run_wall("plummer", n, general, {"NBODY_F32_SYMW": 0}, steps=steps, label="before")
                 run_wall("plummer", n, general, {}, steps=steps, label="default")
-                for R in (2, 4, 8):
+                for R in [int(x) for x in os.environ.get("LAB_RS", "2 4 8").split()]:
                     run_wall("plummer", n, general, dict(wide, NBODY_F32_SYMW_R=R), steps=steps, label=f"warp units R{R}")
     if which == "big":           # the warp-unit pass against the CTA-wide one at large N
         wide = {"NBODY_F32_SYMW_MIN": 1, "NBODY_F32_SYMW_MAX": 1 << 30}
@@ -123,6 +123,6 @@ if __name__ == "__main__":
             for general in (False, True):
                 run("uniform_cube", n, general, {"NBODY_F32_SYMW": 0}, label="CTA-wide " + tag)
                 run("uniform_cube", n, general, {}, label="default " + tag)
-                for R in (4, 8):
+                for R in [int(x) for x in os.environ.get("LAB_RS", "4 8").split()]:
                     run("uniform_cube", n, general, dict(wide, NBODY_F32_SYMW_R=R), label=f"warp units R{R} {tag}")
 

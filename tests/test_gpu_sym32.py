@@ -104,10 +104,10 @@ def test_sym32_bits_do_not_depend_on_the_schedule(nb, general):
 
 def test_sym32_unit_size_only_reorders_fp32_sums(nb):
     s, pm, vel = scene_arrays(nb, "plummer", 65536, False)
-    base, info = force(nb, pm, vel, s.G, s.softening)
-    assert info["f32_symmetric"] == 1          # 128 position tiles: one tile per unit
+    base, info = force(nb, pm, vel, s.G, s.softening, NBODY_F32_SYMW=0)
+    assert info["f32_symmetric"] == 1 and info["f32_sym_warp_units"] == 0          # 128 position tiles: one tile per unit
     for run in (2, 7, 64):
-        acc, info = force(nb, pm, vel, s.G, s.softening, NBODY_F32_SYM_RUN=run)
+        acc, info = force(nb, pm, vel, s.G, s.softening, NBODY_F32_SYM_RUN=run, NBODY_F32_SYMW=0)
         assert info["f32_symmetric"] == run
         assert norm_rel_err(acc, base) < F32_ACC_TOL
 
@@ -179,9 +179,9 @@ def test_warp_units_force_vs_oracle(nb, oracle, scene, n, general, R):
 
 
 def test_warp_units_where_they_are_the_default(nb, oracle):
-    """[6,144, 49,152) bodies whatever the masses; general masses from 6,144 bodies up; equal masses above keep the CTA-wide kernel."""
-    for n, general, fine, R in ((4096, True, None, 0), (8192, False, True, 4), (20000, True, True, 4), (40000, False, True, 8),
-                                (65536, False, False, 8), (65536, True, True, 8), (300000, True, True, 8)):
+    """[6,144, 393,216) bodies whatever the masses; general masses from 6,144 bodies up; equal masses above keep the CTA-wide kernel."""
+    for n, general, fine, R in ((4096, True, None, 0), (6500, False, True, 2), (8192, False, True, 4), (20000, True, True, 4), (40000, False, True, 8),
+                                (65536, False, True, 8), (65536, True, True, 8), (400000, True, True, 8), (400000, False, False, 8)):
         s, pm, vel = scene_arrays(nb, "plummer", n, general)
         acc, info = force(nb, pm, vel, s.G, s.softening)
         if fine is not None:
