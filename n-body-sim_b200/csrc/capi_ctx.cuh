@@ -137,6 +137,9 @@ struct nbody_ctx {
     size_t symw_min_n = 0, symw_max_n = 0;  // body counts that always take the warp-unit form (NBODY_F32_SYMW_MIN / _MAX)
     int symw_R_forced = 0;          // NBODY_F32_SYMW_R at create: 2, 4 or 8
     bool symw_general_large = true; // NBODY_F32_SYMW_GENERAL at create: general masses keep the warp units above symw_max_n
+    bool sym_coop = false;          // cooperative launches work here and NBODY_SYM_COOP is not 0: sym_coop.cuh runs mid-size nbody_step calls
+    size_t sym_coop_max_n = 0;      // ... up to this many bodies (NBODY_SYM_COOP_MAX)
+    int sym_coop_slots[2][4] = {};  // resident CTAs of sym_coop_step_kernel [equal masses][R = 2, 4, -, 8]
     int symw_slots[2][4] = {};      // resident CTAs per device of the warp-unit kernels [equal masses][R = 2, 4, 6, 8]
     size_t medium_max_n = 0;        // largest system that kernel takes (fp32 5,120, fp64 4,096; NBODY_MEDIUM_MAX lowers it)
     int medium_ctas = 0;            // > 0: systems of up to medium_max_n bodies run all steps of a call in one cooperative launch

@@ -36,14 +36,23 @@ struct SymwCouple {
     float2 x, y, z, m;
 };
 
-template <bool UNIFORM> __device__ __forceinline__ SymwCouple symw_fetch(const float* __restrict__ pos, unsigned g, int lane)
+// COHERENT: the positions change DURING the kernel (sym_coop.cuh: other SMs drift them between grid barriers): L2 loads
+// (ld.global.cg) instead of the non-coherent path.
+template <bool UNIFORM, bool COHERENT> __device__ __forceinline__ SymwCouple symw_fetch(const float* __restrict__ pos, unsigned g, int lane)
 {
     const float* b = pos + symw_group_base(g) + 2 * lane;
     SymwCouple c;
-    c.x = __ldg(reinterpret_cast<const float2*>(b));
-    c.y = __ldg(reinterpret_cast<const float2*>(b + kPosTile));
-    c.z = __ldg(reinterpret_cast<const float2*>(b + 2 * kPosTile));
-    c.m = UNIFORM ? make_float2(0.f, 0.f) : __ldg(reinterpret_cast<const float2*>(b + 3 * kPosTile));
+    if (COHERENT) {
+        c.x = __ldcg(reinterpret_cast<const float2*>(b));
+        c.y = __ldcg(reinterpret_cast<const float2*>(b + kPosTile));
+        c.z = __ldcg(reinterpret_cast<const float2*>(b + 2 * kPosTile));
+        c.m = UNIFORM ? make_float2(0.f, 0.f) : __ldcg(reinterpret_cast<const float2*>(b + 3 * kPosTile));
+    } else {
+        c.x = __ldg(reinterpret_cast<const float2*>(b));
+        c.y = __ldg(reinterpret_cast<const float2*>(b + kPosTile));
+        c.z = __ldg(reinterpret_cast<const float2*>(b + 2 * kPosTile));
+        c.m = UNIFORM ? make_float2(0.f, 0.f) : __ldg(reinterpret_cast<const float2*>(b + 3 * kPosTile));
+    }
     return c;
 }
 
@@ -104,7 +113,7 @@ __device__ __forceinline__ void symw_round(const float* __restrict__ slot, const
     }
 }
 
-template <int R, bool UNIFORM> __device__ __forceinline__ void force_f32_symw_body(const Sym32Params& p)
+template <int R, bool UNIFORM, bool COHERENT = false> __device__ __forceinline__ void force_f32_symw_body(const Sym32Params& p)
 {
     static_assert(R == 2 || R == 4 || R == 8, "an i-block is R/2 whole groups (and the padded body count a whole number of i-blocks: powers of two)");
     constexpr int kH = R / 2;  // groups per i-block
@@ -125,12 +134,12 @@ template <int R, bool UNIFORM> __device__ __forceinline__ void force_f32_symw_bo
         const unsigned ib = raw.x, g0 = raw.y & 0xffffffu, count = (raw.y >> 24) & 0x7fu;
         const bool diag = (raw.y & kSymUnitDiag) != 0u;
         NB_CHECK(count >= 1 && size_t(g0 + count) * kSymwGroup <= p.n_pad && size_t(ib + 1) * kH * kSymwGroup <= p.n_pad);
-        SymwCouple nxt = symw_fetch<UNIFORM>(p.pos, g0, lane);
+        SymwCouple nxt = symw_fetch<UNIFORM, COHERENT>(p.pos, g0, lane);
 
         f32x2 nx[R], ny[R], nz[R], mi[R], ax[R], ay[R], az[R];
 #pragma unroll
         for (int h = 0; h < kH; ++h) {
-            const SymwCouple c = symw_fetch<UNIFORM>(p.pos, ib * kH + h, lane);
+            const SymwCouple c = symw_fetch<UNIFORM, COHERENT>(p.pos, ib * kH + h, lane);
             nx[2 * h] = pack2(-c.x.x, -c.x.x);
             nx[2 * h + 1] = pack2(-c.x.y, -c.x.y);
             ny[2 * h] = pack2(-c.y.x, -c.y.x);
@@ -148,7 +157,7 @@ template <int R, bool UNIFORM> __device__ __forceinline__ void force_f32_symw_bo
             float* slot = (k & 1u) ? slot1 : slot0;
             __syncwarp();  // (the lanes are done with this slot's previous group: two rounds ago)
             symw_park<UNIFORM>(slot, nxt, lane);
-            if (k + 1 < count) nxt = symw_fetch<UNIFORM>(p.pos, g0 + k + 1, lane);
+            if (k + 1 < count) nxt = symw_fetch<UNIFORM, COHERENT>(p.pos, g0 + k + 1, lane);
             __syncwarp();
             f32x2 gx, gy, gz;
             if (diag) {

@@ -10,6 +10,7 @@
 #include "force_f32.cuh"
 #include "force_f32_sym.cuh"
 #include "force_f32_symw.cuh"
+#include "sym_coop.cuh"
 #include "force_f64.cuh"
 #include "force_f64_sym.cuh"
 #include "integrate.cuh"
@@ -28,6 +29,7 @@ constexpr size_t kSym32SmallN = 49152;              // below: 4 bodies per threa
 constexpr int kSym32DefaultMinN = 32768;            // smallest system that takes the CTA-wide form (below: too few units for the SMs)
 constexpr int kSymwDefaultMinN = 6144;              // the warp-unit form (force_f32_symw.cuh) takes [min, max) bodies whatever the masses,
 constexpr int kSymwDefaultMaxN = 393216;            // and general masses at every size from min up
+constexpr int kSymCoopDefaultMaxN = 14336;          // sym_coop.cuh: all steps of a call in one cooperative launch up to here
 constexpr size_t kSymwTinyN = 7168;                 // below: 2 bodies per thread (N=6,144: 24.3 us/step against 28.0 with 4; 8,192: 35.4 against 32.6)
 constexpr size_t kSymwSmallN = 28672;               // below: 4 bodies per thread, from here 8
 
@@ -315,6 +317,10 @@ int create_common(nbody_ctx** out, nbody_prec prec, int world, size_t capacity, 
         c->symw_max_n = env_int("NBODY_F32_SYMW", 1) != 0 ? size_t(std::max(env_int("NBODY_F32_SYMW_MAX", kSymwDefaultMaxN), 0)) : 0;
         c->symw_R_forced = env_int("NBODY_F32_SYMW_R", 0);
         c->symw_general_large = env_int("NBODY_F32_SYMW_GENERAL", 1) != 0;
+        // one cooperative launch per call up to 14,336 bodies (us per step, launch per step -> cooperative: N=6,144 25.5 -> 21.1, 8,192
+        // 33.5 -> 28.6, 12,288 57.1 -> 54.4, 16,384 91.3 -> 89.0 with equal and 95.5 -> 96.1 with general masses, 32,768 312.7 -> 319.8:
+        // profiles/r2v_fine_lab.jsonl); the kernel itself takes up to kSymCoopMaxN
+        c->sym_coop_max_n = size_t(std::min<long long>(std::max(env_int("NBODY_SYM_COOP_MAX", kSymCoopDefaultMaxN), 0), (long long)kSymCoopMaxN));
     } else {
         c->f64_math = env_int("NBODY_F64_MATH", 2);
         c->f64_R_forced = env_int("NBODY_F64_R", 0);
@@ -561,6 +567,11 @@ static int create_body(nbody_ctx* c, const int* devs, int n_local_shards, const 
         c->medium_max_n = size_t(c->prec == NBODY_F32 ? medium_max_n<float>() : medium_max_n<double>());
         c->medium_max_n = std::min(c->medium_max_n, size_t(std::max(env_int("NBODY_MEDIUM_MAX", int(c->medium_max_n)), 0)));
         if (coop && per_sm >= 1 && size_t(c->sm_count) * kMediumThreads >= c->medium_max_n) c->medium_ctas = c->sm_count;
+    }
+    if (c->world == 1 && c->prec == NBODY_F32 && env_int("NBODY_SYM_COOP", 1) != 0) {  // sym_coop.cuh needs cooperative launches too
+        int coop = 0;
+        CU(c, cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->shards[0].device));
+        c->sym_coop = coop != 0;
     }
     if (c->medium_ctas == 0 && !getenv("NBODY_SMALL_MAX")) c->small_max_n = kSmallMaxN;  // nobody else runs all steps in one launch
     if (c->world > 1) {
@@ -1762,6 +1773,81 @@ template <typename Real> int launch_medium_steps_t(nbody_ctx* c, Shard& s, doubl
     return NBODY_OK;
 }
 
+template <typename F> void pick_sym_coop_kernel(int R, bool uniform, F&& f)
+{
+    if (R == 8) return uniform ? f(sym_coop_step_kernel<8, true>) : f(sym_coop_step_kernel<8, false>);
+    if (R == 2) return uniform ? f(sym_coop_step_kernel<2, true>) : f(sym_coop_step_kernel<2, false>);
+    return uniform ? f(sym_coop_step_kernel<4, true>) : f(sym_coop_step_kernel<4, false>);
+}
+
+// Mid-size fp32 systems on one GPU: all nsteps steps in ONE cooperative launch around the warp-unit pairs-once pass
+// (sym_coop.cuh).  Returns 1 when it does not apply (the caller launches per step), 0 when it was queued.
+int launch_sym_coop_steps(nbody_ctx* c, double dt, double G, double eps, int nsteps)
+{
+    if (c->prec != NBODY_F32 || c->world != 1 || c->timing || !c->sym_coop || c->n > c->sym_coop_max_n || !(eps > 0.0) || !std::isfinite(eps)) return 1;
+    if (c->has_radius && env_int("NBODY_NEAR", 1) != 0) return 1;  // (the sweep that tracks nearest neighbours)
+    if (c->detect_pending) {
+        const int rcd = resolve_mass_detection(c);
+        if (rcd != NBODY_OK) return rcd;
+    }
+    if (c->sym32_run <= 0 || !c->sym32_fine || (c->uniform && !c->outliers.empty())) return 1;
+    const bool uniform = c->uniform;
+    const double eps2 = double(float(eps) * float(eps));
+    const double bound = 1.001 * (2.0 / (3.0 * std::sqrt(3.0) * eps2)) * (uniform ? double(c->n) : c->sum_abs_mass);  // launch_force_sym32's
+    if (!(bound > 0.0) || !std::isfinite(bound) || bound > 1e37) return 1;
+    int e = 0;
+    std::frexp(bound, &e);
+    if (61 - e < -100) return 1;
+    const int k = std::max(-100, std::min(100, 61 - e));
+    Shard& s = c->shards[0];
+    CU(c, cudaSetDevice(s.device));
+    const int ri = c->sym32_R / 2 - 1;
+    int& slots = c->sym_coop_slots[uniform ? 1 : 0][ri];
+    if (slots == 0) {
+        int per_sm = 0;
+        cudaError_t err = cudaSuccess;
+        pick_sym_coop_kernel(c->sym32_R, uniform, [&](auto kernel) { err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kSymwThreads, 0); });
+        if (err != cudaSuccess || per_sm < 1) return fail(c, NBODY_ECUDA, "sym_coop_step_kernel does not fit an SM: %s", cudaGetErrorString(err));
+        slots = per_sm * c->sm_count;
+    }
+    if (size_t(slots) * kSymwThreads < c->n_pad) return 1;  // one owner thread per body slot
+    SymCoopParams p;
+    p.sym.pos = static_cast<const float*>(s.pos[c->cur]);
+    p.sym.units = static_cast<const SymUnit*>(s.sym_units);
+    p.sym.u_begin = c->sym32_split[0];
+    p.sym.u_end = c->sym32_split[1];
+    p.sym.sched = s.sym_ctl;
+    p.sym.accfix = s.accfix;
+    p.sym.n_pad = c->n_pad;
+    p.sym.eps2 = float(eps) * float(eps);
+    p.sym.scale = std::ldexp(1.0f, k);
+    p.sym.bound = std::nextafter(float(bound), INFINITY);
+    p.pos = static_cast<float*>(s.pos[c->cur]);
+    p.vel = static_cast<float*>(s.vel);
+    p.acc = static_cast<float*>(s.acc);
+    p.temp = c->has_temp ? static_cast<float*>(s.temp) : nullptr;
+    p.arrivals = s.medium_arrivals;
+    p.n = unsigned(c->n);
+    p.nsteps = nsteps;
+    p.G = uniform ? float(G) * float(c->uniform_mass) : float(G);
+    p.half_dt = 0.5f * float(dt);
+    p.dt = float(dt);
+    p.heat_decay = float(c->heat_decay);
+    p.inv_scale = std::ldexp(1.0, -k);
+    CU(c, cudaMemsetAsync(s.medium_arrivals, 0, sizeof(unsigned), s.stream));
+    void* args[] = {&p};
+    cudaError_t err = cudaSuccess;
+    pick_sym_coop_kernel(c->sym32_R, uniform, [&](auto kernel) {
+        err = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kernel), dim3(unsigned(slots)), dim3(kSymwThreads), args, 0, s.stream);
+    });
+    if (err != cudaSuccess) return fail(c, NBODY_ECUDA, "sym_coop_step_kernel: %s", cudaGetErrorString(err));
+    c->launches++;
+    CU(c, cudaMemsetAsync(s.accfix + 3 * c->n_pad, 0, sizeof(unsigned long long), s.stream));  // the (sticky) poison word
+    c->near_valid = false;
+    c->sym32_used = true;
+    return NBODY_OK;
+}
+
 int launch_medium_steps(nbody_ctx* c, double dt, double G, double eps, int nsteps)
 {
     Shard& s = c->shards[0];
@@ -1815,6 +1901,8 @@ extern "C" int nbody_step(nbody_ctx* c, double dt, double G, double softening, i
     if (nsteps == 0) return NBODY_OK;
     if (c->small_path && c->world == 1 && c->n <= c->small_max_n && !c->timing) return launch_small_steps(c, dt, G, softening, nsteps);
     if (c->medium_ctas > 0 && c->n <= c->medium_max_n && !c->timing) return launch_medium_steps(c, dt, G, softening, nsteps);
+    rc = launch_sym_coop_steps(c, dt, G, softening, nsteps);
+    if (rc <= 0) return rc;
     // First loop of integrate() for the first step (idx:250-253); later steps
     // get theirs from the previous force kernel's epilogue, so positions cross
     // HBM once per step.

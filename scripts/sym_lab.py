@@ -114,6 +114,7 @@ if __name__ == "__main__":
             for general in (False, True):
                 steps = 200 if n <= 32768 else 20
                 run_wall("plummer", n, general, {"NBODY_F32_SYMW": 0}, steps=steps, label="before")
+                run_wall("plummer", n, general, {"NBODY_SYM_COOP": 0}, steps=steps, label="per step")
                 run_wall("plummer", n, general, {}, steps=steps, label="default")
                 for R in [int(x) for x in os.environ.get("LAB_RS", "2 4 8").split()]:
                     run_wall("plummer", n, general, dict(wide, NBODY_F32_SYMW_R=R), steps=steps, label=f"warp units R{R}")

@@ -236,6 +236,67 @@ def test_warp_units_non_finite_input_and_third_law(nb):
             assert np.isnan(a[:, :3]).all() if bad else np.isfinite(a).all(), (k, bad)
 
 
+# ---- all steps of a call in one cooperative launch (csrc/sym_coop.cuh) -----------------------------------------------------
+
+def run_steps(nb, pm, vel, temp, s, calls, **kv):
+    with env(**kv):
+        with nb.Engine(len(pm), precision="f32") as e:
+            e.upload(pm, vel, None, temp)
+            for k in calls:
+                e.step(s.dt, s.G, s.softening, k)
+            out = e.download(temp=True)
+            return out, e.info()
+
+
+@pytest.mark.parametrize("general", [False, True])
+@pytest.mark.parametrize("scene,n", [("plummer", 6144), ("two_galaxies", 7002), ("plummer", 12000), ("uniform_cube", 16384), ("cold_collapse", 30001),
+                                     ("plummer", 32768)])
+def test_cooperative_steps_equal_the_launch_per_step_path(nb, oracle, scene, n, general):
+    """The same unit table, integer accumulation and rounded integrator operations: every bit equal, call after call."""
+    s, pm, vel = scene_arrays(nb, scene, n, general)
+    temp = np.random.default_rng(n).uniform(0.0, 50.0, s.n).astype(np.float32)
+    calls = (1, 3, 2)
+    coop, info = run_steps(nb, pm, vel, temp, s, calls, NBODY_SYM_COOP_MAX=32768)   # (the default stops at 14,336 bodies)
+    per_step, info0 = run_steps(nb, pm, vel, temp, s, calls, NBODY_SYM_COOP=0)
+    assert info["f32_sym_warp_units"] == 1 and info["f32_sym_last_pass"] == 1
+    if scene == "two_galaxies" and not general:      # equal masses with two heavy centres: corrected per body by the finish kernel,
+        assert info["kernel_launches"] == info0["kernel_launches"]   # so the launch-per-step path runs on both sides
+    else:                                              # 6 steps in 3 launches (+ upload kernels) against two or three launches per step
+        assert info["kernel_launches"] < info0["kernel_launches"] - 8, (info["kernel_launches"], info0["kernel_launches"])
+    for k in ("pos_mass", "vel", "acc", "temp"):
+        assert np.array_equal(coop[k], per_step[k]), k
+    if s.n > 12000:
+        return          # (the CPU oracle's six steps take a minute there; the launch-per-step path has its own oracle gates)
+    p, v, a, t = oracle.integrate(pm.astype(np.float64), vel.astype(np.float64), np.zeros((s.n, 4)), temp.astype(np.float64), s.dt, s.G, s.softening,
+                                  nsteps=sum(calls))
+    assert norm_rel_err(coop["acc"], a) < 2e-4 and norm_rel_err(coop["pos_mass"], p) < 1e-5 and norm_rel_err(coop["vel"], v) < 5e-5   # six fp32 steps
+
+
+def test_cooperative_steps_default_range(nb):
+    for n, coop in ((5000, False), (6144, True), (14000, True), (16384, False)):
+        s, pm, vel = scene_arrays(nb, "plummer", n, True)
+        _, info = run_steps(nb, pm, vel, None, s, (5,))
+        assert (info["kernel_launches"] <= 4) == (coop or n <= 5120), (n, info["kernel_launches"])   # (up to 5,120 bodies: medium.cuh's one launch)
+
+
+def test_cooperative_steps_poison_and_recovery(nb):
+    s, pm, vel = scene_arrays(nb, "plummer", 9000, True)
+    with nb.Engine(s.n, precision="f32") as e:
+        bad = pm.copy()
+        bad[4321, 0] = np.nan
+        e.upload(bad, vel)
+        e.step(s.dt, s.G, s.softening, 3)
+        o = e.download()
+        assert np.isnan(o["acc"][:, :3]).all() and np.isnan(o["pos_mass"][:, :3]).all()
+        e.upload(pm, vel)                      # the poison word does not outlive the launch
+        e.step(s.dt, s.G, s.softening, 2)
+        e.force(s.G, s.softening)              # ... nor do the counter and the accumulators: the launch-per-step kernels follow cleanly
+        o = e.download()
+        assert np.isfinite(o["acc"]).all() and np.isfinite(o["pos_mass"]).all()
+    ref, _ = run_steps(nb, pm, vel, None, s, (2,), NBODY_SYM_COOP=0)
+    assert np.array_equal(o["pos_mass"], ref["pos_mass"]) and np.array_equal(o["vel"], ref["vel"])
+
+
 def test_warp_units_multi_gpu_same_bits(nb):
     ng = nb.device_count()
     if ng < 2:
