@@ -27,7 +27,7 @@ constexpr int kUniUnroll = NB_UNIFORM_UNROLL;  // inner-loop unroll of the equal
 constexpr int kSym32EqualMassR = 8, kSym32GeneralR = 8;
 constexpr size_t kSym32SmallN = 49152;              // below: 4 bodies per thread
 constexpr int kSym32DefaultMinN = 32768;            // smallest system that takes the CTA-wide form (below: too few units for the SMs)
-constexpr int kSymwDefaultMinN = 6144;              // the warp-unit form (force_f32_symw.cuh) takes [min, max) bodies whatever the masses,
+constexpr int kSymwDefaultMinN = 5121;              // the warp-unit form (force_f32_symw.cuh) takes [min, max) bodies whatever the masses,
 constexpr int kSymwDefaultMaxN = 393216;            // and general masses at every size from min up
 constexpr int kSymCoopDefaultMaxN = 14336;          // sym_coop.cuh: all steps of a call in one cooperative launch up to here
 constexpr size_t kSymwTinyN = 7168;                 // below: 2 bodies per thread (N=6,144: 24.3 us/step against 28.0 with 4; 8,192: 35.4 against 32.6)

@@ -68,11 +68,15 @@ def main():
         for general in (False, True):
             step_case(f"fp32 pairs-once R={R} (force_f32_sym.cuh)", 5000, "f32", dict(per_step, NBODY_F32_SYM_MIN=1, NBODY_F32_SYM_R=R, NBODY_F32_SYMW=0), nsteps=3, general=general)
     step_case("fp32 pairs-once, outliers", 3002, "f32", dict(per_step, NBODY_F32_SYM_MIN=1, NBODY_F32_SYMW=0), scene="two_galaxies")
-    wide = dict(per_step, NBODY_F32_SYMW_MIN=1, NBODY_F32_SYMW_MAX=1 << 30)
+    wide = dict(per_step, NBODY_F32_SYMW_MIN=1, NBODY_F32_SYMW_MAX=1 << 30, NBODY_SYM_COOP=0)
     for R in (2, 4, 8):
         for general in (False, True):
             step_case(f"fp32 pairs-once, warp units R={R} (force_f32_symw.cuh)", 5000, "f32", dict(wide, NBODY_F32_SYMW_R=R), nsteps=3, general=general)
-    step_case("fp32 pairs-once, warp units, default shape", 9001, "f32", per_step, nsteps=3, general=True)
+    step_case("fp32 pairs-once, warp units, default shape", 9001, "f32", dict(per_step, NBODY_SYM_COOP=0), nsteps=3, general=True)
+    for R in (2, 4, 8):
+        for general in (False, True):
+            step_case(f"one cooperative launch, warp units R={R} (sym_coop.cuh)", 5000, "f32", dict(wide, NBODY_SYM_COOP=1, NBODY_F32_SYMW_R=R), nsteps=3, general=general)
+    step_case("one cooperative launch, default shape", 9001, "f32", per_step, nsteps=4, general=True)
 
     # the rows next to the hot path: contacts (flagged and full scan), history ring + ribbons, renderer
     s = nb.scenes.galaxy_default()

@@ -179,7 +179,7 @@ def test_warp_units_force_vs_oracle(nb, oracle, scene, n, general, R):
 
 
 def test_warp_units_where_they_are_the_default(nb, oracle):
-    """[6,144, 393,216) bodies whatever the masses; general masses from 6,144 bodies up; equal masses above keep the CTA-wide kernel."""
+    """[5,121, 393,216) bodies whatever the masses; general masses from 5,121 bodies up; equal masses above keep the CTA-wide kernel."""
     for n, general, fine, R in ((4096, True, None, 0), (6500, False, True, 2), (8192, False, True, 4), (20000, True, True, 4), (40000, False, True, 8),
                                 (65536, False, True, 8), (65536, True, True, 8), (400000, True, True, 8), (400000, False, False, 8)):
         s, pm, vel = scene_arrays(nb, "plummer", n, general)
